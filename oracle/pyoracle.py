@@ -1,0 +1,244 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes access to the two oracle libraries.
+
+* ``Oracle``  -> oracle/liboracle.so       (plain-C restatement, oracle.c; travels to the GPU box)
+* ``Ref``     -> oracle/_ref/libbiolib_ref.so (the reference's own code, ref_tier_a.cpp; built only
+                 where /root/reference exists, but the built .so travels)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / ``--impl reference`` legs may
+import this module. The product package (biolib_b200) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libbiolib_ref.so")
+
+_u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+def build(force: bool = False) -> None:
+    """Compile oracle.c (always possible) and the Tier A library (only if the reference is here)."""
+    if force or not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(HERE, "oracle.c")):
+        subprocess.check_call(["make", "-C", HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference/include"):
+        src = os.path.join(HERE, "ref_tier_a.cpp")
+        if force or not os.path.exists(REF_SO) or os.path.getmtime(REF_SO) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-C", HERE, "_ref/libbiolib_ref.so"], stdout=subprocess.DEVNULL)
+
+
+def _buf(seq) -> bytes:
+    if isinstance(seq, str):
+        return seq.encode("latin-1")
+    if isinstance(seq, np.ndarray):
+        return seq.tobytes()
+    return bytes(seq)
+
+
+def _offs(offsets):
+    if offsets is None:
+        return None, 0
+    o = np.ascontiguousarray(offsets, dtype=np.uint64)
+    return o, len(o) - 1
+
+
+class Oracle:
+    """oracle.c"""
+
+    def __init__(self):
+        build()
+        L = self.lib = C.CDLL(ORACLE_SO)
+        L.orc_nt4.restype = C.c_uint8
+        L.orc_nt4.argtypes = [C.c_uint8]
+        L.orc_hash64_u64.restype = C.c_uint64
+        L.orc_hash64_u64.argtypes = [C.c_uint64, C.c_uint64]
+        L.orc_remix.restype = C.c_uint64
+        L.orc_remix.argtypes = [C.c_uint64]
+        L.orc_double_hash64_u64.argtypes = [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.orc_double_hash64_u128.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.orc_kmer_stream.restype = C.c_size_t
+        L.orc_kmer_stream.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_kmers.restype = C.c_size_t
+        L.orc_kmers.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_mmers.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        for f in (L.orc_super_kmers, L.orc_super_kmers_brute):
+            f.restype = C.c_size_t
+            f.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int,
+                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_generate.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
+        L.orc_mutate.restype = C.c_size_t
+        L.orc_mutate.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+
+    def nt4_table(self):
+        return np.array([self.lib.orc_nt4(i) for i in range(256)], dtype=np.uint8)
+
+    def hash64(self, v, seed):
+        return int(self.lib.orc_hash64_u64(v & (2**64 - 1), seed & (2**64 - 1)))
+
+    def double_hash64(self, v, seed):
+        out = (C.c_uint64 * 2)()
+        self.lib.orc_double_hash64_u64(v, seed, out)
+        return int(out[0]), int(out[1])
+
+    def double_hash64_u128(self, lo, hi, seed):
+        out = (C.c_uint64 * 2)()
+        self.lib.orc_double_hash64_u128(lo, hi, seed, out)
+        return int(out[0]), int(out[1])
+
+    def remix(self, z):
+        return int(self.lib.orc_remix(z))
+
+    def kmer_stream(self, seq, k, canonical):
+        b = _buf(seq)
+        cap = len(b) + 1
+        lo = np.zeros(cap, np.uint64); hi = np.zeros(cap, np.uint64); has = np.zeros(cap, np.uint8)
+        pos = np.zeros(cap, np.uint64); idv = np.zeros(cap, np.uint64)
+        n = self.lib.orc_kmer_stream(b, len(b), k, int(canonical), lo.ctypes.data, hi.ctypes.data, has.ctypes.data, pos.ctypes.data, idv.ctypes.data, cap)
+        return dict(lo=lo[:n], hi=hi[:n], has=has[:n], pos=pos[:n], id=idv[:n])
+
+    def kmers(self, seq, k, canonical, offsets=None):
+        b = _buf(seq)
+        o, ns = _offs(offsets)
+        cap = len(b) + 1
+        lo = np.zeros(cap, np.uint64); hi = np.zeros(cap, np.uint64); pos = np.zeros(cap, np.uint64)
+        n = self.lib.orc_kmers(b, len(b), o.ctypes.data if o is not None else None, ns, k, int(canonical), lo.ctypes.data, hi.ctypes.data, pos.ctypes.data, cap)
+        return dict(lo=lo[:n], hi=hi[:n], pos=pos[:n])
+
+    def mmers(self, seq, m, seed, canonical, offsets=None):
+        b = _buf(seq)
+        o, ns = _offs(offsets)
+        n = len(b)
+        val = np.zeros(n, np.uint64); h = np.zeros(n, np.uint64); ok = np.zeros(n, np.uint8)
+        self.lib.orc_mmers(b, n, o.ctypes.data if o is not None else None, ns, m, seed, int(canonical), val.ctypes.data, h.ctypes.data, ok.ctypes.data)
+        return dict(value=val, hash=h, valid=ok)
+
+    def super_kmers(self, seq, k, m, seed, canonical, offsets=None, brute=False, want=("value", "hash", "mm_start", "sk_start", "size"), cap=None):
+        b = _buf(seq)
+        o, ns = _offs(offsets)
+        n = len(b)
+        if cap is None:
+            cap = max(n - k + 1, 0) + 1
+        arr = dict(value=np.zeros(cap if "value" in want else 0, np.uint64), hash=np.zeros(cap if "hash" in want else 0, np.uint64),
+                   mm_start=np.zeros(cap if "mm_start" in want else 0, np.uint64), sk_start=np.zeros(cap if "sk_start" in want else 0, np.uint64),
+                   size=np.zeros(cap if "size" in want else 0, np.uint8))
+        f = self.lib.orc_super_kmers_brute if brute else self.lib.orc_super_kmers
+        ptr = lambda k_: arr[k_].ctypes.data if k_ in want else None
+        cnt = f(b, n, o.ctypes.data if o is not None else None, ns, k, m, seed, int(canonical),
+                ptr("value"), ptr("hash"), ptr("mm_start"), ptr("sk_start"), ptr("size"), cap if want else 0)
+        out = {k_: v[:min(cnt, cap)] for k_, v in arr.items() if k_ in want}
+        out["n"] = cnt
+        return out
+
+    def generate(self, seed, length):
+        out = np.empty(length, np.uint8)
+        self.lib.orc_generate(seed, length, out.ctypes.data)
+        return out
+
+    def mutate(self, seq, mutp, indelf, extp, seed):
+        b = _buf(seq)
+        cap = len(b) * 4 + 64
+        out = np.empty(cap, np.uint8)
+        counts = np.zeros(3, np.uint64); tot = C.c_int64(0)
+        n = self.lib.orc_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
+        assert n <= cap
+        return out[:n].copy(), counts, tot.value
+
+
+class Ref:
+    """ref_tier_a.cpp: the reference executed verbatim. ``Ref.available()`` is False on a box where
+    neither /root/reference nor a prebuilt oracle/_ref exists."""
+
+    @staticmethod
+    def available() -> bool:
+        try:
+            build()
+        except Exception:
+            pass
+        return os.path.exists(REF_SO)
+
+    def __init__(self):
+        build()
+        L = self.lib = C.CDLL(REF_SO)
+        L.ref_hash64_u64.restype = C.c_uint64
+        L.ref_hash64_u64.argtypes = [C.c_uint64, C.c_uint64]
+        L.ref_remix.restype = C.c_uint64
+        L.ref_remix.argtypes = [C.c_uint64]
+        L.ref_double_hash64_u64.argtypes = [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.ref_double_hash64_u128.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+        for f in (L.ref_kmer_view_u64, L.ref_kmer_view_u128):
+            f.restype = C.c_size_t
+            f.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.ref_mmer_stream.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_minimizer_view_literal_count.restype = C.c_size_t
+        L.ref_minimizer_view_literal_count.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int]
+        L.ref_generate.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
+        L.ref_mutate.restype = C.c_size_t
+        L.ref_mutate.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        L.ref_nt4_table.argtypes = [C.c_void_p]
+
+    def nt4_table(self):
+        t = np.zeros(256, np.uint8)
+        self.lib.ref_nt4_table(t.ctypes.data)
+        return t
+
+    def hash64(self, v, seed):
+        return int(self.lib.ref_hash64_u64(v & (2**64 - 1), seed & (2**64 - 1)))
+
+    def double_hash64(self, v, seed):
+        out = (C.c_uint64 * 2)()
+        self.lib.ref_double_hash64_u64(v, seed, out)
+        return int(out[0]), int(out[1])
+
+    def double_hash64_u128(self, lo, hi, seed):
+        out = (C.c_uint64 * 2)()
+        self.lib.ref_double_hash64_u128(lo, hi, seed, out)
+        return int(out[0]), int(out[1])
+
+    def remix(self, z):
+        return int(self.lib.ref_remix(z))
+
+    def kmer_stream(self, seq, k, canonical, bits=64):
+        b = _buf(seq)
+        cap = len(b) + 1
+        has = np.zeros(cap, np.uint8); pos = np.zeros(cap, np.uint64); idv = np.zeros(cap, np.uint64)
+        if bits == 64:
+            lo = np.zeros(cap, np.uint64)
+            n = self.lib.ref_kmer_view_u64(b, len(b), k, int(canonical), lo.ctypes.data, has.ctypes.data, pos.ctypes.data, idv.ctypes.data, cap)
+            hi = np.zeros(cap, np.uint64)
+        else:
+            pair = np.zeros(2 * cap, np.uint64)
+            n = self.lib.ref_kmer_view_u128(b, len(b), k, int(canonical), pair.ctypes.data, has.ctypes.data, pos.ctypes.data, idv.ctypes.data, cap)
+            lo, hi = pair[0::2].copy(), pair[1::2].copy()
+        return dict(lo=lo[:n], hi=hi[:n], has=has[:n], pos=pos[:n], id=idv[:n])
+
+    def mmer_stream(self, seq, k, m, seed, canonical):
+        b = _buf(seq)
+        n = len(b)
+        val = np.zeros(n, np.uint64); idx = np.zeros(n, np.uint64); h = np.zeros(n, np.uint64)
+        bslb = np.zeros(n, np.uint64); ok = np.zeros(n, np.uint8)
+        self.lib.ref_mmer_stream(b, n, k, m, seed, int(canonical), val.ctypes.data, idx.ctypes.data, h.ctypes.data, bslb.ctypes.data, ok.ctypes.data)
+        return dict(value=val, idx=idx, hash=h, bslb=bslb, valid=ok)
+
+    def minimizer_view_literal_count(self, seq, k, m, seed, canonical):
+        b = _buf(seq)
+        return int(self.lib.ref_minimizer_view_literal_count(b, len(b), k, m, seed, int(canonical)))
+
+    def generate(self, seed, length):
+        out = np.empty(length, np.uint8)
+        self.lib.ref_generate(seed, length, out.ctypes.data)
+        return out
+
+    def mutate(self, seq, mutp, indelf, extp, seed):
+        b = _buf(seq)
+        cap = len(b) * 4 + 64
+        out = np.empty(cap, np.uint8)
+        counts = np.zeros(3, np.uint64); tot = C.c_int64(0)
+        n = self.lib.ref_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
+        assert n <= cap
+        return out[:n].copy(), counts, tot.value

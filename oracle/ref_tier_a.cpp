@@ -1,0 +1,217 @@
+// TEST INFRASTRUCTURE ONLY -- never linked, imported or executed by the product path.
+//
+// Tier A oracle: the reference's own code, executed verbatim.
+//
+// This translation unit contains NO algorithm of its own. It #includes the reference's
+// headers where they lie (-I/root/reference/include, -I/root/reference/bundled; the
+// recipe is oracle/Makefile, outputs go to oracle/_ref/ only) and exposes a C ABI over
+//   * wrapper::kmer_view iteration                      (include/kmer_view.hpp:155-234)
+//   * wrapper::minimizer_view::const_iterator::read_base (include/minimizer_view.hpp:229-245)
+//   * hash::hash64 / hash::double_hash64                (include/hash.hpp:11-71)
+//   * sequence::generator, wrapper::sequence_mutator    (include/sequence_generator.hpp:14-43,
+//                                                        include/sequence_mutator.hpp:109-169)
+// so the C restatement in oracle/oracle.c (and, through it, the CUDA path) can be pinned
+// against reference-executed results. Guards applied before calling into the reference
+// (SURVEY.md section 8(a), K5/K6/K8):
+//   K5  iterators are placement-constructed in zero-filled storage (kmer_buffer is never
+//       initialised by the reference's constructor);
+//   K6  the input handed to kmer_view is truncated right after the first invalid byte
+//       that follows the last run of >= k valid bases (the reference over-reads and never
+//       terminates otherwise); no such run => the reference is not called at all;
+//   K8  bytes >= 0x80 are replaced by 'N' (negative char index is UB / throws).
+//
+// minimizer_view.hpp is not self-contained (needs <vector>, <cassert>) and read_base()
+// is private: all standard headers are included first, then `private` is opened for the
+// reference headers only.
+
+#include <array>
+#include <cassert>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <optional>
+#include <random>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#define private public
+#include "constants.hpp"
+#include "hash.hpp"
+#include "kmer_view.hpp"
+#include "minimizer_view.hpp"
+#undef private
+#include "sequence_generator.hpp"
+#include "sequence_mutator.hpp"
+
+namespace {
+
+inline bool is_valid_base(unsigned char c) { return constants::seq_nt4_table[c] < 4; }
+
+// K6 + K8: sanitised, truncated copy that is inside kmer_view's defined domain.
+// Returns false when the reference must not be called (no run of >= k valid bases).
+bool kmer_view_safe_input(const char* s, size_t n, unsigned k, std::string& out)
+{
+    out.assign(s, n);
+    for (auto& ch : out)
+        if (static_cast<unsigned char>(ch) >= 0x80) ch = 'N';
+    size_t run = 0, last_good_end = 0;  // end (exclusive) of the last run of >= k valid bases
+    bool found = false;
+    for (size_t i = 0; i <= n; ++i) {
+        bool v = i < n && is_valid_base(static_cast<unsigned char>(out[i]));
+        if (v) { ++run; continue; }
+        if (run >= k) { found = true; last_good_end = i; }
+        run = 0;
+    }
+    if (!found) return false;
+    // keep [0, last_good_end) plus at most one following (invalid) byte
+    if (last_good_end < n) out.resize(last_good_end + 1);
+    else out.resize(last_good_end);
+    return true;
+}
+
+template <typename KmerT>
+size_t run_kmer_view(const char* s, size_t n, unsigned k, int canonical,
+                     KmerT* value, uint8_t* has_value, uint64_t* position, uint64_t* id, size_t cap)
+{
+    std::string safe;
+    if (k == 0 || !kmer_view_safe_input(s, n, k, safe)) return 0;
+    auto view = wrapper::kmer_view_from_cstr<KmerT>(safe.data(), safe.size(), static_cast<uint8_t>(k), canonical != 0);
+    using view_t = decltype(view);
+    using it_t = typename view_t::const_iterator;
+    alignas(it_t) unsigned char storage[sizeof(it_t)];
+    std::memset(storage, 0, sizeof(storage));               // K5
+    it_t* it = new (storage) it_t(&view);
+    auto end = view.cend();
+    size_t cnt = 0;
+    for (; *it != end; ++(*it)) {
+        auto rec = **it;
+        if (cnt < cap) {
+            if (value) value[cnt] = rec.value ? *rec.value : KmerT(0);
+            if (has_value) has_value[cnt] = rec.value ? 1 : 0;
+            if (position) position[cnt] = rec.position;
+            if (id) id[cnt] = rec.id;
+        }
+        ++cnt;
+    }
+    it->~it_t();
+    return cnt;
+}
+
+} // namespace
+
+// Per-base stream of minimizer_view::const_iterator::read_base() + HashFunction::hash,
+// driven exactly as init_window()/operator++ drive it (minimizer_view.hpp:194-203,
+// 252-261) but without the (non-functional, F2) window. For every input byte i:
+//   idx[i]   = value returned by read_base()  (= 1-based m-mer start, D7)
+//   bslb[i]  = bases_since_last_break after the call
+//   valid[i] = bslb[i] >= m ; value[i] = mm_forward_reverse[strand] ; hash[i] = hash64(value, seed)
+// KmerType is __uint128_t when k > 32 (as tests/test_super_kmer_view.cpp:17 does), else uint64_t;
+// it only feeds the mask computation (minimizer_view.hpp:172).
+template <typename KmerT>
+static void mmer_stream_impl(const char* s, size_t n, unsigned k, unsigned m, uint64_t seed, int canonical,
+                             uint64_t* value, uint64_t* idx, uint64_t* hashv, uint64_t* bslb, uint8_t* valid)
+{
+    using view_t = wrapper::minimizer_view<KmerT, uint64_t, hash::hash64, char_iterator>;
+    view_t view(char_iterator(s), char_iterator(s + n), static_cast<uint8_t>(k), static_cast<uint8_t>(m), seed, canonical != 0);
+    typename view_t::const_iterator it(&view, 0);          // end-constructor: no init_window()
+    it.itr = char_iterator(s);
+    it.shift = 2 * (m - 1);                                // as minimizer_view.hpp:171-173
+    it.mask = (KmerT(1) << (2 * m)) - 1;
+    it.mm_forward_reverse = {uint64_t(0), uint64_t(0)};
+    for (size_t i = 0; i < n; ++i) {
+        auto r = it.read_base();
+        bool ok = it.bases_since_last_break >= m;
+        uint64_t v = it.mm_forward_reverse[it.strand];
+        if (idx) idx[i] = r;
+        if (bslb) bslb[i] = it.bases_since_last_break;
+        if (valid) valid[i] = ok;
+        if (value) value[i] = ok ? v : 0;
+        if (hashv) hashv[i] = ok ? hash::hash64::hash(v, view.mseed) : 0;
+    }
+}
+
+extern "C" {
+
+// nt4 table as the reference holds it (include/constants.hpp:12-21)
+void ref_nt4_table(uint8_t out[256]) { for (int i = 0; i < 256; ++i) out[i] = constants::seq_nt4_table[i]; }
+
+uint64_t ref_hash64_u64(uint64_t v, uint64_t seed) { return hash::hash64::hash(v, seed); }
+void ref_double_hash64_u64(uint64_t v, uint64_t seed, uint64_t out[2]) { auto h = hash::double_hash64::hash(v, seed); out[0] = h[0]; out[1] = h[1]; }
+void ref_double_hash64_u128(uint64_t lo, uint64_t hi, uint64_t seed, uint64_t out[2])
+{
+    __uint128_t v = (static_cast<__uint128_t>(hi) << 64) | lo;
+    auto h = hash::double_hash64::hash(v, seed);
+    out[0] = h[0]; out[1] = h[1];
+}
+uint64_t ref_remix(uint64_t z) { return hash::remix(z); }
+
+// Full kmer_view stream, including nullopt records and ids (K1-K4).
+size_t ref_kmer_view_u64(const char* s, size_t n, unsigned k, int canonical,
+                         uint64_t* value, uint8_t* has_value, uint64_t* position, uint64_t* id, size_t cap)
+{
+    return run_kmer_view<uint64_t>(s, n, k, canonical, value, has_value, position, id, cap);
+}
+
+// 128-bit variant: values returned as (lo, hi) pairs. Canonical output for k > 32 is the
+// reference's (wrong, K7) result and is only used to document the divergence.
+size_t ref_kmer_view_u128(const char* s, size_t n, unsigned k, int canonical,
+                          uint64_t* value_lo_hi, uint8_t* has_value, uint64_t* position, uint64_t* id, size_t cap)
+{
+    std::vector<__uint128_t> tmp(cap);
+    size_t cnt = run_kmer_view<__uint128_t>(s, n, k, canonical, tmp.data(), has_value, position, id, cap);
+    for (size_t i = 0; i < cnt && i < cap; ++i) {
+        value_lo_hi[2 * i] = static_cast<uint64_t>(tmp[i]);
+        value_lo_hi[2 * i + 1] = static_cast<uint64_t>(tmp[i] >> 64);
+    }
+    return cnt;
+}
+
+void ref_mmer_stream(const char* s, size_t n, unsigned k, unsigned m, uint64_t seed, int canonical,
+                     uint64_t* value, uint64_t* idx, uint64_t* hashv, uint64_t* bslb, uint8_t* valid)
+{
+    if (k > 32) mmer_stream_impl<__uint128_t>(s, n, k, m, seed, canonical, value, idx, hashv, bslb, valid);
+    else mmer_stream_impl<uint64_t>(s, n, k, m, seed, canonical, value, idx, hashv, bslb, valid);
+}
+
+// The literal minimizer_view iteration (F2: yields nothing). Returns the number of records.
+size_t ref_minimizer_view_literal_count(const char* s, size_t n, unsigned k, unsigned m, uint64_t seed, int canonical)
+{
+    auto view = wrapper::minimizer_view_from_cstr<uint64_t, uint64_t, hash::hash64>(s, n, static_cast<uint8_t>(k), static_cast<uint8_t>(m), seed, canonical != 0);
+    size_t cnt = 0;
+    for (auto it = view.cbegin(); it != view.cend(); ++it) ++cnt;
+    return cnt;
+}
+
+// sequence::generator::nucleic<packed::uniform>::get_sequence
+void ref_generate(uint64_t seed, size_t len, char* out)
+{
+    sequence::generator::packed::uniform gen(seed);
+    sequence::generator::nucleic<sequence::generator::packed::uniform> nuc(gen);
+    std::string s = nuc.get_sequence(len);
+    std::memcpy(out, s.data(), len);
+}
+
+// wrapper::sequence_mutator driven as tests/test_random_sequence_generation.cpp:44-48 does
+// (nullopt dropped). out must hold worst-case growth; returns the mutated length.
+// counts = {substitutions, insertions, deletions}.
+size_t ref_mutate(const char* s, size_t n, double mutp, double indelf, double extp, uint64_t seed,
+                  char* out, size_t cap, uint64_t counts[3], int64_t* total_indel_len)
+{
+    std::string src(s, n);
+    wrapper::sequence_mutator<std::string::const_iterator> mut(src.cbegin(), src.cend(), mutp, indelf, extp);
+    size_t o = 0;
+    auto it = mut.cbegin(seed);
+    for (; it != mut.cend(); ++it) {
+        auto v = *it;
+        if (v) { if (o < cap) out[o] = *v; ++o; }
+    }
+    auto rep = it.get_report();
+    if (counts) { counts[0] = rep.substitution_count; counts[1] = rep.insertion_count; counts[2] = rep.deletion_count; }
+    if (total_indel_len) *total_indel_len = rep.total_indel_len;
+    return o;
+}
+
+} // extern "C"
