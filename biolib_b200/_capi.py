@@ -1,0 +1,91 @@
+"""ctypes binding of the C ABI in include/biolib_gpu.h (biolib_b200/libbiolib_gpu.so).
+
+This is the same thin binding a maintainer of the reference would write for any host language: plain
+pointers and sizes. There is no fallback of any kind here -- if the shared library is missing, or no
+sm_100 device is usable, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libbiolib_gpu.so")
+CSRC = os.path.join(HERE, "csrc")
+
+BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOMEM = range(6)
+F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE = 0x1, 0x2, 0x4, 0x8
+
+EXPORTS = [
+    "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
+    "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
+    "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_free_kmer_out", "blg_free_sk_out",
+]
+
+
+class Params(C.Structure):
+    _fields_ = [("k", C.c_uint8), ("m", C.c_uint8), ("canonical", C.c_uint8), ("reserved", C.c_uint8),
+                ("flags", C.c_uint32), ("seed", C.c_uint64)]
+
+
+class KmerOut(C.Structure):
+    _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value_lo", C.c_void_p), ("value_hi", C.c_void_p),
+                ("position", C.c_void_p), ("owner", C.c_void_p)]
+
+
+class SkOut(C.Structure):
+    _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value", C.c_void_p), ("mm_start", C.c_void_p),
+                ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("owner", C.c_void_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_bases", C.c_uint64), ("n_records", C.c_uint64), ("bytes_h2d", C.c_uint64), ("bytes_d2h", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double)]
+
+
+def build(force: bool = False) -> str:
+    """Compile the CUDA sources for sm_100a into libbiolib_gpu.so (nvcc cross-compiles without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    srcs.append(os.path.join(HERE, "..", "include", "biolib_gpu.h"))
+    stale = force or not os.path.exists(LIB_PATH) or any(
+        os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs)
+    if stale:
+        subprocess.check_call(["make", "-C", CSRC, "-j4"], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, u64, sz = C.c_void_p, C.c_uint64, C.c_size_t
+    L.blg_abi_version.restype = C.c_int
+    L.blg_strerror.restype = C.c_char_p
+    L.blg_strerror.argtypes = [C.c_int]
+    L.blg_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.blg_destroy.argtypes = [vp]
+    L.blg_set_stream.argtypes = [vp, vp]
+    L.blg_last_error.restype = C.c_char_p
+    L.blg_last_error.argtypes = [vp]
+    L.blg_last_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.blg_device_info.argtypes = [vp, C.POINTER(C.c_int), C.c_char_p, sz]
+    L.blg_host_alloc.argtypes = [vp, sz, C.POINTER(vp)]
+    L.blg_host_free.argtypes = [vp, vp]
+    L.blg_kmers.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(KmerOut)]
+    for f in (L.blg_minimizers, L.blg_super_kmers):
+        f.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(SkOut)]
+    L.blg_super_kmers_range.argtypes = [vp, vp, sz, vp, sz, u64, u64, C.POINTER(Params), C.POINTER(SkOut)]
+    L.blg_hash64.argtypes = [vp, vp, sz, u64, C.c_uint32, vp]
+    L.blg_free_kmer_out.argtypes = [vp, C.POINTER(KmerOut)]
+    L.blg_free_kmer_out.restype = None
+    L.blg_free_sk_out.argtypes = [vp, C.POINTER(SkOut)]
+    L.blg_free_sk_out.restype = None
+    _lib = L
+    return L

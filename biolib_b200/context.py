@@ -1,0 +1,155 @@
+"""Host-side convenience over the C ABI: numpy in, numpy out (tests, bench, smoke).
+
+The reference-facing host layer is the C++ shim include/biolib_gpu.hpp (same constructor surface as
+wrapper::kmer_view / minimizer_view / super_kmer_view); this module is the Python harness equivalent and
+calls exactly the same entry points.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, KmerOut, Params, SkOut, Stats
+
+
+class BlgError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"biolib_gpu status {status}: {msg}")
+        self.status = status
+
+
+def _as_bytes_array(seq) -> np.ndarray:
+    if isinstance(seq, np.ndarray):
+        return np.ascontiguousarray(seq.view(np.uint8) if seq.dtype != np.uint8 else seq)
+    if isinstance(seq, str):
+        seq = seq.encode("latin-1")
+    return np.frombuffer(bytes(seq), dtype=np.uint8)
+
+
+class Context:
+    """One GPU, one stream (blg_ctx). Not thread-safe."""
+
+    def __init__(self, device: int = 0):
+        self.L = _capi.lib()
+        h = C.c_void_p()
+        st = self.L.blg_create(device, C.byref(h))
+        if st != _capi.BLG_OK:
+            raise BlgError(st, self.L.blg_strerror(st).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.blg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st: int):
+        if st != _capi.BLG_OK:
+            raise BlgError(st, f"{self.L.blg_strerror(st).decode()}: {self.L.blg_last_error(self.h).decode()}")
+
+    def set_stream(self, cuda_stream: int | None):
+        self._check(self.L.blg_set_stream(self.h, C.c_void_p(cuda_stream or 0)))
+
+    def stats(self) -> dict:
+        s = Stats()
+        self._check(self.L.blg_last_stats(self.h, C.byref(s)))
+        return {f: getattr(s, f) for f, _ in Stats._fields_}
+
+    def device_info(self):
+        n = C.c_int()
+        buf = C.create_string_buffer(128)
+        self._check(self.L.blg_device_info(self.h, C.byref(n), buf, 128))
+        return n.value, buf.value.decode()
+
+    # ------------------------------------------------------------------ host in, host out
+    def kmers(self, seq, k: int, canonical: bool = False, offsets=None) -> dict:
+        b = _as_bytes_array(seq)
+        o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
+        p = Params(k=k, m=0, canonical=int(canonical), flags=0, seed=0)
+        out = KmerOut()
+        self._check(self.L.blg_kmers(self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None,
+                                     0 if o is None else len(o) - 1, C.byref(p), C.byref(out)))
+        n = out.count
+        try:
+            res = dict(lo=_copy(out.value_lo, n, np.uint64), pos=_copy(out.position, n, np.uint64),
+                       hi=_copy(out.value_hi, n, np.uint64) if out.value_hi else np.zeros(n, np.uint64))
+        finally:
+            self.L.blg_free_kmer_out(self.h, C.byref(out))
+        return res
+
+    def super_kmers(self, seq, k: int, m: int, seed: int = 0, canonical: bool = False, offsets=None, want_hash=True,
+                    win_range=None, minimizers_only=False) -> dict:
+        b = _as_bytes_array(seq)
+        o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
+        p = Params(k=k, m=m, canonical=int(canonical), flags=F_EMIT_HASH if want_hash else 0, seed=seed & (2**64 - 1))
+        out = SkOut()
+        args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1)
+        if win_range is not None:
+            st = self.L.blg_super_kmers_range(*args, int(win_range[0]), int(win_range[1]), C.byref(p), C.byref(out))
+        elif minimizers_only:
+            st = self.L.blg_minimizers(*args, C.byref(p), C.byref(out))
+        else:
+            st = self.L.blg_super_kmers(*args, C.byref(p), C.byref(out))
+        self._check(st)
+        n = out.count
+        try:
+            res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=_copy(out.mm_start, n, np.uint64))
+            if not minimizers_only:
+                res["size"] = _copy(out.size, n, np.uint8)
+                res["mm_pos"] = _copy(out.mm_pos, n, np.uint8)
+                res["sk_start"] = res["mm_start"] - res["mm_pos"].astype(np.uint64)
+            if want_hash:
+                res["hash"] = _copy(out.hash, n, np.uint64)
+        finally:
+            self.L.blg_free_sk_out(self.h, C.byref(out))
+        return res
+
+    def minimizers(self, seq, k, m, seed=0, canonical=False, offsets=None, want_hash=True) -> dict:
+        return self.super_kmers(seq, k, m, seed, canonical, offsets, want_hash, minimizers_only=True)
+
+    def hash64(self, values, seed: int) -> np.ndarray:
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        out = np.empty_like(v)
+        self._check(self.L.blg_hash64(self.h, v.ctypes.data, v.size, seed & (2**64 - 1), 0, out.ctypes.data))
+        return out
+
+    # ------------------------------------------------------------------ device resident (raw pointers)
+    def super_kmers_device(self, d_bases: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, d_value: int,
+                           d_mm_start: int, d_size: int, d_mm_pos: int, capacity: int, d_offsets: int = 0, n_seq: int = 0,
+                           win_range=None, d_hash: int = 0) -> int:
+        """Everything already in HBM: enqueue on the context stream, return the record count."""
+        flags = F_DEVICE_INPUT | F_DEVICE_OUTPUT | (F_EMIT_HASH if d_hash else 0)
+        if not d_size:
+            flags |= _capi.F_NO_SIZE
+        p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
+        out = SkOut(count=0, capacity=capacity, value=d_value, mm_start=d_mm_start, size=d_size or None,
+                    mm_pos=d_mm_pos or None, hash=d_hash or None, owner=None)
+        lo, hi = (0, 2**64 - 1) if win_range is None else win_range
+        st = self.L.blg_super_kmers_range(self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq,
+                                          int(lo), int(hi), C.byref(p), C.byref(out))
+        self._check(st)
+        return out.count
+
+    def kmers_device(self, d_bases: int, n_bases: int, k: int, canonical: bool, d_lo: int, d_hi: int, d_pos: int,
+                     capacity: int, d_offsets: int = 0, n_seq: int = 0) -> int:
+        p = Params(k=k, m=0, canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT, seed=0)
+        out = KmerOut(count=0, capacity=capacity, value_lo=d_lo, value_hi=d_hi or None, position=d_pos or None, owner=None)
+        self._check(self.L.blg_kmers(self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq,
+                                     C.byref(p), C.byref(out)))
+        return out.count
+
+
+def _copy(ptr, n, dtype) -> np.ndarray:
+    if not n or not ptr:
+        return np.zeros(0, dtype)
+    nbytes = int(n) * np.dtype(dtype).itemsize
+    buf = (C.c_uint8 * nbytes).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype, count=int(n)).copy()

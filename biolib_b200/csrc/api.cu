@@ -1,0 +1,600 @@
+// api.cu -- the C ABI declared in include/biolib_gpu.h: context, validation, transfers, launches.
+// No algorithm lives here and nothing here computes on the CPU: without a usable CUDA device every
+// compute entry point fails with BLG_E_CUDA.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/biolib_gpu.h"
+#include "kernels.h"
+
+using namespace blg;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct Owner {
+    int device_mem;  // 1: cudaFree, 0: cudaFreeHost
+    void* ptrs[5];
+};
+
+}  // namespace
+
+struct blg_ctx {
+    int device = 0;
+    int sm_count = 0;
+    char name[128] = {0};
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
+    DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_lo, o_hi, o_position;
+    unsigned long long* h_total = nullptr;  // pinned
+    std::string err;
+    blg_stats stats{};
+};
+
+namespace {
+
+#define CK(ctx, call)                                                                                  \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return e_ == cudaErrorMemoryAllocation ? BLG_E_NOMEM : BLG_E_CUDA;                         \
+        }                                                                                              \
+    } while (0)
+
+int ensure(blg_ctx* c, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return BLG_OK;
+    if (b.p) { CK(c, cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    CK(c, cudaMalloc(&b.p, want));
+    b.cap = want;
+    return BLG_OK;
+}
+
+struct Timer {
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    double ms() const { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
+int check_offsets_host(const uint64_t* offs, size_t n_seq, size_t n_bases)
+{
+    if (!offs) return BLG_OK;
+    if (n_seq == 0) return n_bases == 0 ? BLG_OK : BLG_E_INVALID;
+    if (offs[0] != 0 || offs[n_seq] != n_bases) return BLG_E_INVALID;
+    for (size_t i = 0; i < n_seq; ++i)
+        if (offs[i] > offs[i + 1]) return BLG_E_INVALID;
+    return BLG_OK;
+}
+
+// upload (or adopt) bases + offsets; returns device pointers
+int place_input(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint32_t flags,
+                const unsigned char** d_bases, const unsigned long long** d_offs)
+{
+    if (flags & BLG_F_DEVICE_INPUT) {
+        *d_bases = reinterpret_cast<const unsigned char*>(bases);
+        *d_offs = reinterpret_cast<const unsigned long long*>(offs);
+        return BLG_OK;
+    }
+    int rc = check_offsets_host(offs, n_seq, n);
+    if (rc != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
+    if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+    if (n) CK(c, cudaMemcpyAsync(c->in.p, bases, n, cudaMemcpyHostToDevice, c->stream));
+    c->stats.bytes_h2d += n;
+    *d_bases = static_cast<const unsigned char*>(c->in.p);
+    *d_offs = nullptr;
+    if (offs) {
+        const size_t ob = (n_seq + 1) * sizeof(uint64_t);
+        if ((rc = ensure(c, c->offs, ob)) != BLG_OK) return rc;
+        CK(c, cudaMemcpyAsync(c->offs.p, offs, ob, cudaMemcpyHostToDevice, c->stream));
+        c->stats.bytes_h2d += ob;
+        *d_offs = static_cast<const unsigned long long*>(c->offs.p);
+    }
+    return BLG_OK;
+}
+
+int prep_scratch(blg_ctx* c, long long num_tiles)
+{
+    int rc;
+    if ((rc = ensure(c, c->small, 64)) != BLG_OK) return rc;
+    if ((rc = ensure(c, c->status, (size_t)(num_tiles > 0 ? num_tiles : 1) * 8)) != BLG_OK) return rc;
+    CK(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
+    if (num_tiles > 0) CK(c, cudaMemsetAsync(c->status.p, 0, (size_t)num_tiles * 8, c->stream));
+    return BLG_OK;
+}
+
+int read_total(blg_ctx* c, uint64_t* total)
+{
+    CK(c, cudaMemcpyAsync(c->h_total, static_cast<unsigned long long*>(c->small.p) + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    *total = *c->h_total;
+    c->stats.bytes_d2h += 8;
+    return BLG_OK;
+}
+
+void add_kernel_time(blg_ctx* c)
+{
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.kernel_ms += ms;
+}
+
+// one launch of the fused kernel into device arrays
+int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
+{
+    SkLaunchPlan plan;
+    CK(c, sk_plan(a, c->sm_count, &plan));
+    if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
+    int rc = prep_scratch(c, a.num_tiles);
+    if (rc != BLG_OK) return rc;
+    a.tile_counter = static_cast<unsigned int*>(c->small.p);
+    a.total = static_cast<unsigned long long*>(c->small.p) + 1;
+    a.tile_status = static_cast<unsigned long long*>(c->status.p);
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, sk_launch(a, plan, c->stream));
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->stats.kernel_launches += 1;
+    rc = read_total(c, total);
+    if (rc == BLG_OK) add_kernel_time(c);
+    return rc;
+}
+
+int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
+{
+    KmerLaunchPlan plan;
+    CK(c, kmer_plan(a, c->sm_count, &plan));
+    if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
+    int rc = prep_scratch(c, a.num_tiles);
+    if (rc != BLG_OK) return rc;
+    a.tile_counter = static_cast<unsigned int*>(c->small.p);
+    a.total = static_cast<unsigned long long*>(c->small.p) + 1;
+    a.tile_status = static_cast<unsigned long long*>(c->status.p);
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, kmer_launch(a, plan, c->stream));
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->stats.kernel_launches += 1;
+    rc = read_total(c, total);
+    if (rc == BLG_OK) add_kernel_time(c);
+    return rc;
+}
+
+int validate_sk(blg_ctx* c, const blg_params* p, const blg_sk_out* out)
+{
+    if (!c || !p || !out) return BLG_E_INVALID;
+    if (p->k == 0 || p->k > 64 || p->m == 0 || p->m > 32 || p->m > p->k) {
+        c->err = "need 1 <= m <= min(k, 32) and k <= 64";
+        return BLG_E_INVALID;
+    }
+    if (out->capacity > 0 && (!out->value || !out->mm_start)) { c->err = "capacity > 0 needs value and mm_start arrays"; return BLG_E_INVALID; }
+    return BLG_OK;
+}
+
+uint64_t estimate_records(uint64_t nwin, int w)
+{
+    if (w <= 2) return nwin;
+    // random hashes give 2/(w+1) records per k-mer; leave 30% + slack, never above one per k-mer
+    const double est = (double)nwin * 2.0 / (w + 1) * 1.3 + 65536.0;
+    return est > (double)nwin ? nwin : (uint64_t)est;
+}
+
+template <typename T>
+int alloc_owned(blg_ctx* c, bool device_mem, size_t count, T** out, Owner* ow, int slot)
+{
+    void* p = nullptr;
+    const size_t bytes = (count ? count : 1) * sizeof(T);
+    if (device_mem) CK(c, cudaMalloc(&p, bytes));
+    else CK(c, cudaMallocHost(&p, bytes));
+    ow->ptrs[slot] = p;
+    *out = static_cast<T*>(p);
+    return BLG_OK;
+}
+
+void free_owner(Owner* ow)
+{
+    if (!ow) return;
+    for (void* p : ow->ptrs)
+        if (p) { if (ow->device_mem) cudaFree(p); else cudaFreeHost(p); }
+    delete ow;
+}
+
+int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t win_begin,
+              uint64_t win_end, const blg_params* p, blg_sk_out* out, bool with_size)
+{
+    int rc = validate_sk(c, p, out);
+    if (rc != BLG_OK) return rc;
+    Timer tm;
+    c->stats = blg_stats{};
+    c->stats.n_bases = n;
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    const int k = p->k, m = p->m, w = k - m + 1;
+    const bool dev_out = (p->flags & BLG_F_DEVICE_OUTPUT) != 0;
+    const bool want_hash = (p->flags & BLG_F_EMIT_HASH) != 0;
+    with_size = with_size && !(p->flags & BLG_F_NO_SIZE);
+    if (out->capacity > 0 && with_size && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
+    if (out->capacity > 0 && want_hash && !out->hash) { c->err = "BLG_F_EMIT_HASH needs a hash array"; return BLG_E_INVALID; }
+
+    uint64_t hi = n >= (size_t)k ? n - k + 1 : 0;
+    if (win_end < hi) hi = win_end;
+    const uint64_t lo = win_begin < hi ? win_begin : hi;
+    const uint64_t nwin = hi - lo;
+    out->count = 0;
+    if (nwin == 0) {
+        if (out->capacity == 0) { out->value = out->mm_start = out->hash = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
+        c->stats.total_ms = tm.ms();
+        return BLG_OK;
+    }
+
+    const unsigned char* d_bases = nullptr;
+    const unsigned long long* d_offs = nullptr;
+    if ((rc = place_input(c, bases, n, offs, n_seq, p->flags, &d_bases, &d_offs)) != BLG_OK) return rc;
+
+    SkArgs a{};
+    a.bases = d_bases;
+    a.buf_lo = 0; a.buf_hi = (long long)n;
+    a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
+    a.win_lo = (long long)lo; a.win_hi = (long long)hi;
+    a.k = k; a.m = m; a.w = w;
+    a.canonical = p->canonical ? 1 : 0;
+    a.s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL;
+    a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
+
+    uint64_t total = 0;
+    if (dev_out && out->capacity > 0) {
+        // caller-owned device arrays: one launch, no retry
+        a.value = reinterpret_cast<unsigned long long*>(out->value);
+        a.mm_start = reinterpret_cast<unsigned long long*>(out->mm_start);
+        a.size = with_size ? out->size : nullptr;
+        a.mm_pos = with_size ? out->mm_pos : nullptr;
+        a.hash = want_hash ? reinterpret_cast<unsigned long long*>(out->hash) : nullptr;
+        a.capacity = out->capacity;
+        if ((rc = run_sk_once(c, a, &total)) != BLG_OK) return rc;
+        out->count = total;
+        c->stats.n_records = total;
+        c->stats.total_ms = tm.ms();
+        if (total > out->capacity) { c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+        return BLG_OK;
+    }
+
+    // library-managed device arrays (grow-only scratch for host output, fresh allocations for device output)
+    uint64_t cap = estimate_records(nwin, w);
+    if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
+    Owner* ow = nullptr;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (dev_out) {
+            free_owner(ow);
+            ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+            if (!ow) return BLG_E_NOMEM;
+            unsigned long long *v = nullptr, *s = nullptr, *h = nullptr;
+            unsigned char *sz = nullptr, *mp = nullptr;
+            if ((rc = alloc_owned(c, true, cap, &v, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &s, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+            if (with_size && ((rc = alloc_owned(c, true, cap, &sz, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, cap, &mp, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
+            if (want_hash && (rc = alloc_owned(c, true, cap, &h, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
+            a.value = v; a.mm_start = s; a.size = sz; a.mm_pos = mp; a.hash = h;
+        } else {
+            if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * 8)) != BLG_OK) return rc;
+            if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
+            if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
+            a.value = static_cast<unsigned long long*>(c->o_value.p);
+            a.mm_start = static_cast<unsigned long long*>(c->o_mm.p);
+            a.size = with_size ? static_cast<unsigned char*>(c->o_size.p) : nullptr;
+            a.mm_pos = with_size ? static_cast<unsigned char*>(c->o_pos.p) : nullptr;
+            a.hash = want_hash ? static_cast<unsigned long long*>(c->o_hash.p) : nullptr;
+        }
+        a.capacity = cap;
+        if ((rc = run_sk_once(c, a, &total)) != BLG_OK) { free_owner(ow); return rc; }
+        if (total <= cap) break;
+        if (!dev_out && out->capacity > 0 && total > out->capacity) break;  // the caller's arrays cannot hold it anyway
+        cap = total;                                                       // exact size, run again
+    }
+    out->count = total;
+    c->stats.n_records = total;
+    if (dev_out) {
+        out->value = reinterpret_cast<uint64_t*>(a.value);
+        out->mm_start = reinterpret_cast<uint64_t*>(a.mm_start);
+        out->size = a.size; out->mm_pos = a.mm_pos;
+        out->hash = reinterpret_cast<uint64_t*>(a.hash);
+        out->owner = ow;
+        c->stats.total_ms = tm.ms();
+        return BLG_OK;
+    }
+    if (out->capacity > 0) {
+        if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+    } else {
+        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        if (!ow) return BLG_E_NOMEM;
+        out->size = out->mm_pos = nullptr; out->hash = nullptr;
+        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        if (with_size && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
+        if (want_hash && (rc = alloc_owned(c, false, total, &out->hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
+        out->owner = ow;
+    }
+    if (total) {
+        CK(c, cudaMemcpyAsync(out->value, a.value, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaMemcpyAsync(out->mm_start, a.mm_start, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * 16;
+        if (with_size) {
+            CK(c, cudaMemcpyAsync(out->size, a.size, total, cudaMemcpyDeviceToHost, c->stream));
+            CK(c, cudaMemcpyAsync(out->mm_pos, a.mm_pos, total, cudaMemcpyDeviceToHost, c->stream));
+            c->stats.bytes_d2h += total * 2;
+        }
+        if (want_hash) {
+            CK(c, cudaMemcpyAsync(out->hash, a.hash, total * 8, cudaMemcpyDeviceToHost, c->stream));
+            c->stats.bytes_d2h += total * 8;
+        }
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    c->stats.total_ms = tm.ms();
+    return BLG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int blg_abi_version(void) { return BLG_ABI_VERSION; }
+
+const char* blg_strerror(int status)
+{
+    switch (status) {
+    case BLG_OK: return "ok";
+    case BLG_E_INVALID: return "invalid argument";
+    case BLG_E_UNSUPPORTED: return "unsupported combination";
+    case BLG_E_CAPACITY: return "output capacity too small";
+    case BLG_E_CUDA: return "CUDA error (no device, or a runtime failure; see blg_last_error)";
+    case BLG_E_NOMEM: return "out of memory";
+    default: return "unknown status";
+    }
+}
+
+int blg_create(int device, blg_ctx** out)
+{
+    if (!out) return BLG_E_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) return BLG_E_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return BLG_E_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return BLG_E_CUDA;
+    if (prop.major != 10) return BLG_E_UNSUPPORTED;  // built for sm_100a only
+    blg_ctx* c = new (std::nothrow) blg_ctx();
+    if (!c) return BLG_E_NOMEM;
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    snprintf(c->name, sizeof(c->name), "%s", prop.name);
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+        cudaMallocHost(reinterpret_cast<void**>(&c->h_total), 64) != cudaSuccess) {
+        blg_destroy(c);
+        return BLG_E_CUDA;
+    }
+    c->stream = c->own_stream;
+    *out = c;
+    return BLG_OK;
+}
+
+int blg_destroy(blg_ctx* c)
+{
+    if (!c) return BLG_OK;
+    cudaSetDevice(c->device);
+    if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
+                      &c->o_lo, &c->o_hi, &c->o_position})
+        if (b->p) cudaFree(b->p);
+    if (c->h_total) cudaFreeHost(c->h_total);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return BLG_OK;
+}
+
+int blg_set_stream(blg_ctx* c, void* s)
+{
+    if (!c) return BLG_E_INVALID;
+    c->stream = s ? static_cast<cudaStream_t>(s) : c->own_stream;
+    return BLG_OK;
+}
+
+const char* blg_last_error(blg_ctx* c) { return c ? c->err.c_str() : "no context"; }
+
+int blg_last_stats(blg_ctx* c, blg_stats* out)
+{
+    if (!c || !out) return BLG_E_INVALID;
+    *out = c->stats;
+    return BLG_OK;
+}
+
+int blg_device_info(blg_ctx* c, int* sm_count, char* name, size_t name_len)
+{
+    if (!c) return BLG_E_INVALID;
+    if (sm_count) *sm_count = c->sm_count;
+    if (name && name_len) snprintf(name, name_len, "%s", c->name);
+    return BLG_OK;
+}
+
+int blg_host_alloc(blg_ctx* c, size_t bytes, void** out)
+{
+    if (!c || !out) return BLG_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMallocHost(out, bytes ? bytes : 1));
+    return BLG_OK;
+}
+
+int blg_host_free(blg_ctx* c, void* p)
+{
+    if (!c) return BLG_E_INVALID;
+    if (p) CK(c, cudaFreeHost(p));
+    return BLG_OK;
+}
+
+int blg_super_kmers_range(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t win_begin,
+                          uint64_t win_end, const blg_params* p, blg_sk_out* out)
+{
+    return sk_common(c, bases, n, offs, n_seq, win_begin, win_end, p, out, true);
+}
+
+int blg_super_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                    blg_sk_out* out)
+{
+    return sk_common(c, bases, n, offs, n_seq, 0, ~0ULL, p, out, true);
+}
+
+int blg_minimizers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                   blg_sk_out* out)
+{
+    return sk_common(c, bases, n, offs, n_seq, 0, ~0ULL, p, out, false);
+}
+
+int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+              blg_kmer_out* out)
+{
+    if (!c || !p || !out) return BLG_E_INVALID;
+    if (p->k == 0 || p->k > 64) { c->err = "need 1 <= k <= 64"; return BLG_E_INVALID; }
+    const bool wide = p->k > 32;
+    if (out->capacity > 0 && (!out->value_lo || (wide && !out->value_hi))) { c->err = "value arrays missing"; return BLG_E_INVALID; }
+    Timer tm;
+    c->stats = blg_stats{};
+    c->stats.n_bases = n;
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    const bool dev_out = (p->flags & BLG_F_DEVICE_OUTPUT) != 0;
+    const int k = p->k;
+    const uint64_t nwin = n >= (size_t)k ? n - k + 1 : 0;
+    out->count = 0;
+    if (nwin == 0) {
+        if (out->capacity == 0) { out->value_lo = out->value_hi = out->position = nullptr; out->owner = nullptr; }
+        c->stats.total_ms = tm.ms();
+        return BLG_OK;
+    }
+    int rc;
+    const unsigned char* d_bases = nullptr;
+    const unsigned long long* d_offs = nullptr;
+    if ((rc = place_input(c, bases, n, offs, n_seq, p->flags, &d_bases, &d_offs)) != BLG_OK) return rc;
+    KmerArgs a{};
+    a.bases = d_bases; a.buf_lo = 0; a.buf_hi = (long long)n;
+    a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
+    a.win_lo = 0; a.win_hi = (long long)nwin;
+    a.k = k; a.canonical = p->canonical ? 1 : 0;
+    a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
+    uint64_t total = 0;
+    if (dev_out && out->capacity > 0) {
+        a.value_lo = reinterpret_cast<unsigned long long*>(out->value_lo);
+        a.value_hi = wide ? reinterpret_cast<unsigned long long*>(out->value_hi) : nullptr;
+        a.position = reinterpret_cast<unsigned long long*>(out->position);
+        a.capacity = out->capacity;
+        if ((rc = run_kmer_once(c, a, &total)) != BLG_OK) return rc;
+        out->count = total;
+        c->stats.n_records = total;
+        c->stats.total_ms = tm.ms();
+        if (total > out->capacity) { c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+        return BLG_OK;
+    }
+    // at most one record per k-mer start: size the device arrays for that, no retry needed
+    uint64_t cap = nwin;
+    if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
+    Owner* ow = nullptr;
+    if (dev_out) {
+        ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        if (!ow) return BLG_E_NOMEM;
+        unsigned long long *lo = nullptr, *hi = nullptr, *pos = nullptr;
+        if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
+        if (wide && (rc = alloc_owned(c, true, cap, &hi, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        a.value_lo = lo; a.value_hi = hi; a.position = pos;
+    } else {
+        if ((rc = ensure(c, c->o_lo, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_position, cap * 8)) != BLG_OK) return rc;
+        if (wide && (rc = ensure(c, c->o_hi, cap * 8)) != BLG_OK) return rc;
+        a.value_lo = static_cast<unsigned long long*>(c->o_lo.p);
+        a.value_hi = wide ? static_cast<unsigned long long*>(c->o_hi.p) : nullptr;
+        a.position = static_cast<unsigned long long*>(c->o_position.p);
+    }
+    a.capacity = cap;
+    if ((rc = run_kmer_once(c, a, &total)) != BLG_OK) { free_owner(ow); return rc; }
+    out->count = total;
+    c->stats.n_records = total;
+    if (dev_out) {
+        out->value_lo = reinterpret_cast<uint64_t*>(a.value_lo);
+        out->value_hi = reinterpret_cast<uint64_t*>(a.value_hi);
+        out->position = reinterpret_cast<uint64_t*>(a.position);
+        out->owner = ow;
+        c->stats.total_ms = tm.ms();
+        return BLG_OK;
+    }
+    if (out->capacity > 0) {
+        if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+    } else {
+        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        if (!ow) return BLG_E_NOMEM;
+        out->value_hi = nullptr;
+        if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
+        if (wide && (rc = alloc_owned(c, false, total, &out->value_hi, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        out->owner = ow;
+    }
+    if (total) {
+        CK(c, cudaMemcpyAsync(out->value_lo, a.value_lo, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        if (wide) CK(c, cudaMemcpyAsync(out->value_hi, a.value_hi, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        if (out->position) CK(c, cudaMemcpyAsync(out->position, a.position, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * (wide ? 24 : 16);
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    c->stats.total_ms = tm.ms();
+    return BLG_OK;
+}
+
+int blg_hash64(blg_ctx* c, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out)
+{
+    if (!c || (n && (!values || !out))) return BLG_E_INVALID;
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    const unsigned long long s8 = (unsigned long long)(uint32_t)seed ^ 8ULL;
+    if (flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT)) {
+        CK(c, hash64_launch(reinterpret_cast<const unsigned long long*>(values), reinterpret_cast<unsigned long long*>(out), n, s8, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        return BLG_OK;
+    }
+    int rc;
+    if ((rc = ensure(c, c->o_value, n * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, n * 8)) != BLG_OK) return rc;
+    if (n) {
+        CK(c, cudaMemcpyAsync(c->o_value.p, values, n * 8, cudaMemcpyHostToDevice, c->stream));
+        CK(c, hash64_launch(static_cast<unsigned long long*>(c->o_value.p), static_cast<unsigned long long*>(c->o_mm.p), n, s8, c->stream));
+        CK(c, cudaMemcpyAsync(out, c->o_mm.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    return BLG_OK;
+}
+
+void blg_free_kmer_out(blg_ctx* c, blg_kmer_out* out)
+{
+    if (!out) return;
+    if (c) cudaSetDevice(c->device);
+    if (out->owner) {
+        free_owner(static_cast<Owner*>(out->owner));
+        out->value_lo = out->value_hi = out->position = nullptr;
+        out->owner = nullptr;
+        out->count = 0;
+    }
+}
+
+void blg_free_sk_out(blg_ctx* c, blg_sk_out* out)
+{
+    if (!out) return;
+    if (c) cudaSetDevice(c->device);
+    if (out->owner) {
+        free_owner(static_cast<Owner*>(out->owner));
+        out->value = out->mm_start = out->hash = nullptr;
+        out->size = out->mm_pos = nullptr;
+        out->owner = nullptr;
+        out->count = 0;
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,170 @@
+// common.cuh -- device helpers shared by the kernels of the streaming k-mer path (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "nt4_swar.h"
+
+namespace blg {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef unsigned char u8;
+
+// ---------------------------------------------------------------------------------------------
+// MurmurHash3_x64_128 specialised to an 8-byte key, low word only: what hash::hash64::hash<uint64_t>
+// returns (reference include/hash.hpp:55-59 -> :16-21 -> bundled/MurmurHash3.cpp:263-341, tail case 8
+// at :314-322, finalisation :328-337, fmix64 :81-90). For len == 8 the second lane h2 is still the
+// seed when finalisation starts, so s8 = (uint64)(uint32)seed ^ 8 folds both `^= len` steps.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 rotl64(u64 x, int r) { return (x << r) | (x >> (64 - r)); }
+
+__device__ __forceinline__ u64 fmix64(u64 h)
+{
+    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL;
+    h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL;
+    h ^= h >> 33;
+    return h;
+}
+
+__device__ __forceinline__ u64 murmur3_key8(u64 key, u64 s8)
+{
+    u64 k1 = key * 0x87c37b91114253d5ULL;
+    k1 = rotl64(k1, 31);
+    k1 *= 0x4cf5ad432745937fULL;
+    u64 h1 = k1 ^ s8;      // (seed ^ k1) ^ len
+    u64 h2 = s8;           // seed ^ len
+    h1 += h2; h2 += h1;
+    h1 = fmix64(h1); h2 = fmix64(h2);
+    return h1 + h2;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 2-bit streams. Bases are packed 16 per 32-bit word, base q of a word at bits [2q, 2q+2)
+// (little-endian stream: earlier base = lower bits). With that geometry
+//   reverse-complement word of bases [p, p+len)  = ~stream & mask            (free)
+//   forward word (first base most significant)   = pair-reverse of the stream (one BREV + swap)
+// which are the `rev` / `fwd` words of reference include/kmer_view.hpp:194-195 and
+// include/minimizer_view.hpp:236-237.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 pairrev64(u64 x)
+{
+    x = __brevll(x);
+    return ((x >> 1) & 0x5555555555555555ULL) | ((x & 0x5555555555555555ULL) << 1);
+}
+
+// tile staging word: x = 16 codes, y = 16 flag pairs (bit0 = not ACGTU, bit1 = a sequence starts here)
+__device__ __forceinline__ u64 stream64_codes(const uint2* cf, int base_idx)
+{
+    const int wi = base_idx >> 4, sh = (base_idx & 15) * 2;
+    const u32 a = cf[wi].x, b = cf[wi + 1].x, c = cf[wi + 2].x;
+    return ((u64)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
+}
+__device__ __forceinline__ u64 stream64_flags(const uint2* cf, int base_idx)
+{
+    const int wi = base_idx >> 4, sh = (base_idx & 15) * 2;
+    const u32 a = cf[wi].y, b = cf[wi + 1].y, c = cf[wi + 2].y;
+    return ((u64)__funnelshift_r(b, c, sh) << 32) | __funnelshift_r(a, b, sh);
+}
+
+__device__ __forceinline__ u64 lowmask64(int bits) { return bits >= 64 ? ~0ULL : ((1ULL << bits) - 1); }
+
+// ---------------------------------------------------------------------------------------------
+// Staging: ASCII bases [A0, A0 + 16*nw) -> cf[0..nw) (+2 all-bad pad words). Positions outside
+// [buf_lo, buf_hi) read as byte 0, which the table maps to "break". 16-byte vector loads when the
+// buffer's position 0 is 16-byte aligned (vec_ok), byte loads otherwise and at the edges.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_tile(uint2* cf, int nw, const u8* __restrict__ bases, long long buf_lo,
+                                           long long buf_hi, long long A0, int vec_ok, int tid, int nthreads)
+{
+    for (int wi = tid; wi < nw + 2; wi += nthreads) {
+        u32 codes = 0, flags = 0x55555555u;
+        if (wi < nw) {
+            const long long P = A0 + 16LL * wi;
+            u32 w0, w1, w2, w3;
+            if (vec_ok && P >= buf_lo && P + 16 <= buf_hi) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(bases + (P - buf_lo)));
+                w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+            } else {
+                u32 ww[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const long long pos = P + q;
+                    if (pos >= buf_lo && pos < buf_hi) ww[q >> 2] |= (u32)bases[pos - buf_lo] << (8 * (q & 3));
+                }
+                w0 = ww[0]; w1 = ww[1]; w2 = ww[2]; w3 = ww[3];
+            }
+            blg_pack16(w0, w1, w2, w3, &codes, &flags);
+        }
+        cf[wi] = make_uint2(codes, flags);
+    }
+}
+
+// Mark the sequence starts that fall inside the staged range (interior offsets only): one warp.
+__device__ __forceinline__ void mark_sequence_starts(uint2* cf, int nw, const u64* __restrict__ offs, long long n_seq,
+                                                     long long A0, int lane)
+{
+    // first q in [1, n_seq) with offs[q] >= A0
+    long long lo = 1, hi = n_seq;
+    const long long lo_pos = A0 < 0 ? 0 : A0, end_pos = A0 + 16LL * nw;
+    while (lo < hi) {
+        const long long mid = (lo + hi) >> 1;
+        if ((long long)offs[mid] < lo_pos) lo = mid + 1; else hi = mid;
+    }
+    for (long long q = lo + lane; q < n_seq; q += 32) {
+        const long long o = (long long)offs[q];
+        if (o >= end_pos) break;
+        const int rel = (int)(o - A0);
+        atomicOr(&cf[rel >> 4].y, 2u << (2 * (rel & 15)));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Cross-tile ordered compaction: single-pass chained scan with decoupled look-back.
+// status word = flag (bits 63..62: 1 = tile aggregate, 2 = inclusive prefix) | 62-bit count.
+// Tile ids come from an atomic ticket, so every lower tile is held by a CTA that is already
+// running: the spin below cannot deadlock. Called by one full warp; returns the exclusive prefix.
+// ---------------------------------------------------------------------------------------------
+static constexpr u64 ST_AGG = 1ULL << 62, ST_INCL = 2ULL << 62, ST_VAL = (1ULL << 62) - 1;
+
+__device__ __forceinline__ u64 ld_status(const u64* p)
+{
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_status(u64* p, u64 v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ u64 lookback_exclusive(u64* status, long long tile, u64 aggregate, int lane)
+{
+    const unsigned full = 0xffffffffu;
+    if (tile == 0) {
+        if (lane == 0) st_status(&status[0], ST_INCL | aggregate);
+        return 0;
+    }
+    if (lane == 0) st_status(&status[tile], ST_AGG | aggregate);
+    u64 excl = 0;
+    long long look = tile - 1;
+    for (;;) {
+        const long long idx = look - lane;
+        u64 st = idx >= 0 ? ld_status(&status[idx]) : ST_INCL;
+        while (__any_sync(full, (st >> 62) == 0)) {
+            if ((st >> 62) == 0) st = ld_status(&status[idx]);
+        }
+        const unsigned incl = __ballot_sync(full, (st >> 62) == 2);
+        const int first_incl = incl ? (__ffs(incl) - 1) : 32;
+        u64 c = lane <= first_incl ? (st & ST_VAL) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(full, c, o);
+        excl += c;
+        if (incl) break;
+        look -= 32;
+    }
+    if (lane == 0) st_status(&status[tile], ST_INCL | (excl + aggregate));
+    return excl;
+}
+
+}  // namespace blg

@@ -1,0 +1,74 @@
+// kernels.h -- launch interface between the C-ABI layer (api.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace blg {
+
+// One launch of the fused minimizer / super-k-mer kernel over windows [win_lo, win_hi).
+struct SkArgs {
+    const unsigned char* bases;  // address of global position buf_lo
+    long long buf_lo, buf_hi;    // positions present in `bases`
+    const unsigned long long* seq_offsets;  // device, n_seq + 1 entries, global positions; may be null
+    long long n_seq;
+    long long win_lo, win_hi;    // emit the records whose first k-mer starts in [win_lo, win_hi)
+    int k, m, w;
+    int canonical;
+    unsigned long long s8;       // (uint64)(uint32)seed ^ 8
+    int vec_ok;                  // (bases - buf_lo) is 16-byte aligned
+    int rb;                      // real w-blocks per tile = blockDim.x - 3
+    int nwords;                  // staged 16-base words per tile (without the 2 pad words)
+    long long num_tiles;
+    unsigned long long* value;   // outputs (device); size / mm_pos / hash may be null
+    unsigned long long* mm_start;
+    unsigned char* size;
+    unsigned char* mm_pos;
+    unsigned long long* hash;
+    unsigned long long capacity;
+    unsigned int* tile_counter;        // zeroed before launch
+    unsigned long long* tile_status;   // num_tiles entries, zeroed before launch
+    unsigned long long* total;         // out: number of records
+};
+
+struct SkLaunchPlan {
+    int threads;       // w-blocks per tile (= CTA size)
+    size_t smem_bytes;
+    int grid;
+};
+
+// Fills args.rb / args.nwords / args.num_tiles and the launch plan for (k, m) on a device with `sm_count` SMs.
+cudaError_t sk_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
+cudaError_t sk_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
+
+// kmer_view: every valid k-mer as (value, position), in position order.
+struct KmerArgs {
+    const unsigned char* bases;
+    long long buf_lo, buf_hi;
+    const unsigned long long* seq_offsets;
+    long long n_seq;
+    long long win_lo, win_hi;
+    int k;
+    int canonical;
+    int vec_ok;
+    int nwords;
+    long long num_tiles;
+    unsigned long long* value_lo;
+    unsigned long long* value_hi;  // null for k <= 32
+    unsigned long long* position;
+    unsigned long long capacity;
+    unsigned int* tile_counter;
+    unsigned long long* tile_status;
+    unsigned long long* total;
+};
+struct KmerLaunchPlan {
+    int threads;
+    size_t smem_bytes;
+    int grid;
+};
+cudaError_t kmer_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
+cudaError_t kmer_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
+
+cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
+                          cudaStream_t stream);
+
+}  // namespace blg

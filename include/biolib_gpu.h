@@ -1,0 +1,158 @@
+/*
+ * biolib_gpu.h -- C ABI of the B200 (sm_100a) streaming k-mer path.
+ *
+ * This is the drop-in boundary for ONE path of yhhshb/biolib: ASCII DNA -> 2-bit codes ->
+ * k-mers / m-mer hashes -> window minimizers -> super-k-mers. The reference has no FFI or
+ * plugin layer for it; its boundary is three header-only class templates, and each entry point
+ * below replaces one of them in batched form (file:line relative to the reference tree):
+ *
+ *   blg_kmers        <- wrapper::kmer_view<KmerType,Iterator>(start, stop, k, canonical)
+ *                       include/kmer_view.hpp:61, iteration :155-234
+ *   blg_minimizers   <- wrapper::minimizer_view<K,M,Hash,Iterator>(start, stop, k, m, seed, canonical)
+ *                       include/minimizer_view.hpp:88, iteration :166-266, hash include/hash.hpp:55-59
+ *   blg_super_kmers  <- wrapper::super_kmer_view<K,M,Hash>(contig, len, k, m, canonical)
+ *                       include/super_kmer_view.hpp:48-49, iteration :104-135
+ *   blg_hash64       <- hash::hash64::hash<uint64_t>(val, seed)          include/hash.hpp:55-59
+ *
+ * The C++ shim that keeps the reference's constructor surface over these calls is
+ * include/biolib_gpu.hpp. Plain pointers and sizes only; no exceptions cross this boundary;
+ * every function returns a blg_status. There is no CPU fallback: without a CUDA device every
+ * compute call fails with BLG_E_CUDA.
+ *
+ * Coordinates. `bases` is one buffer of n_bases ASCII bytes. `seq_offsets` (n_seq + 1 entries,
+ * offsets[0] == 0, offsets[n_seq] == n_bases, non-decreasing) splits it into independent
+ * sequences; NULL means one sequence. All positions returned are 0-based offsets into `bases`
+ * (the shim rebases them per sequence and applies the reference's +1).
+ * Nothing spans two sequences, and nothing spans a byte that is not one of AaCcGgTtUu
+ * (include/constants.hpp:12-21).
+ */
+#ifndef BIOLIB_GPU_H
+#define BIOLIB_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BLG_ABI_VERSION 1
+
+typedef enum blg_status {
+    BLG_OK = 0,
+    BLG_E_INVALID = 1,     /* bad argument: k == 0, k > 64, m == 0, m > 32, m > k, bad offsets ... */
+    BLG_E_UNSUPPORTED = 2, /* a combination this build does not implement */
+    BLG_E_CAPACITY = 3,    /* caller-provided output too small; out->count holds the required size */
+    BLG_E_CUDA = 4,        /* CUDA runtime error or no device; see blg_last_error() */
+    BLG_E_NOMEM = 5
+} blg_status;
+
+/* flags */
+#define BLG_F_DEVICE_INPUT  0x1u /* bases / seq_offsets are device pointers on the context's GPU */
+#define BLG_F_DEVICE_OUTPUT 0x2u /* output arrays live in device memory (caller- or library-owned) */
+#define BLG_F_EMIT_HASH     0x4u /* also fill out->hash (parity / debugging; not algorithmic bytes) */
+#define BLG_F_NO_SIZE       0x8u /* blg_minimizers sets it: skip size / mm_pos (16 B records) */
+
+typedef struct blg_params {
+    uint8_t k;          /* k-mer length, 1..64 (kmers), m..64 (minimizers / super-k-mers) */
+    uint8_t m;          /* minimizer length, 1..32 (MinimizerType = uint64_t); unused by blg_kmers */
+    uint8_t canonical;  /* 0 / 1: value = min(fwd, reverse complement) */
+    uint8_t reserved;
+    uint32_t flags;     /* BLG_F_* */
+    uint64_t seed;      /* narrowed to 32 bits exactly as include/hash.hpp:50 does */
+} blg_params;
+
+/*
+ * Output of blg_kmers: one entry per valid k-mer, in position order.
+ *   value_lo[i] (and value_hi[i] when k > 32; may be NULL for k <= 32), position[i].
+ * The reference's exact record stream (nullopt records after breaks, ids, the dropped last
+ * k-mer: SURVEY K1-K4) is rebuilt from `position` by the shim.
+ */
+typedef struct blg_kmer_out {
+    uint64_t count;     /* out: number of records (required size on BLG_E_CAPACITY) */
+    uint64_t capacity;  /* in: entries available in caller arrays; 0 = library allocates */
+    uint64_t* value_lo;
+    uint64_t* value_hi;
+    uint64_t* position;
+    void* owner;        /* library bookkeeping for blg_free_*; leave NULL */
+} blg_kmer_out;
+
+/*
+ * Output of blg_minimizers / blg_super_kmers: one record per maximal run of consecutive valid
+ * k-mers sharing the same minimizer occurrence, in order of first k-mer.
+ *   value[i]    canonical-or-forward 2-bit m-mer (minimizer_context_t::value, minimizer_view.hpp:22)
+ *   mm_start[i] 0-based start of the minimizer in `bases`
+ *   size[i]     number of k-mers in the run, 1..k-m+1       (super_kmer_t::size, super_kmer_view.hpp:23)
+ *   mm_pos[i]   mm_start - (start of the first k-mer), 0..k-m (super_kmer_t::mm_pos, :22)
+ *   hash[i]     hash64(value, seed), only with BLG_F_EMIT_HASH
+ * blg_minimizers leaves size / mm_pos untouched (may be NULL).
+ */
+typedef struct blg_sk_out {
+    uint64_t count;
+    uint64_t capacity;
+    uint64_t* value;
+    uint64_t* mm_start;
+    uint8_t* size;
+    uint8_t* mm_pos;
+    uint64_t* hash;
+    void* owner;
+} blg_sk_out;
+
+typedef struct blg_stats {
+    uint64_t n_bases;        /* bases of the last call */
+    uint64_t n_records;      /* records produced */
+    uint64_t bytes_h2d;      /* bytes copied host -> device by the last call */
+    uint64_t bytes_d2h;      /* bytes copied device -> host by the last call */
+    uint64_t kernel_launches;/* kernels of this library launched by the last call */
+    double kernel_ms;        /* device time of those kernels (CUDA events on the context stream) */
+    double total_ms;         /* wall time of the call */
+} blg_stats;
+
+typedef struct blg_ctx blg_ctx;
+
+/* context: one GPU, one stream; not thread-safe (one context per host thread / GPU) */
+int blg_create(int device, blg_ctx** out);
+int blg_destroy(blg_ctx* ctx);
+/* Run on a caller stream (cudaStream_t passed as void*); NULL restores the context's own stream.
+ * Device-resident calls (BLG_F_DEVICE_INPUT|BLG_F_DEVICE_OUTPUT with caller arrays) then only
+ * enqueue work and one 8-byte count read-back. */
+int blg_set_stream(blg_ctx* ctx, void* cuda_stream);
+int blg_abi_version(void);
+const char* blg_strerror(int status);
+const char* blg_last_error(blg_ctx* ctx);
+int blg_last_stats(blg_ctx* ctx, blg_stats* out);
+/* number of SMs / device name of the context's GPU (for sizing and reports) */
+int blg_device_info(blg_ctx* ctx, int* sm_count, char* name, size_t name_len);
+
+/* pinned host memory for callers that want full-speed H2D / D2H */
+int blg_host_alloc(blg_ctx* ctx, size_t bytes, void** out);
+int blg_host_free(blg_ctx* ctx, void* p);
+
+int blg_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+              const blg_params* p, blg_kmer_out* out);
+int blg_minimizers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                   const blg_params* p, blg_sk_out* out);
+int blg_super_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                    const blg_params* p, blg_sk_out* out);
+
+/*
+ * Range form used by the multi-GPU driver: emit only the records whose FIRST k-mer starts in
+ * [win_begin, win_end) (positions in `bases` coordinates); the call reads the k+w-2 halo it needs
+ * from `bases` itself, so ranks given the same buffer (or a slice with halos, rebased by the
+ * caller) produce disjoint, concatenable outputs.
+ */
+int blg_super_kmers_range(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                          uint64_t win_begin, uint64_t win_end, const blg_params* p, blg_sk_out* out);
+
+/* batched hash::hash64::hash<uint64_t> (host pointers unless BLG_F_DEVICE_INPUT|OUTPUT semantics
+ * are requested through `flags`: both arrays then are device pointers) */
+int blg_hash64(blg_ctx* ctx, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out);
+
+/* release library-allocated output arrays (host pinned or device); caller-provided arrays are untouched */
+void blg_free_kmer_out(blg_ctx* ctx, blg_kmer_out* out);
+void blg_free_sk_out(blg_ctx* ctx, blg_sk_out* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BIOLIB_GPU_H */

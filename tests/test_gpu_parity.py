@@ -1,0 +1,170 @@
+"""CUDA path vs the oracle, through the C ABI (bit-exact: everything here is integer work)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+WORKED = "ACGGTCATTGACNCGTAGGATCCAGTT"
+
+
+def rand_seq(rng, n, p_n=0.0, lower=0.0):
+    s = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=n)
+    if p_n > 0:
+        s = s.copy()
+        s[rng.random(n) < p_n] = ord("N")
+    if lower > 0:
+        m = rng.random(n) < lower
+        s = np.where(m, s | 0x20, s).astype(np.uint8)
+    return s
+
+
+def check_sk(gpu, oracle, seq, k, m, seed, canon, offsets=None):
+    g = gpu.super_kmers(seq, k, m, seed, canon, offsets=offsets)
+    o = oracle.super_kmers(seq, k, m, seed, canon, offsets=offsets)
+    assert g["n"] == o["n"], (k, m, seed, canon, g["n"], o["n"])
+    for key in ("value", "hash", "mm_start", "sk_start", "size"):
+        assert np.array_equal(g[key], o[key]), (key, k, m, canon)
+    assert np.array_equal(g["mm_pos"].astype(np.uint64), o["mm_start"] - o["sk_start"])
+
+
+def test_worked_example(gpu, oracle):
+    for canon in (False, True):
+        check_sk(gpu, oracle, WORKED, 7, 4, 42, canon)
+    g = gpu.super_kmers(WORKED, 7, 4, 42, False)
+    assert g["value"].tolist() == [107, 173, 62, 178, 40, 212]
+    assert g["mm_start"].tolist() == [1, 2, 6, 14, 16, 20]
+    assert g["size"].tolist() == [2, 1, 3, 2, 2, 4]
+    assert g["mm_pos"].tolist() == [1, 0, 3, 1, 1, 3]
+
+
+@pytest.mark.parametrize("k,m", [(7, 4), (31, 19), (21, 11), (63, 31), (15, 10), (5, 5), (8, 4), (64, 32), (33, 1), (13, 12), (40, 9)])
+@pytest.mark.parametrize("canon", [False, True])
+def test_random_clean(gpu, oracle, k, m, canon):
+    rng = np.random.default_rng(k * 100 + m)
+    for n in (0, 1, k - 1, k, k + 1, 100, 5000, 70001):
+        check_sk(gpu, oracle, rand_seq(rng, n), k, m, 42, canon)
+
+
+@pytest.mark.parametrize("k,m", [(7, 4), (31, 19), (21, 11), (63, 31), (16, 8)])
+def test_random_with_breaks(gpu, oracle, k, m):
+    rng = np.random.default_rng(7 * k + m)
+    for n, pn in ((300, 0.05), (20000, 0.01), (20000, 0.2), (150000, 0.002)):
+        s = rand_seq(rng, n, p_n=pn, lower=0.1)
+        for canon in (False, True):
+            check_sk(gpu, oracle, s, k, m, 0x10000002A, canon)
+
+
+def test_low_complexity_ties(gpu, oracle):
+    # repeats give equal hashes inside one window: leftmost must win, and a repeated value at a new position cuts
+    for s in ("A" * 500, "AT" * 400, "ACG" * 300, "A" * 100 + "N" + "A" * 100, "ACGT" * 50 + "TTTT" * 30):
+        for k, m in ((7, 4), (31, 19), (12, 6), (9, 9)):
+            for canon in (False, True):
+                check_sk(gpu, oracle, s, k, m, 1, canon)
+
+
+def test_all_byte_values(gpu, oracle):
+    rng = np.random.default_rng(5)
+    s = rng.integers(0, 256, size=40000, dtype=np.uint8)
+    acgt = rand_seq(rng, 40000)
+    s = np.where(rng.random(40000) < 0.97, acgt, s).astype(np.uint8)
+    check_sk(gpu, oracle, s, 15, 7, 9, True)
+    check_sk(gpu, oracle, s, 31, 19, 9, False)
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (9, 5)])
+def test_multi_sequence(gpu, oracle, k, m):
+    rng = np.random.default_rng(11 + k)
+    lens = rng.integers(0, 400, size=300)
+    lens[::17] = 0
+    lens[5] = k
+    lens[6] = k - 1
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    s = rand_seq(rng, int(offsets[-1]), p_n=0.003)
+    for canon in (False, True):
+        check_sk(gpu, oracle, s, k, m, 42, canon, offsets=offsets)
+    # 150 bp reads
+    offsets = (np.arange(0, 2001) * 150).astype(np.uint64)
+    s = rand_seq(rng, int(offsets[-1]), p_n=0.001)
+    check_sk(gpu, oracle, s, k, m, 42, True, offsets=offsets)
+
+
+def test_minimizers_entry_point(gpu, oracle):
+    rng = np.random.default_rng(3)
+    s = rand_seq(rng, 100000, p_n=0.001)
+    g = gpu.minimizers(s, 31, 19, 42, True)
+    o = oracle.super_kmers(s, 31, 19, 42, True)
+    assert g["n"] == o["n"]
+    assert np.array_equal(g["value"], o["value"]) and np.array_equal(g["mm_start"], o["mm_start"])
+    assert np.array_equal(g["hash"], o["hash"])
+
+
+def test_window_ranges_concatenate(gpu, oracle):
+    rng = np.random.default_rng(4)
+    s = rand_seq(rng, 200000, p_n=0.0005)
+    full = gpu.super_kmers(s, 31, 19, 42, True)
+    cuts = [0, 1, 777, 65536, 65537, 131072, 199000, 200000]
+    parts = [gpu.super_kmers(s, 31, 19, 42, True, win_range=(a, b)) for a, b in zip(cuts[:-1], cuts[1:])]
+    for key in ("value", "mm_start", "size", "mm_pos", "hash"):
+        assert np.array_equal(np.concatenate([p[key] for p in parts]), full[key]), key
+
+
+def test_hash64(gpu, oracle):
+    vals = np.array([0, 1, 0x1234567890ABCDEF, 0xFFFFFFFFFFFFFFFF], dtype=np.uint64)
+    assert gpu.hash64(vals, 0).tolist() == [0x28DF63B7CC57C3CB, 0x004403B7FB05C44A, 0x495AE5FABBE9F68B, 0xA0E4B27A1ABAED73]
+    assert gpu.hash64(vals, 42).tolist() == [0x434B9AFE2C3E9543, 0xD3FE46E112F04C44, 0x05E73E3913CB8728, 0xB6A86CA16A85A979]
+    assert gpu.hash64(vals, 0x10000002A).tolist() == gpu.hash64(vals, 42).tolist()
+    rng = np.random.default_rng(0)
+    v = rng.integers(0, 2**63, size=10000, dtype=np.uint64)
+    assert gpu.hash64(v, 7).tolist() == [oracle.hash64(int(x), 7) for x in v]
+
+
+@pytest.mark.parametrize("k", [1, 3, 15, 31, 32, 33, 47, 63, 64])
+@pytest.mark.parametrize("canon", [False, True])
+def test_kmers(gpu, oracle, k, canon):
+    rng = np.random.default_rng(k)
+    for n, pn in ((0, 0), (k - 1, 0), (k, 0), (k + 1, 0), (5000, 0.0), (70000, 0.01), (5000, 0.2)):
+        s = rand_seq(rng, n, p_n=pn, lower=0.05)
+        g = gpu.kmers(s, k, canon)
+        o = oracle.kmers(s, k, canon)
+        assert len(g["lo"]) == len(o["lo"]), (k, n)
+        for key in ("lo", "hi", "pos"):
+            assert np.array_equal(g[key], o[key]), (key, k, n, pn)
+
+
+def test_kmers_multi_sequence(gpu, oracle):
+    rng = np.random.default_rng(8)
+    lens = rng.integers(0, 300, size=200)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    s = rand_seq(rng, int(offsets[-1]), p_n=0.005)
+    for k in (31, 40):
+        g = gpu.kmers(s, k, True, offsets=offsets)
+        o = oracle.kmers(s, k, True, offsets=offsets)
+        for key in ("lo", "hi", "pos"):
+            assert np.array_equal(g[key], o[key]), (key, k)
+
+
+def test_config1_kmer_view_1mbp(gpu, oracle):
+    """BASELINE config 1: kmer_view k=31 canonical over the 1 Mbp sequence_generator(42) sequence."""
+    s = oracle.generate(42, 1_000_000)
+    g = gpu.kmers(s, 31, True)
+    assert len(g["lo"]) == 1_000_000 - 31 + 1
+    # the reference's iterator drops the last k-mer (K1): its 999 969 values have these checksums
+    v = g["lo"][:-1]
+    assert int(np.bitwise_xor.reduce(v)) == 4314334728908509064
+    assert int(v.sum(dtype=np.uint64)) == 8341584218946238560
+    assert int(v[0]) == 2246878431356894220 and int(v[-1]) == 1070654462582993322
+
+
+def test_errors(gpu):
+    import biolib_b200
+    with pytest.raises(biolib_b200.BlgError) as e:
+        gpu.super_kmers("ACGT", 3, 4, 0, False)
+    assert e.value.status == biolib_b200._capi.BLG_E_INVALID
+    with pytest.raises(biolib_b200.BlgError):
+        gpu.super_kmers("ACGT", 65, 4, 0, False)
+    with pytest.raises(biolib_b200.BlgError):
+        gpu.super_kmers("ACGT", 40, 33, 0, False)
+    with pytest.raises(biolib_b200.BlgError):
+        gpu.kmers("ACGT", 0, False)
+    with pytest.raises(biolib_b200.BlgError):
+        gpu.super_kmers("ACGTACGT", 3, 2, 0, False, offsets=np.array([0, 9], dtype=np.uint64))
