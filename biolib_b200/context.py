@@ -138,6 +138,26 @@ class Context:
         self._check(st)
         return out.count
 
+    def super_kmers_raw(self, bases_ptr: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, value_ptr: int,
+                        mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int, flags: int = 0,
+                        offsets_ptr: int = 0, n_seq: int = 0, win_range=None) -> int:
+        """Raw-pointer call with caller-owned arrays (host pointers unless the DEVICE flags are set)."""
+        p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
+        out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr, size=size_ptr or None,
+                    mm_pos=mm_pos_ptr or None, hash=None, owner=None)
+        lo, hi = (0, 2**64 - 1) if win_range is None else win_range
+        self._check(self.L.blg_super_kmers_range(self.h, C.c_void_p(bases_ptr), n_bases, C.c_void_p(offsets_ptr or 0), n_seq,
+                                                 int(lo), int(hi), C.byref(p), C.byref(out)))
+        return out.count
+
+    def host_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._check(self.L.blg_host_alloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def host_free(self, ptr: int):
+        self._check(self.L.blg_host_free(self.h, C.c_void_p(ptr)))
+
     def kmers_device(self, d_bases: int, n_bases: int, k: int, canonical: bool, d_lo: int, d_hi: int, d_pos: int,
                      capacity: int, d_offsets: int = 0, n_seq: int = 0) -> int:
         p = Params(k=k, m=0, canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT, seed=0)

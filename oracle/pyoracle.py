@@ -181,6 +181,8 @@ class Ref:
         L.ref_mutate.restype = C.c_size_t
         L.ref_mutate.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_nt4_table.argtypes = [C.c_void_p]
+        L.ref_super_kmers_sums.restype = C.c_size_t
+        L.ref_super_kmers_sums.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int, C.c_void_p]
 
     def nt4_table(self):
         t = np.zeros(256, np.uint8)
@@ -224,6 +226,13 @@ class Ref:
         bslb = np.zeros(n, np.uint64); ok = np.zeros(n, np.uint8)
         self.lib.ref_mmer_stream(b, n, k, m, seed, int(canonical), val.ctypes.data, idx.ctypes.data, h.ctypes.data, bslb.ctypes.data, ok.ctypes.data)
         return dict(value=val, idx=idx, hash=h, bslb=bslb, valid=ok)
+
+    def super_kmers_sums(self, seq, k, m, seed, canonical):
+        """count + wrapping sums (value, mm_start, size, hash): reference arithmetic + restated windowing."""
+        b = seq if isinstance(seq, np.ndarray) else np.frombuffer(_buf(seq), np.uint8)
+        sums = np.zeros(4, np.uint64)
+        n = self.lib.ref_super_kmers_sums(b.ctypes.data_as(C.c_char_p), b.size, k, m, seed & (2**64 - 1), int(canonical), sums.ctypes.data)
+        return int(n), sums
 
     def minimizer_view_literal_count(self, seq, k, m, seed, canonical):
         b = _buf(seq)

@@ -215,3 +215,57 @@ size_t ref_mutate(const char* s, size_t n, double mutp, double indelf, double ex
 }
 
 } // extern "C"
+
+// CPU arm of the benchmark: the reference's own per-base arithmetic executed verbatim
+// (read_base(): minimizer_view.hpp:229-245; hash::hash64::hash: hash.hpp:55-59 -> bundled Murmur)
+// feeding the restated window-minimum / cut rules D4-D8 (monotone deque, as oracle.c mode 1) -- the
+// reference's own window never fills (F2), so this is the closest runnable "reference CPU path".
+// Single sequence. Returns the record count; sums[0..3] = wrapping sums of value, mm_start, size, hash.
+template <typename KmerT>
+static size_t super_kmers_sum_impl(const char* s, size_t n, unsigned k, unsigned m, uint64_t seed, int canonical, uint64_t sums[4])
+{
+    using view_t = wrapper::minimizer_view<KmerT, uint64_t, hash::hash64, char_iterator>;
+    view_t view(char_iterator(s), char_iterator(s + n), static_cast<uint8_t>(k), static_cast<uint8_t>(m), seed, canonical != 0);
+    typename view_t::const_iterator it(&view, 0);
+    it.itr = char_iterator(s);
+    it.shift = 2 * (m - 1);
+    it.mask = (KmerT(1) << (2 * m)) - 1;
+    it.mm_forward_reverse = {uint64_t(0), uint64_t(0)};
+    const unsigned w = k - m + 1;
+    uint64_t hring[64], vring[64];
+    size_t dq[64];
+    unsigned head = 0, len = 0;
+    size_t cnt = 0, cur_arg = 0, cur_n = 0;
+    bool open = false;
+    uint64_t sv = 0, sp = 0, ss = 0, sh = 0;
+    auto emit = [&]() { sv += vring[cur_arg & 63]; sp += cur_arg; ss += cur_n; sh += hring[cur_arg & 63]; ++cnt; open = false; };
+    for (size_t i = 0; i < n; ++i) {
+        it.read_base();
+        const size_t b = it.bases_since_last_break;
+        if (b == 0) { if (open) emit(); len = 0; continue; }
+        if (b < m) continue;
+        const size_t j = i + 1 - m;
+        const uint64_t v = it.mm_forward_reverse[it.strand];
+        const uint64_t h = hash::hash64::hash(v, view.mseed);
+        hring[j & 63] = h; vring[j & 63] = v;
+        while (len && hring[dq[(head + len - 1) & 63] & 63] > h) --len;
+        dq[(head + len) & 63] = j; ++len;
+        if (b < k) continue;
+        const size_t st = i + 1 - k;
+        while (dq[head & 63] < st) { head = (head + 1) & 63; --len; }
+        const size_t arg = dq[head & 63];
+        if (open && arg == cur_arg) ++cur_n;
+        else { if (open) emit(); open = true; cur_arg = arg; cur_n = 1; }
+    }
+    if (open) emit();
+    (void)w;
+    if (sums) { sums[0] = sv; sums[1] = sp; sums[2] = ss; sums[3] = sh; }
+    return cnt;
+}
+
+extern "C" size_t ref_super_kmers_sums(const char* s, size_t n, unsigned k, unsigned m, uint64_t seed, int canonical, uint64_t sums[4])
+{
+    if (m == 0 || m > 32 || k < m || k > 64) return 0;
+    if (k > 32) return super_kmers_sum_impl<__uint128_t>(s, n, k, m, seed, canonical, sums);
+    return super_kmers_sum_impl<uint64_t>(s, n, k, m, seed, canonical, sums);
+}
