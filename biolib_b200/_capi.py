@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(HERE, "libbiolib_gpu.so")
 CSRC = os.path.join(HERE, "csrc")
 
 BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOMEM = range(6)
-F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE = 0x1, 0x2, 0x4, 0x8
+F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID = 0x1, 0x2, 0x4, 0x8, 0x10
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
@@ -36,7 +36,7 @@ class KmerOut(C.Structure):
 
 class SkOut(C.Structure):
     _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value", C.c_void_p), ("mm_start", C.c_void_p),
-                ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("owner", C.c_void_p)]
+                ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("id", C.c_void_p), ("owner", C.c_void_p)]
 
 
 class Stats(C.Structure):

@@ -86,10 +86,11 @@ class Context:
         return res
 
     def super_kmers(self, seq, k: int, m: int, seed: int = 0, canonical: bool = False, offsets=None, want_hash=True,
-                    win_range=None, minimizers_only=False) -> dict:
+                    win_range=None, minimizers_only=False, want_id=False) -> dict:
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=m, canonical=int(canonical), flags=F_EMIT_HASH if want_hash else 0, seed=seed & (2**64 - 1))
+        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0),
+                   seed=seed & (2**64 - 1))
         out = SkOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1)
         if win_range is not None:
@@ -108,12 +109,14 @@ class Context:
                 res["sk_start"] = res["mm_start"] - res["mm_pos"].astype(np.uint64)
             if want_hash:
                 res["hash"] = _copy(out.hash, n, np.uint64)
+            if want_id:
+                res["id"] = _copy(out.id, n, np.uint64)
         finally:
             self.L.blg_free_sk_out(self.h, C.byref(out))
         return res
 
-    def minimizers(self, seq, k, m, seed=0, canonical=False, offsets=None, want_hash=True) -> dict:
-        return self.super_kmers(seq, k, m, seed, canonical, offsets, want_hash, minimizers_only=True)
+    def minimizers(self, seq, k, m, seed=0, canonical=False, offsets=None, want_hash=True, want_id=False) -> dict:
+        return self.super_kmers(seq, k, m, seed, canonical, offsets, want_hash, minimizers_only=True, want_id=want_id)
 
     def hash64(self, values, seed: int) -> np.ndarray:
         v = np.ascontiguousarray(values, dtype=np.uint64)
@@ -131,7 +134,7 @@ class Context:
             flags |= _capi.F_NO_SIZE
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
         out = SkOut(count=0, capacity=capacity, value=d_value, mm_start=d_mm_start, size=d_size or None,
-                    mm_pos=d_mm_pos or None, hash=d_hash or None, owner=None)
+                    mm_pos=d_mm_pos or None, hash=d_hash or None, id=None, owner=None)
         lo, hi = (0, 2**64 - 1) if win_range is None else win_range
         st = self.L.blg_super_kmers_range(self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq,
                                           int(lo), int(hi), C.byref(p), C.byref(out))
@@ -144,7 +147,7 @@ class Context:
         """Raw-pointer call with caller-owned arrays (host pointers unless the DEVICE flags are set)."""
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
         out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr, size=size_ptr or None,
-                    mm_pos=mm_pos_ptr or None, hash=None, owner=None)
+                    mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None)
         lo, hi = (0, 2**64 - 1) if win_range is None else win_range
         self._check(self.L.blg_super_kmers_range(self.h, C.c_void_p(bases_ptr), n_bases, C.c_void_p(offsets_ptr or 0), n_seq,
                                                  int(lo), int(hi), C.byref(p), C.byref(out)))

@@ -22,7 +22,7 @@ struct DevBuf {
 
 struct Owner {
     int device_mem;  // 1: cudaFree, 0: cudaFreeHost
-    void* ptrs[5];
+    void* ptrs[6];
 };
 
 }  // namespace
@@ -35,7 +35,7 @@ struct blg_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
-    DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_lo, o_hi, o_position;
+    DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
     unsigned long long* h_total = nullptr;  // pinned
     std::string err;
     blg_stats stats{};
@@ -167,6 +167,19 @@ int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
     return rc;
 }
 
+// BLG_F_EMIT_ID: rank directory over the valid-m-mer bits + one query per record (rank_kernel.cu)
+int run_ids(blg_ctx* c, const SkArgs& a, uint64_t total, unsigned long long* d_id)
+{
+    if (total == 0) return BLG_OK;
+    const long long n = a.buf_hi - a.buf_lo;
+    int rc = ensure(c, c->rank, rank_scratch_bytes(n));
+    if (rc != BLG_OK) return rc;
+    int launches = 0;
+    CK(c, record_ids_launch(a.bases, n, a.seq_offsets, a.n_seq, a.m, a.mm_start, total, c->rank.p, d_id, c->stream, &launches));
+    c->stats.kernel_launches += launches;
+    return BLG_OK;
+}
+
 int validate_sk(blg_ctx* c, const blg_params* p, const blg_sk_out* out)
 {
     if (!c || !p || !out) return BLG_E_INVALID;
@@ -219,9 +232,11 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const int k = p->k, m = p->m, w = k - m + 1;
     const bool dev_out = (p->flags & BLG_F_DEVICE_OUTPUT) != 0;
     const bool want_hash = (p->flags & BLG_F_EMIT_HASH) != 0;
+    const bool want_id = (p->flags & BLG_F_EMIT_ID) != 0;
     with_size = with_size && !(p->flags & BLG_F_NO_SIZE);
     if (out->capacity > 0 && with_size && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
     if (out->capacity > 0 && want_hash && !out->hash) { c->err = "BLG_F_EMIT_HASH needs a hash array"; return BLG_E_INVALID; }
+    if (out->capacity > 0 && want_id && !out->id) { c->err = "BLG_F_EMIT_ID needs an id array"; return BLG_E_INVALID; }
 
     uint64_t hi = n >= (size_t)k ? n - k + 1 : 0;
     if (win_end < hi) hi = win_end;
@@ -229,7 +244,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const uint64_t nwin = hi - lo;
     out->count = 0;
     if (nwin == 0) {
-        if (out->capacity == 0) { out->value = out->mm_start = out->hash = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
+        if (out->capacity == 0) { out->value = out->mm_start = out->hash = out->id = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
         c->stats.total_ms = tm.ms();
         return BLG_OK;
     }
@@ -260,8 +275,9 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         if ((rc = run_sk_once(c, a, &total)) != BLG_OK) return rc;
         out->count = total;
         c->stats.n_records = total;
+        if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+        if (want_id && (rc = run_ids(c, a, total, reinterpret_cast<unsigned long long*>(out->id))) != BLG_OK) return rc;
         c->stats.total_ms = tm.ms();
-        if (total > out->capacity) { c->err = "output capacity too small"; return BLG_E_CAPACITY; }
         return BLG_OK;
     }
 
@@ -269,21 +285,25 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     uint64_t cap = estimate_records(nwin, w);
     if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
     Owner* ow = nullptr;
+    unsigned long long* d_id = nullptr;
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (dev_out) {
             free_owner(ow);
-            ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+            ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
             if (!ow) return BLG_E_NOMEM;
-            unsigned long long *v = nullptr, *s = nullptr, *h = nullptr;
+            unsigned long long *v = nullptr, *s = nullptr, *h = nullptr, *idp = nullptr;
             unsigned char *sz = nullptr, *mp = nullptr;
             if ((rc = alloc_owned(c, true, cap, &v, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &s, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
             if (with_size && ((rc = alloc_owned(c, true, cap, &sz, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, cap, &mp, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
             if (want_hash && (rc = alloc_owned(c, true, cap, &h, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
-            a.value = v; a.mm_start = s; a.size = sz; a.mm_pos = mp; a.hash = h;
+            if (want_id && (rc = alloc_owned(c, true, cap, &idp, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
+            a.value = v; a.mm_start = s; a.size = sz; a.mm_pos = mp; a.hash = h; d_id = idp;
         } else {
             if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * 8)) != BLG_OK) return rc;
             if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
             if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
+            if (want_id && (rc = ensure(c, c->o_id, cap * 8)) != BLG_OK) return rc;
+            d_id = want_id ? static_cast<unsigned long long*>(c->o_id.p) : nullptr;
             a.value = static_cast<unsigned long long*>(c->o_value.p);
             a.mm_start = static_cast<unsigned long long*>(c->o_mm.p);
             a.size = with_size ? static_cast<unsigned char*>(c->o_size.p) : nullptr;
@@ -298,7 +318,10 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     }
     out->count = total;
     c->stats.n_records = total;
+    const bool fits = total <= cap;
+    if (want_id && fits && (rc = run_ids(c, a, total, d_id)) != BLG_OK) { free_owner(ow); return rc; }
     if (dev_out) {
+        out->id = reinterpret_cast<uint64_t*>(d_id);
         out->value = reinterpret_cast<uint64_t*>(a.value);
         out->mm_start = reinterpret_cast<uint64_t*>(a.mm_start);
         out->size = a.size; out->mm_pos = a.mm_pos;
@@ -310,12 +333,13 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
         if (!ow) return BLG_E_NOMEM;
-        out->size = out->mm_pos = nullptr; out->hash = nullptr;
+        out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         if (with_size && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, total, &out->hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
+        if (want_id && (rc = alloc_owned(c, false, total, &out->id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
         out->owner = ow;
     }
     if (total) {
@@ -329,6 +353,10 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         }
         if (want_hash) {
             CK(c, cudaMemcpyAsync(out->hash, a.hash, total * 8, cudaMemcpyDeviceToHost, c->stream));
+            c->stats.bytes_d2h += total * 8;
+        }
+        if (want_id) {
+            CK(c, cudaMemcpyAsync(out->id, d_id, total * 8, cudaMemcpyDeviceToHost, c->stream));
             c->stats.bytes_d2h += total * 8;
         }
         CK(c, cudaStreamSynchronize(c->stream));
@@ -388,7 +416,7 @@ int blg_destroy(blg_ctx* c)
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
     for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
-                      &c->o_lo, &c->o_hi, &c->o_position})
+                      &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -504,7 +532,7 @@ int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
     Owner* ow = nullptr;
     if (dev_out) {
-        ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
         if (!ow) return BLG_E_NOMEM;
         unsigned long long *lo = nullptr, *hi = nullptr, *pos = nullptr;
         if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
@@ -532,7 +560,7 @@ int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
         if (!ow) return BLG_E_NOMEM;
         out->value_hi = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
@@ -590,7 +618,7 @@ void blg_free_sk_out(blg_ctx* c, blg_sk_out* out)
     if (c) cudaSetDevice(c->device);
     if (out->owner) {
         free_owner(static_cast<Owner*>(out->owner));
-        out->value = out->mm_start = out->hash = nullptr;
+        out->value = out->mm_start = out->hash = out->id = nullptr;
         out->size = out->mm_pos = nullptr;
         out->owner = nullptr;
         out->count = 0;

@@ -68,6 +68,12 @@ struct KmerLaunchPlan {
 cudaError_t kmer_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
 cudaError_t kmer_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
 
+// minimizer_context_t::id for records already on the device: rank directory over the valid-m-mer bit vector
+size_t rank_scratch_bytes(long long n_bases);
+cudaError_t record_ids_launch(const unsigned char* bases, long long n_bases, const unsigned long long* offs, long long n_seq,
+                              int m, const unsigned long long* mm_start, unsigned long long n_records, void* scratch,
+                              unsigned long long* id, cudaStream_t stream, int* launches);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

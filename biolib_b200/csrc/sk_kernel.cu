@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(256) sk_kernel(const SkArgs a)
         // ---- phase A: roll + hash + prefix minima -----------------------------------------------
         const int lp = off0 + (tid - 1) * w;  // stream index of this thread's first m-mer
         u64 minv = 0;                         // bit i: m-mer i of the block is invalid
+        u64 smask = 0;                        // m == 1 only: bit i: a sequence starts at m-mer i (no m-mer straddles it)
         {
             u64 chunk = stream64_codes(S.cf, lp) & mask1;
             const u64 fchunk = stream64_flags(S.cf, lp) & mask1;
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(256) sk_kernel(const SkArgs a)
                 if (i == 0 || h < ph) { ph = h; pi = i; }   // strict: leftmost wins (minimizer_view.hpp:283)
                 pinv |= inv;
                 minv |= (u64)inv << i;
+                if (m == 1) { const u32 st = f >> 1; smask |= (u64)st << i; pinv |= st; }
                 S.H[i * NB + tid] = h;
                 S.PRE[i * NB + tid] = ph;
                 S.PREI[i * NB + tid] = (u8)(pi | (pinv << 7));
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(256) sk_kernel(const SkArgs a)
                 const u64 h = S.H[i * NB + tid];
                 if (i == w - 1 || h <= sh_) { sh_ = h; si = i; }   // '<=': the left element wins ties
                 sinv |= (u32)(minv >> i) & 1u;
-                u32 am = si, winv = sinv;
+                u32 am = si, winv = sinv | (u32)((smask >> i) >> 1 != 0);   // a sequence start after window start i
                 if (i > 0) {
                     const u64 ph = S.PRE[(i - 1) * NB + tid + 1];
                     const u32 pb = S.PREI[(i - 1) * NB + tid + 1];

@@ -52,6 +52,7 @@ typedef enum blg_status {
 #define BLG_F_DEVICE_OUTPUT 0x2u /* output arrays live in device memory (caller- or library-owned) */
 #define BLG_F_EMIT_HASH     0x4u /* also fill out->hash (parity / debugging; not algorithmic bytes) */
 #define BLG_F_NO_SIZE       0x8u /* blg_minimizers sets it: skip size / mm_pos (16 B records) */
+#define BLG_F_EMIT_ID       0x10u /* also fill out->id (minimizer_context_t::id; one extra pass over the bases) */
 
 typedef struct blg_params {
     uint8_t k;          /* k-mer length, 1..64 (kmers), m..64 (minimizers / super-k-mers) */
@@ -85,6 +86,8 @@ typedef struct blg_kmer_out {
  *   size[i]     number of k-mers in the run, 1..k-m+1       (super_kmer_t::size, super_kmer_view.hpp:23)
  *   mm_pos[i]   mm_start - (start of the first k-mer), 0..k-m (super_kmer_t::mm_pos, :22)
  *   hash[i]     hash64(value, seed), only with BLG_F_EMIT_HASH
+ *   id[i]       number of valid m-mer starts before mm_start inside the same sequence (minimizer_view.hpp:257,263),
+ *               only with BLG_F_EMIT_ID
  * blg_minimizers leaves size / mm_pos untouched (may be NULL).
  */
 typedef struct blg_sk_out {
@@ -95,6 +98,7 @@ typedef struct blg_sk_out {
     uint8_t* size;
     uint8_t* mm_pos;
     uint64_t* hash;
+    uint64_t* id;       /* only with BLG_F_EMIT_ID: ordinal of the minimizer's m-mer among the valid m-mers of its sequence */
     void* owner;
 } blg_sk_out;
 

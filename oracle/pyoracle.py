@@ -146,7 +146,10 @@ class Oracle:
         out = np.empty(cap, np.uint8)
         counts = np.zeros(3, np.uint64); tot = C.c_int64(0)
         n = self.lib.orc_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
-        assert n <= cap
+        if n > cap:  # long insertions: the call reports the size it needs
+            cap = n
+            out = np.empty(cap, np.uint8)
+            n = self.lib.orc_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
         return out[:n].copy(), counts, tot.value
 
 
@@ -249,5 +252,8 @@ class Ref:
         out = np.empty(cap, np.uint8)
         counts = np.zeros(3, np.uint64); tot = C.c_int64(0)
         n = self.lib.ref_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
-        assert n <= cap
+        if n > cap:  # long insertions: the call reports the size it needs
+            cap = n
+            out = np.empty(cap, np.uint8)
+            n = self.lib.ref_mutate(b, len(b), mutp, indelf, extp, seed, out.ctypes.data, cap, counts.ctypes.data, C.byref(tot))
         return out[:n].copy(), counts, tot.value

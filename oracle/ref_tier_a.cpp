@@ -14,7 +14,9 @@
 // against reference-executed results. Guards applied before calling into the reference
 // (SURVEY.md section 8(a), K5/K6/K8):
 //   K5  iterators are placement-constructed in zero-filled storage (kmer_buffer is never
-//       initialised by the reference's constructor);
+//       initialised by the reference's constructor); this TU must be compiled with
+//       -fno-lifetime-dse (oracle/Makefile), otherwise GCC deletes the zero-fill as a dead
+//       store before the constructor and canonical k-mers come out of stack garbage;
 //   K6  the input handed to kmer_view is truncated right after the first invalid byte
 //       that follows the last run of >= k valid bases (the reference over-reads and never
 //       terminates otherwise); no such run => the reference is not called at all;

@@ -168,3 +168,94 @@ def test_errors(gpu):
         gpu.kmers("ACGT", 0, False)
     with pytest.raises(biolib_b200.BlgError):
         gpu.super_kmers("ACGTACGT", 3, 2, 0, False, offsets=np.array([0, 9], dtype=np.uint64))
+
+
+def oracle_ids(oracle, seq, m, seed, canon, mm_start, offsets=None):
+    """D9 from the oracle's per-position validity: valid m-mer starts before mm_start inside its sequence."""
+    valid = oracle.mmers(seq, m, seed, canon, offsets=offsets)["valid"].astype(np.int64)
+    excl = np.concatenate([[0], np.cumsum(valid)])
+    ids = excl[mm_start.astype(np.int64)]
+    if offsets is not None:
+        o = np.asarray(offsets, dtype=np.int64)
+        q = np.searchsorted(o, mm_start.astype(np.int64), side="right") - 1
+        ids = ids - excl[o[q]]
+    return ids.astype(np.uint64)
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (63, 31), (9, 5), (33, 1), (64, 32)])
+def test_minimizer_ids(gpu, oracle, k, m):
+    rng = np.random.default_rng(k + 3 * m)
+    for n, pn in ((k, 0), (5000, 0.0), (70001, 0.01), (200000, 0.0005), (4000, 0.2)):
+        s = rand_seq(rng, n, p_n=pn)
+        for entry in (gpu.super_kmers, gpu.minimizers):
+            g = entry(s, k, m, 42, True, want_id=True)
+            assert np.array_equal(g["id"], oracle_ids(oracle, s, m, 42, True, g["mm_start"])), (k, m, n, pn)
+    lens = rng.integers(0, 500, size=400)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    s = rand_seq(rng, int(offsets[-1]), p_n=0.003)
+    g = gpu.super_kmers(s, k, m, 42, False, offsets=offsets, want_id=True)
+    o = oracle.super_kmers(s, k, m, 42, False, offsets=offsets)
+    assert np.array_equal(g["mm_start"], o["mm_start"])
+    assert np.array_equal(g["id"], oracle_ids(oracle, s, m, 42, False, g["mm_start"], offsets))
+
+
+CPP_DRIVER = r"""
+#include "biolib_gpu.hpp"
+#include <cstdio>
+#include <fstream>
+#include <iterator>
+#include <string>
+int main(int argc, char** argv) {
+    std::ifstream f(argv[1], std::ios::binary);
+    std::string s((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    const int k = std::atoi(argv[2]), m = std::atoi(argv[3]), canon = std::atoi(argv[4]);
+    auto kv = biolib::gpu::kmer_view_from_cstr<uint64_t>(s.data(), s.size(), k, canon);
+    for (auto it = kv.cbegin(); it != kv.cend(); ++it) {
+        auto r = *it;
+        std::printf("K %d %llu %zu %zu\n", r.value ? 1 : 0, (unsigned long long)(r.value ? *r.value : 0), r.position, r.id);
+    }
+    auto mv = biolib::gpu::minimizer_view_from_string<uint64_t, uint64_t, hash::hash64>(s, k, m, 42, canon);
+    if (mv.get_k() != k || mv.get_m() != m) return 2;
+    for (auto const& r : mv) std::printf("M %llu %zu %zu\n", (unsigned long long)r.value, r.position, r.id);
+    biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> sk(s, k, m, canon, 42);
+    for (auto it = sk.cbegin(); it != sk.cend(); ++it)
+        std::printf("S %llu %zu %zu %u %u\n", (unsigned long long)(*it).minimizer.value, (*it).minimizer.position, (*it).minimizer.id,
+                    (unsigned)(*it).mm_pos, (unsigned)(*it).size);
+    try { biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> bad(s, 3, 4); bad.cbegin(); return 4; }
+    catch (std::invalid_argument const&) {}
+    return 0;
+}
+"""
+
+
+def test_cpp_shim_views(gpu, oracle, tmp_path):
+    """The reference-facing C++ surface (include/biolib_gpu.hpp): record streams of the three views."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "drv.cpp"
+    src.write_text(CPP_DRIVER)
+    exe = tmp_path / "drv"
+    libdir = os.path.join(root, "biolib_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
+                           "-L", libdir, "-lbiolib_gpu", f"-Wl,-rpath,{libdir}"])
+    rng = np.random.default_rng(21)
+    cases = [("ACGTNNNACGT", 3, 2), ("ACGTACGT", 3, 2), ("ACGTNA", 3, 3), ("ACGTNNNACG", 3, 1), ("AC", 3, 2), ("NNNN", 3, 2)]
+    cases += [(rand_seq(rng, 3000, p_n=0.01, lower=0.05).tobytes().decode(), 31, 19),
+              (rand_seq(rng, 2000, p_n=0.0).tobytes().decode(), 21, 11),
+              (rand_seq(rng, 500, p_n=0.1).tobytes().decode(), 7, 4)]
+    for seq, k, m in cases:
+        for canon in (0, 1):
+            f = tmp_path / "seq.txt"
+            f.write_bytes(seq.encode())
+            out = subprocess.check_output([str(exe), str(f), str(k), str(m), str(canon)]).decode().split("\n")
+            K = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("K ")]
+            M = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("M ")]
+            S = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("S ")]
+            ks = oracle.kmer_stream(seq, k, canon)
+            assert K == list(zip(ks["has"].tolist(), ks["lo"].tolist(), ks["pos"].tolist(), ks["id"].tolist())), (seq[:20], k, canon)
+            o = oracle.super_kmers(seq, k, m, 42, canon)
+            ids = oracle_ids(oracle, seq, m, 42, canon, o["mm_start"]).tolist() if o["n"] else []
+            want_m = list(zip(o["value"].tolist(), (o["mm_start"] + 1).tolist(), ids))       # D7: position = start + 1
+            assert M == want_m, (seq[:20], k, m, canon)
+            assert S == [a + (int(p), int(z)) for a, p, z in zip(want_m, (o["mm_start"] - o["sk_start"]).tolist(), o["size"].tolist())]
