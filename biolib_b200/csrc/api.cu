@@ -30,6 +30,7 @@ struct Owner {
 struct blg_ctx {
     int device = 0;
     int sm_count = 0;
+    int use_v1 = 0;              // BLG_SK_V1=1: first-generation kernel (development A/B only)
     char name[128] = {0};
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
@@ -132,7 +133,8 @@ void add_kernel_time(blg_ctx* c)
 int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 {
     SkLaunchPlan plan;
-    CK(c, sk_plan(a, c->sm_count, &plan));
+    if (c->use_v1) CK(c, sk_plan(a, c->sm_count, &plan));
+    else CK(c, sk2_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
     int rc = prep_scratch(c, a.num_tiles);
     if (rc != BLG_OK) return rc;
@@ -140,7 +142,8 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    CK(c, sk_launch(a, plan, c->stream));
+    if (c->use_v1) CK(c, sk_launch(a, plan, c->stream));
+    else CK(c, sk2_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -406,6 +409,7 @@ int blg_create(int device, blg_ctx** out)
         return BLG_E_CUDA;
     }
     c->stream = c->own_stream;
+    { const char* e = getenv("BLG_SK_V1"); c->use_v1 = (e && e[0] == '1') ? 1 : 0; }
     *out = c;
     return BLG_OK;
 }

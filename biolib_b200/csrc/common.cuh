@@ -167,4 +167,48 @@ __device__ __forceinline__ u64 lookback_exclusive(u64* status, long long tile, u
     return excl;
 }
 
+// Split, wide variant used by sk2_kernel: a scan unit first PUBLISHES its aggregate (one store, nobody waits), and
+// RESOLVES its exclusive prefix later -- half a tile of other work later -- when every predecessor's aggregate has
+// long been out, so the walk below practically never polls. 128 predecessors per round (four per lane, nearest first).
+__device__ __forceinline__ void scan_publish(u64* status, long long unit, u64 aggregate)
+{
+    // atomicMax: the inclusive word (flag 2) written by whichever warp resolves this unit can never be overwritten
+    // by a late aggregate (flag 1)
+    atomicMax(&status[unit], (unit == 0 ? ST_INCL : ST_AGG) | aggregate);
+}
+
+__device__ __forceinline__ u64 scan_resolve(u64* status, long long unit, u64 aggregate, int lane)
+{
+    const unsigned full = 0xffffffffu;
+    if (unit == 0) return 0;
+    u64 excl = 0;
+    long long look = unit - 1;
+    for (;;) {
+        u64 sum = 0;
+        int found = 0, pending = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const long long idx = look - (4 * lane + j);
+            const u64 st = idx >= 0 ? ld_status(&status[idx]) : ST_INCL;
+            const u32 fl = (u32)(st >> 62);
+            if (!found && !pending) {
+                if (fl == 0) pending = 1;
+                else { sum += st & ST_VAL; found = (fl == 2); }
+            }
+        }
+        const unsigned stop = __ballot_sync(full, found | pending);
+        const int first = stop ? (__ffs(stop) - 1) : 32;
+        const int first_pending = __shfl_sync(full, pending, first & 31) && first < 32;
+        if (first_pending) { __nanosleep(40); continue; }   // the nearest undecided word is still empty: poll again
+        u64 c = lane <= first ? sum : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(full, c, o);
+        excl += c;
+        if (first < 32) break;
+        look -= 128;
+    }
+    if (lane == 0) st_status(&status[unit], ST_INCL | (excl + aggregate));
+    return excl;
+}
+
 }  // namespace blg

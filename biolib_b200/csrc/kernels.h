@@ -19,6 +19,12 @@ struct SkArgs {
     int rb;                      // real w-blocks per tile = blockDim.x - 3
     int nwords;                  // staged 16-base words per tile (without the 2 pad words)
     long long num_tiles;
+    // second-generation kernel (sk2_kernel.cu); filled by sk2_plan
+    long long org;               // win_lo rounded down to a multiple of 16: tile grid origin
+    int R;                       // real windows per tile (multiple of 16)
+    int levels, df;              // doubling levels L = floor(log2 w), last combine offset w - 2^L
+    int pp_off[8], pp_entries;   // shared-memory offsets (in 16-byte entries) of the partial level arrays
+    int warp_smem;               // bytes of shared memory per warp (each warp owns a tile)
     unsigned long long* value;   // outputs (device); size / mm_pos / hash may be null
     unsigned long long* mm_start;
     unsigned char* size;
@@ -39,6 +45,10 @@ struct SkLaunchPlan {
 // Fills args.rb / args.nwords / args.num_tiles and the launch plan for (k, m) on a device with `sm_count` SMs.
 cudaError_t sk_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
 cudaError_t sk_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
+// second generation: same arguments, same results
+#define SK2_THREADS 128
+cudaError_t sk2_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
+cudaError_t sk2_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 
 // kmer_view: every valid k-mer as (value, position), in position order.
 struct KmerArgs {

@@ -16,6 +16,7 @@
 #define BLG_HD __host__ __device__ __forceinline__
 #else
 #define BLG_HD static inline
+
 #endif
 
 // x = four ASCII bytes, byte 0 (least significant) = first base.
@@ -44,5 +45,21 @@ BLG_HD void blg_pack16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint3
     *codes = (p0 & 0xFFu) | ((p1 & 0xFFu) << 8) | ((p2 & 0xFFu) << 16) | ((p3 & 0xFFu) << 24);
     *flags = (p0 >> 8) | ((p1 >> 8) << 8) | ((p2 >> 8) << 16) | ((p3 >> 8) << 24);
 }
+
+// Same classification, different geometry for the second-generation kernel: 32 bits of codes (base q at bits
+// [2q, 2q+2)) and 16 bad bits (base q at bit q).
+BLG_HD void blg_pack16_bits(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t* codes, uint32_t* bad16)
+{
+    const uint32_t p0 = blg_pack4(w0), p1 = blg_pack4(w1), p2 = blg_pack4(w2), p3 = blg_pack4(w3);
+    *codes = (p0 & 0xFFu) | ((p1 & 0xFFu) << 8) | ((p2 & 0xFFu) << 16) | ((p3 & 0xFFu) << 24);
+    // bad flags of blg_pack4 sit at bits 8, 10, 12, 14: squeeze each group of four to bits 0..3
+    const uint32_t f = ((p0 >> 8) & 0x55u) | (((p1 >> 8) & 0x55u) << 8) | (((p2 >> 8) & 0x55u) << 16) | (((p3 >> 8) & 0x55u) << 24);
+    uint32_t x = (f | (f >> 1)) & 0x33333333u;
+    x = (x | (x >> 2)) & 0x0F0F0F0Fu;
+    x = (x | (x >> 4)) & 0x00FF00FFu;
+    x = (x | (x >> 8)) & 0x0000FFFFu;
+    *bad16 = x;
+}
+
 
 #endif
