@@ -36,51 +36,29 @@ constexpr int Q = 16 * NT;        // m-mer starts hashed per tile
 constexpr int NW = NT + 2;        // staged 16-base words
 constexpr int ML_ENTRIES = Q / 16 * 17 + 40;   // 17-entry pitch per lane + slack for reads at +df, +16
 
-// Shared memory of one warp. Arrays with [2] are double buffered: the records of tile i are written out while
-// tile i+1 is being computed.
-struct Sk2Smem {
-    u32* E0;        // [NW + 2] codes, big-endian inside the word (base q at bits 2(15-q))
-    u32* BADW;      // [NW + 8] 16 bad-byte bits per word
-    u32* SEQW;      // [NW + 8] 16 sequence-start bits per word
-    int* FLAG;      // [4] any-sequence-start flag
-    uint4* N1;      // [NT + 2] level-0 entry 0 of every lane
-    uint4* ML;      // [ML_ENTRIES] last doubling level, all 16 entries per lane
-    u32* CW[2];     // [NW + 2] complemented codes, little-endian (base q of a word at bits 2q)
-    u32* FW[2];     // [NW + 2] big-endian stream delayed by 66-2m bits
-    unsigned char* REGION[2];  // partial doubling levels while computing; then IDXF | REC | XM of the finished tile
-};
-constexpr int REG_IDXF = 0;                    // u16 [Q + 16] argmin position of every window
-constexpr int REG_REC = (Q + 16) * 2;          // u16 [Q]      record starts
-constexpr int REG_XM = REG_REC + Q * 2;        // u32 [NT + 8] low 16: "no continuation" bits, high 16: record-end bits
-constexpr int REG_MIN = REG_XM + (NT + 8) * 4;
+// Shared memory of one warp, as byte offsets from the warp's base (plain offsets keep every access an LDS/STS).
+// BUF0 / BUF1 are double buffered: the records of tile i are written out while tile i+1 is being computed.
+constexpr int OFF_E0 = 0;                        // u32 [NW + 2]  codes, big-endian inside the word (base q at bits 2(15-q))
+constexpr int OFF_BADW = OFF_E0 + 144;           // u32 [NW + 8]  16 bad-byte bits per word
+constexpr int OFF_SEQW = OFF_BADW + 176;         // u32 [NW + 8]  16 sequence-start bits per word
+constexpr int OFF_FLAG = OFF_SEQW + 176;         // int [4]       any-sequence-start flag
+constexpr int OFF_N1 = OFF_FLAG + 16;            // uint4 [NT + 2] level-0 entry 0 of every lane
+constexpr int OFF_BUF = OFF_N1 + (NT + 2) * 16;
+constexpr int BUF_CW = 0;                        // u32 [NW + 2]  complemented codes, little-endian (base q at bits 2q)
+constexpr int BUF_FW = BUF_CW + 144;             // u32 [NW + 2]  big-endian stream delayed by 66-2m bits
+constexpr int BUF_IDXF = BUF_FW + 144;           // u16 [Q + 16]  argmin position of every window
+constexpr int BUF_REC = BUF_IDXF + (Q + 16) * 2; // u16 [Q]       record starts
+constexpr int BUF_XM = BUF_REC + Q * 2;          // u32 [NT + 8]  low 16: "no continuation" bits, high 16: record-end bits
+constexpr int BUF_BYTES = BUF_XM + (NT + 8) * 4;
+constexpr int OFF_ML = OFF_BUF + 2 * BUF_BYTES;  // u32 [3][ML_ENTRIES] last doubling level (hi | lo | position);
+                                                 // the partial levels (uint4) use the same bytes before it is written
+constexpr int ML_BYTES = 3 * ML_ENTRIES * 4;
+static_assert(OFF_ML % 16 == 0 && BUF_BYTES % 16 == 0 && OFF_BUF % 16 == 0, "16-byte aligned regions");
 
-__host__ __device__ inline size_t al16(size_t x) { return (x + 15) & ~(size_t)15; }
-
-__host__ __device__ inline size_t sk2_carve(Sk2Smem* s, unsigned char* base, int pp_entries)
+__host__ __device__ inline size_t sk2_warp_bytes(int pp_entries)
 {
-    size_t off = 0;
-    if (s) s->E0 = reinterpret_cast<u32*>(base + off);
-    off += al16((NW + 2) * 4);
-    if (s) s->BADW = reinterpret_cast<u32*>(base + off);
-    off += al16((NW + 8) * 4);
-    if (s) s->SEQW = reinterpret_cast<u32*>(base + off);
-    off += al16((NW + 8) * 4);
-    if (s) s->FLAG = reinterpret_cast<int*>(base + off);
-    off += 16;
-    if (s) s->N1 = reinterpret_cast<uint4*>(base + off);
-    off += (size_t)(NT + 2) * 16;
-    if (s) s->ML = reinterpret_cast<uint4*>(base + off);
-    off += (size_t)ML_ENTRIES * 16;
-    const size_t region = al16((size_t)pp_entries * 16 > (size_t)REG_MIN ? (size_t)pp_entries * 16 : (size_t)REG_MIN);
-    for (int b = 0; b < 2; ++b) {
-        if (s) s->CW[b] = reinterpret_cast<u32*>(base + off);
-        off += al16((NW + 2) * 4);
-        if (s) s->FW[b] = reinterpret_cast<u32*>(base + off);
-        off += al16((NW + 2) * 4);
-        if (s) s->REGION[b] = base + off;
-        off += region;
-    }
-    return off;
+    const size_t pp = (size_t)pp_entries * 16;
+    return (size_t)OFF_ML + (pp > (size_t)ML_BYTES ? pp : (size_t)ML_BYTES);
 }
 
 __device__ __forceinline__ u32 pairrev32(u32 x)
@@ -150,16 +128,26 @@ struct TileConst {
 // records that start in the tile. `resolve_unit >= 0`: this warp also resolves that (earlier) scan unit's prefix,
 // after the window minima, where nothing but the argmin positions is live.
 template <bool CANON, bool MW>
-__device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, const TileConst& c, int b, long long tile, int t,
+__device__ __forceinline__ u32 compute_tile(const SkArgs& a, unsigned char* wsm, const TileConst& c, int b, long long tile, int t,
+                                            bool have_pre, uint4 pre0, uint4 pre1,
                                             long long resolve_unit, u64 resolve_agg, u64* resolve_out)
 {
     const long long tbase = a.org + tile * (long long)a.R - 16;    // global position of local 0 (multiple of 16)
-    u32* CW = S.CW[b];
-    u32* FW = S.FW[b];
-    uint4* PP = reinterpret_cast<uint4*>(S.REGION[b]);
-    unsigned short* IDXF = reinterpret_cast<unsigned short*>(S.REGION[b] + REG_IDXF);
-    unsigned short* REC = reinterpret_cast<unsigned short*>(S.REGION[b] + REG_REC);
-    u32* XM = reinterpret_cast<u32*>(S.REGION[b] + REG_XM);
+    unsigned char* buf = wsm + OFF_BUF + b * BUF_BYTES;
+    u32* E0 = reinterpret_cast<u32*>(wsm + OFF_E0);
+    u32* BADW = reinterpret_cast<u32*>(wsm + OFF_BADW);
+    u32* SEQW = reinterpret_cast<u32*>(wsm + OFF_SEQW);
+    int* FLAG = reinterpret_cast<int*>(wsm + OFF_FLAG);
+    uint4* N1 = reinterpret_cast<uint4*>(wsm + OFF_N1);
+    uint4* PP = reinterpret_cast<uint4*>(wsm + OFF_ML);
+    u32* MLH = reinterpret_cast<u32*>(wsm + OFF_ML);
+    u32* MLL = MLH + ML_ENTRIES;
+    u32* MLX = MLL + ML_ENTRIES;
+    u32* CW = reinterpret_cast<u32*>(buf + BUF_CW);
+    u32* FW = reinterpret_cast<u32*>(buf + BUF_FW);
+    unsigned short* IDXF = reinterpret_cast<unsigned short*>(buf + BUF_IDXF);
+    unsigned short* REC = reinterpret_cast<unsigned short*>(buf + BUF_REC);
+    u32* XM = reinterpret_cast<u32*>(buf + BUF_XM);
 
     // ---- stage: ASCII -> packed streams + bad-byte bits -----------------------------------------------------------
     int anybad = 0;
@@ -168,7 +156,10 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
         if (wi < NW) {
             const long long P = tbase + 16LL * wi;
             u32 w0, w1, w2, w3;
-            if (a.vec_ok && P >= a.buf_lo && P + 16 <= a.buf_hi) {
+            if (have_pre) {
+                const uint4 v = wi < NT ? pre0 : pre1;
+                w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+            } else if (a.vec_ok && P >= a.buf_lo && P + 16 <= a.buf_hi) {
                 const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P - a.buf_lo)));
                 w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
             } else {
@@ -182,13 +173,13 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
             }
             blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
             CW[wi] = ~codes;
-            S.E0[wi] = pairrev32(codes);
+            E0[wi] = pairrev32(codes);
             anybad |= (bad != 0);
         }
-        S.BADW[wi] = bad;
-        S.SEQW[wi] = 0;
+        BADW[wi] = bad;
+        SEQW[wi] = 0;
     }
-    if (t == 0) S.FLAG[0] = 0;
+    if (t == 0) FLAG[0] = 0;
     __syncwarp();
     const int dirty = __any_sync(0xffffffffu, anybad);
     if (a.seq_offsets != nullptr) {
@@ -204,18 +195,18 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
             const long long o = (long long)a.seq_offsets[q];
             if (o >= end_pos) break;
             const int rel = (int)(o - tbase);
-            atomicOr(&S.SEQW[rel >> 4], 1u << (rel & 15));
+            atomicOr(&SEQW[rel >> 4], 1u << (rel & 15));
             found = 1;
         }
-        if (found) S.FLAG[0] = 1;
+        if (found) FLAG[0] = 1;
     }
     for (int x = t; x < NW + 2; x += NT) {
         const int i1 = x - c.dl_words, i0 = i1 - 1;
-        const u32 lo_w = (i1 >= 0 && i1 < NW) ? S.E0[i1] : 0u, hi_w = (i0 >= 0 && i0 < NW) ? S.E0[i0] : 0u;
+        const u32 lo_w = (i1 >= 0 && i1 < NW) ? E0[i1] : 0u, hi_w = (i0 >= 0 && i0 < NW) ? E0[i0] : 0u;
         FW[x] = __funnelshift_r(lo_w, hi_w, c.dl_bits);
     }
     __syncwarp();
-    const int seqdirty = (a.seq_offsets != nullptr) && S.FLAG[0];
+    const int seqdirty = (a.seq_offsets != nullptr) && FLAG[0];
 
     // ---- one hash per m-mer start ---------------------------------------------------------------------------------
     u32 hi[16], lo[16], ix[16];
@@ -240,9 +231,9 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
 
     // ---- window minimum by doubling ---------------------------------------------------------------------------------
     if (c.L >= 1) {
-        S.N1[t] = make_uint4(hi[0], lo[0], ix[0], 0u);
+        N1[t] = make_uint4(hi[0], lo[0], ix[0], 0u);
         __syncwarp();
-        const uint4 nb = S.N1[t + 1];
+        const uint4 nb = N1[t + 1];
 #pragma unroll
         for (int i = 0; i < 15; ++i) keep_min(hi[i], lo[i], ix[i], hi[i + 1], lo[i + 1], ix[i + 1]);
         keep_min(hi[15], lo[15], ix[15], nb.x, nb.y, nb.z);
@@ -253,25 +244,24 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
     if (c.L >= 5) doubling_level<16>(hi, lo, ix, PP + a.pp_off[5], t);
     if (c.L >= 6) doubling_level<32>(hi, lo, ix, PP + a.pp_off[6], t);
     // last level in full, 17-entry pitch per lane; window s = min(level[s], level[s + df])
+    __syncwarp();   // every lane is done reading the partial levels, which share these bytes
 #pragma unroll
-    for (int i = 0; i < 16; ++i) S.ML[17 * t + i] = make_uint4(hi[i], lo[i], ix[i], 0u);
+    for (int i = 0; i < 16; ++i) { MLH[17 * t + i] = hi[i]; MLL[17 * t + i] = lo[i]; MLX[17 * t + i] = ix[i]; }
     __syncwarp();
     u32 vix[17];
     {
         const int cross = 16 - (c.df & 15);           // first i whose partner sits in the next lane's row
-        const uint4* rowA = S.ML + 17 * (t + (c.df >> 4)) + (c.df & 15);
-        const uint4* rowB = rowA + 1;                 // one pad entry per row
+        const int rowA = 17 * (t + (c.df >> 4)) + (c.df & 15);
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-            const uint4 e = (i >= cross ? rowB : rowA)[i];
-            const u64 av = ((u64)hi[i] << 32) | lo[i], bv = ((u64)e.x << 32) | e.y;
-            vix[i] = bv < av ? e.z : ix[i];
+            const int e = rowA + i + (i >= cross ? 1 : 0);   // one pad entry per row
+            const u64 av = ((u64)hi[i] << 32) | lo[i], bv = ((u64)MLH[e] << 32) | MLL[e];
+            vix[i] = bv < av ? MLX[e] : ix[i];
         }
-        const uint4 l16 = S.ML[17 * (t + 1)], r16 = rowB[16];
-        const u64 av = ((u64)l16.x << 32) | l16.y, bv = ((u64)r16.x << 32) | r16.y;
-        vix[16] = bv < av ? r16.z : l16.z;
+        const int l16 = 17 * (t + 1), r16 = rowA + 17;
+        const u64 av = ((u64)MLH[l16] << 32) | MLL[l16], bv = ((u64)MLH[r16] << 32) | MLL[r16];
+        vix[16] = bv < av ? MLX[r16] : MLX[l16];
     }
-    __syncwarp();   // the partial levels in REGION[b] are dead from here on: IDXF / REC / XM take their place
 
     if (resolve_unit >= 0) {
         const u64 excl = scan_resolve(a.tile_status, resolve_unit, resolve_agg, t);
@@ -282,8 +272,8 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
     u32 V = 0x1FFFFu;
     if (dirty | seqdirty) {
         u32 inv = 0;
-        if (dirty) inv |= or_span17(S.BADW, t, c.k, 0);
-        if (seqdirty && c.k > 1) inv |= or_span17(S.SEQW, t, c.k - 1, 1);
+        if (dirty) inv |= or_span17(BADW, t, c.k, 0);
+        if (seqdirty && c.k > 1) inv |= or_span17(SEQW, t, c.k - 1, 1);
         V = ~inv & 0x1FFFFu;
     }
     u32 dif = 0;
@@ -331,15 +321,16 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, const Sk2Smem& S, c
 
 // Record-parallel output of a finished tile from buffer set b: `n_rec` records, the first one at global index `base`.
 template <bool CANON, bool MW>
-__device__ __forceinline__ void emit_tile(const SkArgs& a, const Sk2Smem& S, const TileConst& c, int b, long long tile, int t,
+__device__ __forceinline__ void emit_tile(const SkArgs& a, const unsigned char* wsm, const TileConst& c, int b, long long tile, int t,
                                           u32 n_rec, u64 base)
 {
     const long long tbase = a.org + tile * (long long)a.R - 16;
-    const u32* CW = S.CW[b];
-    const u32* FW = S.FW[b];
-    const unsigned short* IDXF = reinterpret_cast<const unsigned short*>(S.REGION[b] + REG_IDXF);
-    const unsigned short* REC = reinterpret_cast<const unsigned short*>(S.REGION[b] + REG_REC);
-    const u32* XM = reinterpret_cast<const u32*>(S.REGION[b] + REG_XM);
+    const unsigned char* buf = wsm + OFF_BUF + b * BUF_BYTES;
+    const u32* CW = reinterpret_cast<const u32*>(buf + BUF_CW);
+    const u32* FW = reinterpret_cast<const u32*>(buf + BUF_FW);
+    const unsigned short* IDXF = reinterpret_cast<const unsigned short*>(buf + BUF_IDXF);
+    const unsigned short* REC = reinterpret_cast<const unsigned short*>(buf + BUF_REC);
+    const u32* XM = reinterpret_cast<const u32*>(buf + BUF_XM);
     for (u32 r = t; r < n_rec; r += NT) {
         const int s0 = REC[r];
         const int j = IDXF[s0];
@@ -378,12 +369,11 @@ __device__ __forceinline__ void emit_tile(const SkArgs& a, const Sk2Smem& S, con
 }  // namespace
 
 template <bool CANON, bool MW>
-__global__ void __launch_bounds__(SK2_THREADS, 3) sk2_kernel(const SkArgs a)
+__global__ void __launch_bounds__(SK2_THREADS, 4) sk2_kernel(const SkArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    Sk2Smem S;
-    sk2_carve(&S, smem_raw + (size_t)warp * a.warp_smem, a.pp_entries);
+    unsigned char* wsm = smem_raw + warp * a.warp_smem;
     // CTA-wide words behind the per-warp regions
     u32* CNT = reinterpret_cast<u32*>(smem_raw + (size_t)WARPS * a.warp_smem);   // [2][WARPS] record counts
     u64* UBASE = reinterpret_cast<u64*>(CNT + 2 * WARPS);                        // [2] resolved prefix of a unit
@@ -405,6 +395,8 @@ __global__ void __launch_bounds__(SK2_THREADS, 3) sk2_kernel(const SkArgs a)
     //   one warp (rotating) resolves the prefix of unit i-1 in the middle of that;
     //   barrier; unit i's aggregate is published; every warp writes out its tile of unit i-1 from buffer set b^1.
     long long unit = NEXT[0], prev_unit = -1;
+    bool have_pre = false;
+    uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
     u32 prev_n = 0, prev_pre = 0;      // this warp's record count / count of the warps before it, in the previous unit
     u64 prev_agg = 0;                  // the previous unit's total (kept by every warp: the resolver rotates)
     int b = 0;
@@ -416,7 +408,7 @@ __global__ void __launch_bounds__(SK2_THREADS, 3) sk2_kernel(const SkArgs a)
         const long long tile = unit * WARPS + warp;
         u32 n_rec = 0;
         if (have && tile < a.num_tiles)
-            n_rec = compute_tile<CANON, MW>(a, S, c, b, tile, t, resolver ? prev_unit : -1, prev_agg, &UBASE[b ^ 1]);
+            n_rec = compute_tile<CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1, resolver ? prev_unit : -1, prev_agg, &UBASE[b ^ 1]);
         else if (resolver) {
             const u64 excl = scan_resolve(a.tile_status, prev_unit, prev_agg, t);
             if (t == 0) UBASE[b ^ 1] = excl;
@@ -434,11 +426,24 @@ __global__ void __launch_bounds__(SK2_THREADS, 3) sk2_kernel(const SkArgs a)
         if (prev_unit >= 0) {
             const u64 ubase = UBASE[b ^ 1];
             if (threadIdx.x == 0 && prev_unit == num_units - 1) *a.total = ubase + prev_agg;
-            emit_tile<CANON, MW>(a, S, c, b ^ 1, prev_unit * WARPS + warp, t, prev_n, ubase + prev_pre);
         }
+        const long long next_unit = NEXT[b ^ 1];
+        // the next tile's bases start their trip from HBM now and arrive while the previous tile's records are written
+        have_pre = false;
+        {
+            const long long nt = next_unit * WARPS + warp;
+            const long long P0 = a.org + nt * (long long)a.R - 16 - a.buf_lo;
+            if (next_unit < num_units && nt < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * NW <= a.buf_hi - a.buf_lo) {
+                have_pre = true;
+                pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + t);
+                if (t < NW - NT) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT + t);
+            }
+        }
+        if (prev_unit >= 0)
+            emit_tile<CANON, MW>(a, wsm, c, b ^ 1, prev_unit * WARPS + warp, t, prev_n, UBASE[b ^ 1] + prev_pre);
         prev_unit = have ? unit : -1;
         prev_n = n_rec; prev_pre = pre; prev_agg = agg;
-        unit = NEXT[b ^ 1];
+        unit = next_unit;
         b ^= 1;
     }
 }
@@ -471,7 +476,7 @@ cudaError_t sk2_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
     const long long nwin = args.win_hi > args.org ? args.win_hi - args.org : 0;
     args.num_tiles = args.win_hi > args.win_lo ? (nwin + args.R - 1) / args.R : 0;
     plan->threads = SK2_THREADS;
-    args.warp_smem = (int)((sk2_carve(nullptr, nullptr, entries) + 127) & ~(size_t)127);
+    args.warp_smem = (int)((sk2_warp_bytes(entries) + 127) & ~(size_t)127);
     plan->smem_bytes = (size_t)args.warp_smem * WARPS + 2 * WARPS * 4 + 16 + 8 + 8;
     int occ = 0;
     cudaError_t e;
