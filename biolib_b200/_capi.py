@@ -62,9 +62,10 @@ def lib() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no CPU fallback)")
-    L = C.CDLL(LIB_PATH)
+    path = os.environ.get("BLG_LIB_PATH", LIB_PATH)   # development A/B of two builds of the same library
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run __graft_entry__.build() (there is no CPU fallback)")
+    L = C.CDLL(path)
     vp, u64, sz = C.c_void_p, C.c_uint64, C.c_size_t
     L.blg_abi_version.restype = C.c_int
     L.blg_strerror.restype = C.c_char_p

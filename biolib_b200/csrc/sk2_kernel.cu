@@ -42,8 +42,7 @@ constexpr int OFF_E0 = 0;                        // u32 [NW + 2]  codes, big-end
 constexpr int OFF_BADW = OFF_E0 + 144;           // u32 [NW + 8]  16 bad-byte bits per word
 constexpr int OFF_SEQW = OFF_BADW + 176;         // u32 [NW + 8]  16 sequence-start bits per word
 constexpr int OFF_FLAG = OFF_SEQW + 176;         // int [4]       any-sequence-start flag
-constexpr int OFF_N1 = OFF_FLAG + 16;            // uint4 [NT + 2] level-0 entry 0 of every lane
-constexpr int OFF_BUF = OFF_N1 + (NT + 2) * 16;
+constexpr int OFF_BUF = OFF_FLAG + 16;
 constexpr int BUF_CW = 0;                        // u32 [NW + 2]  complemented codes, little-endian (base q at bits 2q)
 constexpr int BUF_FW = BUF_CW + 144;             // u32 [NW + 2]  big-endian stream delayed by 66-2m bits
 constexpr int BUF_IDXF = BUF_FW + 144;           // u16 [Q + 16]  argmin position of every window
@@ -138,7 +137,6 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, unsigned char* wsm,
     u32* BADW = reinterpret_cast<u32*>(wsm + OFF_BADW);
     u32* SEQW = reinterpret_cast<u32*>(wsm + OFF_SEQW);
     int* FLAG = reinterpret_cast<int*>(wsm + OFF_FLAG);
-    uint4* N1 = reinterpret_cast<uint4*>(wsm + OFF_N1);
     uint4* PP = reinterpret_cast<uint4*>(wsm + OFF_ML);
     u32* MLH = reinterpret_cast<u32*>(wsm + OFF_ML);
     u32* MLL = MLH + ML_ENTRIES;
@@ -163,13 +161,14 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, unsigned char* wsm,
                 const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P - a.buf_lo)));
                 w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
             } else {
-                u32 ww[4] = {0, 0, 0, 0};
-#pragma unroll
+                w0 = w1 = w2 = w3 = 0;                 // tile edges / unaligned buffers: byte loads, rolled
+#pragma unroll 1
                 for (int q = 0; q < 16; ++q) {
                     const long long pos = P + q;
-                    if (pos >= a.buf_lo && pos < a.buf_hi) ww[q >> 2] |= (u32)a.bases[pos - a.buf_lo] << (8 * (q & 3));
+                    const u32 byte = (pos >= a.buf_lo && pos < a.buf_hi) ? (u32)a.bases[pos - a.buf_lo] : 0u;
+                    const u32 sh = byte << (8 * (q & 3));
+                    if (q < 4) w0 |= sh; else if (q < 8) w1 |= sh; else if (q < 12) w2 |= sh; else w3 |= sh;
                 }
-                w0 = ww[0]; w1 = ww[1]; w2 = ww[2]; w3 = ww[3];
             }
             blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
             CW[wi] = ~codes;
@@ -209,34 +208,47 @@ __device__ __forceinline__ u32 compute_tile(const SkArgs& a, unsigned char* wsm,
     const int seqdirty = (a.seq_offsets != nullptr) && FLAG[0];
 
     // ---- one hash per m-mer start ---------------------------------------------------------------------------------
-    u32 hi[16], lo[16], ix[16];
+    // A loop of 4 x 4 instead of 16 unrolled copies keeps the kernel inside the 32 KB instruction cache (16 warps per
+    // SM sit at different program counters). The hashes take a round trip through shared memory (level-0 array,
+    // 17-entry pitch) because a rolled loop cannot index registers.
     {
         const u32 W0 = FW[t], W1 = FW[t + 1], W2 = FW[t + 2];
         const u32 C0 = CW[t], C1 = CW[t + 1], C2 = CW[t + 2];
+        u32* hh = MLH + 17 * t;
+        u32* hl = MLL + 17 * t;
+#pragma unroll 1
+        for (int it = 0; it < 4; ++it) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            u32 flo = __funnelshift_r(W2, W1, 30 - 2 * i), fhi = 0, rlo = 0, rhi = 0;
-            if (MW) fhi = __funnelshift_r(W1, W0, 30 - 2 * i) & c.maskhi; else flo &= c.masklo;
-            u64 val = ((u64)fhi << 32) | flo;
-            if (CANON) {
-                rlo = __funnelshift_r(C0, C1, 2 * i);
-                if (MW) rhi = __funnelshift_r(C1, C2, 2 * i) & c.maskhi; else rlo &= c.masklo;
-                const u64 rc = ((u64)rhi << 32) | rlo;
-                val = rc < val ? rc : val;
+            for (int j = 0; j < 4; ++j) {
+                const int i = 4 * it + j;
+                u32 flo = __funnelshift_r(W2, W1, 30 - 2 * i), fhi = 0, rlo = 0, rhi = 0;
+                if (MW) fhi = __funnelshift_r(W1, W0, 30 - 2 * i) & c.maskhi; else flo &= c.masklo;
+                u64 val = ((u64)fhi << 32) | flo;
+                if (CANON) {
+                    rlo = __funnelshift_r(C0, C1, 2 * i);
+                    if (MW) rhi = __funnelshift_r(C1, C2, 2 * i) & c.maskhi; else rlo &= c.masklo;
+                    const u64 rc = ((u64)rhi << 32) | rlo;
+                    val = rc < val ? rc : val;
+                }
+                const u64 h = murmur3_key8(val, c.s8);
+                hh[i] = (u32)(h >> 32); hl[i] = (u32)h;
             }
-            const u64 h = murmur3_key8(val, c.s8);
-            hi[i] = (u32)(h >> 32); lo[i] = (u32)h; ix[i] = (u32)(16 * t + i);
         }
     }
+    __syncwarp();
+    u32 hi[16], lo[16], ix[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { hi[i] = MLH[17 * t + i]; lo[i] = MLL[17 * t + i]; ix[i] = (u32)(16 * t + i); }
 
     // ---- window minimum by doubling ---------------------------------------------------------------------------------
-    if (c.L >= 1) {
-        N1[t] = make_uint4(hi[0], lo[0], ix[0], 0u);
-        __syncwarp();
-        const uint4 nb = N1[t + 1];
+    {
+        const u32 nbh = MLH[17 * (t + 1)], nbl = MLL[17 * (t + 1)];
+        __syncwarp();   // level 0 is in registers: the partial levels may now overwrite these bytes
+        if (c.L >= 1) {
 #pragma unroll
-        for (int i = 0; i < 15; ++i) keep_min(hi[i], lo[i], ix[i], hi[i + 1], lo[i + 1], ix[i + 1]);
-        keep_min(hi[15], lo[15], ix[15], nb.x, nb.y, nb.z);
+            for (int i = 0; i < 15; ++i) keep_min(hi[i], lo[i], ix[i], hi[i + 1], lo[i + 1], ix[i + 1]);
+            keep_min(hi[15], lo[15], ix[15], nbh, nbl, (u32)(16 * t + 16));
+        }
     }
     if (c.L >= 2) doubling_level<2>(hi, lo, ix, PP + a.pp_off[2], t);
     if (c.L >= 3) doubling_level<4>(hi, lo, ix, PP + a.pp_off[3], t);
