@@ -46,7 +46,9 @@ struct SkLaunchPlan {
 cudaError_t sk_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
 cudaError_t sk_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 // second generation: same arguments, same results
+#ifndef SK2_THREADS
 #define SK2_THREADS 128
+#endif
 cudaError_t sk2_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
 cudaError_t sk2_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 

@@ -381,7 +381,7 @@ __device__ __forceinline__ void emit_tile(const SkArgs& a, const unsigned char* 
 }  // namespace
 
 template <bool CANON, bool MW>
-__global__ void __launch_bounds__(SK2_THREADS, 4) sk2_kernel(const SkArgs a)
+__global__ void __launch_bounds__(SK2_THREADS, 512 / SK2_THREADS) sk2_kernel(const SkArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;

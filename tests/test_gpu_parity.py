@@ -108,6 +108,42 @@ def test_window_ranges_concatenate(gpu, oracle):
         assert np.array_equal(np.concatenate([p[key] for p in parts]), full[key]), key
 
 
+@pytest.mark.parametrize("k,m,world", [(31, 19, 2), (63, 31, 4), (21, 11, 8)])
+def test_chunk_plan_slices_concatenate(gpu, oracle, k, m, world):
+    """The multi-GPU chunk+halo plan (biolib_b200.shard) on one device: each 'rank' is given ONLY its slice."""
+    from biolib_b200 import shard
+    rng = np.random.default_rng(11)
+    s = rand_seq(rng, 300_000, p_n=0.0004)
+    o = oracle.super_kmers(s, k, m, 42, True)
+    parts = []
+    for pl in shard.plan_chunks(len(s), k, m, world):
+        g = gpu.super_kmers(s[pl.buf_lo:pl.buf_hi], k, m, 42, True, win_range=pl.local_window)
+        g["mm_start"] = g["mm_start"] + np.uint64(pl.buf_lo)
+        g["sk_start"] = g["sk_start"] + np.uint64(pl.buf_lo)
+        parts.append(g)
+    assert sum(p["n"] for p in parts) == o["n"]
+    for key in ("value", "hash", "mm_start", "sk_start", "size"):
+        assert np.array_equal(np.concatenate([p[key] for p in parts]), o[key]), key
+
+
+def test_sequence_plan_slices_concatenate(gpu, oracle):
+    from biolib_b200 import shard
+    rng = np.random.default_rng(12)
+    lens = rng.integers(10, 600, 2000)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    s = rand_seq(rng, int(offs[-1]), p_n=0.002, lower=0.01)
+    o = oracle.super_kmers(s, 21, 11, 42, True, offsets=offs)
+    parts = []
+    for a, b in shard.plan_sequences(offs, 8):
+        base = offs[a]
+        g = gpu.super_kmers(s[int(base):int(offs[b])], 21, 11, 42, True, offsets=offs[a:b + 1] - base)
+        g["mm_start"] = g["mm_start"] + base
+        g["sk_start"] = g["sk_start"] + base
+        parts.append(g)
+    for key in ("value", "hash", "mm_start", "sk_start", "size"):
+        assert np.array_equal(np.concatenate([p[key] for p in parts]), o[key]), key
+
+
 def test_hash64(gpu, oracle):
     vals = np.array([0, 1, 0x1234567890ABCDEF, 0xFFFFFFFFFFFFFFFF], dtype=np.uint64)
     assert gpu.hash64(vals, 0).tolist() == [0x28DF63B7CC57C3CB, 0x004403B7FB05C44A, 0x495AE5FABBE9F68B, 0xA0E4B27A1ABAED73]
