@@ -30,7 +30,7 @@ struct Owner {
 struct blg_ctx {
     int device = 0;
     int sm_count = 0;
-    int use_v1 = 0;              // BLG_SK_V1=1: first-generation kernel (development A/B only)
+    int sk_gen = 0;              // BLG_SK=1|2|3 pins a kernel generation (development A/B only); 0 = newest that covers (k, m)
     char name[128] = {0};
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
@@ -133,8 +133,11 @@ void add_kernel_time(blg_ctx* c)
 int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 {
     SkLaunchPlan plan;
-    if (c->use_v1) CK(c, sk_plan(a, c->sm_count, &plan));
-    else CK(c, sk2_plan(a, c->sm_count, &plan));
+    int gen = c->sk_gen;
+    if (gen == 0 || (gen == 3 && !sk3_supported(a.k, a.m))) gen = (sk3_supported(a.k, a.m) && a.k - a.m == 32) ? 3 : 2;   // TODO: sk3 is not yet faster for w = 11, 13
+    if (gen == 1) CK(c, sk_plan(a, c->sm_count, &plan));
+    else if (gen == 2) CK(c, sk2_plan(a, c->sm_count, &plan));
+    else CK(c, sk3_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
     int rc = prep_scratch(c, a.num_tiles);
     if (rc != BLG_OK) return rc;
@@ -142,8 +145,9 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (c->use_v1) CK(c, sk_launch(a, plan, c->stream));
-    else CK(c, sk2_launch(a, plan, c->stream));
+    if (gen == 1) CK(c, sk_launch(a, plan, c->stream));
+    else if (gen == 2) CK(c, sk2_launch(a, plan, c->stream));
+    else CK(c, sk3_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -409,7 +413,7 @@ int blg_create(int device, blg_ctx** out)
         return BLG_E_CUDA;
     }
     c->stream = c->own_stream;
-    { const char* e = getenv("BLG_SK_V1"); c->use_v1 = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 0; }
     *out = c;
     return BLG_OK;
 }

@@ -52,6 +52,18 @@ cudaError_t sk_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t
 cudaError_t sk2_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
 cudaError_t sk2_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 
+// third generation (sk3_kernel.cu): lane-owned blocks of (w-1)/Q starts, van Herk / Gil-Werman minima in registers.
+// Covers the (k, m) families of the benchmark configurations; sk3_supported() says which, everything else runs sk2.
+#ifndef SK3_THREADS
+#define SK3_THREADS 128
+#endif
+#ifndef SK3_MIN_BLOCKS
+#define SK3_MIN_BLOCKS 4
+#endif
+bool sk3_supported(int k, int m);
+cudaError_t sk3_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
+cudaError_t sk3_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
+
 // kmer_view: every valid k-mer as (value, position), in position order.
 struct KmerArgs {
     const unsigned char* bases;

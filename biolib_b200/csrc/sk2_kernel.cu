@@ -426,7 +426,11 @@ __global__ void __launch_bounds__(SK2_THREADS, 512 / SK2_THREADS) sk2_kernel(con
             if (t == 0) UBASE[b ^ 1] = excl;
         }
         if (t == 0) CNT[b * WARPS + warp] = n_rec;
+#ifndef X_NOBAR
         __syncthreads();
+#else
+        __syncwarp();
+#endif
         u32 pre = 0, agg = 0;
 #pragma unroll
         for (int q = 0; q < WARPS; ++q) {

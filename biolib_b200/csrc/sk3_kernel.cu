@@ -1,0 +1,541 @@
+// sk3_kernel.cu -- fused minimizer / super-k-mer extraction for sm_100a, third generation.
+//
+// Same results as sk2_kernel.cu / sk_kernel.cu (SURVEY.md 8(a) decisions D1-D8; reference intent
+// include/minimizer_view.hpp:184-266, include/super_kmer_view.hpp:121-135). What changed is the instruction count:
+// the profile of sk2 (profiles/r01_s23_sk2_kernel_instmix.txt) shows ~176 executed instructions per m-mer start with
+// the ALU pipe as the busiest unit, 35 of them in the sparse-table window minimum. Here
+//
+//   * a lane owns a BLOCK of B = (w-1)/Q consecutive m-mer starts (Q = 1 or 2), so the window minimum becomes the
+//     van Herk / Gil-Werman scheme entirely in registers: while hashing, the lane keeps the running PREFIX minimum of
+//     its block and hands each prefix entry to shared memory; afterwards it walks its block backwards keeping the
+//     SUFFIX minimum and combines suffix(i) with the prefix(i) of the lane Q to its right (for Q = 2 the block in
+//     between enters as the initial value of the suffix scan). A window [s, s+w) is exactly
+//     suffix-of-own-block + (Q-1 whole blocks) + prefix-of-block-(t+Q): three compare/selects per window instead of
+//     log2(w)+1, and only the argmin position leaves the last one. Ties: every compare keeps the left operand unless
+//     the right one is strictly smaller, so the leftmost minimum wins exactly as the strict '<' of
+//     include/minimizer_view.hpp:283,374 does;
+//   * each lane cuts its own 64- or 96-bit local copies of the two packed streams (reverse-complement side:
+//     complemented little-endian; forward side: big-endian, aligned so that its LAST m-mer sits at bit 0), so every
+//     per-m-mer extraction is one or two funnel shifts with immediate amounts, for any tile alignment;
+//   * tiles need not start on a 16-base boundary any more: lane 0 is the left margin (the previous window's argmin),
+//     lanes 1 .. 31-2Q own the record starts, the Q lanes after them are seen far enough to size those records.
+//
+// The outer structure is sk2's: a warp owns a tile end to end, four warps form one scan unit, and the ordered output
+// offset comes from the software-pipelined decoupled look-back (publish / resolve half a tile later / write out one
+// tile later from the second buffer set).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace blg {
+
+namespace {
+
+constexpr int NT = 32;
+constexpr int WARPS3 = SK3_THREADS / 32;
+constexpr int PADF = 3;     // zero words in front of the big-endian stream
+
+template <int B, int Q>
+struct Geo {
+    static constexpr int S = NT * B;                   // m-mer starts hashed per tile
+    static constexpr int LANES_OUT = 31 - 2 * Q;       // lanes 1 .. 31-2Q own record starts
+    static constexpr int R = LANES_OUT * B;            // new windows per tile
+    static constexpr int NWORDS = S / 16 + 3;          // staged 16-base words: 15 (alignment) + S + 31 (m-1) bases
+    static constexpr int NROW = (NWORDS + 8) / 2 + 2;  // u32 words of the packed bad-byte / sequence-start bit rows
+    // per-warp shared memory, byte offsets
+    static constexpr int OFF_BAD = 0;                              // u32 [NROW]   bit x: base a0 + x is not ACGTU
+    static constexpr int OFF_SEQ = OFF_BAD + NROW * 4;             // u32 [NROW]   bit x: a sequence starts at a0 + x
+    static constexpr int OFF_FLAG = OFF_SEQ + NROW * 4;            // int [4]
+    static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;   // uint4 [B*32 + Q + 1]  prefix minima, [i][lane]
+    static constexpr int OFF_BUF = OFF_P + (B * 32 + Q + 1) * 16;
+    // double-buffered part (tile i is written out while tile i+1 is computed)
+    static constexpr int BUF_CW = 0;                               // u32 [NWORDS + 3]  complemented codes, little-endian
+    static constexpr int BUF_EW = BUF_CW + (NWORDS + 3) * 4;       // u32 [PADF + NWORDS + 3]  codes, big-endian words
+    static constexpr int BUF_IDXF = (BUF_EW + (PADF + NWORDS + 3) * 4 + 15) / 16 * 16;   // u16 [S]  argmin of every window
+    static constexpr int BUF_REC = BUF_IDXF + S * 2;               // u16 [R + 8]  record starts (local window index)
+    static constexpr int BUF_EB = (BUF_REC + (R + 8) * 2 + 15) / 16 * 16;                // u32 [S/32 + 4]  record-end bits
+    static constexpr int BUF_BYTES = (BUF_EB + (S / 32 + 4) * 4 + 15) / 16 * 16;
+    static constexpr int WARP_BYTES = (OFF_BUF + 2 * BUF_BYTES + 127) / 128 * 128;
+};
+
+__device__ __forceinline__ u32 pairrev32(u32 x)
+{
+    x = __brev(x);
+    return ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+}
+
+// running (left) keeps unless cand (right) is strictly smaller
+__device__ __forceinline__ void take_if_less(u32& rhi, u32& rlo, u32& rix, u32 chi, u32 clo, u32 cix)
+{
+    const u64 rv = ((u64)rhi << 32) | rlo, cv = ((u64)chi << 32) | clo;
+    const bool lt = cv < rv;
+    rhi = lt ? chi : rhi; rlo = lt ? clo : rlo; rix = lt ? cix : rix;
+}
+// cand is to the LEFT of running: it wins unless running is strictly smaller
+__device__ __forceinline__ void take_unless_greater(u32& rhi, u32& rlo, u32& rix, u32 chi, u32 clo, u32 cix)
+{
+    const u64 rv = ((u64)rhi << 32) | rlo, cv = ((u64)chi << 32) | clo;
+    const bool keep = rv < cv;
+    rhi = keep ? rhi : chi; rlo = keep ? rlo : clo; rix = keep ? rix : cix;
+}
+
+// low B bits: OR over d in [0, span) of bit (bitpos + i + d + shift) of the packed bit row, for i = 0 .. B-1
+template <int B>
+__device__ __forceinline__ u32 or_span_bits(const u32* row, int bitpos, int span, int shift)
+{
+    const int wq = bitpos >> 5, sh = bitpos & 31;
+    const u32 w0 = row[wq], w1 = row[wq + 1], w2 = row[wq + 2], w3 = row[wq + 3];
+    u32 x0 = __funnelshift_r(w0, w1, sh), x1 = __funnelshift_r(w1, w2, sh), x2 = __funnelshift_r(w2, w3, sh);
+    if (shift) { x0 = __funnelshift_r(x0, x1, 1); x1 = __funnelshift_r(x1, x2, 1); x2 >>= 1; }
+    int covered = 1;
+    while (covered < span) {
+        int step = covered < span - covered ? covered : span - covered;
+        covered += step;
+        u32 y0 = x0, y1 = x1, y2 = x2;
+        if (step >= 32) { y0 = y1; y1 = y2; y2 = 0; step -= 32; }
+        if (step) { y0 = __funnelshift_r(y0, y1, step); y1 = __funnelshift_r(y1, y2, step); y2 >>= step; }
+        x0 |= y0; x1 |= y1; x2 |= y2;
+    }
+    return x0 & ((1u << B) - 1u);
+}
+
+struct TileConst3 {
+    u32 maskhi, masklo;
+    int w, m, k;
+    u64 s8;
+};
+
+template <int B, int Q, int LW, bool CANON, bool MW>
+__device__ __forceinline__ u32 compute_tile3(const SkArgs& a, unsigned char* wsm, const TileConst3& c, int b, long long tile, int t,
+                                             bool have_pre, uint4 pre0, uint4 pre1,
+                                             long long resolve_unit, u64 resolve_agg, u64* resolve_out)
+{
+    using G = Geo<B, Q>;
+    const long long g0 = a.org + tile * (long long)G::R - B;   // global position of local start 0 (lane 0 = left margin)
+    const long long a0 = g0 & ~15LL;                            // staged range starts on a 16-base boundary
+    const int o = (int)(g0 - a0);
+    unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
+    u32* BAD = reinterpret_cast<u32*>(wsm + G::OFF_BAD);
+    u32* SEQ = reinterpret_cast<u32*>(wsm + G::OFF_SEQ);
+    int* FLAG = reinterpret_cast<int*>(wsm + G::OFF_FLAG);
+    uint4* P = reinterpret_cast<uint4*>(wsm + G::OFF_P);
+    u32* CW = reinterpret_cast<u32*>(buf + G::BUF_CW);
+    u32* EW = reinterpret_cast<u32*>(buf + G::BUF_EW);
+    u32* IDXF32 = reinterpret_cast<u32*>(buf + G::BUF_IDXF);
+    unsigned short* REC = reinterpret_cast<unsigned short*>(buf + G::BUF_REC);
+    u32* EB = reinterpret_cast<u32*>(buf + G::BUF_EB);
+
+    // ---- stage: ASCII -> packed streams + bad-byte bits -----------------------------------------------------------
+    int anybad = 0;
+    {
+        unsigned short* BAD16 = reinterpret_cast<unsigned short*>(BAD);
+        for (int wi = t; wi < 2 * G::NROW; wi += NT) {
+            u32 codes = 0, bad = 0xFFFFu;
+            if (wi < G::NWORDS) {
+                const long long P16 = a0 + 16LL * wi;
+                u32 w0, w1, w2, w3;
+                if (have_pre) {
+                    const uint4 v = wi < NT ? pre0 : pre1;
+                    w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                } else if (a.vec_ok && P16 >= a.buf_lo && P16 + 16 <= a.buf_hi) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P16 - a.buf_lo)));
+                    w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                } else {
+                    w0 = w1 = w2 = w3 = 0;                 // tile edges / unaligned buffers: byte loads, rolled
+#pragma unroll 1
+                    for (int q = 0; q < 16; ++q) {
+                        const long long pos = P16 + q;
+                        const u32 byte = (pos >= a.buf_lo && pos < a.buf_hi) ? (u32)a.bases[pos - a.buf_lo] : 0u;
+                        const u32 sh = byte << (8 * (q & 3));
+                        if (q < 4) w0 |= sh; else if (q < 8) w1 |= sh; else if (q < 12) w2 |= sh; else w3 |= sh;
+                    }
+                }
+                blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
+                anybad |= (bad != 0);
+            }
+            if (wi < G::NWORDS + 3) {
+                CW[wi] = ~codes;
+                EW[PADF + wi] = pairrev32(codes);
+            }
+            BAD16[wi] = (unsigned short)bad;
+        }
+        if (t < PADF) EW[t] = 0;
+        for (int x = t; x < G::NROW; x += NT) SEQ[x] = 0;
+        for (int x = t; x < G::S / 32 + 4; x += NT) EB[x] = 0;
+        if (t == 0) FLAG[0] = 0;
+    }
+    __syncwarp();
+    const int dirty = __any_sync(0xffffffffu, anybad);
+    if (a.seq_offsets != nullptr) {
+        // interior sequence starts inside the staged range
+        long long lo = 1, hi = a.n_seq;
+        const long long lo_pos = a0 < 0 ? 0 : a0, end_pos = a0 + 16LL * G::NWORDS;
+        while (lo < hi) {
+            const long long mid = (lo + hi) >> 1;
+            if ((long long)a.seq_offsets[mid] < lo_pos) lo = mid + 1; else hi = mid;
+        }
+        int found = 0;
+        for (long long q = lo + t; q < a.n_seq; q += 32) {
+            const long long off = (long long)a.seq_offsets[q];
+            if (off >= end_pos) break;
+            const int rel = (int)(off - a0);
+            atomicOr(&SEQ[rel >> 5], 1u << (rel & 31));
+            found = 1;
+        }
+        if (found) FLAG[0] = 1;
+        __syncwarp();
+    }
+    const int seqdirty = (a.seq_offsets != nullptr) && FLAG[0];
+
+    // ---- lane-local streams ---------------------------------------------------------------------------------------
+    const int x0 = o + B * t;                                  // base index of this lane's first start, from a0
+    u32 Rl[LW], Fl[LW];
+    {
+        const int wi0 = x0 >> 4, sh = (x0 & 15) * 2;
+        u32 cw[LW + 1];
+#pragma unroll
+        for (int j = 0; j <= LW; ++j) cw[j] = CW[wi0 + j];
+#pragma unroll
+        for (int j = 0; j < LW; ++j) Rl[j] = __funnelshift_r(cw[j], cw[j + 1], sh);   // Rl[0] = least significant
+        // big-endian side: the 32*LW bits that END with the last base of this lane's last m-mer
+        const int bp = 2 * (x0 + B - 1 + c.m) - 32 * LW + 32 * PADF;
+        const int wj = bp >> 5, fs = bp & 31;
+        u32 ew[LW + 1];
+#pragma unroll
+        for (int j = 0; j <= LW; ++j) ew[j] = EW[wj + j];
+#pragma unroll
+        for (int j = 0; j < LW; ++j) Fl[j] = __funnelshift_l(ew[j + 1], ew[j], fs);   // Fl[0] = most significant
+    }
+
+    // ---- one hash per m-mer start, running prefix minimum of the block ----------------------------------------------
+    u32 hh[B], hl[B];
+    {
+        u32 phi = 0, plo = 0, pix = 0;
+#pragma unroll
+        for (int i = 0; i < B; ++i) {
+            const int cI = 2 * (B - 1 - i);
+            u32 flo, fhi = 0;
+            if (LW == 2) {
+                flo = __funnelshift_r(Fl[1], Fl[0], cI);
+                if (MW) fhi = (Fl[0] >> cI) & c.maskhi; else flo &= c.masklo;
+            } else {
+                flo = __funnelshift_r(Fl[2], Fl[1], cI);
+                if (MW) fhi = __funnelshift_r(Fl[1], Fl[0], cI) & c.maskhi; else flo &= c.masklo;
+            }
+            u64 val = ((u64)fhi << 32) | flo;
+            if (CANON) {
+                u32 rlo = __funnelshift_r(Rl[0], Rl[1], 2 * i), rhi = 0;
+                if (MW) rhi = (LW == 2 ? (Rl[1] >> (2 * i)) : __funnelshift_r(Rl[1], Rl[LW - 1], 2 * i)) & c.maskhi;
+                else rlo &= c.masklo;
+                const u64 rc = ((u64)rhi << 32) | rlo;
+                val = rc < val ? rc : val;
+            }
+            const u64 h = murmur3_key8(val, c.s8);
+            hh[i] = (u32)(h >> 32); hl[i] = (u32)h;
+            if (i == 0) { phi = hh[0]; plo = hl[0]; pix = (u32)(B * t); }
+            else take_if_less(phi, plo, pix, hh[i], hl[i], (u32)(B * t + i));
+            P[i * 32 + t] = make_uint4(phi, plo, pix, 0u);
+        }
+    }
+    __syncwarp();
+
+    // ---- suffix minimum + combine: argmin position of every window ----------------------------------------------------
+    u32 vix[B];
+    {
+        u32 shi = 0, slo = 0, six = 0;
+        if (Q == 2) { const uint4 e = P[(B - 1) * 32 + t + 1]; shi = e.x; slo = e.y; six = e.z; }
+#pragma unroll
+        for (int i = B - 1; i >= 0; --i) {
+            if (Q == 1 && i == B - 1) { shi = hh[i]; slo = hl[i]; six = (u32)(B * t + i); }
+            else take_unless_greater(shi, slo, six, hh[i], hl[i], (u32)(B * t + i));
+            const uint4 e = P[i * 32 + t + Q];
+            const u64 sv = ((u64)shi << 32) | slo, ev = ((u64)e.x << 32) | e.y;
+            vix[i] = ev < sv ? e.z : six;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < B; i += 2) IDXF32[(B / 2) * t + (i >> 1)] = vix[i] | (vix[i + 1] << 16);
+
+    if (resolve_unit >= 0) {
+        const u64 excl = scan_resolve(a.tile_status, resolve_unit, resolve_agg, t);
+        if (t == 0) *resolve_out = excl;
+    }
+
+    // ---- validity, boundaries -----------------------------------------------------------------------------------------
+    constexpr u32 MB = (1u << B) - 1u;
+    u32 V = MB;
+    if (dirty | seqdirty) {
+        u32 inv = 0;
+        if (dirty) inv |= or_span_bits<B>(BAD, x0, c.k, 0);
+        if (seqdirty && c.k > 1) inv |= or_span_bits<B>(SEQ, x0, c.k - 1, 1);
+        V = ~inv & MB;
+    }
+    u32 dif = 0;
+#pragma unroll
+    for (int i = 0; i + 1 < B; ++i) dif |= (u32)(vix[i + 1] != vix[i]) << i;
+    {
+        const u32 nv0 = __shfl_down_sync(0xffffffffu, vix[0], 1);
+        dif |= (u32)(nv0 != vix[B - 1]) << (B - 1);
+    }
+    const u32 Vn = (V >> 1) | ((__shfl_down_sync(0xffffffffu, V, 1) & 1u) << (B - 1));
+    const u32 E = V & (~Vn | dif) & MB;        // the record ends with this window
+    const u32 X = (E | ~V) & MB;               // the next window cannot continue a record
+    {
+        const int bp = B * t, wq = bp >> 5, sh = bp & 31;
+        if (E) {
+            atomicOr(&EB[wq], E << sh);
+            if (sh + B > 32) atomicOr(&EB[wq + 1], E >> (32 - sh));
+        }
+    }
+    const u32 xprev = (__shfl_up_sync(0xffffffffu, X, 1) >> (B - 1)) & 1u;
+
+    // ---- record starts ---------------------------------------------------------------------------------------------------
+    u32 start = 0;
+    if (t >= 1 && t <= G::LANES_OUT) {
+        start = V & ((X << 1) | xprev) & MB;
+        // windows outside [win_lo, win_hi) belong to another call / rank
+        const long long gl = g0 + (long long)B * t;
+        long long nlo = a.win_lo - gl, nhi = a.win_hi - gl;
+        nlo = nlo < 0 ? 0 : (nlo > B ? B : nlo);
+        nhi = nhi < 0 ? 0 : (nhi > B ? B : nhi);
+        start &= (MB << nlo) & ((1u << nhi) - 1u);
+    }
+    const u32 cnt = __popc(start);
+    u32 incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (t >= d) incl += v;
+    }
+    u32 off = incl - cnt, sm = start;
+    while (sm) {
+        const int i = __ffs((int)sm) - 1;
+        sm &= sm - 1;
+        REC[off++] = (unsigned short)(B * t + i);
+    }
+    __syncwarp();
+    return __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// Record-parallel output of a finished tile from buffer set b: `n_rec` records, the first one at global index `base`.
+template <int B, int Q, int LW, bool CANON, bool MW>
+__device__ __forceinline__ void emit_tile3(const SkArgs& a, const unsigned char* wsm, const TileConst3& c, int b, long long tile, int t,
+                                           u32 n_rec, u64 base)
+{
+    using G = Geo<B, Q>;
+    const long long g0 = a.org + tile * (long long)G::R - B;
+    const int o = (int)(g0 - (g0 & ~15LL));
+    const unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
+    const u32* CW = reinterpret_cast<const u32*>(buf + G::BUF_CW);
+    const u32* EW = reinterpret_cast<const u32*>(buf + G::BUF_EW);
+    const unsigned short* IDXF = reinterpret_cast<const unsigned short*>(buf + G::BUF_IDXF);
+    const unsigned short* REC = reinterpret_cast<const unsigned short*>(buf + G::BUF_REC);
+    const u32* EB = reinterpret_cast<const u32*>(buf + G::BUF_EB);
+    for (u32 r = t; r < n_rec; r += NT) {
+        const int s0 = REC[r];
+        const int j = IDXF[s0];
+        // size: distance to the first record-end bit at or after s0, at most w
+        int size;
+        {
+            const int wq = s0 >> 5, sh = s0 & 31;
+            const u32 e0 = EB[wq], e1 = EB[wq + 1];
+            u32 bits = __funnelshift_r(e0, e1, sh);
+            if (bits) size = __ffs((int)bits);
+            else {
+                bits = __funnelshift_r(e1, EB[wq + 2], sh);
+                size = bits ? 32 + __ffs((int)bits) : c.w;
+            }
+            size = size < c.w ? size : c.w;
+        }
+        const int xj = o + j;
+        u64 val;
+        {
+            const int e = 2 * xj + 2 * c.m + 32 * PADF - 64;     // the 64 bits that end with the m-mer's last base
+            const int wj = e >> 5, fs = e & 31;
+            const u32 e0 = EW[wj], e1 = EW[wj + 1], e2 = EW[wj + 2];
+            u32 fhi = __funnelshift_l(e1, e0, fs), flo = __funnelshift_l(e2, e1, fs);
+            if (MW) fhi &= c.maskhi; else { fhi = 0; flo &= c.masklo; }
+            val = ((u64)fhi << 32) | flo;
+        }
+        if (CANON) {
+            const int wi = xj >> 4, sh = (xj & 15) * 2;
+            const u32 c0 = CW[wi], c1 = CW[wi + 1], c2 = CW[wi + 2];
+            u32 rlo = __funnelshift_r(c0, c1, sh), rhi = __funnelshift_r(c1, c2, sh);
+            if (MW) rhi &= c.maskhi; else { rhi = 0; rlo &= c.masklo; }
+            const u64 rc = ((u64)rhi << 32) | rlo;
+            val = rc < val ? rc : val;
+        }
+        const u64 g = base + r;
+        if (g < a.capacity) {
+            a.value[g] = val;
+            a.mm_start[g] = (u64)(g0 + j);
+            if (a.size != nullptr) { a.size[g] = (u8)size; a.mm_pos[g] = (u8)(j - s0); }
+            if (a.hash != nullptr) a.hash[g] = murmur3_key8(val, c.s8);
+        }
+    }
+    __syncwarp();   // this buffer set is restaged by the next compute_tile
+}
+
+}  // namespace
+
+template <int B, int Q, int LW, bool CANON, bool MW>
+__global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const SkArgs a)
+{
+    using G = Geo<B, Q>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
+    u32* CNT = reinterpret_cast<u32*>(smem_raw + (size_t)WARPS3 * G::WARP_BYTES);   // [2][WARPS] record counts
+    u64* UBASE = reinterpret_cast<u64*>(CNT + 2 * WARPS3);                          // [2] resolved prefix of a unit
+    u32* NEXT = reinterpret_cast<u32*>(UBASE + 2);                                  // [2] ticket of the following unit
+
+    TileConst3 c;
+    c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = a.s8;
+    c.maskhi = MW ? (c.m == 32 ? 0xFFFFFFFFu : ((1u << (2 * c.m - 32)) - 1u)) : 0u;
+    c.masklo = MW ? 0xFFFFFFFFu : (c.m == 16 ? 0xFFFFFFFFu : ((1u << (2 * c.m)) - 1u));
+
+    const long long num_units = (a.num_tiles + WARPS3 - 1) / WARPS3;
+    if (threadIdx.x == 0) NEXT[0] = atomicAdd(a.tile_counter, 1u);
+    __syncthreads();
+
+    long long unit = NEXT[0], prev_unit = -1;
+    bool have_pre = false;
+    uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
+    u32 prev_n = 0, prev_pre = 0;
+    u64 prev_agg = 0;
+    int b = 0;
+    for (int iter = 0;; ++iter) {
+        const bool have = unit < num_units;
+        if (!have && prev_unit < 0) break;
+        if (threadIdx.x == 0) NEXT[b ^ 1] = have ? atomicAdd(a.tile_counter, 1u) : 0xFFFFFFFFu;
+        const bool resolver = prev_unit >= 0 && warp == (iter % WARPS3);
+        const long long tile = unit * WARPS3 + warp;
+        u32 n_rec = 0;
+        if (have && tile < a.num_tiles)
+            n_rec = compute_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1, resolver ? prev_unit : -1, prev_agg,
+                                                       &UBASE[b ^ 1]);
+        else if (resolver) {
+            const u64 excl = scan_resolve(a.tile_status, prev_unit, prev_agg, t);
+            if (t == 0) UBASE[b ^ 1] = excl;
+        }
+        if (t == 0) CNT[b * WARPS3 + warp] = n_rec;
+        __syncthreads();
+        u32 pre = 0, agg = 0;
+#pragma unroll
+        for (int q = 0; q < WARPS3; ++q) {
+            const u32 v = CNT[b * WARPS3 + q];
+            if (q < warp) pre += v;
+            agg += v;
+        }
+        if (have && threadIdx.x == 0) scan_publish(a.tile_status, unit, agg);
+        if (prev_unit >= 0) {
+            const u64 ubase = UBASE[b ^ 1];
+            if (threadIdx.x == 0 && prev_unit == num_units - 1) *a.total = ubase + prev_agg;
+        }
+        const long long next_unit = NEXT[b ^ 1];
+        // the next tile's bases start their trip from HBM now and arrive while the previous tile's records are written
+        have_pre = false;
+        {
+            const long long nt = next_unit * WARPS3 + warp;
+            const long long ng0 = a.org + nt * (long long)G::R - B;
+            const long long P0 = (ng0 & ~15LL) - a.buf_lo;
+            if (next_unit < num_units && nt < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
+                have_pre = true;
+                if (t < G::NWORDS) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + t);
+                if (G::NWORDS > NT && t < G::NWORDS - NT) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT + t);
+            }
+        }
+        if (prev_unit >= 0)
+            emit_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b ^ 1, prev_unit * WARPS3 + warp, t, prev_n, UBASE[b ^ 1] + prev_pre);
+        prev_unit = have ? unit : -1;
+        prev_n = n_rec; prev_pre = pre; prev_agg = agg;
+        unit = next_unit;
+        b ^= 1;
+    }
+}
+
+// ---- host side: which (k, m) this generation covers, and the launch -------------------------------------------------
+namespace {
+
+struct Variant { int B, Q, LW, MW; };
+
+// k - m = Q * B; m-mer + block must fit the lane-local stream: 2 (m + B - 1) <= 32 LW; MW <=> m > 16
+bool pick_variant(int k, int m, Variant* v)
+{
+    const int d = k - m;
+    if (d == 12 && m >= 17 && m <= 21) { *v = {12, 1, 2, 1}; return true; }   // k=31 m=19 (configs 2, 3)
+    if (d == 10 && m <= 16) { *v = {10, 1, 2, 0}; return true; }              // k=21 m=11 (config 5)
+    if (d == 32 && m >= 17 && m <= 32) { *v = {16, 2, 3, 1}; return true; }   // k=63 m=31 (config 4)
+    return false;
+}
+
+template <int B, int Q, int LW, bool CANON, bool MW>
+cudaError_t setup3(size_t smem, int* occ)
+{
+    cudaError_t e = cudaFuncSetAttribute(sk3_kernel<B, Q, LW, CANON, MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, sk3_kernel<B, Q, LW, CANON, MW>, SK3_THREADS, smem);
+}
+
+template <int B, int Q, int LW, bool MW>
+cudaError_t setup3c(bool canon, size_t smem, int* occ)
+{
+    return canon ? setup3<B, Q, LW, true, MW>(smem, occ) : setup3<B, Q, LW, false, MW>(smem, occ);
+}
+
+template <int B, int Q, int LW, bool MW>
+void launch3c(bool canon, const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
+{
+    if (canon) sk3_kernel<B, Q, LW, true, MW><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    else sk3_kernel<B, Q, LW, false, MW><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+}
+
+template <int B, int Q>
+size_t smem3() { return (size_t)Geo<B, Q>::WARP_BYTES * WARPS3 + 2 * WARPS3 * 4 + 16 + 8 + 8; }
+
+}  // namespace
+
+bool sk3_supported(int k, int m)
+{
+    Variant v;
+    return pick_variant(k, m, &v);
+}
+
+cudaError_t sk3_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
+{
+    Variant v;
+    if (!pick_variant(args.k, args.m, &v)) return cudaErrorInvalidValue;
+    int R = 0;
+    size_t smem = 0;
+    int occ = 0;
+    cudaError_t e = cudaSuccess;
+    const bool canon = args.canonical != 0;
+    if (v.B == 12) { R = Geo<12, 1>::R; smem = smem3<12, 1>(); e = setup3c<12, 1, 2, true>(canon, smem, &occ); }
+    else if (v.B == 10) { R = Geo<10, 1>::R; smem = smem3<10, 1>(); e = setup3c<10, 1, 2, false>(canon, smem, &occ); }
+    else { R = Geo<16, 2>::R; smem = smem3<16, 2>(); e = setup3c<16, 2, 3, true>(canon, smem, &occ); }
+    if (e != cudaSuccess) return e;
+    args.R = R;
+    args.org = args.win_lo;
+    const long long nwin = args.win_hi > args.org ? args.win_hi - args.org : 0;
+    args.num_tiles = args.win_hi > args.win_lo ? (nwin + R - 1) / R : 0;
+    plan->threads = SK3_THREADS;
+    plan->smem_bytes = smem;
+    if (occ < 1) occ = 1;
+    long long grid = (long long)sm_count * occ;
+    const long long units = (args.num_tiles + WARPS3 - 1) / WARPS3;
+    if (grid > units) grid = units;
+    plan->grid = (int)(grid < 1 ? 1 : grid);
+    return cudaSuccess;
+}
+
+cudaError_t sk3_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
+{
+    Variant v;
+    if (!pick_variant(args.k, args.m, &v)) return cudaErrorInvalidValue;
+    const bool canon = args.canonical != 0;
+    if (v.B == 12) launch3c<12, 1, 2, true>(canon, args, plan, stream);
+    else if (v.B == 10) launch3c<10, 1, 2, false>(canon, args, plan, stream);
+    else launch3c<16, 2, 3, true>(canon, args, plan, stream);
+    return cudaGetLastError();
+}
+
+}  // namespace blg
