@@ -134,16 +134,21 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 {
     SkLaunchPlan plan;
     int gen = c->sk_gen;
-    if (gen == 0 || (gen == 3 && !sk3_supported(a.k, a.m))) gen = (sk3_supported(a.k, a.m) && a.k - a.m == 32) ? 3 : 2;   // TODO: sk3 is not yet faster for w = 11, 13
+    if (gen == 0 || (gen == 3 && !sk3_supported(a.k, a.m))) gen = sk3_supported(a.k, a.m) ? 3 : 2;
     if (gen == 1) CK(c, sk_plan(a, c->sm_count, &plan));
     else if (gen == 2) CK(c, sk2_plan(a, c->sm_count, &plan));
     else CK(c, sk3_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
-    int rc = prep_scratch(c, a.num_tiles);
+    int rc = prep_scratch(c, gen == 3 ? a.status_words : a.num_tiles);
     if (rc != BLG_OK) return rc;
     a.tile_counter = static_cast<unsigned int*>(c->small.p);
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
+    if (gen == 3) {
+        const long long groups = (a.num_tiles + 31) / 32;
+        a.grp_acc = a.tile_status + a.num_tiles;
+        a.grp_status = a.grp_acc + groups;
+    }
     CK(c, cudaEventRecord(c->ev0, c->stream));
     if (gen == 1) CK(c, sk_launch(a, plan, c->stream));
     else if (gen == 2) CK(c, sk2_launch(a, plan, c->stream));

@@ -20,9 +20,9 @@
 //   * tiles need not start on a 16-base boundary any more: lane 0 is the left margin (the previous window's argmin),
 //     lanes 1 .. 31-2Q own the record starts, the Q lanes after them are seen far enough to size those records.
 //
-// The outer structure is sk2's: a warp owns a tile end to end, four warps form one scan unit, and the ordered output
-// offset comes from the software-pipelined decoupled look-back (publish / resolve half a tile later / write out one
-// tile later from the second buffer set).
+// A warp owns a tile end to end and never meets another warp at a barrier: tiles come from a ticket counter, the
+// ordered output offset from a two-level chained scan (see tile_base below), and a tile's records are written one tile
+// later from the second buffer set, record-parallel with coalesced stores.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -106,8 +106,7 @@ struct TileConst3 {
 
 template <int B, int Q, int LW, bool CANON, bool MW>
 __device__ __forceinline__ u32 compute_tile3(const SkArgs& a, unsigned char* wsm, const TileConst3& c, int b, long long tile, int t,
-                                             bool have_pre, uint4 pre0, uint4 pre1,
-                                             long long resolve_unit, u64 resolve_agg, u64* resolve_out)
+                                             bool have_pre, uint4 pre0, uint4 pre1)
 {
     using G = Geo<B, Q>;
     const long long g0 = a.org + tile * (long long)G::R - B;   // global position of local start 0 (lane 0 = left margin)
@@ -255,11 +254,6 @@ __device__ __forceinline__ u32 compute_tile3(const SkArgs& a, unsigned char* wsm
 #pragma unroll
     for (int i = 0; i < B; i += 2) IDXF32[(B / 2) * t + (i >> 1)] = vix[i] | (vix[i + 1] << 16);
 
-    if (resolve_unit >= 0) {
-        const u64 excl = scan_resolve(a.tile_status, resolve_unit, resolve_agg, t);
-        if (t == 0) *resolve_out = excl;
-    }
-
     // ---- validity, boundaries -----------------------------------------------------------------------------------------
     constexpr u32 MB = (1u << B) - 1u;
     u32 V = MB;
@@ -375,6 +369,47 @@ __device__ __forceinline__ void emit_tile3(const SkArgs& a, const unsigned char*
     __syncwarp();   // this buffer set is restaged by the next compute_tile
 }
 
+// ---- ordered output offset without any CTA barrier: a two-level chained scan ------------------------------------------
+// Tiles are handed out by ticket, one per warp. Level 1: a tile publishes its record count (one store) and adds it to
+// the accumulator of its GROUP of 32 consecutive tiles (one 64-bit atomicAdd that also counts arrivals). Level 2: the
+// warp whose add completes a group publishes the group total and resolves the group's prefix with a decoupled look-back
+// over GROUPS (32x fewer words than tiles, so one round of 32 loads reaches an inclusive word). A tile's base is then
+// exclusive(group) + the counts of the earlier tiles of its group: one load per lane, issued one tile after everything
+// it reads was written. Nothing here waits on a warp holding a HIGHER ticket, so the spins cannot deadlock.
+constexpr int GS = 32;
+constexpr u64 TS_SET = 1ULL << 62;
+constexpr u64 ACC_ONE = 1ULL << 40, ACC_MASK = ACC_ONE - 1;
+
+__device__ __forceinline__ void spin_guard(u32& spins)
+{
+    __nanosleep(64);
+    if (++spins > (1u << 22)) __trap();   // ~0.3 s: a protocol bug must not hang the GPU
+}
+
+// Exclusive record offset of `tile` (published one tile ago), in two steps so that the loads are in flight while the
+// warp does its group duty: lanes below the tile's index in its group read the earlier tiles' counts, lane 31 the
+// inclusive prefix of the previous group.
+__device__ __forceinline__ const u64* tile_base_addr(const SkArgs& a, long long tile, int t)
+{
+    const long long g = tile / GS;
+    const int idx = (int)(tile - g * GS);
+    if (t < idx) return a.tile_status + g * GS + t;
+    if (t == 31 && g > 0) return a.grp_status + (g - 1);
+    return nullptr;
+}
+__device__ __forceinline__ u64 tile_base_finish(const u64* p, u64 v, int t)
+{
+    if (p != nullptr) {
+        u32 spins = 0;
+        if (t == 31) { while ((v >> 62) != 2) { spin_guard(spins); v = ld_status(p); } }
+        else { while (!(v & TS_SET)) { spin_guard(spins); v = ld_status(p); } }
+        v &= ST_VAL;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
 }  // namespace
 
 template <int B, int Q, int LW, bool CANON, bool MW>
@@ -384,71 +419,69 @@ __global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
-    u32* CNT = reinterpret_cast<u32*>(smem_raw + (size_t)WARPS3 * G::WARP_BYTES);   // [2][WARPS] record counts
-    u64* UBASE = reinterpret_cast<u64*>(CNT + 2 * WARPS3);                          // [2] resolved prefix of a unit
-    u32* NEXT = reinterpret_cast<u32*>(UBASE + 2);                                  // [2] ticket of the following unit
 
     TileConst3 c;
     c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = a.s8;
     c.maskhi = MW ? (c.m == 32 ? 0xFFFFFFFFu : ((1u << (2 * c.m - 32)) - 1u)) : 0u;
     c.masklo = MW ? 0xFFFFFFFFu : (c.m == 16 ? 0xFFFFFFFFu : ((1u << (2 * c.m)) - 1u));
 
-    const long long num_units = (a.num_tiles + WARPS3 - 1) / WARPS3;
-    if (threadIdx.x == 0) NEXT[0] = atomicAdd(a.tile_counter, 1u);
-    __syncthreads();
-
-    long long unit = NEXT[0], prev_unit = -1;
+    const long long num_groups = (a.num_tiles + GS - 1) / GS;
+    u32 tk = 0;
+    if (t == 0) tk = atomicAdd(a.tile_counter, 1u);
+    long long tile = __shfl_sync(0xffffffffu, tk, 0), prev = -1;
     bool have_pre = false;
     uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
-    u32 prev_n = 0, prev_pre = 0;
-    u64 prev_agg = 0;
+    u32 prev_n = 0;
     int b = 0;
-    for (int iter = 0;; ++iter) {
-        const bool have = unit < num_units;
-        if (!have && prev_unit < 0) break;
-        if (threadIdx.x == 0) NEXT[b ^ 1] = have ? atomicAdd(a.tile_counter, 1u) : 0xFFFFFFFFu;
-        const bool resolver = prev_unit >= 0 && warp == (iter % WARPS3);
-        const long long tile = unit * WARPS3 + warp;
+    // Every warp runs on its own: compute tile i, publish its count, write out tile i-1 from the other buffer set.
+    // A ticket is taken only when nothing can block any more before that tile is published (a warp that waits for a
+    // prefix while it holds an uncomputed tile stalls that tile's group, the groups behind it, and so itself: convoys).
+    for (;;) {
+        const bool have = tile < a.num_tiles;
+        if (!have && prev < 0) break;
         u32 n_rec = 0;
-        if (have && tile < a.num_tiles)
-            n_rec = compute_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1, resolver ? prev_unit : -1, prev_agg,
-                                                       &UBASE[b ^ 1]);
-        else if (resolver) {
-            const u64 excl = scan_resolve(a.tile_status, prev_unit, prev_agg, t);
-            if (t == 0) UBASE[b ^ 1] = excl;
+        u64 old = 0;
+        if (have) {
+            n_rec = compute_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1);
+            if (t == 0) {
+                st_status(&a.tile_status[tile], TS_SET | n_rec);
+                old = atomicAdd(&a.grp_acc[tile / GS], ACC_ONE | (u64)n_rec);
+            }
         }
-        if (t == 0) CNT[b * WARPS3 + warp] = n_rec;
-        __syncthreads();
-        u32 pre = 0, agg = 0;
-#pragma unroll
-        for (int q = 0; q < WARPS3; ++q) {
-            const u32 v = CNT[b * WARPS3 + q];
-            if (q < warp) pre += v;
-            agg += v;
+        const u64* bp = prev >= 0 ? tile_base_addr(a, prev, t) : nullptr;
+        u64 bv = 0;
+        if (bp != nullptr) bv = ld_status(bp);
+        if (have) {
+            // did this tile complete its group? then this warp resolves the group
+            const long long g = tile / GS;
+            const long long rest = a.num_tiles - g * GS;
+            const u64 expect = (u64)(rest < GS ? rest : GS);
+            const u64 o0 = __shfl_sync(0xffffffffu, old, 0);
+            if ((o0 >> 40) == expect - 1) {
+                const u64 gsum = (o0 & ACC_MASK) + n_rec;
+                const u64 excl = lookback_exclusive(a.grp_status, g, gsum, t);
+                if (t == 0 && g == num_groups - 1) *a.total = excl + gsum;
+            }
         }
-        if (have && threadIdx.x == 0) scan_publish(a.tile_status, unit, agg);
-        if (prev_unit >= 0) {
-            const u64 ubase = UBASE[b ^ 1];
-            if (threadIdx.x == 0 && prev_unit == num_units - 1) *a.total = ubase + prev_agg;
-        }
-        const long long next_unit = NEXT[b ^ 1];
-        // the next tile's bases start their trip from HBM now and arrive while the previous tile's records are written
+        u64 base = 0;
+        if (prev >= 0) base = tile_base_finish(bp, bv, t);
+        u32 nx = 0xFFFFFFFFu;
+        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u);
+        if (prev >= 0) emit_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b ^ 1, prev, t, prev_n, base);
+        const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
-            const long long nt = next_unit * WARPS3 + warp;
-            const long long ng0 = a.org + nt * (long long)G::R - B;
+            const long long ng0 = a.org + next_tile * (long long)G::R - B;
             const long long P0 = (ng0 & ~15LL) - a.buf_lo;
-            if (next_unit < num_units && nt < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
+            if (next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
                 have_pre = true;
                 if (t < G::NWORDS) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + t);
                 if (G::NWORDS > NT && t < G::NWORDS - NT) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT + t);
             }
         }
-        if (prev_unit >= 0)
-            emit_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b ^ 1, prev_unit * WARPS3 + warp, t, prev_n, UBASE[b ^ 1] + prev_pre);
-        prev_unit = have ? unit : -1;
-        prev_n = n_rec; prev_pre = pre; prev_agg = agg;
-        unit = next_unit;
+        prev = have ? tile : -1;
+        prev_n = n_rec;
+        tile = next_tile;
         b ^= 1;
     }
 }
@@ -490,7 +523,7 @@ void launch3c(bool canon, const SkArgs& args, const SkLaunchPlan& plan, cudaStre
 }
 
 template <int B, int Q>
-size_t smem3() { return (size_t)Geo<B, Q>::WARP_BYTES * WARPS3 + 2 * WARPS3 * 4 + 16 + 8 + 8; }
+size_t smem3() { return (size_t)Geo<B, Q>::WARP_BYTES * WARPS3; }
 
 }  // namespace
 
@@ -517,6 +550,7 @@ cudaError_t sk3_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
     args.org = args.win_lo;
     const long long nwin = args.win_hi > args.org ? args.win_hi - args.org : 0;
     args.num_tiles = args.win_hi > args.win_lo ? (nwin + R - 1) / R : 0;
+    args.status_words = args.num_tiles + 2 * ((args.num_tiles + 31) / 32) + 8;
     plan->threads = SK3_THREADS;
     plan->smem_bytes = smem;
     if (occ < 1) occ = 1;
