@@ -19,12 +19,25 @@ typedef unsigned char u8;
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ u64 rotl64(u64 x, int r) { return (x << r) | (x >> (64 - r)); }
 
+// h ^= h >> 33 only touches the low word: lo ^= hi >> 1. With BLG_HASH_FMA_SHIFTS the shift is issued as IMAD.HI
+// (hi * 2^31 >> 32) on the fma pipe instead of SHF on the ALU pipe (the busiest unit of the fused kernels); measured
+// 2 % slower while the kernel is latency-bound (IMAD.HI holds the fma-heavy pipe twice as long), so it is opt-in.
+__device__ __forceinline__ u64 xorshift33(u64 h)
+{
+#ifdef BLG_HASH_FMA_SHIFTS
+    u32 hi = (u32)(h >> 32), lo = (u32)h, s;
+    asm("mul.hi.u32 %0, %1, 0x80000000;" : "=r"(s) : "r"(hi));
+    return ((u64)hi << 32) | (lo ^ s);
+#else
+    return h ^ (h >> 33);
+#endif
+}
+
 __device__ __forceinline__ u64 fmix64(u64 h)
 {
-    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL;
-    h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL;
-    h ^= h >> 33;
-    return h;
+    h = xorshift33(h); h *= 0xff51afd7ed558ccdULL;
+    h = xorshift33(h); h *= 0xc4ceb9fe1a85ec53ULL;
+    return xorshift33(h);
 }
 
 __device__ __forceinline__ u64 murmur3_key8(u64 key, u64 s8)
