@@ -38,6 +38,17 @@ REC_BYTES = 18               # value u64 + mm_start u64 + size u8 + mm_pos u8
 METRIC = "Gbases/s super-k-mer extraction (k=31,m=19)"
 
 
+def load_traffic():
+    """DRAM bytes per launch of the dominant kernel from the last committed `ncu --set full` capture of this very
+    workload (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); None when there is none."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            d = json.load(f)
+        return d["kernel"], float(d["dram_bytes_per_launch"])
+    except Exception:
+        return "sk3_kernel", None
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -269,6 +280,7 @@ def run_gpu(args):
 
     if rank == 0:
         peak, peak_kind = load_peaks()
+        kname, traffic = load_traffic()
         algo_bytes = nwin + REC_BYTES * count          # this rank's launch
         achieved = algo_bytes / (kernel_ms * 1e-3) / 1e9
         line = {
@@ -283,7 +295,7 @@ def run_gpu(args):
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": e2e_ms},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "sk_kernel", "kernel_ms": kernel_ms,
+                         "traffic": traffic, "peak_kind": peak_kind, "kernel": kname, "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_base": algo_bytes / nwin},
             "clocks": sampler.summary(),
         }
