@@ -20,6 +20,8 @@ struct DevBuf {
     size_t cap = 0;
 };
 
+constexpr int PIPE_MAX = 16;
+
 struct Owner {
     int device_mem;  // 1: cudaFree, 0: cudaFreeHost
     void* ptrs[6];
@@ -35,6 +37,9 @@ struct blg_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr;   // upload / download streams of the pipelined host path
+    cudaEvent_t ev_in[16] = {};
+    int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
     unsigned long long* h_total = nullptr;  // pinned
@@ -231,6 +236,115 @@ void free_owner(Owner* ow)
     delete ow;
 }
 
+// Host in, host out, large input: the same work as the plain path below, cut into chunks of k-mer starts so that the
+// upload of chunk i+1, the kernel of chunk i and the download of chunk i-1's records overlap (PCIe is full duplex and
+// the record download is the longest leg). Chunks own disjoint window ranges of ONE device copy of the bases
+// (blg_super_kmers_range semantics), so the concatenated output is the single-launch output.
+// Returns BLG_OK with *done_flag = 1 when it produced the result, 0 when the caller should take the plain path
+// (small input, id output, or the record estimate was too small).
+int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t lo, uint64_t hi,
+                 const blg_params* p, blg_sk_out* out, bool with_size, bool want_hash, int* done_flag)
+{
+    *done_flag = 0;
+    const uint64_t nwin = hi - lo;
+    const int k = p->k, m = p->m, w = k - m + 1;
+    if (nwin < (8u << 20) || c->no_pipeline) return BLG_OK;
+    int rc;
+    if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
+    const uint64_t cap = out->capacity > 0 ? out->capacity : estimate_records(nwin, w);
+    if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+    if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * 8)) != BLG_OK) return rc;
+    if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
+    if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
+    const unsigned long long* d_offs = nullptr;
+    if (offs) {
+        const size_t ob = (n_seq + 1) * sizeof(uint64_t);
+        if ((rc = ensure(c, c->offs, ob)) != BLG_OK) return rc;
+        CK(c, cudaMemcpyAsync(c->offs.p, offs, ob, cudaMemcpyHostToDevice, c->stream));
+        c->stats.bytes_h2d += ob;
+        d_offs = static_cast<const unsigned long long*>(c->offs.p);
+    }
+    // library-allocated host arrays are sized by the estimate; an overflow falls back to the plain path
+    Owner* ow = nullptr;
+    blg_sk_out h = *out;
+    if (out->capacity == 0) {
+        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        if (!ow) return BLG_E_NOMEM;
+        h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
+        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
+        if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
+    }
+    int nch = (int)(nwin / (6u << 20));
+    nch = nch < 2 ? 2 : (nch > PIPE_MAX ? PIPE_MAX : nch);
+    const size_t halo = (size_t)(k + w - 2) + 64;
+    unsigned char* d_in = static_cast<unsigned char*>(c->in.p);
+    uint64_t cut[PIPE_MAX + 1];
+    size_t up[PIPE_MAX + 1];       // bases uploaded once piece i is in
+    for (int i = 0; i <= nch; ++i) cut[i] = i == nch ? hi : (lo + nwin * (uint64_t)i / nch) / 16 * 16;
+    cut[0] = lo;
+    size_t sent = 0;
+    for (int i = 0; i < nch; ++i) {
+        size_t end = i == nch - 1 ? n : (size_t)cut[i + 1] + halo;
+        end = (end > n ? n : end);
+        if (i < nch - 1) end = end / 16 * 16;
+        if (end > sent) CK(c, cudaMemcpyAsync(d_in + sent, bases + sent, end - sent, cudaMemcpyHostToDevice, c->s_in));
+        CK(c, cudaEventRecord(c->ev_in[i], c->s_in));
+        sent = end > sent ? end : sent;
+        up[i] = sent;
+    }
+    c->stats.bytes_h2d += n;
+    uint64_t done = 0;
+    bool overflow = false;
+    for (int i = 0; i < nch && !overflow; ++i) {
+        if (cut[i + 1] <= cut[i]) continue;
+        CK(c, cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
+        SkArgs a{};
+        a.bases = d_in; a.buf_lo = 0; a.buf_hi = (long long)up[i];
+        a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
+        a.win_lo = (long long)cut[i]; a.win_hi = (long long)cut[i + 1];
+        a.k = k; a.m = m; a.w = w;
+        a.canonical = p->canonical ? 1 : 0;
+        a.s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL;
+        a.vec_ok = (reinterpret_cast<uintptr_t>(d_in) & 15u) == 0;
+        a.value = static_cast<unsigned long long*>(c->o_value.p) + done;
+        a.mm_start = static_cast<unsigned long long*>(c->o_mm.p) + done;
+        a.size = with_size ? static_cast<unsigned char*>(c->o_size.p) + done : nullptr;
+        a.mm_pos = with_size ? static_cast<unsigned char*>(c->o_pos.p) + done : nullptr;
+        a.hash = want_hash ? static_cast<unsigned long long*>(c->o_hash.p) + done : nullptr;
+        a.capacity = cap - done;
+        uint64_t cnt = 0;
+        if ((rc = run_sk_once(c, a, &cnt)) != BLG_OK) { free_owner(ow); return rc; }   // returns after the kernel: count is known
+        if (cnt > cap - done) { overflow = true; done += cnt; break; }
+        if (cnt) {
+            CK(c, cudaMemcpyAsync(h.value + done, a.value, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+            CK(c, cudaMemcpyAsync(h.mm_start + done, a.mm_start, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+            c->stats.bytes_d2h += cnt * 16;
+            if (with_size) {
+                CK(c, cudaMemcpyAsync(h.size + done, a.size, cnt, cudaMemcpyDeviceToHost, c->s_out));
+                CK(c, cudaMemcpyAsync(h.mm_pos + done, a.mm_pos, cnt, cudaMemcpyDeviceToHost, c->s_out));
+                c->stats.bytes_d2h += cnt * 2;
+            }
+            if (want_hash) {
+                CK(c, cudaMemcpyAsync(h.hash + done, a.hash, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+                c->stats.bytes_d2h += cnt * 8;
+            }
+        }
+        done += cnt;
+    }
+    CK(c, cudaStreamSynchronize(c->s_out));
+    CK(c, cudaStreamSynchronize(c->s_in));
+    if (overflow) {
+        free_owner(ow);
+        return BLG_OK;             // plain path: exact count, retry / BLG_E_CAPACITY
+    }
+    if (out->capacity == 0) { *out = h; out->owner = ow; out->capacity = 0; }
+    out->count = done;
+    c->stats.n_records = done;
+    *done_flag = 1;
+    return BLG_OK;
+}
+
 int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t win_begin,
               uint64_t win_end, const blg_params* p, blg_sk_out* out, bool with_size)
 {
@@ -259,6 +373,12 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         if (out->capacity == 0) { out->value = out->mm_start = out->hash = out->id = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
         c->stats.total_ms = tm.ms();
         return BLG_OK;
+    }
+
+    if (!(p->flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT)) && !want_id) {
+        int produced = 0;
+        if ((rc = sk_pipelined(c, bases, n, offs, n_seq, lo, hi, p, out, with_size, want_hash, &produced)) != BLG_OK) return rc;
+        if (produced) { c->stats.total_ms = tm.ms(); return BLG_OK; }
     }
 
     const unsigned char* d_bases = nullptr;
@@ -418,6 +538,11 @@ int blg_create(int device, blg_ctx** out)
         return BLG_E_CUDA;
     }
     c->stream = c->own_stream;
+    bool ok = cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
+    { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 0; }
     *out = c;
     return BLG_OK;
@@ -435,6 +560,9 @@ int blg_destroy(blg_ctx* c)
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    for (cudaEvent_t e : c->ev_in) if (e) cudaEventDestroy(e);
+    if (c->s_in) cudaStreamDestroy(c->s_in);
+    if (c->s_out) cudaStreamDestroy(c->s_out);
     delete c;
     return BLG_OK;
 }

@@ -144,6 +144,35 @@ def test_sequence_plan_slices_concatenate(gpu, oracle):
         assert np.array_equal(np.concatenate([p[key] for p in parts]), o[key]), key
 
 
+@pytest.mark.parametrize("k,m,multi", [(31, 19, False), (21, 11, True)])
+def test_pipelined_host_path_large_input(gpu, oracle, k, m, multi):
+    """Inputs above 8 M k-mers take the chunked upload / kernel / download pipeline: same records as the oracle."""
+    from biolib_b200 import synth
+    n = 20_000_000
+    s = synth.generate(77, n).copy()
+    rng = np.random.default_rng(3)
+    for p_ in rng.integers(0, n - 100, 200):
+        s[p_:p_ + int(rng.integers(1, 40))] = ord("N")
+    offs = None
+    if multi:
+        cuts = np.sort(rng.choice(np.arange(1, n), size=3000, replace=False))
+        offs = np.concatenate([[0], cuts, [n]]).astype(np.uint64)
+    g = gpu.super_kmers(s, k, m, 42, True, offsets=offs)
+    assert gpu.stats()["kernel_launches"] >= 2          # it really was cut into chunks
+    o = oracle.super_kmers(s, k, m, 42, True, offsets=offs)
+    assert g["n"] == o["n"]
+    for key in ("value", "hash", "mm_start", "sk_start", "size"):
+        assert np.array_equal(g[key], o[key]), key
+    # caller-provided arrays that are too small: the required count comes back with BLG_E_CAPACITY
+    import biolib_b200
+    buf = np.zeros(1000, np.uint64)
+    buf8 = np.zeros(1000, np.uint8)
+    with pytest.raises(biolib_b200.BlgError) as e:
+        gpu.super_kmers_raw(s.ctypes.data, n, k, m, 42, True, buf.ctypes.data, buf.ctypes.data, buf8.ctypes.data, buf8.ctypes.data, 1000,
+                            offsets_ptr=offs.ctypes.data if offs is not None else 0, n_seq=0 if offs is None else len(offs) - 1)
+    assert e.value.status == 3
+
+
 def test_hash64(gpu, oracle):
     vals = np.array([0, 1, 0x1234567890ABCDEF, 0xFFFFFFFFFFFFFFFF], dtype=np.uint64)
     assert gpu.hash64(vals, 0).tolist() == [0x28DF63B7CC57C3CB, 0x004403B7FB05C44A, 0x495AE5FABBE9F68B, 0xA0E4B27A1ABAED73]
