@@ -54,7 +54,14 @@ struct Geo {
     static constexpr int BUF_REC = BUF_IDXF + S * 2;               // u16 [R + 8]  record starts (local window index)
     static constexpr int BUF_EB = (BUF_REC + (R + 8) * 2 + 15) / 16 * 16;                // u32 [S/32 + 4]  record-end bits
     static constexpr int BUF_BYTES = (BUF_EB + (S / 32 + 4) * 4 + 15) / 16 * 16;
-    static constexpr int WARP_BYTES = (OFF_BUF + 2 * BUF_BYTES + 127) / 128 * 128;
+    // buffer sets: a tile's records are written out KB-1 tiles after it was computed, which is the slack the chained scan
+    // has to deliver the tile's offset without anybody waiting (three sets where shared memory allows 16 warps per SM)
+#ifdef SK3_KB
+    static constexpr int KB = SK3_KB;
+#else
+    static constexpr int KB = B <= 12 ? 3 : 2;
+#endif
+    static constexpr int WARP_BYTES = (OFF_BUF + KB * BUF_BYTES + 127) / 128 * 128;
 };
 
 __device__ __forceinline__ u32 pairrev32(u32 x)
@@ -428,16 +435,24 @@ __global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const 
     const long long num_groups = (a.num_tiles + GS - 1) / GS;
     u32 tk = 0;
     if (t == 0) tk = atomicAdd(a.tile_counter, 1u);
-    long long tile = __shfl_sync(0xffffffffu, tk, 0), prev = -1;
+    long long tile = __shfl_sync(0xffffffffu, tk, 0);
+    // computed, not yet written out: (t0, n0, b0) the newer, (t1, n1, b1) the older (KB == 3 only): tile, records, buffer set
+    long long t0 = -1, t1 = -1;
+    u32 n0 = 0, n1 = 0;
+    int b0 = 0, b1 = 0;
     bool have_pre = false;
     uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
-    u32 prev_n = 0;
-    int b = 0;
-    // Every warp runs on its own: compute tile i, publish its count, write out tile i-1 from the other buffer set.
+    int b = 0;                          // buffer set of the tile computed in this iteration
+    // Every warp runs on its own: compute tile i, publish its count, write out tile i-(KB-1) from its buffer set.
     // A ticket is taken only when nothing can block any more before that tile is published (a warp that waits for a
     // prefix while it holds an uncomputed tile stalls that tile's group, the groups behind it, and so itself: convoys).
     for (;;) {
         const bool have = tile < a.num_tiles;
+        // the tile to write out now: the older pending one once two are queued, or whatever is left when draining
+        const bool from1 = G::KB == 3 && t1 >= 0;
+        const long long prev = G::KB == 3 ? (from1 ? t1 : (have ? -1 : t0)) : t0;
+        const u32 prev_n = from1 ? n1 : n0;
+        const int pb = from1 ? b1 : b0;
         if (!have && prev < 0) break;
         u32 n_rec = 0;
         u64 old = 0;
@@ -452,7 +467,7 @@ __global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const 
         u64 bv = 0;
         if (bp != nullptr) bv = ld_status(bp);
         if (have) {
-            // did this tile complete its group? then this warp resolves the group
+            // did this tile complete its group (the add counts arrivals)? then this warp resolves the group
             const long long g = tile / GS;
             const long long rest = a.num_tiles - g * GS;
             const u64 expect = (u64)(rest < GS ? rest : GS);
@@ -467,7 +482,7 @@ __global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const 
         if (prev >= 0) base = tile_base_finish(bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u);
-        if (prev >= 0) emit_tile3<B, Q, LW, CANON, MW>(a, wsm, c, b ^ 1, prev, t, prev_n, base);
+        if (prev >= 0) emit_tile3<B, Q, LW, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
@@ -479,10 +494,13 @@ __global__ void __launch_bounds__(SK3_THREADS, SK3_MIN_BLOCKS) sk3_kernel(const 
                 if (G::NWORDS > NT && t < G::NWORDS - NT) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT + t);
             }
         }
-        prev = have ? tile : -1;
-        prev_n = n_rec;
+        // queue: drop what was written, push what was computed
+        if (G::KB == 3) {
+            if (have || from1) { t1 = t0; n1 = n0; b1 = b0; }
+            t0 = have ? tile : -1; n0 = n_rec; b0 = b;
+        } else { t0 = have ? tile : -1; n0 = n_rec; b0 = b; }
         tile = next_tile;
-        b ^= 1;
+        b = (b + 1) % G::KB;
     }
 }
 
