@@ -39,6 +39,7 @@ struct blg_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;   // upload / download streams of the pipelined host path
     cudaEvent_t ev_in[16] = {};
+    int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi (BLG_PIPE_CHUNK_M overrides; development only)
     int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
@@ -275,7 +276,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
     }
-    int nch = (int)(nwin / (6u << 20));
+    int nch = (int)(nwin / ((uint64_t)c->pipe_chunk_m << 20));
     nch = nch < 2 ? 2 : (nch > PIPE_MAX ? PIPE_MAX : nch);
     const size_t halo = (size_t)(k + w - 2) + 64;
     unsigned char* d_in = static_cast<unsigned char*>(c->in.p);
@@ -542,6 +543,7 @@ int blg_create(int device, blg_ctx** out)
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
+    { const char* e = getenv("BLG_PIPE_CHUNK_M"); if (e && atoi(e) > 0) c->pipe_chunk_m = atoi(e); }
     { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 0; }
     *out = c;
