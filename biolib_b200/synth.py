@@ -68,3 +68,15 @@ def inject_n_runs(reads: np.ndarray, read_len: int, seed: int = 44, p_read: floa
     low = np.nonzero(rng.random(n_reads) < lower_frac)[0]
     view[low] |= 0x20
     return reads
+
+
+def generate_sharded_parallel(seed0: int, length: int, shard: int = 1 << 26, threads: int | None = None) -> np.ndarray:
+    """generate_sharded with the shards drawn concurrently (numpy's generator releases the GIL): a 3 Gbp genome in
+    seconds instead of a minute. Same bytes as generate_sharded(seed0, length, shard)."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    out = np.empty(length, dtype=np.uint8)
+    jobs = [(i, lo, min(shard, length - lo)) for i, lo in enumerate(range(0, length, shard))]
+    with ThreadPoolExecutor(threads or min(32, os.cpu_count() or 1)) as ex:
+        list(ex.map(lambda j: generate(seed0 + j[0], j[2], out=out[j[1]:j[1] + j[2]]), jobs))
+    return out
