@@ -124,6 +124,13 @@ class Context:
         self._check(self.L.blg_hash64(self.h, v.ctypes.data, v.size, seed & (2**64 - 1), 0, out.ctypes.data))
         return out
 
+    def minimizer_positions(self, kmer_values, k: int, m: int) -> np.ndarray:
+        """hash::minimizer_position_extractor for an array of k-mer values (k <= 32)."""
+        v = np.ascontiguousarray(kmer_values, dtype=np.uint64)
+        out = np.empty(v.size, dtype=np.uint8)
+        self._check(self.L.blg_minimizer_positions(self.h, v.ctypes.data, v.size, k, m, 0, out.ctypes.data))
+        return out
+
     # ------------------------------------------------------------------ device resident (raw pointers)
     def super_kmers_device(self, d_bases: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, d_value: int,
                            d_mm_start: int, d_size: int, d_mm_pos: int, capacity: int, d_offsets: int = 0, n_seq: int = 0,

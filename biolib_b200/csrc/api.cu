@@ -743,6 +743,28 @@ int blg_hash64(blg_ctx* c, const uint64_t* values, size_t n, uint64_t seed, uint
     return BLG_OK;
 }
 
+int blg_minimizer_positions(blg_ctx* c, const uint64_t* values, size_t n, uint8_t k, uint8_t m, uint32_t flags, uint8_t* out)
+{
+    if (!c || (n && (!values || !out))) return BLG_E_INVALID;
+    c->err.clear();
+    if (k == 0 || k > 32 || m == 0 || m > k) { c->err = "need 1 <= m <= k <= 32 (k-mer values held in uint64_t)"; return BLG_E_INVALID; }
+    CK(c, cudaSetDevice(c->device));
+    if (flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT)) {
+        CK(c, minpos_launch(reinterpret_cast<const unsigned long long*>(values), n, k, m, out, c->sm_count, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        return BLG_OK;
+    }
+    int rc;
+    if ((rc = ensure(c, c->o_value, n * 8)) != BLG_OK || (rc = ensure(c, c->o_size, n)) != BLG_OK) return rc;
+    if (n) {
+        CK(c, cudaMemcpyAsync(c->o_value.p, values, n * 8, cudaMemcpyHostToDevice, c->stream));
+        CK(c, minpos_launch(static_cast<unsigned long long*>(c->o_value.p), n, k, m, static_cast<unsigned char*>(c->o_size.p), c->sm_count, c->stream));
+        CK(c, cudaMemcpyAsync(out, c->o_size.p, n, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    return BLG_OK;
+}
+
 void blg_free_kmer_out(blg_ctx* c, blg_kmer_out* out)
 {
     if (!out) return;

@@ -102,6 +102,9 @@ cudaError_t record_ids_launch(const unsigned char* bases, long long n_bases, con
                               int m, const unsigned long long* mm_start, unsigned long long n_records, void* scratch,
                               unsigned long long* id, cudaStream_t stream, int* launches);
 
+// hash::minimizer_position_extractor for k-mer values held in uint64_t (k <= 32)
+cudaError_t minpos_launch(const unsigned long long* values, size_t n, int k, int m, unsigned char* out, int sm_count, cudaStream_t stream);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

@@ -230,4 +230,37 @@ cudaError_t record_ids_launch(const unsigned char* bases, long long n_bases, con
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// hash::minimizer_position_extractor, batched (reference include/kmer_view.hpp:266-283, ctor src/kmer_view.cpp:7-15):
+// one thread per k-mer value (k <= 32). The k-m+1 m-mers are visited from the right (km >>= 2), hashed with seed 0,
+// and a later (further left) m-mer replaces the minimum on '>=' -- smallest hash, leftmost on ties. out = k - m - minpos.
+// Algorithmic bytes: 8 in + 1 out per k-mer; w hashes per k-mer make it ALU-bound like the fused kernels.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) minpos_kernel(const u64* __restrict__ values, size_t n, int k, int m, unsigned char* __restrict__ out)
+{
+    const u64 mask = (2 * m != 64) ? ((1ULL << (2 * m)) - 1ULL) : ~0ULL;
+    const int w = k - m + 1;
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (size_t)gridDim.x * blockDim.x) {
+        u64 km = values[q];
+        u64 mval = ~0ULL;
+        int minpos = 0;
+        for (int i = 0; i < w; ++i) {
+            const u64 val = murmur3_key8(km & mask, 8ULL);     // seed 0: s8 = 0 ^ 8
+            if (mval >= val) { mval = val; minpos = i; }
+            km >>= 2;
+        }
+        out[q] = (unsigned char)(k - m - minpos);
+    }
+}
+
+cudaError_t minpos_launch(const unsigned long long* values, size_t n, int k, int m, unsigned char* out, int sm_count, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    size_t blocks = (n + 255) / 256;
+    const size_t cap = (size_t)sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    minpos_kernel<<<(unsigned)blocks, 256, 0, stream>>>(values, n, k, m, out);
+    return cudaGetLastError();
+}
+
 }  // namespace blg

@@ -13,6 +13,7 @@
  *   blg_super_kmers  <- wrapper::super_kmer_view<K,M,Hash>(contig, len, k, m, canonical)
  *                       include/super_kmer_view.hpp:48-49, iteration :104-135
  *   blg_hash64       <- hash::hash64::hash<uint64_t>(val, seed)          include/hash.hpp:55-59
+ *   blg_minimizer_positions <- hash::minimizer_position_extractor::operator()   include/kmer_view.hpp:266-283
  *
  * The C++ shim that keeps the reference's constructor surface over these calls is
  * include/biolib_gpu.hpp. Plain pointers and sizes only; no exceptions cross this boundary;
@@ -151,6 +152,16 @@ int blg_super_kmers_range(blg_ctx* ctx, const char* bases, size_t n_bases, const
 /* batched hash::hash64::hash<uint64_t> (host pointers unless BLG_F_DEVICE_INPUT|OUTPUT semantics
  * are requested through `flags`: both arrays then are device pointers) */
 int blg_hash64(blg_ctx* ctx, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out);
+
+/*
+ * batched hash::minimizer_position_extractor::operator() (include/kmer_view.hpp:266-283; the PropertyExtractor that
+ * sampler::syncmer_sampler is built on): for every k-mer value (2-bit packed, k <= 32, as blg_kmers returns them)
+ * the 0-based offset, from the left end of the k-mer, of its minimum-hash m-mer (hash64 with seed 0 of the plain
+ * m-mer bits; leftmost on ties). Host pointers unless `flags` has BLG_F_DEVICE_INPUT|BLG_F_DEVICE_OUTPUT (both arrays
+ * then are device pointers). The reference's nullopt branch (returns k + 1) belongs to the shim: values here are plain.
+ */
+int blg_minimizer_positions(blg_ctx* ctx, const uint64_t* kmer_values, size_t n, uint8_t k, uint8_t m, uint32_t flags,
+                            uint8_t* out_positions);
 
 /* release library-allocated output arrays (host pinned or device); caller-provided arrays are untouched */
 void blg_free_kmer_out(blg_ctx* ctx, blg_kmer_out* out);

@@ -11,6 +11,7 @@
 //   biolib::gpu::super_kmer_view<KmerType, MinimizerType, HashFunction>(contig, len, k, m, canonical = false [, seed = 0])
 //                                                                                            include/super_kmer_view.hpp:48-49
 //       value_type super_kmer_t{minimizer; mm_pos; size}                                     :20-24
+//   biolib::gpu::minimizer_position_extractor(k, m)                                          include/kmer_view.hpp:250-283
 // A caller switches by replacing `wrapper::` with `biolib::gpu::` and linking libbiolib_gpu.so.
 //
 // Differences that are deliberate:
@@ -234,6 +235,42 @@ kmer_view<KmerType, char_iterator> kmer_view_from_cstr(char const* s, std::size_
 {
     return kmer_view<KmerType, char_iterator>(char_iterator(s), char_iterator(s + len), k, canonical);
 }
+
+// ------------------------------------------------------------------------------------------------ minimizer_position_extractor
+// hash::minimizer_position_extractor (reference include/kmer_view.hpp:250-283, ctor src/kmer_view.cpp:7-15): same
+// constructor and accessors; operator() keeps the reference's one-record form (one device round trip per call: use it
+// for spot checks) and gains a batched form over the records of a gpu::kmer_view or a plain array of k-mer values.
+class minimizer_position_extractor
+{
+    public:
+        using value_type = uint64_t;
+        minimizer_position_extractor(uint8_t k, uint8_t m) : klen(k), mlen(m)
+        {
+            if (k == 0 || k > 32 || m == 0 || m > k) throw std::invalid_argument("[biolib::gpu] minimizer_position_extractor: need 1 <= m <= k <= 32");
+        }
+        uint8_t get_k() const noexcept { return klen; }
+        uint8_t get_m() const noexcept { return mlen; }
+        template <typename KmerType>
+        std::size_t operator()(kmer_context_t<KmerType> const& kmer) const
+        {
+            static_assert(sizeof(KmerType) == 8, "k-mer values held in uint64_t");
+            if (!kmer.value) return static_cast<std::size_t>(klen) + 1;          // include/kmer_view.hpp:270
+            uint64_t v = *kmer.value;
+            uint8_t out = 0;
+            context& ctx = context::thread_default();
+            ctx.check(blg_minimizer_positions(ctx.get(), &v, 1, klen, mlen, 0, &out), "minimizer_position_extractor");
+            return out;
+        }
+        std::vector<uint8_t> operator()(uint64_t const* values, std::size_t n) const
+        {
+            std::vector<uint8_t> out(n);
+            context& ctx = context::thread_default();
+            ctx.check(blg_minimizer_positions(ctx.get(), values, n, klen, mlen, 0, out.data()), "minimizer_position_extractor");
+            return out;
+        }
+    private:
+        uint8_t klen, mlen;
+};
 
 // ------------------------------------------------------------------------------------------------ minimizer_view
 template <typename MinimizerType>

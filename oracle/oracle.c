@@ -260,6 +260,26 @@ void orc_mmers(const char* s, size_t n, const uint64_t* offsets, size_t n_seq, u
     free(rl);
 }
 
+/* hash::minimizer_position_extractor (reference include/kmer_view.hpp:266-283): for one k-mer value (k <= 32), the
+ * k-m+1 m-mers are visited from the RIGHT (km >>= 2 each step), hashed with seed 0, and a later (more to the left)
+ * m-mer replaces the current minimum on '>=' : smallest hash, leftmost on ties. Returned: k - m - minpos, the 0-based
+ * offset of that m-mer from the left end of the k-mer. */
+void orc_minimizer_positions(const uint64_t* values, size_t n, unsigned k, unsigned m, uint64_t* out)
+{
+    const uint64_t mask = (2 * m != 64) ? (((uint64_t)1 << (2 * m)) - 1) : ~(uint64_t)0;
+    for (size_t q = 0; q < n; ++q) {
+        uint64_t km = values[q];
+        uint64_t mval = orc_hash64_u64(km & mask, 0);
+        unsigned minpos = 0;
+        for (unsigned i = 0; i < k - m + 1; ++i) {
+            uint64_t val = orc_hash64_u64(km & mask, 0);
+            if (mval >= val) { mval = val; minpos = i; }
+            km >>= 2;
+        }
+        out[q] = (uint64_t)(k - m - minpos);
+    }
+}
+
 /* ------------------------------------------------ minimizers / super-k-mers -- */
 /*
  * D4-D8: k-mer at start s valid iff bases [s, s+k) valid and in one

@@ -94,6 +94,14 @@ class Oracle:
     def remix(self, z):
         return int(self.lib.orc_remix(z))
 
+    def minimizer_positions(self, values, k, m):
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        out = np.empty(v.size, dtype=np.uint64)
+        self.lib.orc_minimizer_positions.argtypes = [C.c_void_p, C.c_size_t, C.c_uint, C.c_uint, C.c_void_p]
+        self.lib.orc_minimizer_positions.restype = None
+        self.lib.orc_minimizer_positions(v.ctypes.data, v.size, k, m, out.ctypes.data)
+        return out
+
     def kmer_stream(self, seq, k, canonical):
         b = _buf(seq)
         cap = len(b) + 1
@@ -207,6 +215,15 @@ class Ref:
 
     def remix(self, z):
         return int(self.lib.ref_remix(z))
+
+    def minimizer_positions(self, values, k, m, has_value=None):
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        hv = None if has_value is None else np.ascontiguousarray(has_value, dtype=np.uint8)
+        out = np.empty(v.size, dtype=np.uint64)
+        self.lib.ref_minimizer_positions.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint, C.c_uint, C.c_void_p]
+        self.lib.ref_minimizer_positions.restype = None
+        self.lib.ref_minimizer_positions(v.ctypes.data, None if hv is None else hv.ctypes.data, v.size, k, m, out.ctypes.data)
+        return out
 
     def kmer_stream(self, seq, k, canonical, bits=64):
         b = _buf(seq)

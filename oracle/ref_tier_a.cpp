@@ -150,6 +150,19 @@ void ref_double_hash64_u128(uint64_t lo, uint64_t hi, uint64_t seed, uint64_t ou
 }
 uint64_t ref_remix(uint64_t z) { return hash::remix(z); }
 
+// hash::minimizer_position_extractor::operator() verbatim (include/kmer_view.hpp:266-283, ctor src/kmer_view.cpp:7-15),
+// for k-mers held in uint64_t (k <= 32). has_value == 0 exercises the nullopt branch (returns k + 1).
+void ref_minimizer_positions(const uint64_t* values, const uint8_t* has_value, size_t n, unsigned k, unsigned m, uint64_t* out)
+{
+    hash::minimizer_position_extractor ex(static_cast<uint8_t>(k), static_cast<uint8_t>(m));
+    for (size_t i = 0; i < n; ++i) {
+        wrapper::kmer_context_t<uint64_t> ctx;
+        if (!has_value || has_value[i]) ctx.value = values[i]; else ctx.value = std::nullopt;
+        ctx.position = i; ctx.id = i;
+        out[i] = ex(ctx);
+    }
+}
+
 // Full kmer_view stream, including nullopt records and ids (K1-K4).
 size_t ref_kmer_view_u64(const char* s, size_t n, unsigned k, int canonical,
                          uint64_t* value, uint8_t* has_value, uint64_t* position, uint64_t* id, size_t cap)

@@ -154,3 +154,23 @@ for seed, (mp, idf, ep) in ((7, (0.1, 0.3, 0.3)), (47, (0.10, 0.3, 0.3)), (3, (0
     gen["mutate"].append(dict(src=src, mutp=mp, indelf=idf, extp=ep, seed=seed, out=out.tobytes().decode(),
                               counts=counts.tolist(), total_indel_len=int(tot)))
 dump("generator.json", gen)
+
+
+def minpos(ref, path):
+    """tests/golden/minpos.json: hash::minimizer_position_extractor (reference include/kmer_view.hpp:266-283) executed
+    verbatim over seeded k-mer values, incl. all-A, all-T, (AC)n-like and 1."""
+    import json
+    import numpy as np
+    rng = np.random.default_rng(20261104)
+    cases = []
+    for k, m in [(31, 19), (21, 11), (15, 10), (32, 32), (32, 1), (7, 4), (5, 5), (32, 16), (17, 16)]:
+        v = rng.integers(0, 2**63, size=64, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=64, dtype=np.uint64)
+        full = (1 << (2 * k)) - 1 if k < 32 else 2**64 - 1
+        if k < 32:
+            v &= np.uint64(full)
+        v[:4] = [0, full, 0x5555555555555555 & full, 1]
+        pos = ref.minimizer_positions(v, k, m)
+        cases.append(dict(k=k, m=m, values=[int(x) for x in v], positions=[int(x) for x in pos]))
+    nullopt = int(ref.minimizer_positions(np.array([5], np.uint64), 7, 4, has_value=np.array([0], np.uint8))[0])
+    json.dump(dict(source="hash::minimizer_position_extractor executed verbatim (oracle/_ref)", nullopt_k7_m4=nullopt, cases=cases),
+              open(path, "w"))

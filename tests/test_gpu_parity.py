@@ -173,6 +173,31 @@ def test_pipelined_host_path_large_input(gpu, oracle, k, m, multi):
     assert e.value.status == 3
 
 
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (9, 5), (32, 32), (32, 7), (12, 12), (3, 1), (32, 16)])
+def test_minimizer_position_extractor(gpu, oracle, k, m):
+    """blg_minimizer_positions vs hash::minimizer_position_extractor (reference include/kmer_view.hpp:266-283)."""
+    rng = np.random.default_rng(80 + k)
+    v = rng.integers(0, 2**63, size=100_000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=100_000, dtype=np.uint64)
+    if k < 32:
+        v &= np.uint64((1 << (2 * k)) - 1)
+    v[:500] &= np.uint64(0xFF)
+    got = gpu.minimizer_positions(v, k, m)
+    assert np.array_equal(got.astype(np.uint64), oracle.minimizer_positions(v, k, m))
+    # through the k-mers of a sequence: offset of the minimizer inside each canonical k-mer value
+    s = rand_seq(rng, 5000)
+    km = gpu.kmers(s, k, True)
+    assert np.array_equal(gpu.minimizer_positions(km["lo"], k, m).astype(np.uint64), oracle.minimizer_positions(km["lo"], k, m))
+
+
+def test_minimizer_position_extractor_errors(gpu):
+    import biolib_b200
+    for k, m in [(33, 5), (5, 6), (0, 0), (5, 0)]:
+        with pytest.raises(biolib_b200.BlgError) as e:
+            gpu.minimizer_positions(np.zeros(4, np.uint64), k, m)
+        assert e.value.status == 1
+    assert gpu.minimizer_positions(np.zeros(0, np.uint64), 31, 19).size == 0
+
+
 def test_hash64(gpu, oracle):
     vals = np.array([0, 1, 0x1234567890ABCDEF, 0xFFFFFFFFFFFFFFFF], dtype=np.uint64)
     assert gpu.hash64(vals, 0).tolist() == [0x28DF63B7CC57C3CB, 0x004403B7FB05C44A, 0x495AE5FABBE9F68B, 0xA0E4B27A1ABAED73]
@@ -286,6 +311,16 @@ int main(int argc, char** argv) {
     for (auto it = sk.cbegin(); it != sk.cend(); ++it)
         std::printf("S %llu %zu %zu %u %u\n", (unsigned long long)(*it).minimizer.value, (*it).minimizer.position, (*it).minimizer.id,
                     (unsigned)(*it).mm_pos, (unsigned)(*it).size);
+    {
+        biolib::gpu::minimizer_position_extractor ex(k, m);
+        std::vector<uint64_t> vals;
+        for (auto it = kv.cbegin(); it != kv.cend(); ++it) if ((*it).value) vals.push_back(*(*it).value);
+        auto pos = ex(vals.data(), vals.size());
+        for (std::size_t i = 0; i < vals.size(); ++i) std::printf("X %llu %u\n", (unsigned long long)vals[i], (unsigned)pos[i]);
+        biolib::gpu::kmer_context_t<uint64_t> none{std::nullopt, 0, 0};
+        if (ex(none) != (std::size_t)k + 1 || ex.get_k() != k || ex.get_m() != m) return 5;
+        if (!vals.empty()) { biolib::gpu::kmer_context_t<uint64_t> one{vals[0], 0, 0}; if (ex(one) != pos[0]) return 6; }
+    }
     try { biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> bad(s, 3, 4); bad.cbegin(); return 4; }
     catch (std::invalid_argument const&) {}
     return 0;
@@ -324,3 +359,6 @@ def test_cpp_shim_views(gpu, oracle, tmp_path):
             want_m = list(zip(o["value"].tolist(), (o["mm_start"] + 1).tolist(), ids))       # D7: position = start + 1
             assert M == want_m, (seq[:20], k, m, canon)
             assert S == [a + (int(p), int(z)) for a, p, z in zip(want_m, (o["mm_start"] - o["sk_start"]).tolist(), o["size"].tolist())]
+            X = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("X ")]
+            xv = np.array([v for v, _ in X], dtype=np.uint64)
+            assert [p for _, p in X] == oracle.minimizer_positions(xv, k, m).tolist() if len(X) else True

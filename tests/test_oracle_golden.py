@@ -138,3 +138,14 @@ def test_generator_and_mutator(oracle):
         out, counts, tot = oracle.mutate(c["src"], c["mutp"], c["indelf"], c["extp"], c["seed"])
         assert out.tobytes().decode() == c["out"], c["seed"]
         assert counts.tolist() == c["counts"] and tot == c["total_indel_len"]
+
+
+def test_minimizer_position_extractor_golden(oracle):
+    """hash::minimizer_position_extractor (reference include/kmer_view.hpp:266-283) against reference-executed vectors."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "minpos.json")))
+    assert g["nullopt_k7_m4"] == 8                      # k + 1 for a valueless record (kmer_view.hpp:270)
+    for c in g["cases"]:
+        got = oracle.minimizer_positions(np.array(c["values"], dtype=np.uint64), c["k"], c["m"])
+        assert [int(x) for x in got] == c["positions"], (c["k"], c["m"])

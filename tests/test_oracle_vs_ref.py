@@ -135,3 +135,13 @@ def test_generator_and_mutator(oracle, ref):
         a, ca, ta = oracle.mutate(src, mp, idf, ep, seed)
         b, cb, tb = ref.mutate(src, mp, idf, ep, seed)
         assert np.array_equal(a, b) and np.array_equal(ca, cb) and ta == tb
+
+
+def test_minimizer_position_extractor_live(oracle, ref):
+    rng = np.random.default_rng(8)
+    for k, m in [(31, 19), (21, 11), (9, 5), (32, 32), (32, 7), (12, 12), (3, 1)]:
+        v = rng.integers(0, 2**63, size=5000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=5000, dtype=np.uint64)
+        if k < 32:
+            v &= np.uint64((1 << (2 * k)) - 1)
+        v[:200] &= np.uint64(0xFF)                      # low-complexity values: hash ties between equal m-mers
+        assert np.array_equal(oracle.minimizer_positions(v, k, m), ref.minimizer_positions(v, k, m)), (k, m)
