@@ -185,6 +185,29 @@ def build_rank_input(rank: int, world: int):
     return bases, win_lo, win_hi
 
 
+def bind_to_gpu_numa_node(local: int) -> str:
+    """Run this rank (and so first-touch its pinned buffers) on the CPU cores of the NUMA node its GPU hangs off:
+    with 8 ranks the host<->device copies otherwise cross the socket interconnect. Best effort, never fatal."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = int(open(base + "/numa_node").read())
+        if node < 0:
+            return "numa: none"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return f"numa node {node}, {len(cpus)} cpus"
+    except Exception as e:  # noqa: BLE001
+        return f"numa: unavailable ({type(e).__name__})"
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -197,6 +220,7 @@ def run_gpu(args):
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -290,7 +314,8 @@ def run_gpu(args):
             "config": {"workload": "super_kmer_view k=31 m=19 canonical seed=42 over 100 Mbp/GPU of sequence_generator "
                                    "uniform(42+shard) (BASELINE configs[1])",
                        "k": K, "m": M, "bases_per_gpu": SHARD, "records": total_records, "kmers": total_win,
-                       "l2": "256 MiB flush write between timed steps", "sharding": f"chunk+halo x{world}"},
+                       "l2": "256 MiB flush write between timed steps", "sharding": f"chunk+halo x{world}",
+                       "host": numa},
             "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": e2e_ms},
             "gpu_launches": args.steps,
