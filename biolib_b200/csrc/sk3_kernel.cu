@@ -423,7 +423,7 @@ constexpr u64 ACC_ONE = 1ULL << 40, ACC_MASK = ACC_ONE - 1;
 __device__ __forceinline__ void spin_guard(u32& spins)
 {
     __nanosleep(64);
-    if (++spins > (1u << 22)) __trap();   // ~0.3 s: a protocol bug must not hang the GPU
+    if (++spins > (1u << 25)) __trap();   // seconds of waiting: a protocol bug must not hang the GPU
 }
 
 // Exclusive record offset of `tile` (published one tile ago), in two steps so that the loads are in flight while the
