@@ -36,6 +36,7 @@ struct SkArgs {
     unsigned long long* total;         // out: number of records
     // third-generation kernel (sk3_kernel.cu): two-level scan; filled by sk3_plan / the C-ABI layer
     long long status_words;            // u64 words of scan scratch to zero: num_tiles + 2 * groups
+    int gq, gr, gl;                    // general form: k - m = gq * B + gr; lanes 1 .. gl own record starts
     unsigned long long* grp_acc;       // [groups] arrivals << 40 | records of a group of 32 tiles
     unsigned long long* grp_status;    // [groups] look-back words over groups
 };

@@ -301,10 +301,11 @@ static size_t super_kmers_impl(const char* s, size_t n, const uint64_t* offsets,
     const unsigned w = k - m + 1;
     uint32_t* rl = run_lengths(s, n, offsets, n_seq);
     size_t cnt = 0;
-    /* ring of (hash, value) for the last w m-mers and the deque of candidate positions */
-    uint64_t* hring = (uint64_t*)malloc(64 * sizeof(uint64_t));
-    uint64_t* vring = (uint64_t*)malloc(64 * sizeof(uint64_t));
-    size_t dq[64]; unsigned dq_head = 0, dq_len = 0;              /* positions, increasing; hashes strictly increasing front->back */
+    /* ring of (hash, value) for the last w m-mers and the deque of candidate positions. 128 slots, not 64: with
+     * w = 64 the m-mer at cur_arg + 64 is pushed before the record of cur_arg is closed and must not overwrite it */
+    uint64_t* hring = (uint64_t*)malloc(128 * sizeof(uint64_t));
+    uint64_t* vring = (uint64_t*)malloc(128 * sizeof(uint64_t));
+    size_t dq[128]; unsigned dq_head = 0, dq_len = 0;              /* positions, increasing; hashes strictly increasing front->back */
     uint64_t fw = 0, rc = 0;                                      /* rolling m-mer words */
     const uint64_t mmask = m == 32 ? ~0ULL : ((1ULL << (2 * m)) - 1);
     const unsigned rshift = 2 * (m - 1);
@@ -314,8 +315,8 @@ static size_t super_kmers_impl(const char* s, size_t n, const uint64_t* offsets,
 
 #define EMIT_RECORD() do { \
         if (cnt < cap) { \
-            if (value) value[cnt] = vring[cur_arg & 63]; \
-            if (hashv) hashv[cnt] = hring[cur_arg & 63]; \
+            if (value) value[cnt] = vring[cur_arg & 127]; \
+            if (hashv) hashv[cnt] = hring[cur_arg & 127]; \
             if (mm_start) mm_start[cnt] = cur_arg; \
             if (sk_start) sk_start[cnt] = cur_start; \
             if (size) size[cnt] = (uint8_t)cur_n; \
@@ -341,13 +342,13 @@ static size_t super_kmers_impl(const char* s, size_t n, const uint64_t* offsets,
             size_t j = i + 1 - m;                                 /* 0-based m-mer start */
             uint64_t v = (canonical && rc < fw) ? rc : fw;
             uint64_t h = orc_hash64_u64(v, seed);
-            hring[j & 63] = h; vring[j & 63] = v;
-            while (dq_len && hring[dq[(dq_head + dq_len - 1) & 63] & 63] > h) --dq_len;   /* equal stays: leftmost wins */
-            dq[(dq_head + dq_len) & 63] = j; ++dq_len;
+            hring[j & 127] = h; vring[j & 127] = v;
+            while (dq_len && hring[dq[(dq_head + dq_len - 1) & 127] & 127] > h) --dq_len;   /* equal stays: leftmost wins */
+            dq[(dq_head + dq_len) & 127] = j; ++dq_len;
             if (since_break < k) continue;
             size_t st = i + 1 - k;                                /* k-mer start */
-            while (dq[dq_head & 63] < st) { dq_head = (dq_head + 1) & 63; --dq_len; }
-            size_t arg = dq[dq_head & 63];
+            while (dq[dq_head & 127] < st) { dq_head = (dq_head + 1) & 127; --dq_len; }
+            size_t arg = dq[dq_head & 127];
             if (open && arg == cur_arg) { ++cur_n; }
             else {
                 if (open) EMIT_RECORD();
@@ -382,7 +383,7 @@ static size_t super_kmers_impl(const char* s, size_t n, const uint64_t* offsets,
             else {
                 if (open) EMIT_RECORD();
                 open = 1; cur_arg = arg; cur_start = st; cur_n = 1;
-                hring[arg & 63] = H[arg]; vring[arg & 63] = V[arg];
+                hring[arg & 127] = H[arg]; vring[arg & 127] = V[arg];
             }
             prev_valid = 1; prev_arg = arg;
         }

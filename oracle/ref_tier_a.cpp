@@ -247,13 +247,13 @@ static size_t super_kmers_sum_impl(const char* s, size_t n, unsigned k, unsigned
     it.mask = (KmerT(1) << (2 * m)) - 1;
     it.mm_forward_reverse = {uint64_t(0), uint64_t(0)};
     const unsigned w = k - m + 1;
-    uint64_t hring[64], vring[64];
-    size_t dq[64];
+    uint64_t hring[128], vring[128];   // 128: with w = 64 m-mer cur_arg + 64 arrives before cur_arg's record closes
+    size_t dq[128];
     unsigned head = 0, len = 0;
     size_t cnt = 0, cur_arg = 0, cur_n = 0;
     bool open = false;
     uint64_t sv = 0, sp = 0, ss = 0, sh = 0;
-    auto emit = [&]() { sv += vring[cur_arg & 63]; sp += cur_arg; ss += cur_n; sh += hring[cur_arg & 63]; ++cnt; open = false; };
+    auto emit = [&]() { sv += vring[cur_arg & 127]; sp += cur_arg; ss += cur_n; sh += hring[cur_arg & 127]; ++cnt; open = false; };
     for (size_t i = 0; i < n; ++i) {
         it.read_base();
         const size_t b = it.bases_since_last_break;
@@ -262,13 +262,13 @@ static size_t super_kmers_sum_impl(const char* s, size_t n, unsigned k, unsigned
         const size_t j = i + 1 - m;
         const uint64_t v = it.mm_forward_reverse[it.strand];
         const uint64_t h = hash::hash64::hash(v, view.mseed);
-        hring[j & 63] = h; vring[j & 63] = v;
-        while (len && hring[dq[(head + len - 1) & 63] & 63] > h) --len;
-        dq[(head + len) & 63] = j; ++len;
+        hring[j & 127] = h; vring[j & 127] = v;
+        while (len && hring[dq[(head + len - 1) & 127] & 127] > h) --len;
+        dq[(head + len) & 127] = j; ++len;
         if (b < k) continue;
         const size_t st = i + 1 - k;
-        while (dq[head & 63] < st) { head = (head + 1) & 63; --len; }
-        const size_t arg = dq[head & 63];
+        while (dq[head & 127] < st) { head = (head + 1) & 127; --len; }
+        const size_t arg = dq[head & 127];
         if (open && arg == cur_arg) ++cur_n;
         else { if (open) emit(); open = true; cur_arg = arg; cur_n = 1; }
     }

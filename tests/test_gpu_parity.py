@@ -45,6 +45,32 @@ def test_random_clean(gpu, oracle, k, m, canon):
         check_sk(gpu, oracle, rand_seq(rng, n), k, m, 42, canon)
 
 
+def _sweep_pairs():
+    """One (k, m) for every k - m in 0 .. 63 (the general kernel form splits k - m = q B + r with B = 16, 12, 8, 6 and
+    picks 2- or 3-word lane streams from m), plus the corners of each block size and the largest m per stream width."""
+    rng = np.random.default_rng(20240)
+    out = []
+    for d in range(0, 64):
+        m = int(rng.integers(1, min(32, 64 - d) + 1))
+        out.append((m + d, m))
+    out += [(32 + 15, 32), (17 + 15, 17), (18 + 16, 18), (21 + 11, 21), (22 + 14, 22), (25 + 7, 25), (26 + 10, 26), (27 + 5, 27), (28 + 6, 28),
+            (32 + 31, 32), (1 + 63, 1), (16 + 47, 16), (17 + 47, 17), (32 + 5, 32), (1 + 5, 1), (30 + 12, 30), (12 + 10, 17 - 5)]
+    return sorted(set(out))
+
+
+@pytest.mark.parametrize("k,m", _sweep_pairs())
+def test_every_window_length(gpu, oracle, k, m):
+    rng = np.random.default_rng(k * 131 + m)
+    for canon in (False, True):
+        check_sk(gpu, oracle, rand_seq(rng, 30011), k, m, 42, canon)
+    s = rand_seq(rng, 40000, p_n=0.004, lower=0.05)
+    check_sk(gpu, oracle, s, k, m, 7, True)
+    lens = rng.integers(0, 3 * k, size=400)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    check_sk(gpu, oracle, rand_seq(rng, int(offsets[-1]), p_n=0.002), k, m, 42, True, offsets=offsets)
+    check_sk(gpu, oracle, "ACGT" * 300 + "A" * 700 + "AT" * 300, k, m, 42, True)
+
+
 @pytest.mark.parametrize("k,m", [(7, 4), (31, 19), (21, 11), (63, 31), (16, 8)])
 def test_random_with_breaks(gpu, oracle, k, m):
     rng = np.random.default_rng(7 * k + m)

@@ -92,7 +92,7 @@ def test_minimizer_view_literal_is_empty(ref):
         assert ref.minimizer_view_literal_count(s, k, m, 42, 1) == 0
 
 
-@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (63, 31), (9, 5), (16, 8)])
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (63, 31), (9, 5), (16, 8), (64, 1), (64, 32), (40, 9), (33, 1)])
 def test_super_kmers_linear_vs_brute_vs_reference_arithmetic(oracle, ref, k, m):
     rng = np.random.default_rng(k + m)
     for n, pn in ((3000, 0.0), (6000, 0.004), (2000, 0.05)):
