@@ -32,6 +32,7 @@ struct Owner {
 struct blg_ctx {
     int device = 0;
     int sm_count = 0;
+    int kmer_gen = 0;            // BLG_KMER=1 pins the first-generation k-mer kernel (development A/B only)
     int sk_gen = 0;              // BLG_SK=1|2|3 pins a kernel generation (development A/B only); 0 = newest that covers (k, m)
     char name[128] = {0};
     cudaStream_t own_stream = nullptr;
@@ -169,7 +170,9 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
 {
     KmerLaunchPlan plan;
-    CK(c, kmer_plan(a, c->sm_count, &plan));
+    const bool gen2 = c->kmer_gen != 1;
+    if (gen2) CK(c, kmer2_plan(a, c->sm_count, &plan));
+    else CK(c, kmer_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
     int rc = prep_scratch(c, a.num_tiles);
     if (rc != BLG_OK) return rc;
@@ -177,7 +180,8 @@ int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    CK(c, kmer_launch(a, plan, c->stream));
+    if (gen2) CK(c, kmer2_launch(a, plan, c->stream));
+    else CK(c, kmer_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -545,6 +549,7 @@ int blg_create(int device, blg_ctx** out)
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
     { const char* e = getenv("BLG_PIPE_CHUNK_M"); if (e && atoi(e) > 0) c->pipe_chunk_m = atoi(e); }
     { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("BLG_KMER"); c->kmer_gen = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 0; }
     *out = c;
     return BLG_OK;

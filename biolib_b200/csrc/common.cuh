@@ -132,6 +132,43 @@ __device__ __forceinline__ void mark_sequence_starts(uint2* cf, int nw, const u6
     }
 }
 
+// First q in [1, n_seq) with offs[q] >= pos (n_seq if none), found by the whole warp: one probe of 32 consecutive
+// entries around the position-proportional guess (exact for equal-length reads), then 32-ary narrowing (5 rounds for
+// 10^8 sequences instead of 27 dependent loads per lane).
+__device__ __forceinline__ long long first_offset_at_or_after(const u64* __restrict__ offs, long long n_seq, long long pos,
+                                                              long long total, int t)
+{
+    long long lo = 1, hi = n_seq;                      // the answer lies in [lo, hi]
+    if (hi <= lo) return hi;
+    {
+        long long g = total > 0 ? (long long)((double)pos / (double)total * (double)n_seq) - 15 : 1;
+        g = g < 1 ? 1 : (g > n_seq - 1 ? n_seq - 1 : g);
+        const long long q = g + t;
+        const bool ge = q >= n_seq || (long long)offs[q] >= pos;
+        const unsigned m = __ballot_sync(0xffffffffu, ge);
+        if (m == 0) lo = g + 32 < hi ? g + 32 : hi;               // everything probed is below pos
+        else {
+            const int f = __ffs((int)m) - 1;
+            if (f > 0 || g == 1) return (g + f) < n_seq ? g + f : n_seq;   // the entry before it was probed and is below
+            hi = g;                                               // the first probe already is >= pos
+        }
+    }
+    while (hi - lo > 0) {
+        const long long span = hi - lo;                // candidates lo .. hi-1 (hi itself is known to satisfy or is n_seq)
+        const long long step = (span + 31) / 32;
+        const long long q = lo + (long long)t * step;
+        const bool ge = q >= hi || (long long)offs[q] >= pos;
+        const unsigned m = __ballot_sync(0xffffffffu, ge);
+        if (m == 0) { lo = lo + 31 * step + 1 < hi ? lo + 31 * step + 1 : hi; continue; }   // all probed are below
+        const int f = __ffs((int)m) - 1;
+        const long long qf = lo + (long long)f * step;             // first probed entry that is >= pos
+        if (step == 1) return qf < hi ? qf : hi;
+        hi = qf < hi ? qf : hi;
+        lo = f > 0 ? qf - step + 1 : lo;
+    }
+    return hi;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Cross-tile ordered compaction: single-pass chained scan with decoupled look-back.
 // status word = flag (bits 63..62: 1 = tile aggregate, 2 = inclusive prefix) | 62-bit count.

@@ -96,6 +96,9 @@ struct KmerLaunchPlan {
 };
 cudaError_t kmer_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
 cudaError_t kmer_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
+// second generation (kmer2_kernel.cu): same arguments and results
+cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
+cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
 
 // minimizer_context_t::id for records already on the device: rank directory over the valid-m-mer bit vector
 size_t rank_scratch_bytes(long long n_bases);

@@ -1,0 +1,374 @@
+// kmer2_kernel.cu -- batched wrapper::kmer_view for sm_100a, second generation: every valid k-mer as (value, position).
+//
+// Same results as kmer_kernel.cu (reference semantics include/kmer_view.hpp:181-202, 213-234). What
+// changed is the instruction count: the profile of the first kernel (profiles/r01_s29_kmer_kernel_details.txt) shows 94
+// executed instructions per k-mer with the ALU pipe 69 % busy and DRAM at 44 % -- the per-base rolling update of two
+// 64-bit words, the [step][thread] transposition through shared memory and the per-element offset lookup cost more than
+// the memory traffic. Here
+//
+//   * nothing rolls: the tile's bases are staged once as two packed 2-bit streams (complemented little-endian for the
+//     reverse complement, big-endian for the forward word) and every k-mer is CUT out of them with funnel shifts. Lane l
+//     of a warp takes start 32 j + l, so the shift amounts are per-lane constants, the word indices advance by two per
+//     step (immediate offsets), and the 8-byte stores of a warp are one contiguous 256-byte line -- no transposition;
+//   * validity is a bit test on one bad-base bit row (and a sequence-start row for multi-sequence input): a k-mer is
+//     valid iff its k bits (k-1 for the start row) are clear. Lane j of a warp computes the valid mask of the 32 starts
+//     of step j in one go (log2 k doubling steps on a 96-bit window); tiles without any flagged base skip all of it and
+//     write base + start index with unconditional stores;
+//   * a CTA is 31 output warps + one SCAN warp. Tile i is staged (from registers requested one iteration earlier)
+//     while tile i-1 is written out; the scan warp takes the tickets, runs the decoupled look-back of tile i and marks
+//     the sequence starts of tile i+1 during that time, so nobody waits for the chained scan. Counts of flagged tiles
+//     reach the scan warp through a named barrier the output warps only ARRIVE at; one CTA barrier per phase is left.
+//
+// Measured (profiles/r01_s29_kmer2_kernel_details.txt, tools/kmerbench.py, 100 Mbp, value + position per k-mer):
+// k=31 0.36 ms = 4.7 TB/s = 72 % of the measured HBM copy peak (first generation 0.45 ms), k=63 0.46 ms = 83 %
+// (0.73 ms), 40 executed instructions per k-mer, DRAM traffic 1.64 GB per launch against 1.70 GB algorithmic.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace blg {
+
+namespace {
+#ifndef K2_MIN_BLOCKS
+#define K2_MIN_BLOCKS 1
+#endif
+#ifndef K2_THREADS
+#define K2_THREADS 992
+#endif
+constexpr int K2T = K2_THREADS;     // threads
+constexpr int K2W = K2T / 32;       // warps
+constexpr int K2S = 16;             // steps: a warp owns 32 * K2S consecutive starts
+constexpr int K2TILE = K2T * K2S;   // 4096 starts per tile
+constexpr int K2NW = K2TILE / 16 + 6;   // staged 16-base words: 15 (alignment) + 4096 + 63 bases
+constexpr int K2PAD = 4;            // words in front of the big-endian stream
+constexpr int K2WORDS = K2NW + 8;   // every stream is padded so that cuts near the end stay inside
+constexpr int K2ROW = K2WORDS / 2 + 2;
+
+struct K2Buf {                       // one staged tile; two sets: tile i is staged while tile i-1 is written out
+    u32 le[K2WORDS];                 // ~codes, base q of word j at bits [2q, 2q+2)
+    u32 be[K2PAD + K2WORDS];         // codes, first base of a word in its top bits
+    u32 bad[K2ROW];                  // bit x: base A0 + x is not ACGTU (or outside the buffer)
+    u32 seq[K2ROW];                  // bit x: a sequence starts at A0 + x (interior starts only)
+    u32 bal[K2W][K2S];               // valid masks of every warp's steps (tiles with flagged bases only)
+};
+struct K2Smem {
+    K2Buf buf[2];
+    u32 wsum[K2W];
+    u64 base[2];
+    int next;
+    int seqdirty[2];
+};
+
+__device__ __forceinline__ u32 pairrev32_k(u32 x)
+{
+    x = __brev(x);
+    return ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+}
+
+// For the 32 consecutive starts x = bit .. bit + 31: bit x - bit of the result = OR of row bits [x, x + span), by ONE lane
+// (log2(span) doubling steps on a 96-bit window instead of one span test per start). span <= 64.
+__device__ __forceinline__ u32 or_span32(const u32* row, int bit, int span)
+{
+    if (span <= 0) return 0u;
+    const int wq = bit >> 5, sh = bit & 31;
+    const u32 w0 = row[wq], w1 = row[wq + 1], w2 = row[wq + 2], w3 = row[wq + 3];
+    u32 x0 = __funnelshift_r(w0, w1, sh), x1 = __funnelshift_r(w1, w2, sh), x2 = __funnelshift_r(w2, w3, sh);
+    int covered = 1;
+    while (covered < span) {
+        int step = covered < span - covered ? covered : span - covered;
+        covered += step;
+        u32 y0 = x0, y1 = x1, y2 = x2;
+        if (step >= 32) { y0 = y1; y1 = y2; y2 = 0; step -= 32; }
+        if (step) { y0 = __funnelshift_r(y0, y1, step); y1 = __funnelshift_r(y1, y2, step); y2 >>= step; }
+        x0 |= y0; x1 |= y1; x2 |= y2;
+    }
+    return x0;
+}
+
+// Sequence-start bit row of the tile at `tile_lo` (interior starts inside the staged range), by one warp.
+__device__ __forceinline__ int mark_tile_sequence_starts(const KmerArgs& a, long long tile_lo, u32* row, int nrow, int nw, int lane)
+{
+    for (int j = lane; j < nrow; j += 32) row[j] = 0;
+    __syncwarp();
+    const long long A0 = tile_lo & ~15LL;
+    const long long lo_pos = A0 < 0 ? 0 : A0, end_pos = A0 + 16LL * nw;
+    const long long lo = first_offset_at_or_after(a.seq_offsets, a.n_seq, lo_pos, a.buf_hi, lane);
+    int found = 0;
+    for (long long q = lo + lane; q < a.n_seq; q += 32) {
+        const long long o = (long long)a.seq_offsets[q];
+        if (o >= end_pos) break;
+        const int rel = (int)(o - A0);
+        atomicOr(&row[rel >> 5], 1u << (rel & 31));
+        found = 1;
+    }
+    return __any_sync(0xffffffffu, found);
+}
+}  // namespace
+
+// One step of the output pass: the k-mer at (per-lane constant shifts, word indices advanced by two per step) is cut
+// out of the two streams; returns the value words.
+template <bool WIDE, bool CANON>
+__device__ __forceinline__ void cut_kmer(const u32* le, const u32* be, int s, int fs, const u32 (&vm)[4], u64& lo, u64& hi)
+{
+    constexpr int NV = WIDE ? 4 : 2;                            // 32-bit words of a value
+    u32 r[NV], f[NV], c[NV + 1], d[NV + 1];
+#pragma unroll
+    for (int q = 0; q <= NV; ++q) { c[q] = le[q]; d[q] = be[q]; }
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+        r[q] = __funnelshift_r(c[q], c[q + 1], s) & vm[q];                          // reverse complement, low word first
+        f[NV - 1 - q] = __funnelshift_l(d[q + 1], d[q], fs) & vm[NV - 1 - q];       // forward, d[0] holds the top bits
+    }
+    lo = ((u64)f[1] << 32) | f[0];
+    hi = 0;
+    if (WIDE) hi = ((u64)f[3] << 32) | f[2];
+    if (CANON) {
+        const u64 rlo = ((u64)r[1] << 32) | r[0];
+        if (WIDE) {
+            const u64 rhi = ((u64)r[3] << 32) | r[2];
+            const bool lt = rhi < hi || (rhi == hi && rlo < lo);
+            lo = lt ? rlo : lo; hi = lt ? rhi : hi;
+        } else lo = rlo < lo ? rlo : lo;
+    }
+}
+
+template <bool WIDE, bool CANON>
+__global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const KmerArgs a)
+{
+    __shared__ K2Smem sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool is_scan = warp == K2W;                               // the extra warp: tickets and the look-back only
+    const int k = a.k;
+    // masks of the value words (k-mer = low 2k bits)
+    u32 vm[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int bits = 2 * k - 32 * j;
+        vm[j] = bits >= 32 ? 0xFFFFFFFFu : (bits > 0 ? ((1u << bits) - 1u) : 0u);
+    }
+    constexpr int NV = WIDE ? 4 : 2;
+    const int wp = warp * (32 * K2S);                               // first start of this warp, tile-local
+
+    if (tid == 0) sm.next = (int)atomicAdd(a.tile_counter, 1u);
+    __syncthreads();
+    long long tile = (unsigned)sm.next;                             // the tile staged in this iteration
+    __syncthreads();
+    // sequence-start rows are the scan warp's: the row of a tile is marked one iteration before the tile is staged
+    if (is_scan && a.seq_offsets != nullptr && tile < a.num_tiles) {
+        const int f = mark_tile_sequence_starts(a, a.win_lo + tile * (long long)K2TILE, sm.buf[0].seq, K2ROW, K2NW, lane);
+        if (lane == 0) sm.seqdirty[0] = f;
+    }
+    // the tile staged in the previous iteration, written out in this one (buffer set b ^ 1)
+    bool have_prev = false, prev_all = false;
+    long long prev_lo = 0;
+    u32 prev_off = 0;
+    int b = 0;
+    // bases of the tile about to be staged, requested one iteration ahead (word tid, and K2T + tid)
+    bool have_pre = false;
+    uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
+    for (;;) {
+        const bool have = tile < a.num_tiles;
+        if (!have && !have_prev) break;
+        if (have_prev && !prev_all && !is_scan) {
+            // counts of the previous tile's warps (written before the last barrier, rewritten after the next one)
+            prev_off = 0;
+#pragma unroll
+            for (int q = 0; q < K2W; ++q) {
+                const u32 v = sm.wsum[q];
+                if (q < warp) prev_off += v;
+            }
+        }
+        K2Buf& cur = sm.buf[b];
+        const long long tile_lo = a.win_lo + tile * (long long)K2TILE;
+        const long long A0 = tile_lo & ~15LL;
+        const int off0 = (int)(tile_lo - A0);
+        int anybad = 0;
+        if (have) {
+            // the ticket after this one: every thread knows it after the next barrier, one whole iteration before it is staged
+            if (is_scan && lane == 0) sm.next = (int)atomicAdd(a.tile_counter, 1u);
+            // ---- stage: ASCII -> two packed streams + bad bits --------------------------------------------------------
+            if (!is_scan) {
+#pragma unroll
+                for (int it = 0; it < (K2WORDS + K2T - 1) / K2T; ++it) {
+                    const int wi = tid + it * K2T;
+                    if (wi >= K2WORDS) break;
+                    u32 codes = 0, bad16 = 0xFFFFu;
+                    if (wi < K2NW) {
+                        const long long P = A0 + 16LL * wi;
+                        u32 w0, w1, w2, w3;
+                        if (have_pre && it < 2) {
+                            const uint4 v = it == 0 ? pre0 : pre1;
+                            w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                        } else if (a.vec_ok && P >= a.buf_lo && P + 16 <= a.buf_hi) {
+                            const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P - a.buf_lo)));
+                            w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                        } else {
+                            u32 ww[4] = {0, 0, 0, 0};
+#pragma unroll
+                            for (int q = 0; q < 16; ++q) {
+                                const long long pos = P + q;
+                                if (pos >= a.buf_lo && pos < a.buf_hi) ww[q >> 2] |= (u32)a.bases[pos - a.buf_lo] << (8 * (q & 3));
+                            }
+                            w0 = ww[0]; w1 = ww[1]; w2 = ww[2]; w3 = ww[3];
+                        }
+                        blg_pack16_bits(w0, w1, w2, w3, &codes, &bad16);
+                        anybad |= (int)bad16;
+                    }
+                    cur.le[wi] = ~codes;
+                    cur.be[K2PAD + wi] = pairrev32_k(codes);
+                    reinterpret_cast<unsigned short*>(cur.bad)[wi] = (unsigned short)bad16;
+                }
+                if (tid < K2PAD) cur.be[tid] = 0;
+            }
+        }
+        const int dirty = __syncthreads_or(anybad);
+        const long long next_tile = have ? (long long)(unsigned)sm.next : a.num_tiles;
+        const bool seqdirty = have && a.seq_offsets != nullptr && sm.seqdirty[b];
+        // every start of the tile is a valid k-mer inside the window range: no masks, no counting
+        const bool all_valid = have && !dirty && !seqdirty && tile_lo + K2TILE <= a.win_hi;
+        if (have && !all_valid) {
+            // ---- valid masks of every warp's steps (kept in shared memory for the output pass), and their count -------
+            if (!is_scan) {
+                long long nwin = a.win_hi - (tile_lo + wp);     // starts of this warp inside the window range
+                nwin = nwin < 0 ? 0 : (nwin > 32 * K2S ? 32 * K2S : nwin);
+                // lane j owns step j: the valid mask of its 32 starts in one go
+                u32 mrange = 0;
+                if (lane < K2S) {
+                    const int n = (int)nwin - 32 * lane;
+                    mrange = n >= 32 ? 0xFFFFFFFFu : (n > 0 ? ((1u << n) - 1u) : 0u);
+                    const int lp = off0 + wp + 32 * lane;
+                    u32 bad = 0;
+                    if (dirty) bad = or_span32(cur.bad, lp, k);
+                    if (seqdirty) bad |= or_span32(cur.seq, lp + 1, k - 1);
+                    mrange &= ~bad;
+                    cur.bal[warp][lane] = mrange;
+                }
+                u32 cnt = __popc(mrange);
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+                if (lane == 0) sm.wsum[warp] = cnt;
+                // hand the counts to the scan warp without waiting for it (producer side of named barrier 1)
+                __threadfence_block();
+                asm volatile("bar.arrive 1, %0;" ::"r"(K2T + 32) : "memory");
+            }
+        }
+        if (is_scan) {
+            if (have) {
+                u32 tile_total = K2TILE;
+                if (!all_valid) {
+                    asm volatile("bar.sync 1, %0;" ::"r"(K2T + 32) : "memory");
+                    tile_total = 0;
+#pragma unroll
+                    for (int q = 0; q < K2W; ++q) tile_total += sm.wsum[q];
+                }
+                const u64 excl = lookback_exclusive(a.tile_status, tile, tile_total, lane);
+                if (lane == 0) {
+                    sm.base[b] = excl;
+                    if (tile == a.num_tiles - 1) *a.total = excl + tile_total;
+                }
+            }
+            if (a.seq_offsets != nullptr && next_tile < a.num_tiles) {
+                // buffer set b ^ 1: its start row was last read by the counting pass of the previous iteration
+                const int f = mark_tile_sequence_starts(a, a.win_lo + next_tile * (long long)K2TILE, sm.buf[b ^ 1].seq, K2ROW, K2NW, lane);
+                if (lane == 0) sm.seqdirty[b ^ 1] = f;
+            }
+        } else {
+            // ---- the next tile's bases are requested before the previous tile is written out ---------------------------
+            {
+                const long long nlo = a.win_lo + next_tile * (long long)K2TILE;
+                const long long P0 = (nlo & ~15LL) - a.buf_lo;
+                have_pre = next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * K2NW <= a.buf_hi - a.buf_lo;
+                if (have_pre) {
+                    pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + tid);
+                    if (K2T + tid < K2NW) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + K2T + tid);
+                }
+            }
+            // ---- write out the previous tile: its offset was resolved by the scan warp during the previous iteration ----
+            if (have_prev) {
+                const K2Buf& pv = sm.buf[b ^ 1];
+                const int poff0 = (int)(prev_lo - (prev_lo & ~15LL));
+                const int lp0 = poff0 + wp + lane;
+                const int s = (lp0 & 15) * 2;
+                const int e = 2 * lp0 + 2 * k + 32 * K2PAD - 32 * NV;   // the 32 NV bits that end with the k-mer's last base
+                const int fs = e & 31;
+                const u32* le = pv.le + (lp0 >> 4);
+                const u32* be = pv.be + (e >> 5);
+                const u64 g0 = sm.base[b ^ 1] + prev_off;
+                const u64 p0 = (u64)(prev_lo + wp + lane);
+                if (prev_all && g0 + 32 * K2S <= a.capacity) {
+                    u64* vlo = a.value_lo + g0 + lane;
+                    u64* vhi = WIDE ? a.value_hi + g0 + lane : nullptr;
+                    u64* pos = a.position != nullptr ? a.position + g0 + lane : nullptr;
+#pragma unroll
+                    for (int j = 0; j < K2S; ++j) {
+                        u64 lo, hi;
+                        cut_kmer<WIDE, CANON>(le + 2 * j, be + 2 * j, s, fs, vm, lo, hi);
+                        vlo[32 * j] = lo;
+                        if (WIDE) vhi[32 * j] = hi;
+                        if (pos != nullptr) pos[32 * j] = p0 + 32 * j;
+                    }
+                } else {
+                    u64 g = g0;
+                    const u32 below = (1u << lane) - 1u;
+                    const bool fits = g0 + 32 * K2S <= a.capacity;      // this warp writes at most 32 K2S values
+#pragma unroll 4
+                    for (int j = 0; j < K2S; ++j) {
+                        const u32 mj = prev_all ? 0xFFFFFFFFu : pv.bal[warp][j];
+                        if (mj == 0) continue;
+                        u64 lo, hi;
+                        cut_kmer<WIDE, CANON>(le + 2 * j, be + 2 * j, s, fs, vm, lo, hi);
+                        if (mj == 0xFFFFFFFFu && fits) {
+                            const u64 o = g + lane;
+                            a.value_lo[o] = lo;
+                            if (WIDE) a.value_hi[o] = hi;
+                            if (a.position != nullptr) a.position[o] = p0 + 32 * j;
+                        } else {
+                            const u64 o = g + __popc(mj & below);
+                            if (((mj >> lane) & 1u) && o < a.capacity) {
+                                a.value_lo[o] = lo;
+                                if (WIDE) a.value_hi[o] = hi;
+                                if (a.position != nullptr) a.position[o] = p0 + 32 * j;
+                            }
+                        }
+                        g += __popc(mj);
+                    }
+                }
+            }
+        }
+        __syncthreads();    // base[b] and the next ticket are out; buffer set b ^ 1 may be restaged
+        have_prev = have; prev_all = all_valid; prev_lo = tile_lo; prev_off = (u32)wp;
+        tile = next_tile;
+        b ^= 1;
+    }
+}
+
+cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
+{
+    args.nwords = K2NW;
+    const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
+    args.num_tiles = (nwin + K2TILE - 1) / K2TILE;
+    plan->threads = K2T + 32;
+    plan->smem_bytes = 0;
+    int occ = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kmer2_kernel<false, true>, K2T + 32, 0);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    long long grid = (long long)sm_count * occ;
+    if (grid > args.num_tiles) grid = args.num_tiles;
+    plan->grid = (int)(grid < 1 ? 1 : grid);
+    return cudaSuccess;
+}
+
+cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
+{
+    const bool canon = args.canonical != 0;
+    if (args.k > 32) {
+        if (canon) kmer2_kernel<true, true><<<plan.grid, plan.threads, 0, stream>>>(args);
+        else kmer2_kernel<true, false><<<plan.grid, plan.threads, 0, stream>>>(args);
+    } else {
+        if (canon) kmer2_kernel<false, true><<<plan.grid, plan.threads, 0, stream>>>(args);
+        else kmer2_kernel<false, false><<<plan.grid, plan.threads, 0, stream>>>(args);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace blg
