@@ -259,6 +259,39 @@ def test_kmers_multi_sequence(gpu, oracle):
             assert np.array_equal(g[key], o[key]), (key, k)
 
 
+@pytest.mark.parametrize("k,canon", [(31, True), (63, True), (17, False)])
+def test_kmers_many_tiles_both_generations(gpu, oracle, k, canon):
+    """Hundreds of tiles of the second-generation kernel (clean tiles, tiles with N runs, read boundaries, a ragged
+    end), against the oracle and against the first-generation kernel (BLG_KMER=1 pins it at context creation)."""
+    import os
+    import biolib_b200
+    rng = np.random.default_rng(900 + k)
+    n = 2_000_003
+    s = rand_seq(rng, n)
+    for p in rng.integers(0, n - 3000, 40):
+        s[p:p + int(rng.integers(1, 2500))] = ord("N")
+    lens = rng.integers(0, 40000, size=200)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    offsets = offsets[offsets < n]
+    offsets = np.concatenate([offsets, [n]]).astype(np.uint64)
+    os.environ["BLG_KMER"] = "1"
+    try:
+        first = biolib_b200.Context(0)
+    finally:
+        del os.environ["BLG_KMER"]
+    try:
+        for offs in (None, offsets):
+            g = gpu.kmers(s, k, canon, offsets=offs)
+            o = oracle.kmers(s, k, canon, offsets=offs)
+            f = first.kmers(s, k, canon, offsets=offs)
+            assert len(g["lo"]) == len(o["lo"]) > 1_000_000
+            for key in ("lo", "hi", "pos"):
+                assert np.array_equal(g[key], o[key]), (key, k)
+                assert np.array_equal(g[key], f[key]), (key, k)
+    finally:
+        first.close()
+
+
 def test_config1_kmer_view_1mbp(gpu, oracle):
     """BASELINE config 1: kmer_view k=31 canonical over the 1 Mbp sequence_generator(42) sequence."""
     s = oracle.generate(42, 1_000_000)
