@@ -80,6 +80,7 @@ struct KmerArgs {
     int canonical;
     int vec_ok;
     int nwords;
+    int steps;                     // kmer2: tile size chosen by kmer2_plan
     long long num_tiles;
     unsigned long long* value_lo;
     unsigned long long* value_hi;  // null for k <= 32

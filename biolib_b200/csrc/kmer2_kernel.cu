@@ -17,11 +17,12 @@
 //   * a CTA is 31 output warps + one SCAN warp. Tile i is staged (from registers requested one iteration earlier)
 //     while tile i-1 is written out; the scan warp takes the tickets, runs the decoupled look-back of tile i and marks
 //     the sequence starts of tile i+1 during that time, so nobody waits for the chained scan. Counts of flagged tiles
-//     reach the scan warp through a named barrier the output warps only ARRIVE at; one CTA barrier per phase is left.
+//     reach the scan warp through a named barrier the output warps only ARRIVE at; one CTA barrier per phase is left,
+//     and tiles are large (27 776 starts; 7 936 for inputs below 20 Mbp) to amortise it.
 //
 // Measured (profiles/r01_s29_kmer2_kernel_details.txt, tools/kmerbench.py, 100 Mbp, value + position per k-mer):
-// k=31 0.36 ms = 4.7 TB/s = 72 % of the measured HBM copy peak (first generation 0.45 ms), k=63 0.46 ms = 83 %
-// (0.73 ms), 40 executed instructions per k-mer, DRAM traffic 1.64 GB per launch against 1.70 GB algorithmic.
+// k=31 0.317 ms = 5.36 TB/s = 82 % of the measured HBM copy peak (first generation 0.446 ms), k=63 0.444 ms = 86 %
+// (0.734 ms), 150-bp reads 0.43 ms (0.57), 1 % N 0.34 ms (0.44); 40 executed instructions per k-mer.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -36,22 +37,31 @@ namespace {
 #endif
 constexpr int K2T = K2_THREADS;     // threads
 constexpr int K2W = K2T / 32;       // warps
-constexpr int K2S = 16;             // steps: a warp owns 32 * K2S consecutive starts
-constexpr int K2TILE = K2T * K2S;   // 4096 starts per tile
-constexpr int K2NW = K2TILE / 16 + 6;   // staged 16-base words: 15 (alignment) + 4096 + 63 bases
 constexpr int K2PAD = 4;            // words in front of the big-endian stream
-constexpr int K2WORDS = K2NW + 8;   // every stream is padded so that cuts near the end stay inside
-constexpr int K2ROW = K2WORDS / 2 + 2;
 
-struct K2Buf {                       // one staged tile; two sets: tile i is staged while tile i-1 is written out
-    u32 le[K2WORDS];                 // ~codes, base q of word j at bits [2q, 2q+2)
-    u32 be[K2PAD + K2WORDS];         // codes, first base of a word in its top bits
-    u32 bad[K2ROW];                  // bit x: base A0 + x is not ACGTU (or outside the buffer)
-    u32 seq[K2ROW];                  // bit x: a sequence starts at A0 + x (interior starts only)
-    u32 bal[K2W][K2S];               // valid masks of every warp's steps (tiles with flagged bases only)
+// S = steps (<= 32: lane j owns the valid mask of step j): a warp owns 32 S consecutive starts, a tile K2T * S.
+// Two sizes are compiled: large tiles amortise the per-tile phases (barriers, look-back) on large inputs, small tiles
+// keep every SM busy on small ones.
+constexpr int K2S_LARGE = 28, K2S_SMALL = 8;
+template <int S>
+struct K2Geo {
+    static constexpr int TILE = K2T * S;        // starts per tile
+    static constexpr int NW = TILE / 16 + 6;    // staged 16-base words: 15 (alignment) + TILE + 63 bases
+    static constexpr int WORDS = NW + 8;        // every stream is padded so that cuts near the end stay inside
+    static constexpr int ROW = WORDS / 2 + 2;
 };
+
+template <int S>
+struct K2Buf {                       // one staged tile; two sets: tile i is staged while tile i-1 is written out
+    u32 le[K2Geo<S>::WORDS];         // ~codes, base q of word j at bits [2q, 2q+2)
+    u32 be[K2PAD + K2Geo<S>::WORDS]; // codes, first base of a word in its top bits
+    u32 bad[K2Geo<S>::ROW];          // bit x: base A0 + x is not ACGTU (or outside the buffer)
+    u32 seq[K2Geo<S>::ROW];          // bit x: a sequence starts at A0 + x (interior starts only)
+    u32 bal[K2W][S];                 // valid masks of every warp's steps (tiles with flagged bases only)
+};
+template <int S>
 struct K2Smem {
-    K2Buf buf[2];
+    K2Buf<S> buf[2];
     u32 wsum[K2W];
     u64 base[2];
     int next;
@@ -131,10 +141,13 @@ __device__ __forceinline__ void cut_kmer(const u32* le, const u32* be, int s, in
     }
 }
 
-template <bool WIDE, bool CANON>
+template <int S, bool WIDE, bool CANON>
 __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const KmerArgs a)
 {
-    __shared__ K2Smem sm;
+    constexpr int K2S = S, K2TILE = K2Geo<S>::TILE, K2NW = K2Geo<S>::NW, K2WORDS = K2Geo<S>::WORDS, K2ROW = K2Geo<S>::ROW;
+    using K2Buf = K2Buf<S>;
+    extern __shared__ __align__(16) unsigned char k2_raw[];
+    K2Smem<S>& sm = *reinterpret_cast<K2Smem<S>*>(k2_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool is_scan = warp == K2W;                               // the extra warp: tickets and the look-back only
     const int k = a.k;
@@ -341,15 +354,48 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
     }
 }
 
+namespace {
+template <int S, bool WIDE, bool CANON>
+cudaError_t k2_setup(int* occ)
+{
+    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem<S>));
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON>, K2T + 32, sizeof(K2Smem<S>));
+}
+template <int S>
+cudaError_t k2_setup_s(bool wide, bool canon, int* occ)
+{
+    return wide ? (canon ? k2_setup<S, true, true>(occ) : k2_setup<S, true, false>(occ))
+                : (canon ? k2_setup<S, false, true>(occ) : k2_setup<S, false, false>(occ));
+}
+template <int S>
+void k2_launch_s(bool wide, bool canon, const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
+{
+    if (wide) {
+        if (canon) kmer2_kernel<S, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<S, true, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    } else {
+        if (canon) kmer2_kernel<S, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<S, false, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    }
+}
+// large tiles once every CTA of the persistent grid gets five of them (tickets balance the rest)
+bool k2_large(long long nwin, int sm_count) { return nwin >= 5LL * sm_count * K2Geo<K2S_LARGE>::TILE; }
+}  // namespace
+
 cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 {
-    args.nwords = K2NW;
     const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
-    args.num_tiles = (nwin + K2TILE - 1) / K2TILE;
+    const bool large = k2_large(nwin, sm_count);
+    const int tile = large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE;
+    args.nwords = large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW;
+    args.steps = large ? K2S_LARGE : K2S_SMALL;
+    args.num_tiles = (nwin + tile - 1) / tile;
     plan->threads = K2T + 32;
-    plan->smem_bytes = 0;
+    plan->smem_bytes = large ? sizeof(K2Smem<K2S_LARGE>) : sizeof(K2Smem<K2S_SMALL>);
     int occ = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kmer2_kernel<false, true>, K2T + 32, 0);
+    const bool canon = args.canonical != 0, wide = args.k > 32;
+    cudaError_t e = large ? k2_setup_s<K2S_LARGE>(wide, canon, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, &occ);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     long long grid = (long long)sm_count * occ;
@@ -360,14 +406,9 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 
 cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
-    const bool canon = args.canonical != 0;
-    if (args.k > 32) {
-        if (canon) kmer2_kernel<true, true><<<plan.grid, plan.threads, 0, stream>>>(args);
-        else kmer2_kernel<true, false><<<plan.grid, plan.threads, 0, stream>>>(args);
-    } else {
-        if (canon) kmer2_kernel<false, true><<<plan.grid, plan.threads, 0, stream>>>(args);
-        else kmer2_kernel<false, false><<<plan.grid, plan.threads, 0, stream>>>(args);
-    }
+    const bool canon = args.canonical != 0, wide = args.k > 32;
+    if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, args, plan, stream);
+    else k2_launch_s<K2S_SMALL>(wide, canon, args, plan, stream);
     return cudaGetLastError();
 }
 
