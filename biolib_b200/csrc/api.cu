@@ -40,6 +40,7 @@ struct blg_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;   // upload / download streams of the pipelined host path
     cudaEvent_t ev_in[16] = {};
+    int pipe_first_div = 4;      // first pipeline piece = a regular piece / this (BLG_PIPE_FIRST_DIV; development only)
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi (BLG_PIPE_CHUNK_M overrides; development only)
     int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
@@ -286,8 +287,9 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     unsigned char* d_in = static_cast<unsigned char*>(c->in.p);
     uint64_t cut[PIPE_MAX + 1];
     size_t up[PIPE_MAX + 1];       // bases uploaded once piece i is in
-    for (int i = 0; i <= nch; ++i) cut[i] = i == nch ? hi : (lo + nwin * (uint64_t)i / nch) / 16 * 16;
-    cut[0] = lo;
+    // the first piece is a fraction of the others: the record download (the longest of the three streams) starts sooner
+    const uint64_t first = nwin / nch / (uint64_t)c->pipe_first_div;
+    for (int i = 0; i <= nch; ++i) cut[i] = i == nch ? hi : i == 0 ? lo : (lo + first + (nwin - first) * (uint64_t)(i - 1) / (nch - 1)) / 16 * 16;
     size_t sent = 0;
     for (int i = 0; i < nch; ++i) {
         size_t end = i == nch - 1 ? n : (size_t)cut[i + 1] + halo;
@@ -547,6 +549,7 @@ int blg_create(int device, blg_ctx** out)
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
+    { const char* e = getenv("BLG_PIPE_FIRST_DIV"); if (e && atoi(e) > 0) c->pipe_first_div = atoi(e); }
     { const char* e = getenv("BLG_PIPE_CHUNK_M"); if (e && atoi(e) > 0) c->pipe_chunk_m = atoi(e); }
     { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BLG_KMER"); c->kmer_gen = (e && e[0] == '1') ? 1 : 0; }
