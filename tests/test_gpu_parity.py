@@ -114,6 +114,27 @@ def test_multi_sequence(gpu, oracle, k, m):
     check_sk(gpu, oracle, s, k, m, 42, True, offsets=offsets)
 
 
+def test_mutated_long_reads_config5_shape(gpu, oracle):
+    """configs[4] in small: reads drawn by the reference generator, passed through the reference's sequence_mutator
+    (restated in the oracle and pinned to the reference: substitutions, insertions, deletions; absent values dropped as
+    tests/test_random_sequence_generation.cpp:44-48 does), k=21 m=11, one call over all reads."""
+    rng = np.random.default_rng(55)
+    reads = []
+    for i in range(40):
+        src = oracle.generate(1000 + i, int(rng.integers(2_000, 12_000)))
+        out, _, _ = oracle.mutate(src, 0.1, 0.3, 0.2, 2000 + i)
+        reads.append(np.asarray(out, dtype=np.uint8))
+    offsets = np.concatenate([[0], np.cumsum([len(r) for r in reads])]).astype(np.uint64)
+    s = np.concatenate(reads)
+    assert len(s) > 100_000
+    for canon in (False, True):
+        check_sk(gpu, oracle, s, 21, 11, 42, canon, offsets=offsets)
+    g = gpu.kmers(s, 21, True, offsets=offsets)
+    o = oracle.kmers(s, 21, True, offsets=offsets)
+    for key in ("lo", "pos"):
+        assert np.array_equal(g[key], o[key])
+
+
 def test_minimizers_entry_point(gpu, oracle):
     rng = np.random.default_rng(3)
     s = rand_seq(rng, 100000, p_n=0.001)
