@@ -253,6 +253,14 @@ def test_hash64(gpu, oracle):
     rng = np.random.default_rng(0)
     v = rng.integers(0, 2**63, size=10000, dtype=np.uint64)
     assert gpu.hash64(v, 7).tolist() == [oracle.hash64(int(x), 7) for x in v]
+    # ragged sizes around the vector width and the unrolled stride of the kernel (two values per access, four accesses)
+    big = rng.integers(0, 2**63, size=2_500_003, dtype=np.uint64)
+    ref = gpu.hash64(big, 9)
+    idx = rng.integers(0, big.size, 2000)
+    assert [int(ref[i]) for i in idx] == [oracle.hash64(int(big[i]), 9) for i in idx]
+    assert int(ref[-1]) == oracle.hash64(int(big[-1]), 9)
+    for n in (0, 1, 2, 3, 7, 8, 9, 1001):
+        assert gpu.hash64(big[:n], 9).tolist() == ref[:n].tolist()
 
 
 @pytest.mark.parametrize("k", [1, 3, 15, 31, 32, 33, 47, 63, 64])
