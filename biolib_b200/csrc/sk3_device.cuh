@@ -260,6 +260,10 @@ __device__ __forceinline__ u32 compute_tile3(const SkArgs& a, unsigned char* wsm
                 for (int x = 2; x < q; ++x) { const uint4 f = P[(B - 1) * 32 + t + x]; take_if_less(shi, slo, six, f.x, f.y, f.z); }
             }
             const uint4 bq = P[(B - 1) * 32 + t + (q >= 1 ? q : 0)];
+            // prefix entries: row (i + r) mod B of block t + q (+1 after the wrap): two base pointers, the row offset
+            // i * 32 is then an immediate
+            const uint4* pa = P + r * 32 + t + q;
+            const uint4* pb = pa - B * 32 + 1;
 #pragma unroll
             for (int i = B - 1; i >= 0; --i) {
                 if (i == B - 1 && q < 2) { shi = hh[i]; slo = hl[i]; six = (u32)(B * t + i); }
@@ -267,7 +271,7 @@ __device__ __forceinline__ u32 compute_tile3(const SkArgs& a, unsigned char* wsm
                 const bool wrap = i + r >= B;
                 u32 chi = shi, clo = slo, cix = six;
                 if (wrap && q >= 1) take_if_less(chi, clo, cix, bq.x, bq.y, bq.z);
-                const uint4 e = P[(wrap ? i + r - B : i + r) * 32 + t + q + (wrap ? 1 : 0)];
+                const uint4 e = (wrap ? pb : pa)[i * 32];
                 const u64 sv = ((u64)chi << 32) | clo, ev = ((u64)e.x << 32) | e.y;
                 vix[i] = ev < sv ? e.z : cix;
             }
