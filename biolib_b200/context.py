@@ -70,13 +70,18 @@ class Context:
         return n.value, buf.value.decode()
 
     # ------------------------------------------------------------------ host in, host out
-    def kmers(self, seq, k: int, canonical: bool = False, offsets=None) -> dict:
+    def kmers(self, seq, k: int, canonical: bool = False, offsets=None, syncmer=None) -> dict:
+        """Valid k-mers in position order; syncmer=(m, start_offset, end_offset) keeps only those that
+        sampler::syncmer_sampler over hash::minimizer_position_extractor(k, m) would (blg_syncmers)."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=0, canonical=int(canonical), flags=0, seed=0)
+        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=0, seed=0)
         out = KmerOut()
-        self._check(self.L.blg_kmers(self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None,
-                                     0 if o is None else len(o) - 1, C.byref(p), C.byref(out)))
+        args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1, C.byref(p))
+        if syncmer is None:
+            self._check(self.L.blg_kmers(*args, C.byref(out)))
+        else:
+            self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         n = out.count
         try:
             res = dict(lo=_copy(out.value_lo, n, np.uint64), pos=_copy(out.position, n, np.uint64),
@@ -124,6 +129,10 @@ class Context:
         self._check(self.L.blg_hash64(self.h, v.ctypes.data, v.size, seed & (2**64 - 1), 0, out.ctypes.data))
         return out
 
+    def syncmers(self, seq, k: int, m: int, start_offset: int = 0, end_offset=None, canonical: bool = False, offsets=None) -> dict:
+        """sampler::syncmer_sampler (reference include/syncmer_sampler.hpp:130-137); closed syncmers by default."""
+        return self.kmers(seq, k, canonical, offsets, syncmer=(m, start_offset, k - m if end_offset is None else end_offset))
+
     def minimizer_positions(self, kmer_values, k: int, m: int) -> np.ndarray:
         """hash::minimizer_position_extractor for an array of k-mer values (k <= 32)."""
         v = np.ascontiguousarray(kmer_values, dtype=np.uint64)
@@ -169,11 +178,14 @@ class Context:
         self._check(self.L.blg_host_free(self.h, C.c_void_p(ptr)))
 
     def kmers_device(self, d_bases: int, n_bases: int, k: int, canonical: bool, d_lo: int, d_hi: int, d_pos: int,
-                     capacity: int, d_offsets: int = 0, n_seq: int = 0) -> int:
-        p = Params(k=k, m=0, canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT, seed=0)
+                     capacity: int, d_offsets: int = 0, n_seq: int = 0, syncmer=None) -> int:
+        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT, seed=0)
         out = KmerOut(count=0, capacity=capacity, value_lo=d_lo, value_hi=d_hi or None, position=d_pos or None, owner=None)
-        self._check(self.L.blg_kmers(self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq,
-                                     C.byref(p), C.byref(out)))
+        args = (self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq, C.byref(p))
+        if syncmer is None:
+            self._check(self.L.blg_kmers(*args, C.byref(out)))
+        else:
+            self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         return out.count
 
 

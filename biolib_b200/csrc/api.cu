@@ -171,7 +171,7 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
 {
     KmerLaunchPlan plan;
-    const bool gen2 = c->kmer_gen != 1;
+    const bool gen2 = c->kmer_gen != 1 || a.sync_on;            // the syncmer filter lives in the second-generation kernel only
     if (gen2) CK(c, kmer2_plan(a, c->sm_count, &plan));
     else CK(c, kmer_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
@@ -634,11 +634,14 @@ int blg_minimizers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs
     return sk_common(c, bases, n, offs, n_seq, 0, ~0ULL, p, out, false);
 }
 
-int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
-              blg_kmer_out* out)
+namespace {
+// sync_s < 0: every valid k-mer (blg_kmers); else the closed-syncmer filter with m-mers of p->m bases (blg_syncmers)
+int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                 int sync_s, int sync_e, blg_kmer_out* out)
 {
     if (!c || !p || !out) return BLG_E_INVALID;
     if (p->k == 0 || p->k > 64) { c->err = "need 1 <= k <= 64"; return BLG_E_INVALID; }
+    if (sync_s >= 0 && (p->k > 32 || p->m == 0 || p->m > p->k)) { c->err = "syncmers need 1 <= m <= k <= 32"; return BLG_E_INVALID; }
     const bool wide = p->k > 32;
     if (out->capacity > 0 && (!out->value_lo || (wide && !out->value_hi))) { c->err = "value arrays missing"; return BLG_E_INVALID; }
     Timer tm;
@@ -665,6 +668,7 @@ int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     a.win_lo = 0; a.win_hi = (long long)nwin;
     a.k = k; a.canonical = p->canonical ? 1 : 0;
     a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
+    if (sync_s >= 0) { a.sync_on = 1; a.sync_m = p->m; a.sync_s = sync_s; a.sync_e = sync_e; }
     uint64_t total = 0;
     if (dev_out && out->capacity > 0) {
         a.value_lo = reinterpret_cast<unsigned long long*>(out->value_lo);
@@ -727,6 +731,19 @@ int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     }
     c->stats.total_ms = tm.ms();
     return BLG_OK;
+}
+}  // namespace
+
+int blg_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+              blg_kmer_out* out)
+{
+    return kmers_common(c, bases, n, offs, n_seq, p, -1, -1, out);
+}
+
+int blg_syncmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                 uint16_t start_offset, uint16_t end_offset, blg_kmer_out* out)
+{
+    return kmers_common(c, bases, n, offs, n_seq, p, (int)start_offset, (int)end_offset, out);
 }
 
 int blg_hash64(blg_ctx* c, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out)

@@ -81,6 +81,9 @@ struct KmerArgs {
     int vec_ok;
     int nwords;
     int steps;                     // kmer2: tile size chosen by kmer2_plan
+    // closed-syncmer filter (sampler::syncmer_sampler over hash::minimizer_position_extractor): keep a k-mer iff the
+    // offset of its minimum-hash m-mer is sync_s or sync_e; k <= 32 only; sync_on = 0: every valid k-mer
+    int sync_on, sync_m, sync_s, sync_e;
     long long num_tiles;
     unsigned long long* value_lo;
     unsigned long long* value_hi;  // null for k <= 32

@@ -141,7 +141,7 @@ __device__ __forceinline__ void cut_kmer(const u32* le, const u32* be, int s, in
     }
 }
 
-template <int S, bool WIDE, bool CANON>
+template <int S, bool WIDE, bool CANON, bool SYNC>
 __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const KmerArgs a)
 {
     constexpr int K2S = S, K2TILE = K2Geo<S>::TILE, K2NW = K2Geo<S>::NW, K2WORDS = K2Geo<S>::WORDS, K2ROW = K2Geo<S>::ROW;
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
         const long long next_tile = have ? (long long)(unsigned)sm.next : a.num_tiles;
         const bool seqdirty = have && a.seq_offsets != nullptr && sm.seqdirty[b];
         // every start of the tile is a valid k-mer inside the window range: no masks, no counting
-        const bool all_valid = have && !dirty && !seqdirty && tile_lo + K2TILE <= a.win_hi;
+        const bool all_valid = !SYNC && have && !dirty && !seqdirty && tile_lo + K2TILE <= a.win_hi;
         if (have && !all_valid) {
             // ---- valid masks of every warp's steps (kept in shared memory for the output pass), and their count -------
             if (!is_scan) {
@@ -254,6 +254,36 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                     if (seqdirty) bad |= or_span32(cur.seq, lp + 1, k - 1);
                     mrange &= ~bad;
                     cur.bal[warp][lane] = mrange;
+                }
+                if (SYNC) {
+                    // closed syncmers (include/syncmer_sampler.hpp:130-137 over include/kmer_view.hpp:266-283): of the valid
+                    // k-mers keep those whose minimum-hash m-mer (hash64, seed 0, scanned from the right end with '>=', so
+                    // the leftmost wins) sits at offset sync_s or sync_e from the left
+                    const int lp0 = off0 + wp + lane;
+                    const int s = (lp0 & 15) * 2;
+                    const int e = 2 * lp0 + 2 * k + 32 * K2PAD - 32 * NV;
+                    const int fs = e & 31;
+                    const u32* le = cur.le + (lp0 >> 4);
+                    const u32* be = cur.be + (e >> 5);
+                    const u64 mmask = a.sync_m >= 32 ? ~0ULL : ((1ULL << (2 * a.sync_m)) - 1ULL);
+                    const int w = k - a.sync_m + 1;
+                    for (int j = 0; j < K2S; ++j) {
+                        const u32 mj = __shfl_sync(0xffffffffu, mrange, j);
+                        if (mj == 0) continue;
+                        u64 km, hi_;
+                        cut_kmer<WIDE, CANON>(le + 2 * j, be + 2 * j, s, fs, vm, km, hi_);
+                        u64 mval = ~0ULL;
+                        int minpos = 0;
+                        for (int i = 0; i < w; ++i) {
+                            const u64 val = murmur3_key8(km & mmask, 8ULL);     // seed 0: s8 = 0 ^ 8
+                            if (mval >= val) { mval = val; minpos = i; }
+                            km >>= 2;
+                        }
+                        const int off = k - a.sync_m - minpos;
+                        const u32 keep = __ballot_sync(0xffffffffu, off == a.sync_s || off == a.sync_e);
+                        if (lane == j) mrange = mj & keep;
+                    }
+                    if (lane < K2S) cur.bal[warp][lane] = mrange;
                 }
                 u32 cnt = __popc(mrange);
 #pragma unroll
@@ -355,28 +385,32 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
 }
 
 namespace {
-template <int S, bool WIDE, bool CANON>
+template <int S, bool WIDE, bool CANON, bool SYNC>
 cudaError_t k2_setup(int* occ)
 {
-    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem<S>));
+    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem<S>));
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON>, K2T + 32, sizeof(K2Smem<S>));
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, sizeof(K2Smem<S>));
 }
 template <int S>
-cudaError_t k2_setup_s(bool wide, bool canon, int* occ)
+cudaError_t k2_setup_s(bool wide, bool canon, bool sync, int* occ)
 {
-    return wide ? (canon ? k2_setup<S, true, true>(occ) : k2_setup<S, true, false>(occ))
-                : (canon ? k2_setup<S, false, true>(occ) : k2_setup<S, false, false>(occ));
+    if (sync) return canon ? k2_setup<S, false, true, true>(occ) : k2_setup<S, false, false, true>(occ);   // k <= 32 only
+    return wide ? (canon ? k2_setup<S, true, true, false>(occ) : k2_setup<S, true, false, false>(occ))
+                : (canon ? k2_setup<S, false, true, false>(occ) : k2_setup<S, false, false, false>(occ));
 }
 template <int S>
-void k2_launch_s(bool wide, bool canon, const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
+void k2_launch_s(bool wide, bool canon, bool sync, const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
-    if (wide) {
-        if (canon) kmer2_kernel<S, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
-        else kmer2_kernel<S, true, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    if (sync) {
+        if (canon) kmer2_kernel<S, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<S, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    } else if (wide) {
+        if (canon) kmer2_kernel<S, true, true, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<S, true, false, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
     } else {
-        if (canon) kmer2_kernel<S, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
-        else kmer2_kernel<S, false, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        if (canon) kmer2_kernel<S, false, true, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<S, false, false, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
     }
 }
 // large tiles once every CTA of the persistent grid gets five of them (tickets balance the rest)
@@ -386,7 +420,9 @@ bool k2_large(long long nwin, int sm_count) { return nwin >= 5LL * sm_count * K2
 cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 {
     const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
-    const bool large = k2_large(nwin, sm_count);
+    if (args.sync_on && (args.k > 32 || args.sync_m < 1 || args.sync_m > args.k)) return cudaErrorInvalidValue;
+    // the syncmer predicate is w hashes per k-mer: small tiles keep the look-back chain short
+    const bool large = !args.sync_on && k2_large(nwin, sm_count);
     const int tile = large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE;
     args.nwords = large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW;
     args.steps = large ? K2S_LARGE : K2S_SMALL;
@@ -395,7 +431,8 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
     plan->smem_bytes = large ? sizeof(K2Smem<K2S_LARGE>) : sizeof(K2Smem<K2S_SMALL>);
     int occ = 0;
     const bool canon = args.canonical != 0, wide = args.k > 32;
-    cudaError_t e = large ? k2_setup_s<K2S_LARGE>(wide, canon, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, &occ);
+    const bool sync = args.sync_on != 0;
+    cudaError_t e = large ? k2_setup_s<K2S_LARGE>(wide, canon, sync, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, sync, &occ);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     long long grid = (long long)sm_count * occ;
@@ -407,8 +444,9 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
     const bool canon = args.canonical != 0, wide = args.k > 32;
-    if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, args, plan, stream);
-    else k2_launch_s<K2S_SMALL>(wide, canon, args, plan, stream);
+    const bool sync = args.sync_on != 0;
+    if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, sync, args, plan, stream);
+    else k2_launch_s<K2S_SMALL>(wide, canon, sync, args, plan, stream);
     return cudaGetLastError();
 }
 

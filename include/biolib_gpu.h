@@ -163,6 +163,18 @@ int blg_hash64(blg_ctx* ctx, const uint64_t* values, size_t n, uint64_t seed, ui
 int blg_minimizer_positions(blg_ctx* ctx, const uint64_t* kmer_values, size_t n, uint8_t k, uint8_t m, uint32_t flags,
                             uint8_t* out_positions);
 
+/*
+ * sampler::syncmer_sampler<kmer_view::const_iterator, hash::minimizer_position_extractor>
+ * (include/syncmer_sampler.hpp:130-137 over include/kmer_view.hpp:266-283), fused into the k-mer kernel: the entries
+ * blg_kmers would return, restricted to the k-mers whose minimizer_position_extractor(k, p->m) offset equals
+ * start_offset or end_offset (closed syncmers: 0 and k - m). The offset is that of the minimum hash64(seed 0) among the
+ * plain m-mer bit fields of the (canonical, if p->canonical) k-mer VALUE, leftmost on ties - not of the minimizer_view
+ * m-mers. 1 <= p->m <= p->k <= 32; p->seed is unused. The reference's record stream drops the last k-mer of a sequence
+ * that ends in a valid base and its nullopt records never pass the filter: the shim applies K1 as for blg_kmers.
+ */
+int blg_syncmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                 const blg_params* p, uint16_t start_offset, uint16_t end_offset, blg_kmer_out* out);
+
 /* release library-allocated output arrays (host pinned or device); caller-provided arrays are untouched */
 void blg_free_kmer_out(blg_ctx* ctx, blg_kmer_out* out);
 void blg_free_sk_out(blg_ctx* ctx, blg_sk_out* out);

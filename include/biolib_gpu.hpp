@@ -37,6 +37,7 @@
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <utility>
 #include <vector>
 
 #include "biolib_gpu.h"
@@ -270,6 +271,47 @@ class minimizer_position_extractor
         }
     private:
         uint8_t klen, mlen;
+};
+
+// ------------------------------------------------------------------------------------------------ syncmer_sampler
+// sampler::syncmer_sampler<kmer_view::const_iterator, hash::minimizer_position_extractor> (reference
+// include/syncmer_sampler.hpp:9-66, selection rule :130-137), with the filter fused into the k-mer kernel (blg_syncmers):
+// iterates the k-mers of [start, stop) whose extractor offset is start_offset or end_offset. The reference's sampler
+// template also works unchanged over gpu::kmer_view iterators with gpu::minimizer_position_extractor (one device round
+// trip per k-mer); this class is the batched form. Records are kmer_context_t with the k-mer's value and position;
+// `id` here is the ordinal among the SAMPLED k-mers (the reference's is the kmer_view ordinal, which needs the unsampled
+// stream). The final k-mer of an input that ends in a valid base is dropped, as the reference's iteration does.
+template <class Iterator>
+class syncmer_sampler
+{
+    public:
+        using value_type = kmer_context_t<uint64_t>;
+        using const_iterator = typename std::vector<value_type>::const_iterator;
+        syncmer_sampler(Iterator start, Iterator stop, minimizer_position_extractor const& extractor, uint16_t start_offset,
+                        uint16_t end_offset, bool canonical = false)
+            : soffset(start_offset), eoffset(end_offset)
+        {
+            const std::size_t n = detail::range_length(start, stop);
+            char const* s = detail::contiguous_begin(start, n);
+            context& c = context::thread_default();
+            blg_params p{};
+            p.k = extractor.get_k(); p.m = extractor.get_m(); p.canonical = canonical ? 1 : 0;
+            blg_kmer_out o{};
+            c.check(blg_syncmers(c.get(), s, n, nullptr, 0, &p, start_offset, end_offset, &o), "blg_syncmers");
+            detail::out_guard<blg_kmer_out, void (*)(blg_ctx*, blg_kmer_out*)> g{c, o, blg_free_kmer_out};
+            uint64_t cnt = o.count;
+            if (cnt > 0 && o.position[cnt - 1] + p.k == n) --cnt;                                       // K1
+            records.reserve(cnt);
+            for (uint64_t i = 0; i < cnt; ++i) records.push_back(value_type{o.value_lo[i], static_cast<std::size_t>(o.position[i]), static_cast<std::size_t>(i)});
+        }
+        const_iterator cbegin() const { return records.cbegin(); }
+        const_iterator cend() const { return records.cend(); }
+        const_iterator begin() const { return cbegin(); }
+        const_iterator end() const { return cend(); }
+        std::pair<uint16_t, uint16_t> get_offsets() const { return std::make_pair(soffset, eoffset); }
+    private:
+        uint16_t soffset, eoffset;
+        std::vector<value_type> records;
 };
 
 // ------------------------------------------------------------------------------------------------ minimizer_view

@@ -118,6 +118,23 @@ class Oracle:
         n = self.lib.orc_kmers(b, len(b), o.ctypes.data if o is not None else None, ns, k, int(canonical), lo.ctypes.data, hi.ctypes.data, pos.ctypes.data, cap)
         return dict(lo=lo[:n], hi=hi[:n], pos=pos[:n])
 
+    def syncmers(self, seq, k, m, soff, eoff, canonical, offsets=None):
+        """sampler::syncmer_sampler::const_iterator::find_first_syncmer (reference include/syncmer_sampler.hpp:130-137)
+        in the batched form blg_syncmers returns: the valid k-mers whose minimizer_position_extractor(k, m) offset
+        (include/kmer_view.hpp:266-283) is soff or eoff, in position order."""
+        km = self.kmers(seq, k, canonical, offsets)
+        p = self.minimizer_positions(km["lo"], k, m)
+        keep = (p == soff) | (p == eoff)
+        return {key: v[keep] for key, v in km.items()}
+
+    def syncmer_stream(self, seq, k, m, soff, eoff, canonical):
+        """The reference's record stream for one sequence: syncmer_sampler over kmer_view (K1-K4 apply: the final k-mer
+        of a sequence ending in a valid base never appears; nullopt records have offset k + 1 and never pass)."""
+        ks = self.kmer_stream(seq, k, canonical)
+        p = self.minimizer_positions(ks["lo"], k, m)
+        keep = (ks["has"] == 1) & ((p == soff) | (p == eoff))
+        return dict(lo=ks["lo"][keep], pos=ks["pos"][keep], id=ks["id"][keep])
+
     def mmers(self, seq, m, seed, canonical, offsets=None):
         b = _buf(seq)
         o, ns = _offs(offsets)
@@ -224,6 +241,16 @@ class Ref:
         self.lib.ref_minimizer_positions.restype = None
         self.lib.ref_minimizer_positions(v.ctypes.data, None if hv is None else hv.ctypes.data, v.size, k, m, out.ctypes.data)
         return out
+
+    def syncmer_stream(self, seq, k, m, soff, eoff, canonical):
+        b = _buf(seq)
+        cap = len(b) + 1
+        lo = np.zeros(cap, np.uint64); pos = np.zeros(cap, np.uint64); idv = np.zeros(cap, np.uint64)
+        self.lib.ref_syncmers_u64.restype = C.c_size_t
+        self.lib.ref_syncmers_u64.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_int,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        n = self.lib.ref_syncmers_u64(bytes(b), len(b), k, m, soff, eoff, int(canonical), lo.ctypes.data, pos.ctypes.data, idv.ctypes.data, cap)
+        return dict(lo=lo[:n], pos=pos[:n], id=idv[:n])
 
     def kmer_stream(self, seq, k, canonical, bits=64):
         b = _buf(seq)

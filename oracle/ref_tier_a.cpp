@@ -7,6 +7,7 @@
 // recipe is oracle/Makefile, outputs go to oracle/_ref/ only) and exposes a C ABI over
 //   * wrapper::kmer_view iteration                      (include/kmer_view.hpp:155-234)
 //   * wrapper::minimizer_view::const_iterator::read_base (include/minimizer_view.hpp:229-245)
+//   * sampler::syncmer_sampler over hash::minimizer_position_extractor (include/syncmer_sampler.hpp:130-137)
 //   * hash::hash64 / hash::double_hash64                (include/hash.hpp:11-71)
 //   * sequence::generator, wrapper::sequence_mutator    (include/sequence_generator.hpp:14-43,
 //                                                        include/sequence_mutator.hpp:109-169)
@@ -44,6 +45,7 @@
 #include "hash.hpp"
 #include "kmer_view.hpp"
 #include "minimizer_view.hpp"
+#include "syncmer_sampler.hpp"
 #undef private
 #include "sequence_generator.hpp"
 #include "sequence_mutator.hpp"
@@ -168,6 +170,35 @@ size_t ref_kmer_view_u64(const char* s, size_t n, unsigned k, int canonical,
                          uint64_t* value, uint8_t* has_value, uint64_t* position, uint64_t* id, size_t cap)
 {
     return run_kmer_view<uint64_t>(s, n, k, canonical, value, has_value, position, id, cap);
+}
+
+// sampler::syncmer_sampler<kmer_view<uint64_t>::const_iterator, hash::minimizer_position_extractor> driven over the
+// reference's kmer_view (same guards as run_kmer_view). operator* of the sampler does not instantiate for this pair
+// (kmer_context_t does not convert to value_type), so the current record is read through the (opened) itr_start member.
+size_t ref_syncmers_u64(const char* s, size_t n, unsigned k, unsigned m, unsigned soff, unsigned eoff, int canonical,
+                        uint64_t* value, uint64_t* position, uint64_t* id, size_t cap)
+{
+    std::string safe;
+    if (k == 0 || !kmer_view_safe_input(s, n, k, safe)) return 0;
+    auto view = wrapper::kmer_view_from_cstr<uint64_t>(safe.data(), safe.size(), static_cast<uint8_t>(k), canonical != 0);
+    using it_t = decltype(view)::const_iterator;
+    alignas(it_t) unsigned char storage[sizeof(it_t)];
+    std::memset(storage, 0, sizeof(storage));               // K5
+    it_t* first = new (storage) it_t(&view);
+    hash::minimizer_position_extractor ex(static_cast<uint8_t>(k), static_cast<uint8_t>(m));
+    sampler::syncmer_sampler<it_t, hash::minimizer_position_extractor> smp(*first, view.cend(), ex, static_cast<uint16_t>(soff), static_cast<uint16_t>(eoff));
+    size_t cnt = 0;
+    for (auto it = smp.cbegin(); it != smp.cend(); ++it) {
+        auto rec = *it.itr_start;
+        if (cnt < cap) {
+            value[cnt] = rec.value ? *rec.value : 0;
+            position[cnt] = rec.position;
+            id[cnt] = rec.id;
+        }
+        ++cnt;
+    }
+    first->~it_t();
+    return cnt;
 }
 
 // 128-bit variant: values returned as (lo, hi) pairs. Canonical output for k > 32 is the

@@ -174,3 +174,27 @@ def minpos(ref, path):
     nullopt = int(ref.minimizer_positions(np.array([5], np.uint64), 7, 4, has_value=np.array([0], np.uint8))[0])
     json.dump(dict(source="hash::minimizer_position_extractor executed verbatim (oracle/_ref)", nullopt_k7_m4=nullopt, cases=cases),
               open(path, "w"))
+
+
+def syncmers(ref, path):
+    """tests/golden/syncmers.json: sampler::syncmer_sampler<kmer_view::const_iterator, hash::minimizer_position_extractor>
+    (reference include/syncmer_sampler.hpp:130-137) executed verbatim over the reference's kmer_view.
+    Run: python -c "import sys; sys.path.insert(0,'oracle'); import pyoracle, runpy; ..."  or call from here."""
+    import json
+    import numpy as np
+    rng = np.random.default_rng(20261105)
+    cases = []
+    for k, m, n, pn in [(31, 19, 600, 0.0), (21, 11, 500, 0.01), (15, 10, 400, 0.02), (7, 4, 200, 0.05), (32, 16, 500, 0.0), (5, 5, 60, 0.0),
+                        (9, 2, 300, 0.0)]:
+        seq = rand_seq(rng, n, p_n=pn, lower=0.05)
+        for canon in (0, 1):
+            for soff, eoff in ((0, k - m), (1, 1)):
+                r = ref.syncmer_stream(seq, k, m, soff, eoff, canon)
+                cases.append(dict(seq=seq, k=k, m=m, soff=soff, eoff=eoff, canonical=canon, value=[int(x) for x in r["lo"]],
+                                  position=[int(x) for x in r["pos"]], id=[int(x) for x in r["id"]]))
+    json.dump(dict(provenance="reference sampler::syncmer_sampler over wrapper::kmer_view executed verbatim (oracle/ref_tier_a.cpp "
+                              "ref_syncmers_u64)", cases=cases), open(path, "w"), separators=(",", ":"))
+
+
+minpos(ref, os.path.join(HERE, "minpos.json"))
+syncmers(ref, os.path.join(HERE, "syncmers.json"))

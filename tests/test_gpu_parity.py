@@ -276,6 +276,54 @@ def test_kmers(gpu, oracle, k, canon):
             assert np.array_equal(g[key], o[key]), (key, k, n, pn)
 
 
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (32, 32), (32, 1), (9, 5), (3, 1), (15, 10), (32, 16)])
+@pytest.mark.parametrize("canon", [False, True])
+def test_syncmers(gpu, oracle, k, m, canon):
+    """blg_syncmers vs sampler::syncmer_sampler over minimizer_position_extractor (reference include/syncmer_sampler.hpp:130-137,
+    include/kmer_view.hpp:266-283; the restatement is pinned by tests/golden/syncmers.json)."""
+    rng = np.random.default_rng(1000 * k + m)
+    for n, pn in ((0, 0), (k - 1, 0), (k, 0), (k + 1, 0), (5000, 0.0), (70000, 0.01), (5000, 0.2), (300000, 0.0005)):
+        s = rand_seq(rng, n, p_n=pn, lower=0.05)
+        if n >= 5000:
+            s[1000:1400] = ord("A")                     # equal m-mers: ties go to the leftmost
+        for soff, eoff in ((0, k - m), (1 % (k - m + 1), 1 % (k - m + 1))):
+            g = gpu.syncmers(s, k, m, soff, eoff, canon)
+            o = oracle.syncmers(s, k, m, soff, eoff, canon)
+            assert len(g["lo"]) == len(o["lo"]), (k, m, n, pn, soff)
+            for key in ("lo", "pos"):
+                assert np.array_equal(g[key], o[key]), (key, k, m, n, pn, soff)
+
+
+def test_syncmers_multi_sequence_and_errors(gpu, oracle):
+    rng = np.random.default_rng(88)
+    lens = rng.integers(0, 300, size=400)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    s = rand_seq(rng, int(offsets[-1]), p_n=0.005)
+    for k, m in ((31, 19), (21, 11)):
+        g = gpu.syncmers(s, k, m, canonical=True, offsets=offsets)
+        o = oracle.syncmers(s, k, m, 0, k - m, True, offsets=offsets)
+        for key in ("lo", "pos"):
+            assert np.array_equal(g[key], o[key]), (key, k)
+    for k, m in ((33, 19), (31, 0), (19, 31)):
+        with pytest.raises(Exception):
+            gpu.syncmers("ACGT" * 100, k, m)
+    # an offset no m-mer can have: nothing passes (as the reference's loop would run to the end)
+    assert len(gpu.syncmers("ACGT" * 100, 11, 5, 9, 9)["lo"]) == 0
+
+
+def test_syncmers_large_cross_check(gpu):
+    """20 Mbp: the fused filter equals blg_kmers filtered by the separate blg_minimizer_positions kernel."""
+    rng = np.random.default_rng(99)
+    s = rand_seq(rng, 20_000_000, p_n=0.0001)
+    k, m = 31, 19
+    g = gpu.syncmers(s, k, m, canonical=True)
+    km = gpu.kmers(s, k, True)
+    p = gpu.minimizer_positions(km["lo"], k, m)
+    keep = (p == 0) | (p == k - m)
+    assert np.array_equal(g["lo"], km["lo"][keep]) and np.array_equal(g["pos"], km["pos"][keep])
+    assert 0.1 < len(g["lo"]) / len(km["lo"]) < 0.2         # closed syncmers: about 2 / (k - m + 1)
+
+
 def test_kmers_multi_sequence(gpu, oracle):
     rng = np.random.default_rng(8)
     lens = rng.integers(0, 300, size=200)
@@ -409,6 +457,12 @@ int main(int argc, char** argv) {
         if (ex(none) != (std::size_t)k + 1 || ex.get_k() != k || ex.get_m() != m) return 5;
         if (!vals.empty()) { biolib::gpu::kmer_context_t<uint64_t> one{vals[0], 0, 0}; if (ex(one) != pos[0]) return 6; }
     }
+    if (k <= 32) {
+        biolib::gpu::minimizer_position_extractor ex(k, m);
+        biolib::gpu::syncmer_sampler<std::string::const_iterator> sy(s.cbegin(), s.cend(), ex, 0, k - m, canon);
+        if (sy.get_offsets() != std::make_pair<uint16_t, uint16_t>(0, k - m)) return 7;
+        for (auto const& r : sy) std::printf("Y %llu %zu\n", (unsigned long long)*r.value, r.position);
+    }
     try { biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> bad(s, 3, 4); bad.cbegin(); return 4; }
     catch (std::invalid_argument const&) {}
     return 0;
@@ -447,6 +501,9 @@ def test_cpp_shim_views(gpu, oracle, tmp_path):
             want_m = list(zip(o["value"].tolist(), (o["mm_start"] + 1).tolist(), ids))       # D7: position = start + 1
             assert M == want_m, (seq[:20], k, m, canon)
             assert S == [a + (int(p), int(z)) for a, p, z in zip(want_m, (o["mm_start"] - o["sk_start"]).tolist(), o["size"].tolist())]
+            Y = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("Y ")]
+            sy = oracle.syncmer_stream(seq, k, m, 0, k - m, canon)
+            assert Y == list(zip(sy["lo"].tolist(), sy["pos"].tolist())), (seq[:20], k, m, canon)
             X = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("X ")]
             xv = np.array([v for v, _ in X], dtype=np.uint64)
             assert [p for _, p in X] == oracle.minimizer_positions(xv, k, m).tolist() if len(X) else True

@@ -149,3 +149,22 @@ def test_minimizer_position_extractor_golden(oracle):
     for c in g["cases"]:
         got = oracle.minimizer_positions(np.array(c["values"], dtype=np.uint64), c["k"], c["m"])
         assert [int(x) for x in got] == c["positions"], (c["k"], c["m"])
+
+
+def test_syncmer_sampler_golden(oracle):
+    """sampler::syncmer_sampler over kmer_view (reference include/syncmer_sampler.hpp:130-137) against reference-executed
+    record streams (values, positions, ids; K1-K4 included), and the batched form blg_syncmers returns against them."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "syncmers.json")))
+    assert len(g["cases"]) >= 20
+    for c in g["cases"]:
+        o = oracle.syncmer_stream(c["seq"], c["k"], c["m"], c["soff"], c["eoff"], c["canonical"])
+        assert o["lo"].tolist() == c["value"] and o["pos"].tolist() == c["position"] and o["id"].tolist() == c["id"], (c["k"], c["m"])
+        # the batched form holds the same records plus, at most, the final k-mer the reference's iteration drops (K1)
+        b = oracle.syncmers(c["seq"], c["k"], c["m"], c["soff"], c["eoff"], c["canonical"])
+        n = len(c["value"])
+        assert b["lo"][:n].tolist() == c["value"] and b["pos"][:n].tolist() == c["position"]
+        assert len(b["lo"]) - n in (0, 1)
+        if len(b["lo"]) > n:
+            assert int(b["pos"][-1]) == len(c["seq"]) - c["k"]

@@ -145,3 +145,20 @@ def test_minimizer_position_extractor_live(oracle, ref):
             v &= np.uint64((1 << (2 * k)) - 1)
         v[:200] &= np.uint64(0xFF)                      # low-complexity values: hash ties between equal m-mers
         assert np.array_equal(oracle.minimizer_positions(v, k, m), ref.minimizer_positions(v, k, m)), (k, m)
+
+
+def test_syncmer_sampler_live(oracle, ref):
+    """The restated syncmer stream vs sampler::syncmer_sampler executed verbatim over the reference's kmer_view."""
+    rng = np.random.default_rng(31)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    for k, m in [(31, 19), (21, 11), (32, 32), (32, 1), (9, 5), (3, 1)]:
+        for pn in (0.0, 0.01):
+            s = rng.choice(acgt, size=20000).copy()
+            s[rng.random(s.size) < pn] = ord("N")
+            s[5000:5400] = ord("A")                     # low complexity: equal m-mers, ties resolved to the leftmost
+            for canon in (0, 1):
+                for soff, eoff in ((0, k - m), (2 % (k - m + 1), 2 % (k - m + 1))):
+                    a = oracle.syncmer_stream(s, k, m, soff, eoff, canon)
+                    b = ref.syncmer_stream(s, k, m, soff, eoff, canon)
+                    for key in ("lo", "pos", "id"):
+                        assert np.array_equal(a[key], b[key]), (key, k, m, pn, canon, soff)
