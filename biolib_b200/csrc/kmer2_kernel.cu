@@ -141,6 +141,33 @@ __device__ __forceinline__ void cut_kmer(const u32* le, const u32* be, int s, in
     }
 }
 
+// Forward and reverse-complement value of the `len` (<= 32) bases at tile-local base index lp (mm = masks of 2 len bits).
+__device__ __forceinline__ void cut_both(const u32* le_row, const u32* be_row, int lp, int len, const u32* mm, u64& f, u64& r)
+{
+    const int s = (lp & 15) * 2;
+    const int e = 2 * lp + 2 * len + 32 * K2PAD - 64;             // the 64 bits that end with the last base
+    const int fs = e & 31;
+    const u32* le = le_row + (lp >> 4);
+    const u32* be = be_row + (e >> 5);
+    const u32 c0 = le[0], c1 = le[1], c2 = le[2], d0 = be[0], d1 = be[1], d2 = be[2];
+    r = ((u64)(__funnelshift_r(c1, c2, s) & mm[1]) << 32) | (__funnelshift_r(c0, c1, s) & mm[0]);
+    f = ((u64)(__funnelshift_l(d1, d0, fs) & mm[1]) << 32) | (__funnelshift_l(d2, d1, fs) & mm[0]);
+}
+
+// Syncmer filter only: per output warp, the hashes of its forward and reverse-complement m-mers (behind K2Smem).
+template <int S>
+struct K2SyncRow { static constexpr int N = 32 * S + 32; };
+template <int S>
+__device__ __forceinline__ u64* k2_sync_rows(unsigned char* raw)
+{
+    return reinterpret_cast<u64*>(raw + ((sizeof(K2Smem<S>) + 15) & ~(size_t)15));
+}
+template <int S>
+constexpr size_t k2_smem_bytes(bool sync)
+{
+    return ((sizeof(K2Smem<S>) + 15) & ~(size_t)15) + (sync ? (size_t)K2W * 2 * K2SyncRow<S>::N * 8 : 0);
+}
+
 template <int S, bool WIDE, bool CANON, bool SYNC>
 __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const KmerArgs a)
 {
@@ -257,31 +284,50 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                 }
                 if (SYNC) {
                     // closed syncmers (include/syncmer_sampler.hpp:130-137 over include/kmer_view.hpp:266-283): of the valid
-                    // k-mers keep those whose minimum-hash m-mer (hash64, seed 0, scanned from the right end with '>=', so
-                    // the leftmost wins) sits at offset sync_s or sync_e from the left
-                    const int lp0 = off0 + wp + lane;
-                    const int s = (lp0 & 15) * 2;
-                    const int e = 2 * lp0 + 2 * k + 32 * K2PAD - 32 * NV;
-                    const int fs = e & 31;
-                    const u32* le = cur.le + (lp0 >> 4);
-                    const u32* be = cur.be + (e >> 5);
-                    const u64 mmask = a.sync_m >= 32 ? ~0ULL : ((1ULL << (2 * a.sync_m)) - 1ULL);
-                    const int w = k - a.sync_m + 1;
-                    for (int j = 0; j < K2S; ++j) {
-                        const u32 mj = __shfl_sync(0xffffffffu, mrange, j);
-                        if (mj == 0) continue;
-                        u64 km, hi_;
-                        cut_kmer<WIDE, CANON>(le + 2 * j, be + 2 * j, s, fs, vm, km, hi_);
-                        u64 mval = ~0ULL;
-                        int minpos = 0;
-                        for (int i = 0; i < w; ++i) {
-                            const u64 val = murmur3_key8(km & mmask, 8ULL);     // seed 0: s8 = 0 ^ 8
-                            if (mval >= val) { mval = val; minpos = i; }
-                            km >>= 2;
+                    // k-mers keep those whose minimum-hash m-mer (hash64, seed 0; the extractor scans the bit fields of the
+                    // k-mer VALUE from the right with '>=', so the leftmost field wins) sits at offset sync_s or sync_e.
+                    // The reference hashes k-m+1 fields per k-mer; here every m-mer of the warp's span is hashed ONCE per
+                    // strand into shared memory and a k-mer takes the minimum of its window: the fields of a forward value
+                    // at start p are the forward m-mers at p .. p+w-1 (offset = position - p), those of a reverse-complement
+                    // value are the reverse-complement m-mers of the same positions in reverse order (offset = p+w-1 -
+                    // position, so its leftmost field is the LAST position and ties go to the larger position).
+                    const int m = a.sync_m, w = k - m + 1;
+                    u64* hf = k2_sync_rows<S>(k2_raw) + warp * (2 * K2SyncRow<S>::N);
+                    u64* hr = hf + K2SyncRow<S>::N;
+                    if (__ballot_sync(0xffffffffu, mrange != 0)) {
+                        u32 mm[2];
+                        mm[0] = 2 * m >= 32 ? 0xFFFFFFFFu : ((1u << (2 * m)) - 1u);
+                        mm[1] = 2 * m >= 64 ? 0xFFFFFFFFu : (2 * m > 32 ? ((1u << (2 * m - 32)) - 1u) : 0u);
+                        const int lpw = off0 + wp + lane;
+                        for (int j = 0; j <= K2S; ++j) {
+                            if (j == K2S && lane >= w - 1) break;
+                            u64 f, r;
+                            cut_both(cur.le, cur.be, lpw + 32 * j, m, mm, f, r);
+                            hf[32 * j + lane] = murmur3_key8(f, 8ULL);              // seed 0: s8 = 0 ^ 8
+                            if (CANON) hr[32 * j + lane] = murmur3_key8(r, 8ULL);
                         }
-                        const int off = k - a.sync_m - minpos;
-                        const u32 keep = __ballot_sync(0xffffffffu, off == a.sync_s || off == a.sync_e);
-                        if (lane == j) mrange = mj & keep;
+                        __syncwarp();
+                        for (int j = 0; j < K2S; ++j) {
+                            const u32 mj = __shfl_sync(0xffffffffu, mrange, j);
+                            if (mj == 0) continue;
+                            bool use_r = false;
+                            if (CANON) {
+                                u64 f, r;
+                                cut_both(cur.le, cur.be, lpw + 32 * j, k, vm, f, r);
+                                use_r = r < f;
+                            }
+                            const u64* h = (use_r ? hr : hf) + 32 * j + lane;
+                            u64 best = h[0];
+                            int pos = 0;
+                            for (int i = 1; i < w; ++i) {
+                                const u64 v = h[i];
+                                if (v < best || (use_r && v == best)) { best = v; pos = i; }
+                            }
+                            const int off = use_r ? w - 1 - pos : pos;
+                            const u32 keep = __ballot_sync(0xffffffffu, off == a.sync_s || off == a.sync_e);
+                            if (lane == j) mrange = mj & keep;
+                        }
+                        __syncwarp();
                     }
                     if (lane < K2S) cur.bal[warp][lane] = mrange;
                 }
@@ -388,9 +434,9 @@ namespace {
 template <int S, bool WIDE, bool CANON, bool SYNC>
 cudaError_t k2_setup(int* occ)
 {
-    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K2Smem<S>));
+    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem_bytes<S>(SYNC));
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, sizeof(K2Smem<S>));
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(SYNC));
 }
 template <int S>
 cudaError_t k2_setup_s(bool wide, bool canon, bool sync, int* occ)
@@ -428,7 +474,7 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
     args.steps = large ? K2S_LARGE : K2S_SMALL;
     args.num_tiles = (nwin + tile - 1) / tile;
     plan->threads = K2T + 32;
-    plan->smem_bytes = large ? sizeof(K2Smem<K2S_LARGE>) : sizeof(K2Smem<K2S_SMALL>);
+    plan->smem_bytes = large ? k2_smem_bytes<K2S_LARGE>(false) : k2_smem_bytes<K2S_SMALL>(args.sync_on != 0);
     int occ = 0;
     const bool canon = args.canonical != 0, wide = args.k > 32;
     const bool sync = args.sync_on != 0;
