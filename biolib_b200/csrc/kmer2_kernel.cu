@@ -32,6 +32,9 @@ namespace {
 #ifndef K2_MIN_BLOCKS
 #define K2_MIN_BLOCKS 1
 #endif
+#ifndef K2_SYNC_STEPS
+#define K2_SYNC_STEPS 11
+#endif
 #ifndef K2_THREADS
 #define K2_THREADS 992
 #endif
@@ -43,6 +46,8 @@ constexpr int K2PAD = 4;            // words in front of the big-endian stream
 // Two sizes are compiled: large tiles amortise the per-tile phases (barriers, look-back) on large inputs, small tiles
 // keep every SM busy on small ones.
 constexpr int K2S_LARGE = 28, K2S_SMALL = 8;
+// the syncmer filter (k <= 32) keeps two hash rows per warp in shared memory: measured at 100 Mbp, k=31 m=19 canonical: 4 steps (two CTAs per SM) 2.33 ms, 8 steps 1.77 ms; 11 is the most that fits 227 KB
+constexpr int K2S_SYNC = K2_SYNC_STEPS;
 template <int S>
 struct K2Geo {
     static constexpr int TILE = K2T * S;        // starts per tile
@@ -290,7 +295,7 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                     // strand into shared memory and a k-mer takes the minimum of its window: the fields of a forward value
                     // at start p are the forward m-mers at p .. p+w-1 (offset = position - p), those of a reverse-complement
                     // value are the reverse-complement m-mers of the same positions in reverse order (offset = p+w-1 -
-                    // position, so its leftmost field is the LAST position and ties go to the larger position).
+                    // position: its leftmost field is the LAST position).
                     const int m = a.sync_m, w = k - m + 1;
                     u64* hf = k2_sync_rows<S>(k2_raw) + warp * (2 * K2SyncRow<S>::N);
                     u64* hr = hf + K2SyncRow<S>::N;
@@ -316,14 +321,17 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                                 cut_both(cur.le, cur.be, lpw + 32 * j, k, vm, f, r);
                                 use_r = r < f;
                             }
-                            const u64* h = (use_r ? hr : hf) + 32 * j + lane;
+                            // walk the fields in the order of the value's own string (offset 0 first): a strict '<' then
+                            // keeps the leftmost minimum on either strand
+                            const u64* h = use_r ? hr + 32 * j + lane + (w - 1) : hf + 32 * j + lane;
+                            const int dir = use_r ? -1 : 1;
                             u64 best = h[0];
-                            int pos = 0;
+                            int off = 0;
+#pragma unroll 4
                             for (int i = 1; i < w; ++i) {
-                                const u64 v = h[i];
-                                if (v < best || (use_r && v == best)) { best = v; pos = i; }
+                                const u64 v = h[i * dir];
+                                if (v < best) { best = v; off = i; }
                             }
-                            const int off = use_r ? w - 1 - pos : pos;
                             const u32 keep = __ballot_sync(0xffffffffu, off == a.sync_s || off == a.sync_e);
                             if (lane == j) mrange = mj & keep;
                         }
@@ -439,19 +447,15 @@ cudaError_t k2_setup(int* occ)
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(SYNC));
 }
 template <int S>
-cudaError_t k2_setup_s(bool wide, bool canon, bool sync, int* occ)
+cudaError_t k2_setup_s(bool wide, bool canon, int* occ)
 {
-    if (sync) return canon ? k2_setup<S, false, true, true>(occ) : k2_setup<S, false, false, true>(occ);   // k <= 32 only
     return wide ? (canon ? k2_setup<S, true, true, false>(occ) : k2_setup<S, true, false, false>(occ))
                 : (canon ? k2_setup<S, false, true, false>(occ) : k2_setup<S, false, false, false>(occ));
 }
 template <int S>
-void k2_launch_s(bool wide, bool canon, bool sync, const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
+void k2_launch_s(bool wide, bool canon, const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
-    if (sync) {
-        if (canon) kmer2_kernel<S, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
-        else kmer2_kernel<S, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
-    } else if (wide) {
+    if (wide) {
         if (canon) kmer2_kernel<S, true, true, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
         else kmer2_kernel<S, true, false, false><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
     } else {
@@ -467,18 +471,19 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 {
     const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
     if (args.sync_on && (args.k > 32 || args.sync_m < 1 || args.sync_m > args.k)) return cudaErrorInvalidValue;
-    // the syncmer predicate is w hashes per k-mer: small tiles keep the look-back chain short
-    const bool large = !args.sync_on && k2_large(nwin, sm_count);
-    const int tile = large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE;
-    args.nwords = large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW;
-    args.steps = large ? K2S_LARGE : K2S_SMALL;
+    const bool sync = args.sync_on != 0;
+    const bool large = !sync && k2_large(nwin, sm_count);
+    const int tile = sync ? K2Geo<K2S_SYNC>::TILE : (large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE);
+    args.nwords = sync ? K2Geo<K2S_SYNC>::NW : (large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW);
+    args.steps = sync ? K2S_SYNC : (large ? K2S_LARGE : K2S_SMALL);
     args.num_tiles = (nwin + tile - 1) / tile;
     plan->threads = K2T + 32;
-    plan->smem_bytes = large ? k2_smem_bytes<K2S_LARGE>(false) : k2_smem_bytes<K2S_SMALL>(args.sync_on != 0);
+    plan->smem_bytes = sync ? k2_smem_bytes<K2S_SYNC>(true) : (large ? k2_smem_bytes<K2S_LARGE>(false) : k2_smem_bytes<K2S_SMALL>(false));
     int occ = 0;
     const bool canon = args.canonical != 0, wide = args.k > 32;
-    const bool sync = args.sync_on != 0;
-    cudaError_t e = large ? k2_setup_s<K2S_LARGE>(wide, canon, sync, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, sync, &occ);
+    cudaError_t e;
+    if (sync) e = canon ? k2_setup<K2S_SYNC, false, true, true>(&occ) : k2_setup<K2S_SYNC, false, false, true>(&occ);
+    else e = large ? k2_setup_s<K2S_LARGE>(wide, canon, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, &occ);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     long long grid = (long long)sm_count * occ;
@@ -490,9 +495,11 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
     const bool canon = args.canonical != 0, wide = args.k > 32;
-    const bool sync = args.sync_on != 0;
-    if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, sync, args, plan, stream);
-    else k2_launch_s<K2S_SMALL>(wide, canon, sync, args, plan, stream);
+    if (args.sync_on) {
+        if (canon) kmer2_kernel<K2S_SYNC, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<K2S_SYNC, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    } else if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, args, plan, stream);
+    else k2_launch_s<K2S_SMALL>(wide, canon, args, plan, stream);
     return cudaGetLastError();
 }
 
