@@ -20,7 +20,7 @@ F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID = 0x1, 0x2, 0
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
     "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
-    "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_free_kmer_out", "blg_free_sk_out",
+    "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
 ]
 
 
@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
     L.blg_host_free.argtypes = [vp, vp]
     L.blg_kmers.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(KmerOut)]
     L.blg_syncmers.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.c_uint16, C.c_uint16, C.POINTER(KmerOut)]
+    L.blg_hash_sampled_kmers.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), u64, C.POINTER(KmerOut)]
     for f in (L.blg_minimizers, L.blg_super_kmers):
         f.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(SkOut)]
     L.blg_super_kmers_range.argtypes = [vp, vp, sz, vp, sz, u64, u64, C.POINTER(Params), C.POINTER(SkOut)]

@@ -70,15 +70,18 @@ class Context:
         return n.value, buf.value.decode()
 
     # ------------------------------------------------------------------ host in, host out
-    def kmers(self, seq, k: int, canonical: bool = False, offsets=None, syncmer=None) -> dict:
+    def kmers(self, seq, k: int, canonical: bool = False, offsets=None, syncmer=None, hash_sample=None) -> dict:
         """Valid k-mers in position order; syncmer=(m, start_offset, end_offset) keeps only those that
         sampler::syncmer_sampler over hash::minimizer_position_extractor(k, m) would (blg_syncmers)."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=0, seed=0)
+        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=0,
+                   seed=0 if hash_sample is None else hash_sample[0] & (2**64 - 1))
         out = KmerOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1, C.byref(p))
-        if syncmer is None:
+        if hash_sample is not None:
+            self._check(self.L.blg_hash_sampled_kmers(*args, int(hash_sample[1]), C.byref(out)))
+        elif syncmer is None:
             self._check(self.L.blg_kmers(*args, C.byref(out)))
         else:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
@@ -133,6 +136,17 @@ class Context:
         """sampler::syncmer_sampler (reference include/syncmer_sampler.hpp:130-137); closed syncmers by default."""
         return self.kmers(seq, k, canonical, offsets, syncmer=(m, start_offset, k - m if end_offset is None else end_offset))
 
+    @staticmethod
+    def hash_sampler_threshold(sampling_rate: float) -> int:
+        """hash_sampler's constructor (reference include/hash_sampler.hpp:76-77): same check, same double product."""
+        if sampling_rate > 1 or sampling_rate < 0:
+            raise ValueError("[hash_sampler] Invalid sampling rate")
+        return min(int(sampling_rate * float(2**64 - 1)), 2**64 - 1)
+
+    def hash_sampled_kmers(self, seq, k: int, seed: int, sampling_rate: float, canonical: bool = False, offsets=None) -> dict:
+        """sampler::hash_sampler over the k-mer values (reference include/hash_sampler.hpp:138-141)."""
+        return self.kmers(seq, k, canonical, offsets, hash_sample=(seed, self.hash_sampler_threshold(sampling_rate)))
+
     def minimizer_positions(self, kmer_values, k: int, m: int) -> np.ndarray:
         """hash::minimizer_position_extractor for an array of k-mer values (k <= 32)."""
         v = np.ascontiguousarray(kmer_values, dtype=np.uint64)
@@ -178,11 +192,14 @@ class Context:
         self._check(self.L.blg_host_free(self.h, C.c_void_p(ptr)))
 
     def kmers_device(self, d_bases: int, n_bases: int, k: int, canonical: bool, d_lo: int, d_hi: int, d_pos: int,
-                     capacity: int, d_offsets: int = 0, n_seq: int = 0, syncmer=None) -> int:
-        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT, seed=0)
+                     capacity: int, d_offsets: int = 0, n_seq: int = 0, syncmer=None, hash_sample=None) -> int:
+        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=F_DEVICE_INPUT | F_DEVICE_OUTPUT,
+                   seed=0 if hash_sample is None else hash_sample[0] & (2**64 - 1))
         out = KmerOut(count=0, capacity=capacity, value_lo=d_lo, value_hi=d_hi or None, position=d_pos or None, owner=None)
         args = (self.h, C.c_void_p(d_bases), n_bases, C.c_void_p(d_offsets or 0), n_seq, C.byref(p))
-        if syncmer is None:
+        if hash_sample is not None:
+            self._check(self.L.blg_hash_sampled_kmers(*args, int(hash_sample[1]), C.byref(out)))
+        elif syncmer is None:
             self._check(self.L.blg_kmers(*args, C.byref(out)))
         else:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))

@@ -635,13 +635,15 @@ int blg_minimizers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs
 }
 
 namespace {
-// sync_s < 0: every valid k-mer (blg_kmers); else the closed-syncmer filter with m-mers of p->m bases (blg_syncmers)
+// sync_s < 0: every valid k-mer (blg_kmers); else the closed-syncmer filter with m-mers of p->m bases (blg_syncmers);
+// threshold != nullptr: the hash-threshold filter (blg_hash_sampled_kmers)
 int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
-                 int sync_s, int sync_e, blg_kmer_out* out)
+                 int sync_s, int sync_e, blg_kmer_out* out, const uint64_t* threshold = nullptr)
 {
     if (!c || !p || !out) return BLG_E_INVALID;
     if (p->k == 0 || p->k > 64) { c->err = "need 1 <= k <= 64"; return BLG_E_INVALID; }
     if (sync_s >= 0 && (p->k > 32 || p->m == 0 || p->m > p->k)) { c->err = "syncmers need 1 <= m <= k <= 32"; return BLG_E_INVALID; }
+    if (threshold && p->k > 32) { c->err = "hash sampling needs k <= 32 (hash64 of a 64-bit value)"; return BLG_E_INVALID; }
     const bool wide = p->k > 32;
     if (out->capacity > 0 && (!out->value_lo || (wide && !out->value_hi))) { c->err = "value arrays missing"; return BLG_E_INVALID; }
     Timer tm;
@@ -669,6 +671,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     a.k = k; a.canonical = p->canonical ? 1 : 0;
     a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
     if (sync_s >= 0) { a.sync_on = 1; a.sync_m = p->m; a.sync_s = sync_s; a.sync_e = sync_e; }
+    if (threshold) { a.sync_on = 2; a.samp_s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL; a.samp_threshold = *threshold; }
     uint64_t total = 0;
     if (dev_out && out->capacity > 0) {
         a.value_lo = reinterpret_cast<unsigned long long*>(out->value_lo);
@@ -744,6 +747,12 @@ int blg_syncmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
                  uint16_t start_offset, uint16_t end_offset, blg_kmer_out* out)
 {
     return kmers_common(c, bases, n, offs, n_seq, p, (int)start_offset, (int)end_offset, out);
+}
+
+int blg_hash_sampled_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                           uint64_t threshold, blg_kmer_out* out)
+{
+    return kmers_common(c, bases, n, offs, n_seq, p, -1, -1, out, &threshold);
 }
 
 int blg_hash64(blg_ctx* c, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out)

@@ -84,6 +84,8 @@ struct KmerArgs {
     // closed-syncmer filter (sampler::syncmer_sampler over hash::minimizer_position_extractor): keep a k-mer iff the
     // offset of its minimum-hash m-mer is sync_s or sync_e; k <= 32 only; sync_on = 0: every valid k-mer
     int sync_on, sync_m, sync_s, sync_e;
+    // sync_on = 2: sampler::hash_sampler instead (include/hash_sampler.hpp:138-141): keep iff hash64(value, seed) < samp_threshold
+    unsigned long long samp_s8, samp_threshold;
     long long num_tiles;
     unsigned long long* value_lo;
     unsigned long long* value_hi;  // null for k <= 32

@@ -299,7 +299,25 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                     const int m = a.sync_m, w = k - m + 1;
                     u64* hf = k2_sync_rows<S>(k2_raw) + warp * (2 * K2SyncRow<S>::N);
                     u64* hr = hf + K2SyncRow<S>::N;
-                    if (__ballot_sync(0xffffffffu, mrange != 0)) {
+                    if (a.sync_on == 2) {
+                        // sampler::hash_sampler (include/hash_sampler.hpp:138-141): a k-mer is skipped while
+                        // hash(value, seed) >= threshold
+                        if (__ballot_sync(0xffffffffu, mrange != 0)) {
+                            const int lp0 = off0 + wp + lane;
+                            const int s = (lp0 & 15) * 2;
+                            const int e = 2 * lp0 + 2 * k + 32 * K2PAD - 32 * NV;
+                            const u32* le = cur.le + (lp0 >> 4);
+                            const u32* be = cur.be + (e >> 5);
+                            for (int j = 0; j < K2S; ++j) {
+                                const u32 mj = __shfl_sync(0xffffffffu, mrange, j);
+                                if (mj == 0) continue;
+                                u64 km, hi_;
+                                cut_kmer<WIDE, CANON>(le + 2 * j, be + 2 * j, s, e & 31, vm, km, hi_);
+                                const u32 keep = __ballot_sync(0xffffffffu, murmur3_key8(km, a.samp_s8) < a.samp_threshold);
+                                if (lane == j) mrange = mj & keep;
+                            }
+                        }
+                    } else if (__ballot_sync(0xffffffffu, mrange != 0)) {
                         u32 mm[2];
                         mm[0] = 2 * m >= 32 ? 0xFFFFFFFFu : ((1u << (2 * m)) - 1u);
                         mm[1] = 2 * m >= 64 ? 0xFFFFFFFFu : (2 * m > 32 ? ((1u << (2 * m - 32)) - 1u) : 0u);
@@ -470,7 +488,8 @@ bool k2_large(long long nwin, int sm_count) { return nwin >= 5LL * sm_count * K2
 cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 {
     const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
-    if (args.sync_on && (args.k > 32 || args.sync_m < 1 || args.sync_m > args.k)) return cudaErrorInvalidValue;
+    if (args.sync_on && args.k > 32) return cudaErrorInvalidValue;
+    if (args.sync_on == 1 && (args.sync_m < 1 || args.sync_m > args.k)) return cudaErrorInvalidValue;
     const bool sync = args.sync_on != 0;
     const bool large = !sync && k2_large(nwin, sm_count);
     const int tile = sync ? K2Geo<K2S_SYNC>::TILE : (large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE);

@@ -175,6 +175,16 @@ int blg_minimizer_positions(blg_ctx* ctx, const uint64_t* kmer_values, size_t n,
 int blg_syncmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
                  const blg_params* p, uint16_t start_offset, uint16_t end_offset, blg_kmer_out* out);
 
+/*
+ * sampler::hash_sampler<Iterator, hash::hash64> over the k-mer values of a kmer_view (include/hash_sampler.hpp:73-78,
+ * 138-141), fused into the k-mer kernel: the entries blg_kmers would return, restricted to those with
+ * hash64(value, p->seed) < threshold. `threshold` is the reference's
+ * static_cast<uint64_t>(sampling_rate * std::numeric_limits<uint64_t>::max()) (hash_sampler.hpp:77), computed by the
+ * caller so that the double arithmetic stays on the reference's side. k <= 32 (64-bit values); p->m is unused.
+ */
+int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                           const blg_params* p, uint64_t threshold, blg_kmer_out* out);
+
 /* release library-allocated output arrays (host pinned or device); caller-provided arrays are untouched */
 void blg_free_kmer_out(blg_ctx* ctx, blg_kmer_out* out);
 void blg_free_sk_out(blg_ctx* ctx, blg_sk_out* out);

@@ -127,6 +127,14 @@ class Oracle:
         keep = (p == soff) | (p == eoff)
         return {key: v[keep] for key, v in km.items()}
 
+    def hash_sampled_kmers(self, seq, k, seed, threshold, canonical, offsets=None):
+        """sampler::hash_sampler::const_iterator::find_first_kmer (reference include/hash_sampler.hpp:138-141) over the valid
+        k-mer values: kept iff hash64(value, seed) < threshold (threshold as the constructor computes it, :77)."""
+        km = self.kmers(seq, k, canonical, offsets)
+        h = np.array([self.hash64(int(x), seed) for x in km["lo"]], dtype=np.uint64) if len(km["lo"]) else np.zeros(0, np.uint64)
+        keep = h < np.uint64(threshold)
+        return {key: v[keep] for key, v in km.items()}
+
     def syncmer_stream(self, seq, k, m, soff, eoff, canonical):
         """The reference's record stream for one sequence: syncmer_sampler over kmer_view (K1-K4 apply: the final k-mer
         of a sequence ending in a valid base never appears; nullopt records have offset k + 1 and never pass)."""
@@ -241,6 +249,15 @@ class Ref:
         self.lib.ref_minimizer_positions.restype = None
         self.lib.ref_minimizer_positions(v.ctypes.data, None if hv is None else hv.ctypes.data, v.size, k, m, out.ctypes.data)
         return out
+
+    def hash_sampler(self, values, seed, rate):
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        kept = np.zeros(v.size, np.uint64)
+        thr = C.c_uint64()
+        self.lib.ref_hash_sampler_u64.restype = C.c_size_t
+        self.lib.ref_hash_sampler_u64.argtypes = [C.c_void_p, C.c_size_t, C.c_uint64, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]
+        n = self.lib.ref_hash_sampler_u64(v.ctypes.data, v.size, seed & (2**64 - 1), float(rate), kept.ctypes.data, C.byref(thr))
+        return kept[:n], int(thr.value)
 
     def syncmer_stream(self, seq, k, m, soff, eoff, canonical):
         b = _buf(seq)

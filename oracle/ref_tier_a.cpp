@@ -46,6 +46,7 @@
 #include "kmer_view.hpp"
 #include "minimizer_view.hpp"
 #include "syncmer_sampler.hpp"
+#include "hash_sampler.hpp"
 #undef private
 #include "sequence_generator.hpp"
 #include "sequence_mutator.hpp"
@@ -198,6 +199,19 @@ size_t ref_syncmers_u64(const char* s, size_t n, unsigned k, unsigned m, unsigne
         ++cnt;
     }
     first->~it_t();
+    return cnt;
+}
+
+// sampler::hash_sampler<std::vector<uint64_t>::const_iterator, hash::hash64> (include/hash_sampler.hpp:73-78,138-141)
+// over an array of k-mer values: the kept values, and the threshold the constructor derived from the rate.
+size_t ref_hash_sampler_u64(const uint64_t* values, size_t n, uint64_t seed, double rate, uint64_t* kept, uint64_t* threshold)
+{
+    std::vector<uint64_t> v(values, values + n);
+    using it_t = std::vector<uint64_t>::const_iterator;
+    sampler::hash_sampler<it_t, hash::hash64> smp(v.cbegin(), v.cend(), hash::hash64(), seed, rate);
+    if (threshold) *threshold = smp.threshold;
+    size_t cnt = 0;
+    for (auto it = smp.cbegin(); it != smp.cend(); ++it) kept[cnt++] = *it;
     return cnt;
 }
 

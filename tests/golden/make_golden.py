@@ -196,5 +196,21 @@ def syncmers(ref, path):
                               "ref_syncmers_u64)", cases=cases), open(path, "w"), separators=(",", ":"))
 
 
+def hash_sampler(ref, path):
+    """tests/golden/hash_sampler.json: sampler::hash_sampler<vector<uint64_t>::const_iterator, hash::hash64> (reference
+    include/hash_sampler.hpp:73-78,138-141) executed verbatim: kept values and the constructor's threshold."""
+    import json
+    import numpy as np
+    rng = np.random.default_rng(20261106)
+    v = rng.integers(0, 2**62, size=400, dtype=np.uint64)
+    cases = []
+    for seed, rate in ((42, 0.1), (0, 0.5), (7, 0.01), (2**32 + 42, 0.25), (1, 0.0), (3, 0.999)):
+        kept, thr = ref.hash_sampler(v, seed, rate)
+        cases.append(dict(seed=seed, rate=rate, threshold=thr, kept=[int(x) for x in kept]))
+    json.dump(dict(provenance="reference sampler::hash_sampler executed verbatim (oracle/ref_tier_a.cpp ref_hash_sampler_u64)",
+                   values=[int(x) for x in v], cases=cases), open(path, "w"), separators=(",", ":"))
+
+
 minpos(ref, os.path.join(HERE, "minpos.json"))
+hash_sampler(ref, os.path.join(HERE, "hash_sampler.json"))
 syncmers(ref, os.path.join(HERE, "syncmers.json"))

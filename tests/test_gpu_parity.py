@@ -311,6 +311,39 @@ def test_syncmers_multi_sequence_and_errors(gpu, oracle):
     assert len(gpu.syncmers("ACGT" * 100, 11, 5, 9, 9)["lo"]) == 0
 
 
+@pytest.mark.parametrize("k,canon", [(31, True), (21, False), (32, True), (5, False)])
+def test_hash_sampled_kmers(gpu, oracle, k, canon):
+    """blg_hash_sampled_kmers vs sampler::hash_sampler (reference include/hash_sampler.hpp:73-78,138-141; the restatement is
+    pinned against the reference-executed sampler in tests/test_oracle_vs_ref.py and tests/golden/hash_sampler.json)."""
+    rng = np.random.default_rng(k)
+    for n, pn in ((0, 0), (k, 0), (5000, 0.0), (40000, 0.01)):
+        s = rand_seq(rng, n, p_n=pn, lower=0.05)
+        for seed, rate in ((42, 0.1), (0, 0.5), (2**32 + 42, 0.01), (7, 0.0), (7, 1.0)):
+            thr = gpu.hash_sampler_threshold(rate)
+            g = gpu.hash_sampled_kmers(s, k, seed, rate, canon)
+            o = oracle.hash_sampled_kmers(s, k, seed, thr, canon)
+            assert len(g["lo"]) == len(o["lo"]), (k, n, seed, rate)
+            for key in ("lo", "pos"):
+                assert np.array_equal(g[key], o[key]), (key, k, n, seed, rate)
+    with pytest.raises(Exception):
+        gpu.hash_sampled_kmers("ACGT" * 100, 33, 0, 0.5)
+    with pytest.raises(ValueError):
+        gpu.hash_sampled_kmers("ACGT" * 100, 31, 0, 1.5)
+
+
+def test_hash_sampled_kmers_large_cross_check(gpu):
+    """20 Mbp, two sequences: the fused filter equals blg_kmers filtered by blg_hash64."""
+    rng = np.random.default_rng(98)
+    s = rand_seq(rng, 20_000_000, p_n=0.0001)
+    offsets = np.array([0, 7_000_001, 20_000_000], dtype=np.uint64)
+    k, seed, rate = 31, 42, 0.125
+    g = gpu.hash_sampled_kmers(s, k, seed, rate, True, offsets=offsets)
+    km = gpu.kmers(s, k, True, offsets=offsets)
+    keep = gpu.hash64(km["lo"], seed) < np.uint64(gpu.hash_sampler_threshold(rate))
+    assert np.array_equal(g["lo"], km["lo"][keep]) and np.array_equal(g["pos"], km["pos"][keep])
+    assert 0.12 < len(g["lo"]) / len(km["lo"]) < 0.13
+
+
 def test_syncmers_large_cross_check(gpu):
     """20 Mbp: the fused filter equals blg_kmers filtered by the separate blg_minimizer_positions kernel."""
     rng = np.random.default_rng(99)

@@ -168,3 +168,15 @@ def test_syncmer_sampler_golden(oracle):
         assert len(b["lo"]) - n in (0, 1)
         if len(b["lo"]) > n:
             assert int(b["pos"][-1]) == len(c["seq"]) - c["k"]
+
+
+def test_hash_sampler_golden(oracle):
+    """sampler::hash_sampler (reference include/hash_sampler.hpp:73-78,138-141) against reference-executed vectors."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "hash_sampler.json")))
+    v = np.array(g["values"], dtype=np.uint64)
+    for c in g["cases"]:
+        assert c["threshold"] == min(int(c["rate"] * float(2**64 - 1)), 2**64 - 1)
+        h = np.array([oracle.hash64(int(x), c["seed"]) for x in v], dtype=np.uint64)
+        assert v[h < np.uint64(c["threshold"])].tolist() == c["kept"], (c["seed"], c["rate"])

@@ -162,3 +162,16 @@ def test_syncmer_sampler_live(oracle, ref):
                     b = ref.syncmer_stream(s, k, m, soff, eoff, canon)
                     for key in ("lo", "pos", "id"):
                         assert np.array_equal(a[key], b[key]), (key, k, m, pn, canon, soff)
+
+
+def test_hash_sampler_live(oracle, ref):
+    """hash64(value, seed) < threshold vs sampler::hash_sampler executed verbatim over a vector of values; the threshold the
+    Python mirror derives from the rate equals the reference constructor's (include/hash_sampler.hpp:77)."""
+    import biolib_b200.context as ctxmod
+    rng = np.random.default_rng(77)
+    v = rng.integers(0, 2**62, size=4000, dtype=np.uint64)
+    for seed, rate in ((42, 0.1), (0, 0.5), (7, 0.01), (2**32 + 42, 0.25), (1, 0.0), (3, 0.999)):
+        kept, thr = ref.hash_sampler(v, seed, rate)
+        assert thr == ctxmod.Context.hash_sampler_threshold(rate)
+        h = np.array([oracle.hash64(int(x), seed) for x in v], dtype=np.uint64)
+        assert np.array_equal(kept, v[h < np.uint64(thr)]), (seed, rate)

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--pos", type=int, default=1)
     ap.add_argument("--breaks", type=float, default=0.0)
     ap.add_argument("--syncmer", type=int, default=0, help="m: closed-syncmer filter (blg_syncmers, offsets 0 and k - m)")
+    ap.add_argument("--hash-sample", type=float, default=-1.0, help="rate: hash_sampler filter (blg_hash_sampled_kmers, seed 42)")
     ap.add_argument("--reads", type=int, default=0, help="split into sequences of this length (0 = one sequence)")
     args = ap.parse_args()
     import torch
@@ -64,7 +65,8 @@ def main():
         flush.zero_()
         count = ctx.kmers_device(d_bases.data_ptr(), args.n, args.k, bool(args.canon), d_lo.data_ptr(), d_hi.data_ptr() if wide else 0,
                                  d_pos.data_ptr() if args.pos else 0, cap, d_offsets=offs_d.data_ptr() if offs_d is not None else 0, n_seq=n_seq,
-                                 syncmer=(args.syncmer, 0, args.k - args.syncmer) if args.syncmer else None)
+                                 syncmer=(args.syncmer, 0, args.k - args.syncmer) if args.syncmer else None,
+                                 hash_sample=(42, ctx.hash_sampler_threshold(args.hash_sample)) if args.hash_sample >= 0 else None)
         if i >= 3:
             ms.append(ctx.stats()["kernel_ms"])
     torch.cuda.synchronize()
@@ -77,7 +79,7 @@ def main():
         chk ^= int((d_pos[:count] * idx).sum().item())
     if wide:
         chk ^= int((d_hi[:count] * (idx + 1)).sum().item())
-    print(f"k={args.k} syncmer_m={args.syncmer} canon={args.canon} pos={args.pos} reads={args.reads} breaks={args.breaks} kmers={count} kernel_ms={med:.4f} min={min(ms):.4f} "
+    print(f"k={args.k} syncmer_m={args.syncmer} hash_sample={args.hash_sample} canon={args.canon} pos={args.pos} reads={args.reads} breaks={args.breaks} kmers={count} kernel_ms={med:.4f} min={min(ms):.4f} "
           f"Gbases/s={args.n / med / 1e6:.1f} GB/s={gb / med * 1e3:.0f} frac_of_{peak:.0f}={gb / med * 1e3 / peak:.3f} chk={chk & (2**64 - 1):016x}", flush=True)
     ctx.close()
 
