@@ -458,11 +458,11 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
 
 namespace {
 template <int S, bool WIDE, bool CANON, bool SYNC>
-cudaError_t k2_setup(int* occ)
+cudaError_t k2_setup(int* occ, bool rows = SYNC)
 {
-    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem_bytes<S>(SYNC));
+    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem_bytes<S>(rows));
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(SYNC));
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(rows));
 }
 template <int S>
 cudaError_t k2_setup_s(bool wide, bool canon, int* occ)
@@ -490,7 +490,9 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
     const long long nwin = args.win_hi > args.win_lo ? args.win_hi - args.win_lo : 0;
     if (args.sync_on && args.k > 32) return cudaErrorInvalidValue;
     if (args.sync_on == 1 && (args.sync_m < 1 || args.sync_m > args.k)) return cudaErrorInvalidValue;
-    const bool sync = args.sync_on != 0;
+    // the syncmer filter has its own tile size (hash rows in shared memory); the hash-threshold filter needs no rows and
+    // runs on the ordinary tiles
+    const bool sync = args.sync_on == 1, samp = args.sync_on == 2;
     const bool large = !sync && k2_large(nwin, sm_count);
     const int tile = sync ? K2Geo<K2S_SYNC>::TILE : (large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE);
     args.nwords = sync ? K2Geo<K2S_SYNC>::NW : (large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW);
@@ -502,6 +504,8 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
     const bool canon = args.canonical != 0, wide = args.k > 32;
     cudaError_t e;
     if (sync) e = canon ? k2_setup<K2S_SYNC, false, true, true>(&occ) : k2_setup<K2S_SYNC, false, false, true>(&occ);
+    else if (samp && large) e = canon ? k2_setup<K2S_LARGE, false, true, true>(&occ, false) : k2_setup<K2S_LARGE, false, false, true>(&occ, false);
+    else if (samp) e = canon ? k2_setup<K2S_SMALL, false, true, true>(&occ, false) : k2_setup<K2S_SMALL, false, false, true>(&occ, false);
     else e = large ? k2_setup_s<K2S_LARGE>(wide, canon, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, &occ);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
@@ -514,9 +518,15 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
 cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream)
 {
     const bool canon = args.canonical != 0, wide = args.k > 32;
-    if (args.sync_on) {
+    if (args.sync_on == 1) {
         if (canon) kmer2_kernel<K2S_SYNC, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
         else kmer2_kernel<K2S_SYNC, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    } else if (args.sync_on == 2 && args.steps == K2S_LARGE) {
+        if (canon) kmer2_kernel<K2S_LARGE, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<K2S_LARGE, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    } else if (args.sync_on == 2) {
+        if (canon) kmer2_kernel<K2S_SMALL, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<K2S_SMALL, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
     } else if (args.steps == K2S_LARGE) k2_launch_s<K2S_LARGE>(wide, canon, args, plan, stream);
     else k2_launch_s<K2S_SMALL>(wide, canon, args, plan, stream);
     return cudaGetLastError();
