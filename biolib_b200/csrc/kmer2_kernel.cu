@@ -23,6 +23,14 @@
 // Measured (profiles/r01_s29_kmer2_kernel_details.txt, tools/kmerbench.py, 100 Mbp, value + position per k-mer):
 // k=31 0.317 ms = 5.36 TB/s = 82 % of the measured HBM copy peak (first generation 0.446 ms), k=63 0.444 ms = 86 %
 // (0.734 ms), 150-bp reads 0.43 ms (0.57), 1 % N 0.34 ms (0.44); 40 executed instructions per k-mer.
+//
+// SYNC = true adds a sampling predicate to the counting pass (k <= 32), so only the sampled k-mers are counted and written:
+//   sync_on = 1  sampler::syncmer_sampler over hash::minimizer_position_extractor (include/syncmer_sampler.hpp:130-137,
+//                include/kmer_view.hpp:266-283; blg_syncmers): every m-mer of a warp's span hashed once per strand into
+//                shared-memory rows, each k-mer takes the minimum of its window; own tile size (K2S_SYNC steps).
+//                1.64 ms per 100 Mbp at k=31 m=19 canonical (profiles/r01_s30_syncmer_bench_v3.txt)
+//   sync_on = 2  sampler::hash_sampler (include/hash_sampler.hpp:138-141; blg_hash_sampled_kmers): hash64(value, seed) <
+//                threshold, on the ordinary tiles. 0.62 ms per 100 Mbp (profiles/r01_s30_hash_sampler_bench.txt)
 #include "common.cuh"
 #include "kernels.h"
 
