@@ -56,6 +56,8 @@ constexpr int K2PAD = 4;            // words in front of the big-endian stream
 constexpr int K2S_LARGE = 28, K2S_SMALL = 8;
 // the syncmer filter (k <= 32) keeps two hash rows per warp in shared memory: measured at 100 Mbp, k=31 m=19 canonical: 4 steps (two CTAs per SM) 2.33 ms, 8 steps 1.77 ms; 11 is the most that fits 227 KB
 constexpr int K2S_SYNC = K2_SYNC_STEPS;
+// non-canonical input needs the forward row only: twice the tile
+constexpr int K2S_SYNC_FWD = 2 * K2_SYNC_STEPS;
 template <int S>
 struct K2Geo {
     static constexpr int TILE = K2T * S;        // starts per tile
@@ -176,9 +178,9 @@ __device__ __forceinline__ u64* k2_sync_rows(unsigned char* raw)
     return reinterpret_cast<u64*>(raw + ((sizeof(K2Smem<S>) + 15) & ~(size_t)15));
 }
 template <int S>
-constexpr size_t k2_smem_bytes(bool sync)
+constexpr size_t k2_smem_bytes(bool sync, bool both_strands = true)
 {
-    return ((sizeof(K2Smem<S>) + 15) & ~(size_t)15) + (sync ? (size_t)K2W * 2 * K2SyncRow<S>::N * 8 : 0);
+    return ((sizeof(K2Smem<S>) + 15) & ~(size_t)15) + (sync ? (size_t)K2W * (both_strands ? 2 : 1) * K2SyncRow<S>::N * 8 : 0);
 }
 
 template <int S, bool WIDE, bool CANON, bool SYNC>
@@ -305,7 +307,7 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                     // value are the reverse-complement m-mers of the same positions in reverse order (offset = p+w-1 -
                     // position: its leftmost field is the LAST position).
                     const int m = a.sync_m, w = k - m + 1;
-                    u64* hf = k2_sync_rows<S>(k2_raw) + warp * (2 * K2SyncRow<S>::N);
+                    u64* hf = k2_sync_rows<S>(k2_raw) + warp * ((CANON ? 2 : 1) * K2SyncRow<S>::N);
                     u64* hr = hf + K2SyncRow<S>::N;
                     if (a.sync_on == 2) {
                         // sampler::hash_sampler (include/hash_sampler.hpp:138-141): a k-mer is skipped while
@@ -468,9 +470,9 @@ namespace {
 template <int S, bool WIDE, bool CANON, bool SYNC>
 cudaError_t k2_setup(int* occ, bool rows = SYNC)
 {
-    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem_bytes<S>(rows));
+    cudaError_t e = cudaFuncSetAttribute(kmer2_kernel<S, WIDE, CANON, SYNC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_smem_bytes<S>(rows, CANON));
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(rows));
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, kmer2_kernel<S, WIDE, CANON, SYNC>, K2T + 32, k2_smem_bytes<S>(rows, CANON));
 }
 template <int S>
 cudaError_t k2_setup_s(bool wide, bool canon, int* occ)
@@ -502,16 +504,18 @@ cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan)
     // runs on the ordinary tiles
     const bool sync = args.sync_on == 1, samp = args.sync_on == 2;
     const bool large = !sync && k2_large(nwin, sm_count);
-    const int tile = sync ? K2Geo<K2S_SYNC>::TILE : (large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE);
-    args.nwords = sync ? K2Geo<K2S_SYNC>::NW : (large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW);
-    args.steps = sync ? K2S_SYNC : (large ? K2S_LARGE : K2S_SMALL);
+    const bool canon = args.canonical != 0, wide = args.k > 32;
+    const bool sync_fwd = sync && !canon;
+    const int tile = sync ? (sync_fwd ? K2Geo<K2S_SYNC_FWD>::TILE : K2Geo<K2S_SYNC>::TILE) : (large ? K2Geo<K2S_LARGE>::TILE : K2Geo<K2S_SMALL>::TILE);
+    args.nwords = sync ? (sync_fwd ? K2Geo<K2S_SYNC_FWD>::NW : K2Geo<K2S_SYNC>::NW) : (large ? K2Geo<K2S_LARGE>::NW : K2Geo<K2S_SMALL>::NW);
+    args.steps = sync ? (sync_fwd ? K2S_SYNC_FWD : K2S_SYNC) : (large ? K2S_LARGE : K2S_SMALL);
     args.num_tiles = (nwin + tile - 1) / tile;
     plan->threads = K2T + 32;
-    plan->smem_bytes = sync ? k2_smem_bytes<K2S_SYNC>(true) : (large ? k2_smem_bytes<K2S_LARGE>(false) : k2_smem_bytes<K2S_SMALL>(false));
+    plan->smem_bytes = sync ? (sync_fwd ? k2_smem_bytes<K2S_SYNC_FWD>(true, false) : k2_smem_bytes<K2S_SYNC>(true, true))
+                            : (large ? k2_smem_bytes<K2S_LARGE>(false) : k2_smem_bytes<K2S_SMALL>(false));
     int occ = 0;
-    const bool canon = args.canonical != 0, wide = args.k > 32;
     cudaError_t e;
-    if (sync) e = canon ? k2_setup<K2S_SYNC, false, true, true>(&occ) : k2_setup<K2S_SYNC, false, false, true>(&occ);
+    if (sync) e = canon ? k2_setup<K2S_SYNC, false, true, true>(&occ) : k2_setup<K2S_SYNC_FWD, false, false, true>(&occ);
     else if (samp && large) e = canon ? k2_setup<K2S_LARGE, false, true, true>(&occ, false) : k2_setup<K2S_LARGE, false, false, true>(&occ, false);
     else if (samp) e = canon ? k2_setup<K2S_SMALL, false, true, true>(&occ, false) : k2_setup<K2S_SMALL, false, false, true>(&occ, false);
     else e = large ? k2_setup_s<K2S_LARGE>(wide, canon, &occ) : k2_setup_s<K2S_SMALL>(wide, canon, &occ);
@@ -528,7 +532,7 @@ cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaS
     const bool canon = args.canonical != 0, wide = args.k > 32;
     if (args.sync_on == 1) {
         if (canon) kmer2_kernel<K2S_SYNC, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
-        else kmer2_kernel<K2S_SYNC, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+        else kmer2_kernel<K2S_SYNC_FWD, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
     } else if (args.sync_on == 2 && args.steps == K2S_LARGE) {
         if (canon) kmer2_kernel<K2S_LARGE, false, true, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
         else kmer2_kernel<K2S_LARGE, false, false, true><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
