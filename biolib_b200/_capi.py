@@ -21,6 +21,7 @@ EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
     "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
+    "blg_synth_generate", "blg_synth_mutate",
 ]
 
 
@@ -41,12 +42,12 @@ class SkOut(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("n_bases", C.c_uint64), ("n_records", C.c_uint64), ("bytes_h2d", C.c_uint64), ("bytes_d2h", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double)]
+                ("kernel_launches", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double), ("exact_tiles", C.c_uint64)]
 
 
 def build(force: bool = False) -> str:
     """Compile the CUDA sources for sm_100a into libbiolib_gpu.so (nvcc cross-compiles without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".cpp"))]
     srcs.append(os.path.join(HERE, "..", "include", "biolib_gpu.h"))
     stale = force or not os.path.exists(LIB_PATH) or any(
         os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs)
@@ -91,5 +92,7 @@ def lib() -> C.CDLL:
     L.blg_free_kmer_out.restype = None
     L.blg_free_sk_out.argtypes = [vp, C.POINTER(SkOut)]
     L.blg_free_sk_out.restype = None
+    L.blg_synth_generate.argtypes = [u64, sz, vp]
+    L.blg_synth_mutate.argtypes = [vp, sz, C.c_double, C.c_double, C.c_double, u64, vp, sz, C.POINTER(sz), vp, vp]
     _lib = L
     return L

@@ -43,7 +43,8 @@ struct blg_ctx {
     int pipe_first_div = 4;      // first pipeline piece = a regular piece / this (BLG_PIPE_FIRST_DIV; development only)
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi (BLG_PIPE_CHUNK_M overrides; development only)
     int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
-    DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total
+    DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
+    DevBuf exact;                    // sk4: per-warp scratch of the exact path
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
     unsigned long long* h_total = nullptr;  // pinned
     std::string err;
@@ -124,10 +125,11 @@ int prep_scratch(blg_ctx* c, long long num_tiles)
 
 int read_total(blg_ctx* c, uint64_t* total)
 {
-    CK(c, cudaMemcpyAsync(c->h_total, static_cast<unsigned long long*>(c->small.p) + 1, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaMemcpyAsync(c->h_total, static_cast<unsigned long long*>(c->small.p) + 1, 16, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
-    *total = *c->h_total;
-    c->stats.bytes_d2h += 8;
+    *total = c->h_total[0];
+    c->stats.exact_tiles += c->h_total[1];
+    c->stats.bytes_d2h += 16;
     return BLG_OK;
 }
 
@@ -142,17 +144,24 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 {
     SkLaunchPlan plan;
     int gen = c->sk_gen;
-    if (gen == 0 || (gen == 3 && !sk3_supported(a.k, a.m))) gen = sk3_supported(a.k, a.m) ? 3 : 2;
-    if (gen == 1) CK(c, sk_plan(a, c->sm_count, &plan));
+    if (gen == 0 || (gen == 4 && !sk4_supported(a.k, a.m))) gen = sk4_supported(a.k, a.m) ? 4 : 3;
+    if (gen == 3 && !sk3_supported(a.k, a.m)) gen = 2;
+    if (gen == 4) CK(c, sk4_plan(a, c->sm_count, &plan));
+    else if (gen == 1) CK(c, sk_plan(a, c->sm_count, &plan));
     else if (gen == 2) CK(c, sk2_plan(a, c->sm_count, &plan));
     else CK(c, sk3_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
-    int rc = prep_scratch(c, gen == 3 ? a.status_words : a.num_tiles);
+    int rc = prep_scratch(c, gen >= 3 ? a.status_words : a.num_tiles);
     if (rc != BLG_OK) return rc;
     a.tile_counter = static_cast<unsigned int*>(c->small.p);
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
-    if (gen == 3) {
+    if (gen == 4) {
+        if ((rc = ensure(c, c->exact, sk4_exact_scratch_bytes(plan))) != BLG_OK) return rc;
+        a.exact_scratch = static_cast<unsigned long long*>(c->exact.p);
+        a.exact_tiles = static_cast<unsigned long long*>(c->small.p) + 2;
+    }
+    if (gen >= 3) {
         const long long groups = (a.num_tiles + 31) / 32;
         a.grp_acc = a.tile_status + a.num_tiles;
         a.grp_status = a.grp_acc + groups;
@@ -160,7 +169,8 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
     CK(c, cudaEventRecord(c->ev0, c->stream));
     if (gen == 1) CK(c, sk_launch(a, plan, c->stream));
     else if (gen == 2) CK(c, sk2_launch(a, plan, c->stream));
-    else CK(c, sk3_launch(a, plan, c->stream));
+    else if (gen == 3) CK(c, sk3_launch(a, plan, c->stream));
+    else CK(c, sk4_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -553,7 +563,7 @@ int blg_create(int device, blg_ctx** out)
     { const char* e = getenv("BLG_PIPE_CHUNK_M"); if (e && atoi(e) > 0) c->pipe_chunk_m = atoi(e); }
     { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BLG_KMER"); c->kmer_gen = (e && e[0] == '1') ? 1 : 0; }
-    { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 0; }
+    { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 0; }
     *out = c;
     return BLG_OK;
 }
@@ -563,7 +573,7 @@ int blg_destroy(blg_ctx* c)
     if (!c) return BLG_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
+    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->exact, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
                       &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
     if (c->h_total) cudaFreeHost(c->h_total);

@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                 const long long P0 = (nlo & ~15LL) - a.buf_lo;
                 have_pre = next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * K2NW <= a.buf_hi - a.buf_lo;
                 if (have_pre) {
-                    pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + tid);
+                    if (tid < K2NW) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + tid);   // K2NW < K2T for the small tiles
                     if (K2T + tid < K2NW) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + K2T + tid);
                 }
             }

@@ -1,0 +1,599 @@
+// sk4_device.cuh -- fused minimizer / super-k-mer extraction for sm_100a, fourth generation (device code; host side sk4_kernel.cu).
+//
+// Same results as sk3 / sk2 (SURVEY.md 8(a) decisions D1-D8; reference intent include/minimizer_view.hpp:184-266,
+// include/super_kmer_view.hpp:121-135). What changed is again the instruction count. The ncu profile of sk3
+// (profiles/r01_s27_sk3_kernel_instmix.txt) shows 160 executed instructions per base with the ALU pipe (LOP3 / SHF /
+// ISETP / SEL / IADD3, 16 lanes per clock per scheduler) as the limiter, and only a third of them are the hash. Here
+//
+//   * the window minimum runs on ONE 32-bit key per m-mer: the top 26 bits of the hash above a 6-bit index (the m-mer's
+//     position inside the lane's span). A running minimum is one VIMNMX; a tie in the hash part -- the only case where
+//     26 bits do not decide what 64 bits decide -- is caught by one VIADDMNMX per compare (min over the key differences,
+//     taken in the direction in which a tie is a small positive number). A tile that saw a tie (true duplicates in
+//     low-complexity sequence, or a 2^-26 collision) is redone by exact_tile4() with full 64-bit compares, so the output
+//     is bit-exact always; sk3 carried (hash hi, hash lo, index) through 2 ISETP + 3 SEL per compare;
+//   * a lane owns NB consecutive blocks of B = w - 1 m-mer starts (its SPAN, L = NB B <= 32 starts), so a window never
+//     reaches further than the next lane's first block: the index alone says where the minimum is (an index below the
+//     window's own offset can only belong to the next lane), the prefix minima of all blocks but the first stay in
+//     registers, and the three margin blocks of a tile (1 left, 2 right) are spread over 32 NB blocks instead of 32;
+//   * everything per tile (tickets, ordered-offset scan, prefetch, warp scans) is paid once per 32 L starts.
+//
+// A warp owns a tile end to end and never meets another warp at a barrier, as in sk3: tiles come from a ticket counter,
+// the ordered output offset from the two-level chained scan, records are written KB-1 tiles after they were computed.
+#pragma once
+#include "common.cuh"
+#include "kernels.h"
+
+namespace blg {
+
+namespace {
+
+constexpr int NT4 = 32;
+constexpr int WARPS4 = SK4_THREADS / 32;
+constexpr int PADF4 = 3;     // zero words in front of the big-endian stream
+
+template <int B, int NB>
+struct Geo4 {
+    static constexpr int L = NB * B;                    // starts per lane (its span), <= 32
+    static constexpr int S = NT4 * L;                   // m-mer starts hashed per tile
+    static constexpr int OWN = NT4 * NB - 3;            // blocks 1 .. 32 NB - 3 own record starts (w = B + 1)
+    static constexpr int R = OWN * B;                   // new windows per tile
+    static constexpr int NWORDS = S / 16 + 3;           // staged 16-base words: 15 (alignment) + S + 32 (m - 1) bases
+    static constexpr int NROW = (NWORDS + 8) / 2 + 2;   // u32 words of the packed bad-byte / sequence-start bit rows
+    static constexpr int BQ = (B + 3) / 4;              // uint4 per block of prefix keys
+    // per-warp shared memory, byte offsets
+    static constexpr int OFF_BAD = 0;                               // u32 [NROW]   bit x: base a0 + x is not ACGTU
+    static constexpr int OFF_SEQ = OFF_BAD + NROW * 4;              // u32 [NROW]   bit x: a sequence starts at a0 + x
+    static constexpr int OFF_FLAG = OFF_SEQ + NROW * 4;             // int [4]
+    static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;    // uint4 [BQ * 32 + 1]  prefix keys of each lane's block 0
+    static constexpr int OFF_BUF = OFF_P + (BQ * 32 + 1) * 16;
+    // per buffer set (tile i is written out while tiles i+1, i+2 are computed)
+    static constexpr int BUF_CW = 0;                                // u32 [NWORDS + 3]  complemented codes, little-endian
+    static constexpr int BUF_EW = BUF_CW + (NWORDS + 3) * 4;        // u32 [PADF4 + NWORDS + 3]  codes, big-endian words
+    static constexpr int BUF_IDX = (BUF_EW + (PADF4 + NWORDS + 3) * 4 + 15) / 16 * 16;   // u8 [32 * 32]  argmin index, [lane][j]
+    static constexpr int BUF_EBW = BUF_IDX + 32 * 32;               // u32 [33 + 3]  record-end bits of each lane's span
+    static constexpr int BUF_REC = BUF_EBW + 36 * 4;                // u16 [R + 8]  record starts (lane << 5 | j)
+    static constexpr int BUF_BYTES = (BUF_REC + (R + 8) * 2 + 15) / 16 * 16;
+#ifdef SK4_KB
+    static constexpr int KB = SK4_KB;
+#else
+    static constexpr int KB = 3;
+#endif
+    static constexpr int WARP_BYTES = (OFF_BUF + KB * BUF_BYTES + 127) / 128 * 128;
+};
+
+__device__ __forceinline__ u32 pairrev32_4(u32 x)
+{
+    x = __brev(x);
+    return ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+}
+
+// (h & mask) | idx in one LOP3: the mask is a kernel argument so that it stays a register / constant-bank operand
+__device__ __forceinline__ u32 make_key(u32 h, u32 mask, u32 idx)
+{
+    u32 k;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(h), "r"(mask), "r"(idx));
+    return k;
+}
+
+// murmur3_key8 with a 32-bit s8 (the seed is 32 bits wide, hash.hpp:50): the high words of both `^= s8` / `+= s8` vanish
+__device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
+{
+    u64 k1 = key * 0x87c37b91114253d5ULL;
+    k1 = rotl64(k1, 31);
+    k1 *= 0x4cf5ad432745937fULL;
+    u64 h1 = k1 ^ (u64)s8;
+    u64 h2 = (u64)s8;
+    h1 += h2; h2 += h1;
+    h1 = fmix64(h1); h2 = fmix64(h2);
+    return h1 + h2;
+}
+
+// low NBITS bits: OR over d in [0, span) of bit (bitpos + i + d + shift) of the packed bit row, for i = 0 .. NBITS-1
+// (NBITS + span + shift <= 96)
+template <int NBITS>
+__device__ __forceinline__ u32 or_span_bits4(const u32* row, int bitpos, int span, int shift)
+{
+    const int wq = bitpos >> 5, sh = bitpos & 31;
+    const u32 w0 = row[wq], w1 = row[wq + 1], w2 = row[wq + 2], w3 = row[wq + 3];
+    u32 x0 = __funnelshift_r(w0, w1, sh), x1 = __funnelshift_r(w1, w2, sh), x2 = __funnelshift_r(w2, w3, sh);
+    if (shift) { x0 = __funnelshift_r(x0, x1, 1); x1 = __funnelshift_r(x1, x2, 1); x2 >>= 1; }
+    int covered = 1;
+    while (covered < span) {
+        int step = covered < span - covered ? covered : span - covered;
+        covered += step;
+        u32 y0 = x0, y1 = x1, y2 = x2;
+        if (step >= 32) { y0 = y1; y1 = y2; y2 = 0; step -= 32; }
+        if (step) { y0 = __funnelshift_r(y0, y1, step); y1 = __funnelshift_r(y1, y2, step); y2 >>= step; }
+        x0 |= y0; x1 |= y1; x2 |= y2;
+    }
+    return NBITS >= 32 ? x0 : (x0 & ((1u << (NBITS & 31)) - 1u));
+}
+
+struct TileConst4 {
+    u32 maskhi, masklo, keymask, s8;
+    int w, m, k;
+};
+
+template <int N>
+__device__ __forceinline__ u32 word_or_zero(const u32 (&a)[N], int i) { return (i >= 0 && i < N) ? a[i] : 0u; }
+
+// canonical-or-forward m-mer value at local base index xj, cut out of the staged streams with run-time shifts
+template <bool CANON, bool MW>
+__device__ __forceinline__ u64 mmer_from_smem(const u32* CW, const u32* EW, int xj, const TileConst4& c)
+{
+    u64 val;
+    {
+        const int e = 2 * xj + 2 * c.m + 32 * PADF4 - 64;     // the 64 bits that end with the m-mer's last base
+        const int wj = e >> 5, fs = e & 31;
+        const u32 e0 = EW[wj], e1 = EW[wj + 1], e2 = EW[wj + 2];
+        u32 fhi = __funnelshift_l(e1, e0, fs), flo = __funnelshift_l(e2, e1, fs);
+        if (MW) fhi &= c.maskhi; else { fhi = 0; flo &= c.masklo; }
+        val = ((u64)fhi << 32) | flo;
+    }
+    if (CANON) {
+        const int wi = xj >> 4, sh = (xj & 15) * 2;
+        const u32 c0 = CW[wi], c1 = CW[wi + 1], c2 = CW[wi + 2];
+        u32 rlo = __funnelshift_r(c0, c1, sh), rhi = __funnelshift_r(c1, c2, sh);
+        if (MW) rhi &= c.maskhi; else { rhi = 0; rlo &= c.masklo; }
+        const u64 rc = ((u64)rhi << 32) | rlo;
+        val = rc < val ? rc : val;
+    }
+    return val;
+}
+
+// Exact redo of a tile's window minima (full 64-bit hash compares, leftmost on ties: the strict '<' of reference
+// include/minimizer_view.hpp:283,374), taken when the 32-bit keys saw a tie in their hash part. Every lane hashes its
+// span once into a per-warp global scratch row (L2-resident) and scans the w entries of each of its windows. Writes the
+// same products as the fast path: the argmin index of every window (IDXB) and the lane's change bits (returned).
+template <int B, int NB, bool CANON, bool MW>
+__device__ __noinline__ u32 exact_tile4(const u32* CW, const u32* EW, unsigned char* IDXB, TileConst4 c, int o, int t, u64* hx)
+{
+    constexpr int L = NB * B, W = B + 1;
+    const int x0 = o + L * t;
+#pragma unroll 1
+    for (int j = 0; j < L; ++j) {
+        const u64 v = mmer_from_smem<CANON, MW>(CW, EW, x0 + j, c);
+        hx[j * 32 + t] = murmur3_key8_s32(v, c.s8);
+    }
+    __syncwarp();
+    u32 dif = 0;
+    int pos_next = 0, pos0 = 0, pos_last = 0;
+#pragma unroll 1
+    for (int j = L - 1; j >= 0; --j) {
+        u64 best = 0;
+        int bd = 0;
+#pragma unroll 1
+        for (int d = 0; d < W; ++d) {
+            int jq = j + d, tq = t;
+            if (jq >= L) { jq -= L; tq = t + 1; }
+            tq = tq > 31 ? 31 : tq;                    // lane 31's last windows are margin: any in-bounds value will do
+            const u64 h = __ldcg(&hx[jq * 32 + tq]);
+            if (d == 0 || h < best) { best = h; bd = d; }
+        }
+        const int pos = j + bd;                         // relative to this lane's first start
+        IDXB[t * 32 + j] = (unsigned char)(pos >= L ? pos - L : pos);
+        if (j < L - 1) dif |= (u32)(pos_next != pos) << j;
+        if (j == L - 1) pos_last = pos;
+        if (j == 0) pos0 = pos;
+        pos_next = pos;
+    }
+    const int nxt = __shfl_down_sync(0xffffffffu, pos0, 1) + L;
+    dif |= (u32)(nxt != pos_last) << (L - 1);
+    __syncwarp();
+    return dif;
+}
+
+// Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
+template <int B, int NB, int LW, bool CANON, bool MW>
+__device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
+                                             bool have_pre, uint4 pre0, uint4 pre1, u64* hx)
+{
+    using G = Geo4<B, NB>;
+    constexpr int L = G::L;
+    constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
+    const long long g0 = a.org + tile * (long long)G::R - B;     // global position of local start 0 (block 0 = left margin)
+    const long long a0 = g0 & ~15LL;                              // staged range starts on a 16-base boundary
+    const int o = (int)(g0 - a0);
+    unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
+    u32* BAD = reinterpret_cast<u32*>(wsm + G::OFF_BAD);
+    u32* SEQ = reinterpret_cast<u32*>(wsm + G::OFF_SEQ);
+    int* FLAG = reinterpret_cast<int*>(wsm + G::OFF_FLAG);
+    uint4* P = reinterpret_cast<uint4*>(wsm + G::OFF_P);
+    u32* CW = reinterpret_cast<u32*>(buf + G::BUF_CW);
+    u32* EW = reinterpret_cast<u32*>(buf + G::BUF_EW);
+    unsigned char* IDXB = buf + G::BUF_IDX;
+    u32* EBW = reinterpret_cast<u32*>(buf + G::BUF_EBW);
+    unsigned short* REC = reinterpret_cast<unsigned short*>(buf + G::BUF_REC);
+
+    // ---- stage: ASCII -> packed streams + bad-byte bits -----------------------------------------------------------
+    int anybad = 0;
+    {
+        unsigned short* BAD16 = reinterpret_cast<unsigned short*>(BAD);
+#pragma unroll
+        for (int wi = t; wi < 2 * G::NROW; wi += NT4) {
+            u32 codes = 0, bad = 0xFFFFu;
+            if (wi < G::NWORDS) {
+                const long long P16 = a0 + 16LL * wi;
+                u32 w0, w1, w2, w3;
+                if (have_pre) {
+                    const uint4 v = wi < NT4 ? pre0 : pre1;
+                    w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                } else if (a.vec_ok && P16 >= a.buf_lo && P16 + 16 <= a.buf_hi) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P16 - a.buf_lo)));
+                    w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                } else {
+                    w0 = w1 = w2 = w3 = 0;                 // tile edges / unaligned buffers: byte loads, rolled
+#pragma unroll 1
+                    for (int q = 0; q < 16; ++q) {
+                        const long long pos = P16 + q;
+                        const u32 byte = (pos >= a.buf_lo && pos < a.buf_hi) ? (u32)a.bases[pos - a.buf_lo] : 0u;
+                        const u32 sh = byte << (8 * (q & 3));
+                        if (q < 4) w0 |= sh; else if (q < 8) w1 |= sh; else if (q < 12) w2 |= sh; else w3 |= sh;
+                    }
+                }
+                blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
+                anybad |= (bad != 0);
+            }
+            if (wi < G::NWORDS + 3) {
+                CW[wi] = ~codes;
+                EW[PADF4 + wi] = pairrev32_4(codes);
+            }
+            BAD16[wi] = (unsigned short)bad;
+        }
+        if (t < PADF4) EW[t] = 0;
+        for (int x = t; x < G::NROW; x += NT4) SEQ[x] = 0;
+        if (t == 0) { FLAG[0] = 0; EBW[32] = 0; }
+    }
+    __syncwarp();
+    const int dirty = __any_sync(0xffffffffu, anybad);
+    if (a.seq_offsets != nullptr) {
+        // interior sequence starts inside the staged range
+        const long long lo_pos = a0 < 0 ? 0 : a0, end_pos = a0 + 16LL * G::NWORDS;
+        const long long lo = first_offset_at_or_after(a.seq_offsets, a.n_seq, lo_pos, a.buf_hi, t);
+        int found = 0;
+        for (long long q = lo + t; q < a.n_seq; q += 32) {
+            const long long off = (long long)a.seq_offsets[q];
+            if (off >= end_pos) break;
+            const int rel = (int)(off - a0);
+            atomicOr(&SEQ[rel >> 5], 1u << (rel & 31));
+            found = 1;
+        }
+        if (found) FLAG[0] = 1;
+        __syncwarp();
+    }
+    const int seqdirty = (a.seq_offsets != nullptr) && FLAG[0];
+
+    // ---- lane-local streams ---------------------------------------------------------------------------------------
+    const int x0 = o + L * t;                                  // base index of this lane's first start, from a0
+    u32 Rl[LW], Fl[LW];
+    {
+        const int wi0 = x0 >> 4, sh = (x0 & 15) * 2;
+        u32 cw[LW + 1];
+#pragma unroll
+        for (int j = 0; j <= LW; ++j) cw[j] = CW[wi0 + j];
+#pragma unroll
+        for (int j = 0; j < LW; ++j) Rl[j] = __funnelshift_r(cw[j], cw[j + 1], sh);   // Rl[0] = least significant
+        // big-endian side: the 32*LW bits that END with the last base of this lane's last m-mer
+        const int bp = 2 * (x0 + L - 1 + c.m) - 32 * LW + 32 * PADF4;
+        const int wj = bp >> 5, fs = bp & 31;
+        u32 ew[LW + 1];
+#pragma unroll
+        for (int j = 0; j <= LW; ++j) ew[j] = EW[wj + j];
+#pragma unroll
+        for (int j = 0; j < LW; ++j) Fl[j] = __funnelshift_l(ew[j + 1], ew[j], fs);   // Fl[0] = most significant
+    }
+
+    // ---- validity of the lane's windows (before the minima: a lane without a valid window cannot force the exact path) --
+    u32 V = ML;
+    if (dirty | seqdirty) {
+        u32 inv = 0;
+        if (dirty) inv |= or_span_bits4<L>(BAD, x0, c.k, 0);
+        if (seqdirty && c.k > 1) inv |= or_span_bits4<L>(SEQ, x0, c.k - 1, 1);
+        V = ~inv & ML;
+    }
+
+    // ---- pass 1: one hash per m-mer start -> 32-bit key; running prefix minimum of every block ------------------------
+    u32 ks[L];
+    u32 pkr[NB > 1 ? (NB - 1) * B : 1];        // prefix keys of blocks 1 .. NB-1 (block 0's go to the previous lane through P)
+    u32 tacc = 0xFFFFFFFFu;                    // min over all compares of (right key - left key): below 32 <=> a hash-part tie
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+        u32 pm = 0;
+        u32 q4[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < B; ++i) {
+            const int j = nb * B + i;
+            u32 flo, fhi = 0;
+            {
+                const int cI = 2 * (L - 1 - j), wq = cI >> 5, sh = cI & 31;
+                flo = __funnelshift_r(word_or_zero(Fl, LW - 1 - wq), word_or_zero(Fl, LW - 2 - wq), sh);
+                if (MW) fhi = __funnelshift_r(word_or_zero(Fl, LW - 2 - wq), word_or_zero(Fl, LW - 3 - wq), sh) & c.maskhi;
+                else flo &= c.masklo;
+            }
+            u64 val = ((u64)fhi << 32) | flo;
+            if (CANON) {
+                const int bo = 2 * j, wq = bo >> 5, sh = bo & 31;
+                u32 rlo = __funnelshift_r(word_or_zero(Rl, wq), word_or_zero(Rl, wq + 1), sh), rhi = 0;
+                if (MW) rhi = __funnelshift_r(word_or_zero(Rl, wq + 1), word_or_zero(Rl, wq + 2), sh) & c.maskhi;
+                else rlo &= c.masklo;
+                const u64 rc = ((u64)rhi << 32) | rlo;
+                val = rc < val ? rc : val;
+            }
+            const u32 hh = (u32)(murmur3_key8_s32(val, c.s8) >> 32);
+            ks[j] = make_key(hh, c.keymask, (u32)j);
+            if (i == 0) pm = ks[j];
+            else { tacc = min(tacc, ks[j] - pm); pm = min(pm, ks[j]); }
+            if (nb == 0) {
+                q4[i & 3] = pm;
+                if ((i & 3) == 3 || i == B - 1) P[(i >> 2) * 32 + t] = make_uint4(q4[0], q4[1], q4[2], q4[3]);
+            } else pkr[(nb - 1) * B + i] = pm;
+        }
+    }
+    __syncwarp();
+
+    // ---- pass 2: suffix minimum + combine with the prefix of the next block: the minimum key of every window -----------
+    u32 mv[L];
+#pragma unroll
+    for (int nb = NB - 1; nb >= 0; --nb) {
+        u32 np[G::BQ * 4];
+        if (nb == NB - 1) {
+#pragma unroll
+            for (int q = 0; q < G::BQ; ++q) {
+                const uint4 e = P[q * 32 + t + 1];
+                np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < B; ++i) np[i] = pkr[nb * B + i];
+        }
+        u32 sm = 0;
+#pragma unroll
+        for (int i = B - 1; i >= 0; --i) {
+            const int j = nb * B + i;
+            if (i == B - 1) sm = ks[j];
+            else { tacc = min(tacc, sm - ks[j]); sm = min(ks[j], sm); }
+            // the next block is the next lane's block 0 (smaller indices) for the last block, this lane's block nb+1 otherwise
+            if (nb == NB - 1) tacc = min(tacc, sm - np[i]);
+            else tacc = min(tacc, np[i] - sm);
+            mv[j] = min(sm, np[i]);
+        }
+    }
+
+    // ---- argmin index of every window -> shared memory; change bits ----------------------------------------------------
+    {
+        u32 wv[(L + 3) / 4];
+#pragma unroll
+        for (int q = 0; q < (L + 3) / 4; ++q) {
+            const u32 m0 = mv[4 * q], m1 = 4 * q + 1 < L ? mv[4 * q + 1] : 0u, m2 = 4 * q + 2 < L ? mv[4 * q + 2] : 0u,
+                      m3 = 4 * q + 3 < L ? mv[4 * q + 3] : 0u;
+            wv[q] = __byte_perm(__byte_perm(m0, m1, 0x0040), __byte_perm(m2, m3, 0x0040), 0x5410);
+        }
+        u32* IW = reinterpret_cast<u32*>(IDXB + t * 32);
+#pragma unroll
+        for (int q = 0; q + 4 <= (L + 3) / 4; q += 4) *reinterpret_cast<uint4*>(IW + q) = make_uint4(wv[q], wv[q + 1], wv[q + 2], wv[q + 3]);
+#pragma unroll
+        for (int q = ((L + 3) / 4) / 4 * 4; q < (L + 3) / 4; ++q) IW[q] = wv[q];
+    }
+    u32 dif = 0;
+#pragma unroll
+    for (int j = 0; j + 1 < L; ++j) dif |= (u32)(mv[j + 1] != mv[j]) << j;
+    {
+        const u32 nv0 = __shfl_down_sync(0xffffffffu, mv[0], 1);
+        dif |= (u32)(nv0 != mv[L - 1]) << (L - 1);
+    }
+#ifndef SK4_NO_EXACT     // timing experiments only: without the redo a tile with ties may be wrong
+    if (__any_sync(0xffffffffu, tacc < 32u && V != 0u)) {
+        dif = exact_tile4<B, NB, CANON, MW>(CW, EW, IDXB, c, o, t, hx);
+        if (t == 0 && a.exact_tiles != nullptr) atomicAdd(a.exact_tiles, 1ULL);
+    }
+#endif
+
+    // ---- record ends / starts -----------------------------------------------------------------------------------------
+    const u32 Vn = (V >> 1) | ((__shfl_down_sync(0xffffffffu, V, 1) & 1u) << (L - 1));
+    const u32 E = V & (~Vn | dif) & ML;        // the record ends with this window
+    const u32 X = (E | ~V) & ML;               // the next window cannot continue a record
+    EBW[t] = E;
+    const u32 xprev = (__shfl_up_sync(0xffffffffu, X, 1) >> (L - 1)) & 1u;
+    u32 start = V & ((X << 1) | xprev) & ML;
+    {
+        // owned windows: local [B, B + R), clipped to the call's [win_lo, win_hi)
+        long long hi_g = a.win_hi - g0;
+        const int hi_s = hi_g > (long long)(B + G::R) ? B + G::R : (int)hi_g;
+        int lo_j = B - L * t, hi_j = hi_s - L * t;
+        lo_j = lo_j < 0 ? 0 : (lo_j > L ? L : lo_j);
+        hi_j = hi_j < 0 ? 0 : (hi_j > L ? L : hi_j);
+        const u32 lom = lo_j >= 32 ? 0u : (0xFFFFFFFFu << lo_j);
+        const u32 him = hi_j >= 32 ? 0xFFFFFFFFu : ((1u << hi_j) - 1u);
+        start &= lom & him;
+    }
+    const u32 cnt = __popc(start);
+    u32 incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (t >= d) incl += v;
+    }
+    {
+        unsigned short* rp = REC + (incl - cnt);
+        u32 sm = start;
+        const u32 tag = (u32)t << 5;
+        while (sm) {
+            const int i = __ffs((int)sm) - 1;
+            sm &= sm - 1;
+            *rp++ = (unsigned short)(tag | (u32)i);
+        }
+    }
+    __syncwarp();
+    return __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// Record-parallel output of a finished tile from buffer set b: `n_rec` records, the first one at global index `base`.
+template <int B, int NB, bool CANON, bool MW>
+__device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
+                                           u32 n_rec, u64 base)
+{
+    using G = Geo4<B, NB>;
+    constexpr int L = G::L;
+    const long long g0 = a.org + tile * (long long)G::R - B;
+    const int o = (int)(g0 - (g0 & ~15LL));
+    const unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
+    const u32* CW = reinterpret_cast<const u32*>(buf + G::BUF_CW);
+    const u32* EW = reinterpret_cast<const u32*>(buf + G::BUF_EW);
+    const unsigned char* IDXB = buf + G::BUF_IDX;
+    const u32* EBW = reinterpret_cast<const u32*>(buf + G::BUF_EBW);
+    const unsigned short* REC = reinterpret_cast<const unsigned short*>(buf + G::BUF_REC);
+    for (u32 r = t; r < n_rec; r += NT4) {
+        const u32 rec = REC[r];
+        const int t0 = (int)(rec >> 5), j0 = (int)(rec & 31u);
+        const int idx = IDXB[rec] & 63;
+        // an index below the window's own offset belongs to the next lane's span (a window is shorter than a span)
+        const int rel = idx - j0 + (idx < j0 ? L : 0);         // mm_pos
+        const int j = L * t0 + j0 + rel;                        // local m-mer start
+        // size: distance to the first record-end bit at or after the start, at most w
+        int size;
+        {
+            const u32 e0 = EBW[t0], e1 = EBW[t0 + 1];
+            const u32 bits = L == 32 ? __funnelshift_r(e0, e1, j0) : ((e0 >> j0) | (e1 << ((L - j0) & 31)));
+            size = bits ? __ffs((int)bits) : c.w;
+            size = size < c.w ? size : c.w;
+        }
+        const u64 val = mmer_from_smem<CANON, MW>(CW, EW, o + j, c);
+        const u64 g = base + r;
+        if (g < a.capacity) {
+            a.value[g] = val;
+            a.mm_start[g] = (u64)(g0 + j);
+            if (a.size != nullptr) { a.size[g] = (u8)size; a.mm_pos[g] = (u8)rel; }
+            if (a.hash != nullptr) a.hash[g] = murmur3_key8_s32(val, c.s8);
+        }
+    }
+    __syncwarp();   // this buffer set is restaged by a later compute_tile
+}
+
+// ---- ordered output offset without any CTA barrier: the two-level chained scan of sk3 (tiles -> groups of 32) ------------
+constexpr int GS4 = 32;
+constexpr u64 TS_SET4 = 1ULL << 62;
+constexpr u64 ACC_ONE4 = 1ULL << 40, ACC_MASK4 = ACC_ONE4 - 1;
+
+__device__ __forceinline__ void spin_wait4(u32& spins)
+{
+    __nanosleep(64);
+#ifdef BLG_DEBUG_SPIN
+    if (++spins > (1u << 28)) __trap();   // debug builds only: a protocol bug must not hang the GPU
+#else
+    (void)spins;
+#endif
+}
+
+__device__ __forceinline__ const u64* tile_base_addr4(const SkArgs& a, long long tile, int t)
+{
+    const long long g = tile / GS4;
+    const int idx = (int)(tile - g * GS4);
+    if (t < idx) return a.tile_status + g * GS4 + t;
+    if (t == 31 && g > 0) return a.grp_status + (g - 1);
+    return nullptr;
+}
+// lanes below the tile's index in its group hold the earlier tiles' counts (small), lane 31 the inclusive prefix of the
+// previous group (64-bit): one REDUX for the counts, one 64-bit broadcast
+__device__ __forceinline__ u64 tile_base_finish4(const u64* p, u64 v, int t)
+{
+    if (p != nullptr) {
+        u32 spins = 0;
+        if (t == 31) { while ((v >> 62) != 2) { spin_wait4(spins); v = ld_status(p); } }
+        else { while (!(v & TS_SET4)) { spin_wait4(spins); v = ld_status(p); } }
+        v &= ST_VAL;
+    }
+    const u32 small = t == 31 ? 0u : (u32)v;
+    const u32 s = __reduce_add_sync(0xffffffffu, small);
+    const u64 g = __shfl_sync(0xffffffffu, v, 31);
+    return g + s;
+}
+
+}  // namespace
+
+template <int B, int NB, int LW, bool CANON, bool MW>
+__global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const SkArgs a)
+{
+    using G = Geo4<B, NB>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
+    u64* hx = a.exact_scratch + ((size_t)blockIdx.x * WARPS4 + warp) * (size_t)(32 * 32);
+
+    TileConst4 c;
+    c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = (u32)a.s8; c.keymask = a.keymask;
+    c.maskhi = MW ? (c.m == 32 ? 0xFFFFFFFFu : ((1u << (2 * c.m - 32)) - 1u)) : 0u;
+    c.masklo = MW ? 0xFFFFFFFFu : (c.m == 16 ? 0xFFFFFFFFu : ((1u << (2 * c.m)) - 1u));
+
+    const long long num_groups = (a.num_tiles + GS4 - 1) / GS4;
+    u32 tk = 0;
+    if (t == 0) tk = atomicAdd(a.tile_counter, 1u);
+    long long tile = __shfl_sync(0xffffffffu, tk, 0);
+    // computed, not yet written out: (t0, n0, b0) the newer, (t1, n1, b1) the older (KB == 3 only): tile, records, buffer set
+    long long t0 = -1, t1 = -1;
+    u32 n0 = 0, n1 = 0;
+    int b0 = 0, b1 = 0;
+    bool have_pre = false;
+    uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
+    int b = 0;                          // buffer set of the tile computed in this iteration
+    // Every warp runs on its own: compute tile i, publish its count, write out tile i-(KB-1) from its buffer set.
+    // A ticket is taken only when nothing can block any more before that tile is published (a warp that waits for a
+    // prefix while it holds an uncomputed tile stalls that tile's group, the groups behind it, and so itself: convoys).
+    for (;;) {
+        const bool have = tile < a.num_tiles;
+        // the tile to write out now: the older pending one once two are queued, or whatever is left when draining
+        const bool from1 = G::KB == 3 && t1 >= 0;
+        const long long prev = G::KB == 3 ? (from1 ? t1 : (have ? -1 : t0)) : t0;
+        const u32 prev_n = from1 ? n1 : n0;
+        const int pb = from1 ? b1 : b0;
+        if (!have && prev < 0) break;
+        u32 n_rec = 0;
+        u64 old = 0;
+        if (have) {
+            n_rec = compute_tile4<B, NB, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1, hx);
+            if (t == 0) {
+                st_status(&a.tile_status[tile], TS_SET4 | n_rec);
+                old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
+            }
+        }
+        const u64* bp = prev >= 0 ? tile_base_addr4(a, prev, t) : nullptr;
+        u64 bv = 0;
+        if (bp != nullptr) bv = ld_status(bp);
+        if (have) {
+            // did this tile complete its group (the add counts arrivals)? then this warp resolves the group
+            const long long g = tile / GS4;
+            const long long rest = a.num_tiles - g * GS4;
+            const u64 expect = (u64)(rest < GS4 ? rest : GS4);
+            const u64 o0 = __shfl_sync(0xffffffffu, old, 0);
+            if ((o0 >> 40) == expect - 1) {
+                const u64 gsum = (o0 & ACC_MASK4) + n_rec;
+                const u64 excl = lookback_exclusive(a.grp_status, g, gsum, t);
+                if (t == 0 && g == num_groups - 1) *a.total = excl + gsum;
+            }
+        }
+        u64 base = 0;
+        if (prev >= 0) base = tile_base_finish4(bp, bv, t);
+        u32 nx = 0xFFFFFFFFu;
+        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u);
+        if (prev >= 0) emit_tile4<B, NB, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
+        const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
+        have_pre = false;
+        {
+            const long long ng0 = a.org + next_tile * (long long)G::R - B;
+            const long long P0 = (ng0 & ~15LL) - a.buf_lo;
+            if (next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
+                have_pre = true;
+                if (t < G::NWORDS) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + t);
+                if (G::NWORDS > NT4 && t < G::NWORDS - NT4) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT4 + t);
+            }
+        }
+        // queue: drop what was written, push what was computed
+        if (G::KB == 3) {
+            if (have || from1) { t1 = t0; n1 = n0; b1 = b0; }
+            t0 = have ? tile : -1; n0 = n_rec; b0 = b;
+        } else { t0 = have ? tile : -1; n0 = n_rec; b0 = b; }
+        tile = next_tile;
+        b = (b + 1) % G::KB;
+    }
+}
+
+}  // namespace blg

@@ -1,0 +1,93 @@
+// sk4_kernel.cu -- host side of the fourth-generation fused minimizer / super-k-mer kernel (device code and the
+// description of the scheme: sk4_device.cuh): which (k, m) it serves, the launch geometry, the launch.
+#include "sk4_device.cuh"
+
+namespace blg {
+
+namespace {
+
+struct Variant4 { int B, NB, LW, MW; };
+
+// w = B + 1 with a lane span L = NB B <= 32 and the lane-local streams wide enough: 2 (L + m - 1) <= 32 LW.
+bool pick_variant4(int k, int m, Variant4* v)
+{
+    const int d = k - m;
+    if (m < 1 || m > 32 || k > 64) return false;
+    if (d == 12 && m >= 17 && m <= 25) { *v = {12, SK4_NB12, 3, 1}; return true; }   // k=31 m=19 (configs 2, 3)
+    if (d == 10 && m <= 16) { *v = {10, SK4_NB10, 3, 0}; return true; }              // k=21 m=11 (config 5)
+    return false;
+}
+
+template <int B, int NB, int LW, bool CANON, bool MW>
+cudaError_t setup4(size_t smem, int* occ)
+{
+    cudaError_t e = cudaFuncSetAttribute(sk4_kernel<B, NB, LW, CANON, MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, sk4_kernel<B, NB, LW, CANON, MW>, SK4_THREADS, smem);
+}
+
+template <int B, int NB, int LW, bool MW>
+cudaError_t setup4c(bool canon, size_t smem, int* occ)
+{
+    return canon ? setup4<B, NB, LW, true, MW>(smem, occ) : setup4<B, NB, LW, false, MW>(smem, occ);
+}
+
+template <int B, int NB, int LW, bool MW>
+void launch4c(bool canon, const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
+{
+    if (canon) sk4_kernel<B, NB, LW, true, MW><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+    else sk4_kernel<B, NB, LW, false, MW><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
+}
+
+template <int B, int NB>
+size_t smem4() { return (size_t)Geo4<B, NB>::WARP_BYTES * WARPS4; }
+
+}  // namespace
+
+bool sk4_supported(int k, int m)
+{
+    Variant4 v;
+    return pick_variant4(k, m, &v);
+}
+
+cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
+{
+    Variant4 v;
+    if (!pick_variant4(args.k, args.m, &v)) return cudaErrorInvalidValue;
+    int R = 0;
+    size_t smem = 0;
+    int occ = 0;
+    cudaError_t e = cudaSuccess;
+    const bool canon = args.canonical != 0;
+    if (v.B == 12) { R = Geo4<12, SK4_NB12>::R; smem = smem4<12, SK4_NB12>(); e = setup4c<12, SK4_NB12, 3, true>(canon, smem, &occ); }
+    else { R = Geo4<10, SK4_NB10>::R; smem = smem4<10, SK4_NB10>(); e = setup4c<10, SK4_NB10, 3, false>(canon, smem, &occ); }
+    if (e != cudaSuccess) return e;
+    args.R = R;
+    args.org = args.win_lo;
+    args.keymask = ~63u;
+    const long long nwin = args.win_hi > args.org ? args.win_hi - args.org : 0;
+    args.num_tiles = args.win_hi > args.win_lo ? (nwin + R - 1) / R : 0;
+    args.status_words = args.num_tiles + 2 * ((args.num_tiles + 31) / 32) + 8;
+    plan->threads = SK4_THREADS;
+    plan->smem_bytes = smem;
+    if (occ < 1) occ = 1;
+    long long grid = (long long)sm_count * occ;
+    const long long units = (args.num_tiles + WARPS4 - 1) / WARPS4;
+    if (grid > units) grid = units;
+    plan->grid = (int)(grid < 1 ? 1 : grid);
+    return cudaSuccess;
+}
+
+size_t sk4_exact_scratch_bytes(const SkLaunchPlan& plan) { return (size_t)plan.grid * WARPS4 * 32 * 32 * sizeof(unsigned long long); }
+
+cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
+{
+    Variant4 v;
+    if (!pick_variant4(args.k, args.m, &v)) return cudaErrorInvalidValue;
+    const bool canon = args.canonical != 0;
+    if (v.B == 12) launch4c<12, SK4_NB12, 3, true>(canon, args, plan, stream);
+    else launch4c<10, SK4_NB10, 3, false>(canon, args, plan, stream);
+    return cudaGetLastError();
+}
+
+}  // namespace blg

@@ -5,8 +5,12 @@ include/sequence_generator.hpp:14-23,34-39): std::mt19937 seeded with the 32-bit
 base through std::uniform_int_distribution<uint8_t>(0,3), mapped through constants::bases = "ACGT"
 (include/constants.hpp:23). With libstdc++ and a 32-bit engine that distribution is the top two bits of each
 draw (Lemire multiply-shift with range 4, never rejecting), so the sequence is "ACGT"[draw >> 30];
-tests/test_synth.py pins this against the reference executed here (seed 42 -> CTTAGTGGACAAACTCGAGG...).
+tests/test_host_side.py pins this against the reference executed here (seed 42 -> CTTAGTGGACAAACTCGAGG...).
 numpy's legacy MT19937 seeding is init_genrand(seed), i.e. exactly std::mt19937(seed).
+
+``mutate`` is wrapper::sequence_mutator (reference include/sequence_mutator.hpp:109-169) through the library's host
+entry point blg_synth_mutate (csrc/synth_host.cpp: libstdc++'s std::mt19937 + std::uniform_real_distribution, the
+reference's own draws), pinned against the reference executed here by tests/test_host_side.py.
 
 The reference's sequence_mutator never produces N (include/sequence_mutator.hpp:133-168), so the read
 configurations use ``inject_n_runs``, a builder-owned seeded N injector.
@@ -80,3 +84,47 @@ def generate_sharded_parallel(seed0: int, length: int, shard: int = 1 << 26, thr
     with ThreadPoolExecutor(threads or min(32, os.cpu_count() or 1)) as ex:
         list(ex.map(lambda j: generate(seed0 + j[0], j[2], out=out[j[1]:j[1] + j[2]]), jobs))
     return out
+
+
+def mutate(seq, mutp: float, indelf: float, extp: float, seed: int, with_report: bool = False):
+    """The reference's ``sequence_mutator(seq, mutp, indelf, extp)`` iterated from ``cbegin(seed)`` to ``cend()`` with the
+    absent values (deleted bases) dropped: uint8 ASCII out. ``seq`` must hold AaCcGgTtUu only."""
+    import ctypes as C
+    from . import _capi
+    L = _capi.lib()
+    src = np.ascontiguousarray(np.frombuffer(seq.encode() if isinstance(seq, str) else seq, dtype=np.uint8)
+                               if not isinstance(seq, np.ndarray) else seq, dtype=np.uint8)
+    cap = int(src.size * (1.0 + 2.0 * mutp) + 1024)
+    counts = (C.c_uint64 * 3)()
+    tot = C.c_int64()
+    n_out = C.c_size_t()
+    for _ in range(2):
+        out = np.empty(cap, dtype=np.uint8)
+        rc = L.blg_synth_mutate(src.ctypes.data, src.size, mutp, indelf, extp, int(seed) & (2**64 - 1), out.ctypes.data, cap,
+                                C.byref(n_out), C.cast(counts, C.c_void_p), C.cast(C.pointer(tot), C.c_void_p))
+        if rc != _capi.BLG_E_CAPACITY:
+            break
+        cap = n_out.value
+    if rc != _capi.BLG_OK:
+        raise ValueError(f"blg_synth_mutate: {L.blg_strerror(rc).decode()} (source must be ACGT/U only)")
+    res = out[: n_out.value].copy()
+    if with_report:
+        return res, dict(substitutions=counts[0], insertions=counts[1], deletions=counts[2], total_indel_len=tot.value)
+    return res
+
+
+def mutated_long_reads(n_reads: int, seed_len: int = 46, seed_src: int = 46, seed_mut0: int = 47, lo: int = 10_000, hi: int = 100_000,
+                       mutp: float = 0.10, indelf: float = 0.3, extp: float = 0.3, threads: int | None = None):
+    """BASELINE config 5 as SURVEY 8(d) states it: read lengths ~U[lo, hi] (mt19937_64(seed_len)), read i =
+    sequence_mutator(source slice i, 0.10, 0.3, 0.3) from cbegin(seed_mut0 + i), the source slices being consecutive pieces of
+    the uniform(seed_src) stream. Returns (bases uint8, offsets uint64[n_reads + 1])."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    rng = np.random.Generator(np.random.MT19937(seed_len))
+    lens = rng.integers(lo, hi + 1, size=n_reads)
+    src = generate(seed_src, int(lens.sum()))
+    starts = np.concatenate([[0], np.cumsum(lens)])
+    with ThreadPoolExecutor(threads or min(32, os.cpu_count() or 1)) as ex:
+        reads = list(ex.map(lambda i: mutate(src[starts[i]:starts[i + 1]], mutp, indelf, extp, seed_mut0 + i), range(n_reads)))
+    offs = np.concatenate([[0], np.cumsum([r.size for r in reads])]).astype(np.uint64)
+    return (np.concatenate(reads) if reads else np.zeros(0, np.uint8)), offs

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define BLG_ABI_VERSION 1
+#define BLG_ABI_VERSION 2
 
 typedef enum blg_status {
     BLG_OK = 0,
@@ -111,6 +111,7 @@ typedef struct blg_stats {
     uint64_t kernel_launches;/* kernels of this library launched by the last call */
     double kernel_ms;        /* device time of those kernels (CUDA events on the context stream) */
     double total_ms;         /* wall time of the call */
+    uint64_t exact_tiles;    /* tiles of the fused kernel redone with full 64-bit hash compares (ties in the 32-bit keys) */
 } blg_stats;
 
 typedef struct blg_ctx blg_ctx;
@@ -184,6 +185,20 @@ int blg_syncmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t
  */
 int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
                            const blg_params* p, uint64_t threshold, blg_kmer_out* out);
+
+/*
+ * Host-side workload generators (csrc/synth_host.cpp). They run on the CPU, as the
+ * reference's own do, and feed the benchmarks / tests; nothing on the GPU path calls them.
+ *   blg_synth_generate <- sequence::generator::nucleic<packed::uniform>::get_sequence(length) with uniform(seed)
+ *                         include/sequence_generator.hpp:14-23,28-43
+ *   blg_synth_mutate   <- wrapper::sequence_mutator(src, src + n, mutp, indelf, extp).cbegin(seed) iterated to cend()
+ *                         with the absent values dropped (include/sequence_mutator.hpp:109-169, consumed as in
+ *                         tests/test_random_sequence_generation.cpp:44-48). *out_len = bases produced (the required
+ *                         size on BLG_E_CAPACITY); counts = {substitutions, insertions, deletions}, may be NULL.
+ */
+int blg_synth_generate(uint64_t seed, size_t length, char* out);
+int blg_synth_mutate(const char* src, size_t n, double mutp, double indelf, double extp, uint64_t seed, char* out,
+                     size_t capacity, size_t* out_len, uint64_t counts[3], int64_t* total_indel_len);
 
 /* release library-allocated output arrays (host pinned or device); caller-provided arrays are untouched */
 void blg_free_kmer_out(blg_ctx* ctx, blg_kmer_out* out);

@@ -540,3 +540,20 @@ def test_cpp_shim_views(gpu, oracle, tmp_path):
             X = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("X ")]
             xv = np.array([v for v, _ in X], dtype=np.uint64)
             assert [p for _, p in X] == oracle.minimizer_positions(xv, k, m).tolist() if len(X) else True
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (32, 20), (9, 5), (16, 8), (32, 1), (13, 12), (28, 12), (32, 17)])
+def test_d4_window_argmin_vs_reference_extractor(gpu, oracle, k, m):
+    """D4 of the fused kernels (sk4 / sk3 / sk2, whichever serves (k, m)) against hash::minimizer_position_extractor
+    (reference include/kmer_view.hpp:266-283): the reference-compiled library when it travelled to this box
+    (oracle/_ref), else the oracle restatement that tests/test_oracle_vs_ref.py pins to it."""
+    import pyoracle
+    from d4_util import check_d4
+    ext = pyoracle.Ref() if pyoracle.Ref.available() else oracle
+    rng = np.random.default_rng(k * 41 + m)
+    low = np.concatenate([np.frombuffer(b"A" * 2000, np.uint8), np.frombuffer(b"AC" * 1500, np.uint8), rand_seq(rng, 3000),
+                          np.frombuffer(b"ACGTTGCA" * 600, np.uint8), np.frombuffer(b"GATTACA" * 700, np.uint8)])
+    for s in (rand_seq(rng, 60_000), rand_seq(rng, 30_000, 0.002, 0.05), low):
+        rec = gpu.super_kmers(s, k, m, 0, False)
+        km = gpu.kmers(s, k, False)
+        check_d4(rec, km, np.asarray(ext.minimizer_positions(km["lo"], k, m)))

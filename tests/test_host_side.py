@@ -138,3 +138,29 @@ def test_synth_matches_reference_generator(oracle):
     assert set(np.unique(reads[changed]).tolist()) <= set(b"Nnacgt")  # lower-cased reads turn N into n (still a break)
     again = synth.inject_n_runs(before.copy(), 150, seed=44)
     assert np.array_equal(again, reads)
+
+
+def test_synth_mutator_matches_reference(oracle):
+    """biolib_b200.synth.mutate (blg_synth_mutate, csrc/synth_host.cpp) against the reference's sequence_mutator executed
+    verbatim when oracle/_ref is here, and against the oracle restatement pinned to it (tests/test_oracle_vs_ref.py)."""
+    import ctypes as C
+    import pyoracle
+    from biolib_b200 import synth, _capi
+    checkers = [oracle] + ([pyoracle.Ref()] if pyoracle.Ref.available() else [])
+    src = synth.generate(5, 6000)
+    out = np.empty(100, np.uint8)
+    assert _capi.lib().blg_synth_generate(2**32 + 42, 100, out.ctypes.data) == 0 and np.array_equal(out, oracle.generate(42, 100))
+    for seed, (mp, idf, ep) in enumerate(((0.1, 0.3, 0.3), (0.5, 0.5, 0.5), (1.0, 1.0, 0.9), (0.02, 0.0, 0.0), (0.0, 0.5, 0.5))):
+        got, rep = synth.mutate(src, mp, idf, ep, seed, with_report=True)
+        for chk in checkers:
+            b, cb, tb = chk.mutate(src, mp, idf, ep, seed)
+            assert np.array_equal(got, b), (seed, type(chk).__name__)
+            assert [rep["substitutions"], rep["insertions"], rep["deletions"]] == [int(x) for x in cb] and rep["total_indel_len"] == tb
+    assert synth.mutate(np.zeros(0, np.uint8), 0.1, 0.3, 0.3, 1).size == 0
+    assert synth.mutate("A", 0.1, 0.3, 0.3, 1).size == 0            # the last source base is never emitted
+    with pytest.raises(ValueError):
+        synth.mutate("ACGNNACGT" * 50, 0.9, 0.0, 0.3, 1)            # the reference indexes bases.at(4) here
+    bases, offs = synth.mutated_long_reads(6, lo=500, hi=900)
+    assert offs[0] == 0 and offs[-1] == bases.size and len(offs) == 7 and set(np.unique(bases).tolist()) <= set(b"ACGT")
+    b2, o2 = synth.mutated_long_reads(6, lo=500, hi=900, threads=1)
+    assert np.array_equal(bases, b2) and np.array_equal(offs, o2)

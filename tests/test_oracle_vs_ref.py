@@ -175,3 +175,19 @@ def test_hash_sampler_live(oracle, ref):
         assert thr == ctxmod.Context.hash_sampler_threshold(rate)
         h = np.array([oracle.hash64(int(x), seed) for x in v], dtype=np.uint64)
         assert np.array_equal(kept, v[h < np.uint64(thr)]), (seed, rate)
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (32, 20), (9, 5), (16, 8), (32, 1), (13, 12), (7, 7), (28, 12)])
+def test_d4_window_argmin_pinned_to_reference_extractor(oracle, ref, k, m):
+    """D4 (smallest hash, leftmost on ties) of the Tier B restatement against the reference's own
+    hash::minimizer_position_extractor executed verbatim (include/kmer_view.hpp:266-283), incl. low-complexity input
+    where ties decide."""
+    from d4_util import check_d4
+    rng = np.random.default_rng(k * 37 + m)
+    low = np.concatenate([np.frombuffer(b"A" * 200, np.uint8), np.frombuffer(b"AC" * 150, np.uint8), rand_seq(rng, 300),
+                          np.frombuffer(b"ACGTTGCA" * 60, np.uint8), np.frombuffer(b"GATTACA" * 70, np.uint8)])
+    for s in (rand_seq(rng, 4000), rand_seq(rng, 3000, 0.004, 0.05), low):
+        for brute in (False, True):
+            rec = oracle.super_kmers(s, k, m, 0, 0, brute=brute)
+            km = oracle.kmers(s, k, 0)
+            check_d4(rec, km, ref.minimizer_positions(km["lo"], k, m))
