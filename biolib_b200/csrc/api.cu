@@ -44,7 +44,6 @@ struct blg_ctx {
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi (BLG_PIPE_CHUNK_M overrides; development only)
     int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
-    DevBuf exact;                    // sk4: per-warp scratch of the exact path
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
     unsigned long long* h_total = nullptr;  // pinned
     std::string err;
@@ -157,8 +156,6 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
     if (gen == 4) {
-        if ((rc = ensure(c, c->exact, sk4_exact_scratch_bytes(plan))) != BLG_OK) return rc;
-        a.exact_scratch = static_cast<unsigned long long*>(c->exact.p);
         a.exact_tiles = static_cast<unsigned long long*>(c->small.p) + 2;
     }
     if (gen >= 3) {
@@ -573,7 +570,7 @@ int blg_destroy(blg_ctx* c)
     if (!c) return BLG_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->exact, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
+    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
                       &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
     if (c->h_total) cudaFreeHost(c->h_total);

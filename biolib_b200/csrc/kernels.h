@@ -41,7 +41,6 @@ struct SkArgs {
     unsigned long long* grp_status;    // [groups] look-back words over groups
     // fourth-generation kernel (sk4_kernel.cu): 32-bit keys (hash bits above an index field) + exact redo on ties
     unsigned int keymask;              // ~(2^index_bits - 1)
-    unsigned long long* exact_scratch; // [grid * warps per CTA][32 * 32] full hashes of a tile being redone exactly
     unsigned long long* exact_tiles;   // optional counter: tiles that took the exact path (may be null)
 };
 
@@ -79,17 +78,10 @@ cudaError_t sk3_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_
 #define SK4_THREADS 128
 #endif
 #ifndef SK4_MIN_BLOCKS
-#define SK4_MIN_BLOCKS 4
-#endif
-#ifndef SK4_NB12
-#define SK4_NB12 2     // blocks per lane for w = 13 (span 24)
-#endif
-#ifndef SK4_NB10
-#define SK4_NB10 3     // blocks per lane for w = 11 (span 30)
+#define SK4_MIN_BLOCKS 5
 #endif
 bool sk4_supported(int k, int m);
 cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
-size_t sk4_exact_scratch_bytes(const SkLaunchPlan& plan);
 cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 
 // kmer_view: every valid k-mer as (value, position), in position order.

@@ -49,7 +49,7 @@ struct Geo4 {
     // per buffer set (tile i is written out while tiles i+1, i+2 are computed)
     static constexpr int BUF_CW = 0;                                // u32 [NWORDS + 3]  complemented codes, little-endian
     static constexpr int BUF_EW = BUF_CW + (NWORDS + 3) * 4;        // u32 [PADF4 + NWORDS + 3]  codes, big-endian words
-    static constexpr int BUF_IDX = (BUF_EW + (PADF4 + NWORDS + 3) * 4 + 15) / 16 * 16;   // u8 [32 * 32]  argmin index, [lane][j]
+    static constexpr int BUF_IDX = (BUF_EW + (PADF4 + NWORDS + 3) * 4 + 15) / 16 * 16;   // u8 [32][2][16]  argmin byte of every window, [lane][block][window]
     static constexpr int BUF_EBW = BUF_IDX + 32 * 32;               // u32 [33 + 3]  record-end bits of each lane's span
     static constexpr int BUF_REC = BUF_EBW + 36 * 4;                // u16 [R + 8]  record starts (lane << 5 | j)
     static constexpr int BUF_BYTES = (BUF_REC + (R + 8) * 2 + 15) / 16 * 16;
@@ -141,52 +141,77 @@ __device__ __forceinline__ u64 mmer_from_smem(const u32* CW, const u32* EW, int 
     return val;
 }
 
-// Exact redo of a tile's window minima (full 64-bit hash compares, leftmost on ties: the strict '<' of reference
-// include/minimizer_view.hpp:283,374), taken when the 32-bit keys saw a tie in their hash part. Every lane hashes its
-// span once into a per-warp global scratch row (L2-resident) and scans the w entries of each of its windows. Writes the
-// same products as the fast path: the argmin index of every window (IDXB) and the lane's change bits (returned).
+// Exact redo of the windows a tie could have changed (full 64-bit hash compares, leftmost on ties: the strict '<' of
+// reference include/minimizer_view.hpp:283,374). `flagged` = lanes whose compares saw equal hash parts. A tie seen by
+// lane f can only concern windows [L f - B, L f + L) (its own span, and the previous lane's last block, which reads lane
+// f's block-0 prefix). The warp redoes them cooperatively in UNITS of NU = 33 - w windows: lane j hashes m-mer start
+// s + j, window s + j scans hashes j .. j + w - 1 through shuffles. A unit costs about 200 instructions, so the usual
+// case -- one equal pair of m-mers in a tile, e.g. reverse-complement neighbours at small m -- adds a fraction of a
+// tile's time, and a tile full of ties (low-complexity sequence) about four tile times. Overwrites the argmin bytes
+// of the redone windows in IDXB; the caller rebuilds its change bits from IDXB afterwards (change_bits_from_idx4).
 template <int B, int NB, bool CANON, bool MW>
-__device__ __noinline__ u32 exact_tile4(const u32* CW, const u32* EW, unsigned char* IDXB, TileConst4 c, int o, int t, u64* hx)
+__device__ __noinline__ void redo_windows4(const u32* CW, const u32* EW, unsigned char* IDXB, TileConst4 c, int o, int t, u32 flagged)
 {
-    constexpr int L = NB * B, W = B + 1;
-    const int x0 = o + L * t;
-#pragma unroll 1
-    for (int j = 0; j < L; ++j) {
-        const u64 v = mmer_from_smem<CANON, MW>(CW, EW, x0 + j, c);
-        hx[j * 32 + t] = murmur3_key8_s32(v, c.s8);
+    constexpr int L = NB * B, W = B + 1, S = 32 * L, NU = 33 - W, UNITS = (S + NU - 1) / NU;
+    static_assert(UNITS <= 64, "unit mask is 64 bits");
+    // units to redo: those that overlap [L f - B, L f + L) of a flagged lane f
+    u64 todo = 0;
+    for (u32 fm = flagged; fm; fm &= fm - 1) {
+        const int f = __ffs((int)fm) - 1;
+        int lo = L * f - B, hi = L * f + L;
+        lo = lo < 0 ? 0 : lo;
+        const int u0 = lo / NU, u1 = (hi - 1) / NU;
+        for (int u = u0; u <= u1 && u < UNITS; ++u) todo |= 1ULL << u;
     }
-    __syncwarp();
-    u32 dif = 0;
-    int pos_next = 0, pos0 = 0, pos_last = 0;
-#pragma unroll 1
-    for (int j = L - 1; j >= 0; --j) {
-        u64 best = 0;
+    for (; todo; todo &= todo - 1) {
+        const int s = (__ffsll((long long)todo) - 1) * NU;
+        const u64 h = murmur3_key8_s32(mmer_from_smem<CANON, MW>(CW, EW, o + s + t, c), c.s8);
+        u64 best = h;
         int bd = 0;
-#pragma unroll 1
-        for (int d = 0; d < W; ++d) {
-            int jq = j + d, tq = t;
-            if (jq >= L) { jq -= L; tq = t + 1; }
-            tq = tq > 31 ? 31 : tq;                    // lane 31's last windows are margin: any in-bounds value will do
-            const u64 h = __ldcg(&hx[jq * 32 + tq]);
-            if (d == 0 || h < best) { best = h; bd = d; }
+#pragma unroll
+        for (int d = 1; d < W; ++d) {
+            const u64 hd = __shfl_down_sync(0xffffffffu, h, d);
+            if (hd < best) { best = hd; bd = d; }
         }
-        const int pos = j + bd;                         // relative to this lane's first start
-        IDXB[t * 32 + j] = (unsigned char)(pos >= L ? pos - L : pos);
-        if (j < L - 1) dif |= (u32)(pos_next != pos) << j;
-        if (j == L - 1) pos_last = pos;
-        if (j == 0) pos0 = pos;
-        pos_next = pos;
+        const int ws = s + t;                          // this lane's window
+        if (t < NU && ws < S) {
+            const int gb = ws / B, i = ws - gb * B;    // block of the tile (= lane * NB + block in lane), window in block
+            const int pb = i + bd;                      // minimizer start relative to the block's first start
+            IDXB[gb * 16 + i] = (unsigned char)(pb < B ? pb : (16 | (pb - B)));
+        }
     }
-    const int nxt = __shfl_down_sync(0xffffffffu, pos0, 1) + L;
-    dif |= (u32)(nxt != pos_last) << (L - 1);
     __syncwarp();
+}
+
+// The lane's change bits (bit j: windows j and j+1 of the span have different minimizer positions) from the argmin bytes
+// in shared memory; only used after redo_windows4.
+template <int B, int NB>
+__device__ __forceinline__ u32 change_bits_from_idx4(const unsigned char* IDXB, int t)
+{
+    constexpr int L = NB * B;
+    const uint4* IW = reinterpret_cast<const uint4*>(IDXB + t * 32);
+    u32 wv[NB * 4];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) { const uint4 e = IW[nb]; wv[4 * nb] = e.x; wv[4 * nb + 1] = e.y; wv[4 * nb + 2] = e.z; wv[4 * nb + 3] = e.w; }
+    const int n0 = IDXB[(t + 1) * 32];                  // lane 31 reads the first byte behind the array: margin, any value
+    u32 dif = 0;
+    int pcur = 0;
+#pragma unroll
+    for (int j = 0; j <= L; ++j) {
+        // position of window j's minimizer relative to the lane's first start (window L = the next lane's window 0)
+        const int nb = j / B, i = j - nb * B;
+        const int byt = j < L ? (int)((wv[4 * nb + (i >> 2)] >> (8 * (i & 3))) & 31u) : (n0 & 31);
+        const int pos = nb * B + (byt & 15) + ((byt & 16) ? B : 0);
+        if (j > 0) dif |= (u32)(pos != pcur) << (j - 1);
+        pcur = pos;
+    }
     return dif;
 }
 
 // Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
 template <int B, int NB, int LW, bool CANON, bool MW>
 __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
-                                             bool have_pre, uint4 pre0, uint4 pre1, u64* hx)
+                                             bool have_pre, uint4 pre0, uint4 pre1)
 {
     using G = Geo4<B, NB>;
     constexpr int L = G::L;
@@ -263,27 +288,8 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
     }
     const int seqdirty = (a.seq_offsets != nullptr) && FLAG[0];
 
-    // ---- lane-local streams ---------------------------------------------------------------------------------------
-    const int x0 = o + L * t;                                  // base index of this lane's first start, from a0
-    u32 Rl[LW], Fl[LW];
-    {
-        const int wi0 = x0 >> 4, sh = (x0 & 15) * 2;
-        u32 cw[LW + 1];
-#pragma unroll
-        for (int j = 0; j <= LW; ++j) cw[j] = CW[wi0 + j];
-#pragma unroll
-        for (int j = 0; j < LW; ++j) Rl[j] = __funnelshift_r(cw[j], cw[j + 1], sh);   // Rl[0] = least significant
-        // big-endian side: the 32*LW bits that END with the last base of this lane's last m-mer
-        const int bp = 2 * (x0 + L - 1 + c.m) - 32 * LW + 32 * PADF4;
-        const int wj = bp >> 5, fs = bp & 31;
-        u32 ew[LW + 1];
-#pragma unroll
-        for (int j = 0; j <= LW; ++j) ew[j] = EW[wj + j];
-#pragma unroll
-        for (int j = 0; j < LW; ++j) Fl[j] = __funnelshift_l(ew[j + 1], ew[j], fs);   // Fl[0] = most significant
-    }
-
     // ---- validity of the lane's windows (before the minima: a lane without a valid window cannot force the exact path) --
+    const int x0 = o + L * t;                                  // base index of this lane's first start, from a0
     u32 V = ML;
     if (dirty | seqdirty) {
         u32 inv = 0;
@@ -292,27 +298,81 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         V = ~inv & ML;
     }
 
-    // ---- pass 1: one hash per m-mer start -> 32-bit key; running prefix minimum of every block ------------------------
-    u32 ks[L];
-    u32 pkr[NB > 1 ? (NB - 1) * B : 1];        // prefix keys of blocks 1 .. NB-1 (block 0's go to the previous lane through P)
+    // ---- the lane's blocks, left to right (a ROLLED loop: the unrolled body of one block is what the instruction cache holds).
+    // Iteration nb hashes block nb -- one 32-bit key per m-mer start (hash bits above the index INSIDE the block), running
+    // prefix minimum pk[] -- and then finishes the windows of block nb-1: suffix minimum of its own keys combined with
+    // pk[] (a window is suffix-of-own-block + prefix-of-next-block). Keys that come from the next block enter with +16, so
+    // the low byte of a window's minimum says where it is: bits 0-3 index in its block, bit 4 = next block.
+    constexpr u32 MB = (1u << B) - 1u;
     u32 tacc = 0xFFFFFFFFu;                    // min over all compares of (right key - left key): below 32 <=> a hash-part tie
+    u32 dif = 0;                               // bit j: windows j and j+1 of the span have different minimizer positions
+    u32 ks_prev[B];
+    u32 mv_first = 0, mv_last = 0;
+    // windows of one block: own keys kk[] (suffix side) and the next block's prefix keys np[]; returns the block's change
+    // bits (bit i: windows i, i+1; bit B-1 is set by the caller) and stores the argmin bytes
+    auto finish_block = [&](const u32 (&kk)[B], const u32 (&np)[G::BQ * 4], int nbp) -> u32 {
+        u32 mvb[B];
+        u32 sm = 0;
 #pragma unroll
+        for (int i = B - 1; i >= 0; --i) {
+            if (i == B - 1) sm = kk[i];
+            else { tacc = min(tacc, sm - kk[i]); sm = min(kk[i], sm); }
+            tacc = min(tacc, sm - np[i]);              // equal hash parts: own index i.. minus next-block index ..i, in [0, B)
+            mvb[i] = min(np[i] + 16u, sm);
+        }
+        u32 wv[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int q = 0; q < (B + 3) / 4; ++q) {
+            const u32 m0 = mvb[4 * q], m1 = 4 * q + 1 < B ? mvb[4 * q + 1] : 0u, m2 = 4 * q + 2 < B ? mvb[4 * q + 2] : 0u,
+                      m3 = 4 * q + 3 < B ? mvb[4 * q + 3] : 0u;
+            wv[q] = __byte_perm(__byte_perm(m0, m1, 0x0040), __byte_perm(m2, m3, 0x0040), 0x5410);
+        }
+        *reinterpret_cast<uint4*>(IDXB + t * 32 + nbp * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        u32 d = 0;
+#pragma unroll
+        for (int i = 0; i + 1 < B; ++i) d |= (u32)(mvb[i + 1] != mvb[i]) << i;
+        // the previous block's last window against this block's first: the same position reads +16 from there
+        if (nbp > 0) dif |= (u32)(mvb[0] + 16u != mv_last) << (nbp * B - 1);
+        else mv_first = mvb[0];
+        mv_last = mvb[B - 1];
+        return d;
+    };
+#pragma unroll 1
     for (int nb = 0; nb < NB; ++nb) {
+        // block-local streams: LW words from the block's first base (complemented little-endian side), and the LW words
+        // that END with the last base of the block's last m-mer (big-endian side)
+        const int xb = x0 + nb * B;
+        u32 Rl[LW], Fl[LW];
+        {
+            const int wi0 = xb >> 4, sh = (xb & 15) * 2;
+            u32 cw[LW + 1];
+#pragma unroll
+            for (int j = 0; j <= LW; ++j) cw[j] = CW[wi0 + j];
+#pragma unroll
+            for (int j = 0; j < LW; ++j) Rl[j] = __funnelshift_r(cw[j], cw[j + 1], sh);   // Rl[0] = least significant
+            const int bp = 2 * (xb + B - 1 + c.m) - 32 * LW + 32 * PADF4;
+            const int wj = bp >> 5, fs = bp & 31;
+            u32 ew[LW + 1];
+#pragma unroll
+            for (int j = 0; j <= LW; ++j) ew[j] = EW[wj + j];
+#pragma unroll
+            for (int j = 0; j < LW; ++j) Fl[j] = __funnelshift_l(ew[j + 1], ew[j], fs);   // Fl[0] = most significant
+        }
+        u32 ks[B];
+        u32 pk[G::BQ * 4];
         u32 pm = 0;
-        u32 q4[4] = {0, 0, 0, 0};
 #pragma unroll
         for (int i = 0; i < B; ++i) {
-            const int j = nb * B + i;
             u32 flo, fhi = 0;
             {
-                const int cI = 2 * (L - 1 - j), wq = cI >> 5, sh = cI & 31;
+                const int cI = 2 * (B - 1 - i), wq = cI >> 5, sh = cI & 31;
                 flo = __funnelshift_r(word_or_zero(Fl, LW - 1 - wq), word_or_zero(Fl, LW - 2 - wq), sh);
                 if (MW) fhi = __funnelshift_r(word_or_zero(Fl, LW - 2 - wq), word_or_zero(Fl, LW - 3 - wq), sh) & c.maskhi;
                 else flo &= c.masklo;
             }
             u64 val = ((u64)fhi << 32) | flo;
             if (CANON) {
-                const int bo = 2 * j, wq = bo >> 5, sh = bo & 31;
+                const int bo = 2 * i, wq = bo >> 5, sh = bo & 31;
                 u32 rlo = __funnelshift_r(word_or_zero(Rl, wq), word_or_zero(Rl, wq + 1), sh), rhi = 0;
                 if (MW) rhi = __funnelshift_r(word_or_zero(Rl, wq + 1), word_or_zero(Rl, wq + 2), sh) & c.maskhi;
                 else rlo &= c.masklo;
@@ -320,71 +380,44 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
                 val = rc < val ? rc : val;
             }
             const u32 hh = (u32)(murmur3_key8_s32(val, c.s8) >> 32);
-            ks[j] = make_key(hh, c.keymask, (u32)j);
-            if (i == 0) pm = ks[j];
-            else { tacc = min(tacc, ks[j] - pm); pm = min(pm, ks[j]); }
-            if (nb == 0) {
-                q4[i & 3] = pm;
-                if ((i & 3) == 3 || i == B - 1) P[(i >> 2) * 32 + t] = make_uint4(q4[0], q4[1], q4[2], q4[3]);
-            } else pkr[(nb - 1) * B + i] = pm;
+            ks[i] = make_key(hh, c.keymask, (u32)i);
+            if (i == 0) pm = ks[i];
+            else { tacc = min(tacc, ks[i] - pm); pm = min(pm, ks[i]); }
+            pk[i] = pm;
         }
+#pragma unroll
+        for (int i = B; i < G::BQ * 4; ++i) pk[i] = 0;
+        if (nb == 0) {
+#pragma unroll
+            for (int q = 0; q < G::BQ; ++q) P[q * 32 + t] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        } else {
+            dif |= finish_block(ks_prev, pk, nb - 1) << ((nb - 1) * B);
+        }
+#pragma unroll
+        for (int i = 0; i < B; ++i) ks_prev[i] = ks[i];
     }
     __syncwarp();
-
-    // ---- pass 2: suffix minimum + combine with the prefix of the next block: the minimum key of every window -----------
-    u32 mv[L];
-#pragma unroll
-    for (int nb = NB - 1; nb >= 0; --nb) {
+    {
+        // the last block: its next block is the next lane's block 0
         u32 np[G::BQ * 4];
-        if (nb == NB - 1) {
 #pragma unroll
-            for (int q = 0; q < G::BQ; ++q) {
-                const uint4 e = P[q * 32 + t + 1];
-                np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < B; ++i) np[i] = pkr[nb * B + i];
+        for (int q = 0; q < G::BQ; ++q) {
+            const uint4 e = P[q * 32 + t + 1];
+            np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
         }
-        u32 sm = 0;
-#pragma unroll
-        for (int i = B - 1; i >= 0; --i) {
-            const int j = nb * B + i;
-            if (i == B - 1) sm = ks[j];
-            else { tacc = min(tacc, sm - ks[j]); sm = min(ks[j], sm); }
-            // the next block is the next lane's block 0 (smaller indices) for the last block, this lane's block nb+1 otherwise
-            if (nb == NB - 1) tacc = min(tacc, sm - np[i]);
-            else tacc = min(tacc, np[i] - sm);
-            mv[j] = min(sm, np[i]);
-        }
-    }
-
-    // ---- argmin index of every window -> shared memory; change bits ----------------------------------------------------
-    {
-        u32 wv[(L + 3) / 4];
-#pragma unroll
-        for (int q = 0; q < (L + 3) / 4; ++q) {
-            const u32 m0 = mv[4 * q], m1 = 4 * q + 1 < L ? mv[4 * q + 1] : 0u, m2 = 4 * q + 2 < L ? mv[4 * q + 2] : 0u,
-                      m3 = 4 * q + 3 < L ? mv[4 * q + 3] : 0u;
-            wv[q] = __byte_perm(__byte_perm(m0, m1, 0x0040), __byte_perm(m2, m3, 0x0040), 0x5410);
-        }
-        u32* IW = reinterpret_cast<u32*>(IDXB + t * 32);
-#pragma unroll
-        for (int q = 0; q + 4 <= (L + 3) / 4; q += 4) *reinterpret_cast<uint4*>(IW + q) = make_uint4(wv[q], wv[q + 1], wv[q + 2], wv[q + 3]);
-#pragma unroll
-        for (int q = ((L + 3) / 4) / 4 * 4; q < (L + 3) / 4; ++q) IW[q] = wv[q];
-    }
-    u32 dif = 0;
-#pragma unroll
-    for (int j = 0; j + 1 < L; ++j) dif |= (u32)(mv[j + 1] != mv[j]) << j;
-    {
-        const u32 nv0 = __shfl_down_sync(0xffffffffu, mv[0], 1);
-        dif |= (u32)(nv0 != mv[L - 1]) << (L - 1);
+        dif |= finish_block(ks_prev, np, NB - 1) << ((NB - 1) * B);
+        const u32 nv0 = __shfl_down_sync(0xffffffffu, mv_first, 1);
+        dif |= (u32)(nv0 + 16u != mv_last) << (L - 1);
     }
 #ifndef SK4_NO_EXACT     // timing experiments only: without the redo a tile with ties may be wrong
-    if (__any_sync(0xffffffffu, tacc < 32u && V != 0u)) {
-        dif = exact_tile4<B, NB, CANON, MW>(CW, EW, IDXB, c, o, t, hx);
-        if (t == 0 && a.exact_tiles != nullptr) atomicAdd(a.exact_tiles, 1ULL);
+    {
+        const u32 flagged = __ballot_sync(0xffffffffu, tacc < 32u && V != 0u);
+        if (flagged) {
+            __syncwarp();
+            redo_windows4<B, NB, CANON, MW>(CW, EW, IDXB, c, o, t, flagged);
+            dif = change_bits_from_idx4<B, NB>(IDXB, t);
+            if (t == 0 && a.exact_tiles != nullptr) atomicAdd(a.exact_tiles, 1ULL);
+        }
     }
 #endif
 
@@ -414,8 +447,10 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         if (t >= d) incl += v;
     }
     {
+        // a record start is named by its slot in IDXB: lane << 5 | block-in-lane << 4 | window-in-block
+        static_assert(NB == 2 && B <= 16, "slot numbering assumes two blocks of at most 16 windows per lane");
         unsigned short* rp = REC + (incl - cnt);
-        u32 sm = start;
+        u32 sm = (start & MB) | ((start >> B) << 16);
         const u32 tag = (u32)t << 5;
         while (sm) {
             const int i = __ffs((int)sm) - 1;
@@ -444,10 +479,10 @@ __device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char*
     const unsigned short* REC = reinterpret_cast<const unsigned short*>(buf + G::BUF_REC);
     for (u32 r = t; r < n_rec; r += NT4) {
         const u32 rec = REC[r];
-        const int t0 = (int)(rec >> 5), j0 = (int)(rec & 31u);
-        const int idx = IDXB[rec] & 63;
-        // an index below the window's own offset belongs to the next lane's span (a window is shorter than a span)
-        const int rel = idx - j0 + (idx < j0 ? L : 0);         // mm_pos
+        const int t0 = (int)(rec >> 5), nb0 = (int)((rec >> 4) & 1u), i0 = (int)(rec & 15u);
+        const int j0 = nb0 * B + i0;                            // the window's offset in its lane's span
+        const int byt = IDXB[rec];                              // bits 0-3: index in the block, bit 4: the NEXT block
+        const int rel = (byt & 15) + ((byt & 16) ? B : 0) - i0; // mm_pos
         const int j = L * t0 + j0 + rel;                        // local m-mer start
         // size: distance to the first record-end bit at or after the start, at most w
         int size;
@@ -517,7 +552,6 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
-    u64* hx = a.exact_scratch + ((size_t)blockIdx.x * WARPS4 + warp) * (size_t)(32 * 32);
 
     TileConst4 c;
     c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = (u32)a.s8; c.keymask = a.keymask;
@@ -549,7 +583,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
         u32 n_rec = 0;
         u64 old = 0;
         if (have) {
-            n_rec = compute_tile4<B, NB, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1, hx);
+            n_rec = compute_tile4<B, NB, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1);
             if (t == 0) {
                 st_status(&a.tile_status[tile], TS_SET4 | n_rec);
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);

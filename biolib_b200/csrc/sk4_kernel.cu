@@ -6,17 +6,19 @@ namespace blg {
 
 namespace {
 
-struct Variant4 { int B, NB, LW, MW; };
+struct Variant4 { int B, LW, MW; };
 
-// w = B + 1 with a lane span L = NB B <= 32 and the lane-local streams wide enough: 2 (L + m - 1) <= 32 LW.
+// w = B + 1 with B = 12 or 10 (the benchmark families: k=31 m=19, k=21 m=11 and their neighbours), any m: MW <=> the m-mer
+// needs a second 32-bit word (m > 16); the block-local streams hold B + m - 1 bases: 2 (B - 1 + m) <= 32 LW.
 bool pick_variant4(int k, int m, Variant4* v)
 {
     const int d = k - m;
-    if (m < 1 || m > 32 || k > 64) return false;
-    if (d == 12 && m >= 17 && m <= 25) { *v = {12, SK4_NB12, 3, 1}; return true; }   // k=31 m=19 (configs 2, 3)
-    if (d == 10 && m <= 16) { *v = {10, SK4_NB10, 3, 0}; return true; }              // k=21 m=11 (config 5)
-    return false;
+    if (m < 1 || m > 32 || k > 64 || (d != 12 && d != 10)) return false;
+    *v = {d, 2 * (d - 1 + m) <= 64 ? 2 : 3, m > 16 ? 1 : 0};
+    return true;
 }
+
+constexpr int NB4 = 2;       // blocks per lane (sk4_device.cuh numbers record slots for two)
 
 template <int B, int NB, int LW, bool CANON, bool MW>
 cudaError_t setup4(size_t smem, int* occ)
@@ -39,8 +41,23 @@ void launch4c(bool canon, const SkArgs& args, const SkLaunchPlan& plan, cudaStre
     else sk4_kernel<B, NB, LW, false, MW><<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(args);
 }
 
-template <int B, int NB>
-size_t smem4() { return (size_t)Geo4<B, NB>::WARP_BYTES * WARPS4; }
+template <int B>
+size_t smem4() { return (size_t)Geo4<B, NB4>::WARP_BYTES * WARPS4; }
+
+// (LW, MW) in {(2, false), (2, true), (3, true)}
+template <int B>
+cudaError_t setup4v(const Variant4& v, bool canon, size_t smem, int* occ)
+{
+    if (!v.MW) return setup4c<B, NB4, 2, false>(canon, smem, occ);
+    return v.LW == 2 ? setup4c<B, NB4, 2, true>(canon, smem, occ) : setup4c<B, NB4, 3, true>(canon, smem, occ);
+}
+template <int B>
+void launch4v(const Variant4& v, bool canon, const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
+{
+    if (!v.MW) launch4c<B, NB4, 2, false>(canon, args, plan, stream);
+    else if (v.LW == 2) launch4c<B, NB4, 2, true>(canon, args, plan, stream);
+    else launch4c<B, NB4, 3, true>(canon, args, plan, stream);
+}
 
 }  // namespace
 
@@ -59,8 +76,8 @@ cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
     int occ = 0;
     cudaError_t e = cudaSuccess;
     const bool canon = args.canonical != 0;
-    if (v.B == 12) { R = Geo4<12, SK4_NB12>::R; smem = smem4<12, SK4_NB12>(); e = setup4c<12, SK4_NB12, 3, true>(canon, smem, &occ); }
-    else { R = Geo4<10, SK4_NB10>::R; smem = smem4<10, SK4_NB10>(); e = setup4c<10, SK4_NB10, 3, false>(canon, smem, &occ); }
+    if (v.B == 12) { R = Geo4<12, NB4>::R; smem = smem4<12>(); e = setup4v<12>(v, canon, smem, &occ); }
+    else { R = Geo4<10, NB4>::R; smem = smem4<10>(); e = setup4v<10>(v, canon, smem, &occ); }
     if (e != cudaSuccess) return e;
     args.R = R;
     args.org = args.win_lo;
@@ -78,15 +95,13 @@ cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
     return cudaSuccess;
 }
 
-size_t sk4_exact_scratch_bytes(const SkLaunchPlan& plan) { return (size_t)plan.grid * WARPS4 * 32 * 32 * sizeof(unsigned long long); }
-
 cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)
 {
     Variant4 v;
     if (!pick_variant4(args.k, args.m, &v)) return cudaErrorInvalidValue;
     const bool canon = args.canonical != 0;
-    if (v.B == 12) launch4c<12, SK4_NB12, 3, true>(canon, args, plan, stream);
-    else launch4c<10, SK4_NB10, 3, false>(canon, args, plan, stream);
+    if (v.B == 12) launch4v<12>(v, canon, args, plan, stream);
+    else launch4v<10>(v, canon, args, plan, stream);
     return cudaGetLastError();
 }
 

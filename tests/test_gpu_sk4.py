@@ -11,8 +11,8 @@ pytestmark = pytest.mark.gpu
 
 from test_gpu_parity import check_sk, rand_seq  # noqa: E402
 
-TILE12 = (32 * 2 - 3) * 12       # k - m = 12 (SK4_NB12 = 2)
-TILE10 = (32 * 3 - 3) * 10       # k - m = 10 (SK4_NB10 = 3)
+TILE12 = (32 * 2 - 3) * 12       # k - m = 12 (two blocks of w - 1 starts per lane)
+TILE10 = (32 * 2 - 3) * 10       # k - m = 10
 
 
 @pytest.mark.parametrize("canon", [False, True])
@@ -23,10 +23,12 @@ def test_tile_edges(gpu, oracle, k, m, tile, canon):
         check_sk(gpu, oracle, rand_seq(rng, nwin + k - 1), k, m, 42, canon)
 
 
-@pytest.mark.parametrize("m", list(range(17, 26)) + list(range(1, 17)))
-def test_every_supported_m(gpu, oracle, m):
-    k = m + (12 if m >= 17 else 10)
-    rng = np.random.default_rng(m)
+@pytest.mark.parametrize("d", [12, 10])
+@pytest.mark.parametrize("m", list(range(1, 33)))
+def test_every_supported_m(gpu, oracle, m, d):
+    """k - m = 12 and 10 for every m: one-word m-mers (m <= 16), two-word with 2- and 3-word block streams."""
+    k = m + d
+    rng = np.random.default_rng(m * 2 + d)
     for canon in (False, True):
         check_sk(gpu, oracle, rand_seq(rng, 20011), k, m, 7, canon)
         check_sk(gpu, oracle, rand_seq(rng, 9000, p_n=0.002, lower=0.1), k, m, 0, canon)
@@ -44,10 +46,11 @@ def test_ties_take_the_exact_path(gpu, oracle, k, m):
     for canon in (False, True):
         check_sk(gpu, oracle, s, k, m, 42, canon)
         assert gpu.stats()["exact_tiles"] > 0
-    # random sequence: practically no tile should need it
+    # random sequence: at m = 19 practically no tile needs it; at m = 11 reverse-complement neighbours (a 12-base
+    # reverse palindrome makes two adjacent canonical 11-mers equal: about 5 per 10^4 positions) flag one tile in eight
     r = rand_seq(rng, 400_000)
     check_sk(gpu, oracle, r, k, m, 42, True)
-    assert gpu.stats()["exact_tiles"] <= 2
+    assert gpu.stats()["exact_tiles"] <= (2 if m == 19 else 100)
 
 
 @pytest.mark.parametrize("k,m", [(31, 19), (21, 11)])
