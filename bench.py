@@ -1,19 +1,26 @@
 #!/usr/bin/env python
 """bench.py -- super-k-mer extraction throughput (k=31, m=19, canonical, seed 42), BASELINE.json's metric.
 
-    python bench.py --gpus N --steps K --warmup W [--impl reference]
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--no-extra]
 
 A "step" is one pass of the hot path (blg_super_kmers_range through the C ABI) over one batch of synthetic input:
 per GPU 100 Mbp of the reference generator's stream (BASELINE configs[1]). With N > 1 (torchrun, one rank per
 GPU) rank r owns windows [r*100M, (r+1)*100M) of one N*100 Mbp genome built from shards uniform(42 + shard), plus
 the k+w-2 halo from the next shard: weak scaling, no data-path collective, one NCCL all-reduce of the counts.
 
-  value      Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream, max over ranks
-  e2e        the same call with HOST (pinned) buffers: H2D of the bases and D2H of the records inside the timing
-  roofline   algorithmic bytes (1 B/base + 18 B/record) / kernel time vs the measured HBM copy peak
-  cpu_baseline  reference read_base()+hash64 (verbatim, oracle/_ref) + restated windowing on the host cores
+  value         Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream, max over ranks
+  e2e           the same call with HOST (pinned) buffers and the compact record layout (BLG_F_POS32, 14 B per record):
+                H2D of the bases and D2H of the records inside the timing; e2e_records18 = the default 18-byte layout
+  roofline      algorithmic bytes (1 B/base + 18 B/record) / kernel time vs the measured HBM copy peak
+  roofline_int  why the HBM fraction is what it is: executed instructions per base and pipe utilisation (from the committed
+                ncu capture, with its git sha), hashes per second of this run against the hash rate the machine sustains
+                (measured live with the minimizer_position_extractor kernel, which does nothing but hash)
+  parity        the records of the timed input are compared with the oracle on a prefix, on the same run
+  cpu_baseline  reference read_base()+hash64 (verbatim, oracle/_ref) + restated windowing on the host cores, same input
+  extra         the other configurations north_star names, device-resident, at this N: config 4 (k=63 m=31, 3 Gbp genome,
+                chunk + halo, STRONG scaling) and config 3 (150-bp reads with N runs, 32 batches dealt to the ranks)
 
---impl reference times that CPU arm alone (all host threads) on the same config.
+--impl reference times that CPU arm alone (all host threads) on the same input.
 """
 from __future__ import annotations
 
@@ -33,20 +40,19 @@ K, M, SEED, CANON = 31, 19, 42, True
 W = K - M + 1
 SHARD = 100_000_000          # bases per GPU per step (configs[1])
 GEN_SEED0 = 42               # shard i of the genome = sequence_generator uniform(42 + i)
-HALO = K + W - 2 + 64        # bases of the next shard a rank needs (rounded up)
+HALO = K + W - 2             # bases of the next shard a rank needs: its last record can reach k + w - 2 bases past its last start
+HALO_PAD = 64                # ... rounded up so that the slice keeps the 16-byte alignment the vector loads want
 REC_BYTES = 18               # value u64 + mm_start u64 + size u8 + mm_pos u8
 METRIC = "Gbases/s super-k-mer extraction (k=31,m=19)"
+PARITY_PREFIX = 2_000_000    # bases of the timed input checked against the oracle on the timed run
 
 
-def load_traffic():
-    """DRAM bytes per launch of the dominant kernel from the last committed `ncu --set full` capture of this very
-    workload (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); None when there is none."""
+def load_json(name):
     try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            d = json.load(f)
-        return d["kernel"], float(d["dram_bytes_per_launch"])
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            return json.load(f)
     except Exception:
-        return "sk3_kernel", None
+        return None
 
 
 def load_peaks():
@@ -55,6 +61,20 @@ def load_peaks():
             return float(json.load(f)["hbm_gbs"]), "measured"
     except Exception:
         return 6650.0, "fallback"
+
+
+def host_description():
+    """CPU model / core count of the box, for the CPU baseline."""
+    model = "?"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return {"cpu": model, "logical_cpus": os.cpu_count() or 1,
+            "build": "g++ -std=c++17 -O3 -DNDEBUG -fno-lifetime-dse (oracle/Makefile): the reference headers compiled where they lie"}
 
 
 class ClockSampler(threading.Thread):
@@ -97,29 +117,33 @@ class ClockSampler(threading.Thread):
 
 
 # ----------------------------------------------------------------------------------------------- CPU arm
-def cpu_arm(sample_bases_per_thread: int, threads: int, repeats: int = 1, chunks=None):
-    """Reference arithmetic on the host cores: each thread runs the whole path over its own chunk
-    (chunks overlap nothing: records at chunk edges are irrelevant for a rate). Returns (Gbases/s, kind, desc)."""
+def cpu_engine():
+    """(callable bases -> record count, kind, description): the reference's own arithmetic when oracle/_ref travelled here."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle
-    from biolib_b200 import synth
-    use_ref = os.path.exists(pyoracle.REF_SO)
-    if use_ref:
+    if os.path.exists(pyoracle.REF_SO):
         eng = pyoracle.Ref()
-        fn = lambda s: eng.super_kmers_sums(s, K, M, SEED, CANON)[0]
-        kind = "reference"
-        what = "reference read_base()+hash64 verbatim (oracle/_ref) + restated deque windowing"
-    else:
-        eng = pyoracle.Oracle()
-        fn = lambda s: eng.super_kmers(s, K, M, SEED, CANON, want=())["n"]
-        kind = "port"
-        what = "oracle.c port (rolling words + Murmur + deque windowing)"
-    if chunks is None:
-        chunks = [synth.generate(GEN_SEED0 + 1000 + t, sample_bases_per_thread) for t in range(threads)]
+        return (lambda s: eng.super_kmers_sums(s, K, M, SEED, CANON)[0]), "reference", \
+            "reference read_base()+hash64 verbatim (oracle/_ref) + restated deque windowing"
+    eng = pyoracle.Oracle()
+    return (lambda s: eng.super_kmers(s, K, M, SEED, CANON, want=())["n"]), "port", "oracle.c port (rolling words + Murmur + deque windowing)"
+
+
+def shard_chunks(total_bases: int, threads: int):
+    """The bench's own input -- the first `total_bases` of shard 0, uniform(42) -- cut into one chunk per thread with the
+    k + w - 2 overlap a record can span, so that the threads together produce exactly the records of those bases."""
+    from biolib_b200 import synth
+    s = synth.generate(GEN_SEED0, min(total_bases + HALO, SHARD))
+    per = (total_bases + threads - 1) // threads
+    return [s[i * per: min((i + 1) * per + HALO, s.size)] for i in range(threads) if i * per < total_bases]
+
+
+def cpu_arm(chunks, repeats: int = 1):
+    """All chunks concurrently, one thread each. Returns (Gbases/s over the owned bases, kind, description, seconds)."""
+    fn, kind, what = cpu_engine()
     best = None
     for _ in range(repeats):
-        res = [0] * threads
-        ths = [threading.Thread(target=lambda i=i: res.__setitem__(i, fn(chunks[i]))) for i in range(threads)]
+        ths = [threading.Thread(target=fn, args=(c,)) for c in chunks]
         t0 = time.perf_counter()
         for t in ths:
             t.start()
@@ -127,8 +151,8 @@ def cpu_arm(sample_bases_per_thread: int, threads: int, repeats: int = 1, chunks
             t.join()
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    total = sample_bases_per_thread * threads
-    return total / best / 1e9, kind, f"{what}; {threads} threads x {sample_bases_per_thread/1e6:.0f} Mbp of the same generator stream, {best:.2f} s"
+    total = sum(c.size for c in chunks) - HALO * len(chunks)
+    return total / best / 1e9, kind, what, best
 
 
 def run_reference(args):
@@ -137,24 +161,27 @@ def run_reference(args):
         return
     threads = os.cpu_count() or 1
     steps, warm = max(args.steps, 1), max(args.warmup, 0)
-    from biolib_b200 import synth
-    # bounded sample: the whole run stays near two minutes at ~30 Mbases/s per thread
-    per_thread = int(min(8_000_000, max(500_000, 120.0 * 30e6 / (steps + warm))))
-    chunks = [synth.generate(GEN_SEED0 + 1000 + t, per_thread) for t in range(threads)]
+    # the GPU arm's own step: the 100 Mbp shard of rank 0 (a step of it is 0.1 - 0.2 s on 16 - 32 host threads); bounded so
+    # that K + W steps stay near two minutes
+    total = int(min(SHARD, max(4_000_000, 120.0 * 25e6 * threads / (steps + warm))))
+    chunks = shard_chunks(total, threads)
     vals = []
-    desc = kind = None
+    kind = what = None
     for i in range(warm + steps):
-        v, kind, desc = cpu_arm(per_thread, threads, chunks=chunks)
+        v, kind, what, _ = cpu_arm(chunks)
         if i >= warm:
             vals.append(v)
     v = float(np.mean(vals))
-    ms = per_thread * threads / (v * 1e9) * 1e3
+    one, _, _, sec1 = cpu_arm(shard_chunks(4_000_000, 1))
+    sample = f"{what}; {len(chunks)} threads over the first {total / 1e6:.0f} Mbp of the GPU arm's shard (uniform(42)), chunk + halo"
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "Gbases/s", "n_gpus": args.gpus, "steps": steps,
-            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": warm, "ms_per_step": total / (v * 1e9) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "super_kmer_view k=31 m=19 canonical seed=42, sequence_generator stream (configs[1])",
-                       "k": K, "m": M, "bases_per_step": per_thread * threads},
-            "cpu_baseline": {"value": v, "unit": "Gbases/s", "cores": threads, "kind": kind, "sample": desc},
+            "config": {"workload": "super_kmer_view k=31 m=19 canonical seed=42 over 100 Mbp/GPU of sequence_generator "
+                                   "uniform(42+shard) (BASELINE configs[1])",
+                       "k": K, "m": M, "bases_per_step": total, "same_input_as_gpu_arm": True},
+            "cpu_baseline": {"value": v, "unit": "Gbases/s", "cores": len(chunks), "kind": kind, "sample": sample,
+                             "one_core_value": one, "host": host_description()},
             "e2e": {"value": v, "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -168,11 +195,11 @@ def np_from_ptr(ptr: int, nbytes: int, dtype) -> np.ndarray:
 
 
 def build_rank_input(rank: int, world: int):
-    """Rank r's slice of the world*SHARD genome: [r*SHARD - LH, (r+1)*SHARD + HALO) clipped to the genome.
+    """Rank r's slice of the world*SHARD genome: [r*SHARD - LH, (r+1)*SHARD + HALO + pad) clipped to the genome.
     Returns (bases uint8, win_lo, win_hi) with the window range in slice coordinates."""
     from biolib_b200 import synth
     LH = 64 if rank > 0 else 0
-    RH = HALO if rank < world - 1 else 0
+    RH = HALO + HALO_PAD if rank < world - 1 else 0
     parts = []
     if LH:
         parts.append(synth.generate(GEN_SEED0 + rank - 1, SHARD)[-LH:])
@@ -208,10 +235,131 @@ def bind_to_gpu_numa_node(local: int) -> str:
         return f"numa: unavailable ({type(e).__name__})"
 
 
+class DeviceRun:
+    """Device-resident runs of blg_super_kmers_range for one (k, m): output arrays sized once, kernel time from the
+    library's CUDA events with the stream idle at launch (an event recorded while the previous operation still runs can
+    time-stamp early on this driver: measured 45 us on the L2 flush), L2 flushed between runs."""
+
+    def __init__(self, torch, ctx, dev, flush, k, m):
+        self.torch, self.ctx, self.dev, self.flush, self.k, self.m = torch, ctx, dev, flush, k, m
+        self.cap = 0
+
+    def ensure(self, cap):
+        if cap > self.cap:
+            t = self.torch
+            self.v = t.empty(cap, dtype=t.int64, device=self.dev); self.mm = t.empty(cap, dtype=t.int64, device=self.dev)
+            self.sz = t.empty(cap, dtype=t.uint8, device=self.dev); self.ps = t.empty(cap, dtype=t.uint8, device=self.dev)
+            self.cap = cap
+
+    def call(self, d_bases, n, win=None, offs=None):
+        n_seq = 0 if offs is None else offs.numel() - 1
+        return self.ctx.super_kmers_device(d_bases.data_ptr(), n, self.k, self.m, SEED, CANON, self.v.data_ptr(), self.mm.data_ptr(),
+                                           self.sz.data_ptr(), self.ps.data_ptr(), self.cap, win_range=win,
+                                           d_offsets=offs.data_ptr() if offs is not None else 0, n_seq=n_seq)
+
+    def kernel_ms(self, d_bases, n, win=None, offs=None, reps=5, warm=1):
+        """(median kernel ms, record count)"""
+        nwin = n if win is None else win[1] - win[0]
+        w = self.k - self.m + 1
+        self.ensure(int(nwin * 2.0 / (w + 1) * 1.35) + 3 * (0 if offs is None else offs.numel()) + 65536)
+        ms, cnt = [], 0
+        for i in range(warm + reps):
+            self.flush.zero_()
+            self.torch.cuda.synchronize()
+            cnt = self.call(d_bases, n, win, offs)
+            if i >= warm:
+                ms.append(self.ctx.stats()["kernel_ms"])
+        return float(np.median(ms)), cnt
+
+
+def hash_rate_ceiling(torch, ctx, dev):
+    """Hashes per second of a kernel that only hashes: hash::minimizer_position_extractor (blg_minimizer_positions) over
+    2^24 k-mer values, w = 13 hashes each, device-resident."""
+    import ctypes as C
+    n = 1 << 24
+    vals = torch.randint(0, 2**62, (n,), dtype=torch.int64, device=dev)
+    out = torch.empty(n, dtype=torch.uint8, device=dev)
+    best = None
+    for _ in range(4):
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        st = ctx.L.blg_minimizer_positions(ctx.h, C.c_void_p(vals.data_ptr()), n, K, M, 3, C.c_void_p(out.data_ptr()))
+        b.record()
+        torch.cuda.synchronize()
+        assert st == 0
+        ms = a.elapsed_time(b)
+        best = ms if best is None else min(best, ms)
+    return n * W / (best * 1e-3)
+
+
+def check_parity(ctx, bases_h, win_lo, d_value, d_mm, d_size, count):
+    """The records of the timed run against the oracle on the first PARITY_PREFIX owned bases (rank 0 of the run)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle
+    orc = pyoracle.Oracle()
+    pre = bases_h[win_lo: win_lo + PARITY_PREFIX]
+    o = orc.super_kmers(pre, K, M, SEED, CANON)
+    keep = int(o["n"]) - 2                       # the last records of a prefix are cut short by its end
+    gv = d_value[:keep].cpu().numpy().view(np.uint64)
+    gm = d_mm[:keep].cpu().numpy().view(np.uint64) - np.uint64(win_lo)
+    gs = d_size[:keep].cpu().numpy()
+    ok = keep > 0 and keep <= count and np.array_equal(gv, o["value"][:keep]) and np.array_equal(gm, o["mm_start"][:keep]) \
+        and np.array_equal(gs, o["size"][:keep])
+    return bool(ok), keep
+
+
+def run_extras(torch, dist, ctx, dev, flush, world, rank):
+    """The other configurations north_star names, device-resident, at this N (STRONG scaling: fixed total work)."""
+    from biolib_b200 import shard, synth
+
+    def reduce(ms, records, bases):
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        c = torch.tensor([records, bases], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        return float(t[0]), int(c[0]), int(c[1])
+
+    out = {}
+    # ---- config 4: k=63 m=31 over a 3 Gbp genome of shards uniform(45 + i) of 64 Mbp, chunk + halo ----------------------
+    n, k, m, shard_len = 3_000_000_000, 63, 31, 1 << 26
+    pl = shard.plan_chunks(n, k, m, world)[rank]
+    first = pl.buf_lo // shard_len
+    s = synth.generate_sharded_parallel(45 + first, pl.buf_hi - first * shard_len, shard_len)[pl.buf_lo - first * shard_len:]
+    d = torch.from_numpy(s).to(dev)
+    run = DeviceRun(torch, ctx, dev, flush, k, m)
+    ms, cnt = run.kernel_ms(d, s.size, win=pl.local_window, reps=3)
+    ms, rec, bases = reduce(ms, cnt, pl.win_hi - pl.win_lo)
+    out["config4_k63_m31_3gbp"] = {"scaling": "strong", "n_gpus": world, "bases": bases, "records": rec, "kernel_ms_max_over_ranks": ms,
+                                   "Gbases_per_s": bases / ms / 1e6, "achieved_GBps_per_gpu": (bases + REC_BYTES * rec) / world / ms / 1e6,
+                                   "sharding": "chunk + k+w-2 halo, records owned by the rank of their first k-mer"}
+    del d, s, run
+    torch.cuda.empty_cache()
+    # ---- config 3: 150-bp reads with N runs: 32 batches of 1 M reads dealt round-robin to the ranks ----------------------
+    k, m, L, per_batch, batches = 31, 19, 150, 1_000_000, 32
+    offs = torch.arange(0, per_batch + 1, dtype=torch.int64, device=dev) * L
+    run = DeviceRun(torch, ctx, dev, flush, k, m)
+    ms_sum, rec_sum, bases_sum = 0.0, 0, 0
+    for bi in range(rank, batches, world):
+        s = synth.generate_sharded_parallel(43 + 100 * bi, per_batch * L, 1 << 24)
+        synth.inject_n_runs(s, L, seed=44 + bi)
+        d = torch.from_numpy(s).to(dev)
+        ms, cnt = run.kernel_ms(d, s.size, offs=offs, reps=2)
+        ms_sum += ms; rec_sum += cnt; bases_sum += s.size
+        del d
+    ms, rec, bases = reduce(ms_sum, rec_sum, bases_sum)
+    out["config3_reads150_nruns"] = {"scaling": "strong", "n_gpus": world, "bases": bases, "records": rec, "kernel_ms_max_over_ranks": ms,
+                                     "Gbases_per_s": bases / ms / 1e6, "reads": batches * per_batch,
+                                     "note": "32 batches of 1 M reads (4.8 Gbp) of the 100 M-read configuration, 32 / N batches per rank"}
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
     import biolib_b200
+    from biolib_b200 import _capi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -228,32 +376,31 @@ def run_gpu(args):
     bases_h, win_lo, win_hi = build_rank_input(rank, world)
     n = bases_h.size
     nwin = win_hi - win_lo
-    cap = int(nwin * 2.0 / (W + 1) * 1.3) + 65536
+    cap = int(nwin * 2.0 / (W + 1) * 1.35) + 65536
 
     d_bases = torch.from_numpy(bases_h).to(dev)
-    d_value = torch.empty(cap, dtype=torch.int64, device=dev)
-    d_mm = torch.empty(cap, dtype=torch.int64, device=dev)
-    d_size = torch.empty(cap, dtype=torch.uint8, device=dev)
-    d_pos = torch.empty(cap, dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
+    main_run = DeviceRun(torch, ctx, dev, flush, K, M)
+    main_run.ensure(cap)
+    d_value, d_mm, d_size = main_run.v, main_run.mm, main_run.sz
 
     def step_device():
-        return ctx.super_kmers_device(d_bases.data_ptr(), n, K, M, SEED, CANON, d_value.data_ptr(), d_mm.data_ptr(),
-                                      d_size.data_ptr(), d_pos.data_ptr(), cap, win_range=(win_lo, win_hi))
+        return main_run.call(d_bases, n, win=(win_lo, win_hi))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
         flush.zero_()
         count = step_device()
     sampler = ClockSampler(local)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms = 0.0
+    exact_tiles = 0
     barrier()
     sampler.start()
     for s, e in ev:
@@ -261,76 +408,105 @@ def run_gpu(args):
         s.record(stream)
         count = step_device()
         e.record(stream)
-        kernel_ms += ctx.stats()["kernel_ms"]
+        exact_tiles = ctx.stats()["exact_tiles"]
     barrier()
     sampler.stop_flag = True
     sampler.join()
     step_ms = sum(s.elapsed_time(e) for s, e in ev) / args.steps
-    kernel_ms /= args.steps
+    kernel_ms, count_k = main_run.kernel_ms(d_bases, n, win=(win_lo, win_hi), reps=min(max(args.steps, 3), 10))
+    assert count_k == count
+    parity_ok, parity_records = check_parity(ctx, bases_h, win_lo, d_value, d_mm, d_size, count) if rank == 0 else (True, 0)
+    hash_ceiling = hash_rate_ceiling(torch, ctx, dev) if rank == 0 else 0.0
 
-    # ---- end to end: host (pinned) buffers in and out through the same entry point ----
+    # ---- end to end: host (pinned) buffers in and out through the same entry point, both record layouts ----
     ctx.set_stream(None)
     e2e_steps = max(3, min(args.steps, 10))
     hp_in = ctx.host_alloc(n)
     np_from_ptr(hp_in, n, np.uint8)[:] = bases_h
     hp = [ctx.host_alloc(cap * 8), ctx.host_alloc(cap * 8), ctx.host_alloc(cap), ctx.host_alloc(cap)]
+    e2e = {}
+    for name, flags in (("records18", 0), ("compact14", _capi.F_POS32)):
+        def step_host():
+            return ctx.super_kmers_raw(hp_in, n, K, M, SEED, CANON, hp[0], hp[1], hp[2], hp[3], cap, flags=flags, win_range=(win_lo, win_hi))
+        for _ in range(2):
+            c2 = step_host()
+        assert c2 == count, (c2, count)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            step_host()
+            st = ctx.stats()
+        torch.cuda.synchronize()
+        e2e[name] = ((time.perf_counter() - t0) * 1e3 / e2e_steps, st["bytes_h2d"], st["bytes_d2h"])
+        # parity of the host path: same records as the device-resident run (checksums over what landed in host memory)
+        hv = np_from_ptr(hp[0], cap * 8, np.uint64)[:count]
+        assert int(hv.sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
+        pos = np_from_ptr(hp[1], cap * 8, np.uint32 if flags else np.uint64)[:count].astype(np.uint64) + np.uint64(win_lo if flags else 0)
+        assert int(pos.sum(dtype=np.uint64)) == int(d_mm[:count].sum().item()) & (2**64 - 1)
+    for p in [hp_in] + hp:
+        ctx.host_free(p)
 
-    def step_host():
-        return ctx.super_kmers_raw(hp_in, n, K, M, SEED, CANON, hp[0], hp[1], hp[2], hp[3], cap, win_range=(win_lo, win_hi))
+    ctx.set_stream(stream.cuda_stream)
+    extras = None if args.no_extra else run_extras(torch, dist, ctx, dev, flush, world, rank)
 
-    for _ in range(2):
-        c2 = step_host()
-    assert c2 == count, (c2, count)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        step_host()
-        st = ctx.stats()
-    torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
-    h2d, d2h = st["bytes_h2d"], st["bytes_d2h"]
-    # parity of the two paths: same records (checksums over what landed in host memory vs HBM)
-    hv = np_from_ptr(hp[0], cap * 8, np.uint64)[:count]
-    assert int(hv.sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
-
-    t = torch.tensor([step_ms, e2e_ms, kernel_ms], dtype=torch.float64, device=dev)
-    cnt = torch.tensor([count, nwin], dtype=torch.int64, device=dev)
+    t = torch.tensor([step_ms, e2e["compact14"][0], kernel_ms, e2e["records18"][0]], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([count, nwin, exact_tiles], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)   # the path's only collective: per-GPU counts
-    step_ms, e2e_ms, kernel_ms = t.tolist()
-    total_records, total_win = cnt.tolist()
+    step_ms, e2e_ms, kernel_ms, e2e18_ms = t.tolist()
+    total_records, total_win, total_exact = cnt.tolist()
     total_bases = SHARD * world
 
     if rank == 0:
         peak, peak_kind = load_peaks()
-        kname, traffic = load_traffic()
+        traffic = load_json("ncu_traffic.json") or {}
+        intmix = load_json("ncu_intmix.json") or {}
         algo_bytes = nwin + REC_BYTES * count          # this rank's launch
         achieved = algo_bytes / (kernel_ms * 1e-3) / 1e9
+        hashes = nwin * 64.0 / 61.0                     # sk4 hashes 64 blocks of m-mer starts per 61 blocks of new windows
         line = {
             "metric": METRIC, "value": total_bases / (step_ms * 1e-3) / 1e9, "unit": "Gbases/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
+            "steps": args.steps, "warmup": warm, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": {"workload": "super_kmer_view k=31 m=19 canonical seed=42 over 100 Mbp/GPU of sequence_generator "
                                    "uniform(42+shard) (BASELINE configs[1])",
                        "k": K, "m": M, "bases_per_gpu": SHARD, "records": total_records, "kmers": total_win,
                        "l2": "256 MiB flush write between timed steps", "sharding": f"chunk+halo x{world}",
-                       "host": numa},
-            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": e2e_ms},
+                       "host": numa, "e2e_layout": "BLG_F_POS32: value u64 + 32-bit position relative to the range start + size u8 + mm_pos u8"},
+            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["compact14"][1]),
+                    "d2h_bytes_per_step": int(e2e["compact14"][2]), "steps": e2e_steps, "ms_per_step": e2e_ms},
+            "e2e_records18": {"value": total_bases / (e2e18_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["records18"][1]),
+                              "d2h_bytes_per_step": int(e2e["records18"][2]), "ms_per_step": e2e18_ms},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_kind": peak_kind, "kernel": kname, "kernel_ms": kernel_ms,
+                         "traffic": traffic.get("dram_bytes_per_launch"), "traffic_capture": {"git_sha": traffic.get("git_sha"), "kernel": traffic.get("kernel")},
+                         "peak_kind": peak_kind, "kernel": "sk4_kernel", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_base": algo_bytes / nwin},
+            "roofline_int": {"bound": "integer issue (ALU pipe: LOP3 / SHF / ISETP / SEL / IADD3 / VIMNMX at 16 lanes per clock per scheduler)",
+                             "inst_per_base": intmix.get("inst_per_base"), "alu_ops_per_base": intmix.get("alu_ops_per_base"),
+                             "imad_per_base": intmix.get("imad_per_base"), "alu_pipe_pct": intmix.get("alu_pipe_pct"),
+                             "fma_pipe_pct": intmix.get("fma_pipe_pct"), "issue_slots_pct": intmix.get("issue_slots_pct"),
+                             "capture": {"git_sha": intmix.get("git_sha"), "kernel": intmix.get("kernel")},
+                             "hashes_per_s": hashes / (kernel_ms * 1e-3), "hash_rate_ceiling": hash_ceiling,
+                             "hash_rate_frac": hashes / (kernel_ms * 1e-3) / hash_ceiling if hash_ceiling else None,
+                             "exact_redo_tiles_per_step": int(total_exact)},
+            "parity_checked": parity_ok, "parity": {"against": "oracle/oracle.c on the first 2 Mbp of the timed input, value + mm_start + size",
+                                                    "records_compared": parity_records},
             "clocks": sampler.summary(),
         }
+        if extras is not None:
+            line["extra"] = extras
         if world == 1:
             threads = os.cpu_count() or 1
-            v, kind, desc = cpu_arm(8_000_000, threads)
-            line["cpu_baseline"] = {"value": v, "unit": "Gbases/s", "cores": threads, "kind": kind, "sample": desc}
+            chunks = shard_chunks(min(SHARD, 8_000_000 * threads), threads)
+            v, kind, what, sec = cpu_arm(chunks)
+            line["cpu_baseline"] = {"value": v, "unit": "Gbases/s", "cores": len(chunks), "kind": kind, "host": host_description(),
+                                    "sample": f"{what}; {len(chunks)} threads over the first {(sum(c.size for c in chunks) - HALO * len(chunks)) / 1e6:.0f} Mbp of this "
+                                              f"run's own shard, {sec:.2f} s"}
+        if not parity_ok:
+            line["error"] = "parity check against the oracle FAILED on the timed run"
         print(json.dumps(line), flush=True)
-    for p in [hp_in] + hp:
-        ctx.host_free(p)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -342,6 +518,7 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-extra", action="store_true", help="skip the config 3 / config 4 runs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

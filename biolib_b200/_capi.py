@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(HERE, "libbiolib_gpu.so")
 CSRC = os.path.join(HERE, "csrc")
 
 BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOMEM = range(6)
-F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID = 0x1, 0x2, 0x4, 0x8, 0x10
+F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID, F_POS32 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",

@@ -94,10 +94,12 @@ class Context:
         return res
 
     def super_kmers(self, seq, k: int, m: int, seed: int = 0, canonical: bool = False, offsets=None, want_hash=True,
-                    win_range=None, minimizers_only=False, want_id=False) -> dict:
+                    win_range=None, minimizers_only=False, want_id=False, pos32=False) -> dict:
+        """pos32: ask for the compact record layout (BLG_F_POS32: 32-bit positions relative to the range start); the
+        returned mm_start / sk_start are widened back to absolute uint64 so that both layouts compare equal."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0),
+        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0) | (_capi.F_POS32 if pos32 else 0),
                    seed=seed & (2**64 - 1))
         out = SkOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1)
@@ -110,7 +112,12 @@ class Context:
         self._check(st)
         n = out.count
         try:
-            res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=_copy(out.mm_start, n, np.uint64))
+            if pos32:
+                base = 0 if win_range is None else min(int(win_range[0]), max(b.size - k + 1, 0))
+                mm = _copy(out.mm_start, n, np.uint32).astype(np.uint64) + np.uint64(base)
+            else:
+                mm = _copy(out.mm_start, n, np.uint64)
+            res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=mm)
             if not minimizers_only:
                 res["size"] = _copy(out.size, n, np.uint8)
                 res["mm_pos"] = _copy(out.mm_pos, n, np.uint8)

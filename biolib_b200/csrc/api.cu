@@ -32,20 +32,23 @@ struct Owner {
 struct blg_ctx {
     int device = 0;
     int sm_count = 0;
-    int kmer_gen = 0;            // BLG_KMER=1 pins the first-generation k-mer kernel (development A/B only)
-    int sk_gen = 0;              // BLG_SK=1|2|3 pins a kernel generation (development A/B only); 0 = newest that covers (k, m)
     char name[128] = {0};
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;   // upload / download streams of the pipelined host path
     cudaEvent_t ev_in[16] = {};
-    int pipe_first_div = 4;      // first pipeline piece = a regular piece / this (BLG_PIPE_FIRST_DIV; development only)
-    int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi (BLG_PIPE_CHUNK_M overrides; development only)
-    int no_pipeline = 0;         // BLG_NO_PIPELINE=1: one upload, one launch, one download (development A/B only)
+    int pipe_first_div = 4;      // first pipeline piece = a regular piece / this
+    int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
-    unsigned long long* h_total = nullptr;  // pinned
+    unsigned long long* h_total = nullptr;  // pinned + mapped: [0] record count, [1] cumulative exact-path tiles (sk4 writes both itself)
+    unsigned long long* d_total = nullptr;  // the device's address of h_total
+    // sk4: scan scratch that is never zeroed between launches (epoch-tagged words, a ticket counter that only grows)
+    DevBuf sk4_status, sk4_small;           // sk4_small: [0] ticket counter, [2] cumulative exact-path tiles
+    long long sk4_cap_tiles = 0;            // roles inside sk4_status are fixed per allocation: tiles | group accumulators | group words
+    unsigned int sk4_epoch = 0, sk4_tickets = 0;
+    unsigned long long sk4_exact_seen = 0;
     std::string err;
     blg_stats stats{};
 };
@@ -142,32 +145,58 @@ void add_kernel_time(blg_ctx* c)
 int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 {
     SkLaunchPlan plan;
-    int gen = c->sk_gen;
-    if (gen == 0 || (gen == 4 && !sk4_supported(a.k, a.m))) gen = sk4_supported(a.k, a.m) ? 4 : 3;
-    if (gen == 3 && !sk3_supported(a.k, a.m)) gen = 2;
+    // one kernel per (k, m): sk4 for the benchmark families (k - m = 12, 10), the general form of sk3 for every other
+    // k - m >= 5, sk2 below that
+    const int gen = sk4_supported(a.k, a.m) ? 4 : sk3_supported(a.k, a.m) ? 3 : 2;
     if (gen == 4) CK(c, sk4_plan(a, c->sm_count, &plan));
-    else if (gen == 1) CK(c, sk_plan(a, c->sm_count, &plan));
     else if (gen == 2) CK(c, sk2_plan(a, c->sm_count, &plan));
     else CK(c, sk3_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
-    int rc = prep_scratch(c, gen >= 3 ? a.status_words : a.num_tiles);
+    int rc;
+    if (gen == 4) {
+        // no memset, no copy: see the protocol note in sk4_device.cuh
+        if (a.num_tiles > c->sk4_cap_tiles || c->sk4_epoch >= (1u << 22) - 1 || !c->sk4_small.p) {
+            const long long cap = a.num_tiles + a.num_tiles / 4 + 1024, groups = (cap + 31) / 32;
+            if ((rc = ensure(c, c->sk4_status, (size_t)(cap + 2 * groups) * 8)) != BLG_OK) return rc;
+            if ((rc = ensure(c, c->sk4_small, 64)) != BLG_OK) return rc;
+            CK(c, cudaMemsetAsync(c->sk4_status.p, 0, c->sk4_status.cap, c->stream));
+            CK(c, cudaMemsetAsync(c->sk4_small.p, 0, 64, c->stream));
+            c->sk4_cap_tiles = cap; c->sk4_epoch = 0; c->sk4_tickets = 0; c->sk4_exact_seen = 0;
+        }
+        const long long cap_groups = (c->sk4_cap_tiles + 31) / 32;
+        a.tile_counter = static_cast<unsigned int*>(c->sk4_small.p);
+        a.exact_tiles = static_cast<unsigned long long*>(c->sk4_small.p) + 2;
+        a.tile_status = static_cast<unsigned long long*>(c->sk4_status.p);
+        a.grp_acc = a.tile_status + c->sk4_cap_tiles;
+        a.grp_status = a.grp_acc + cap_groups;
+        a.total = c->d_total;
+        a.epoch = ++c->sk4_epoch;
+        a.ticket_base = c->sk4_tickets;
+        c->sk4_tickets += sk4_ticket_draws(a, plan);
+        CK(c, cudaEventRecord(c->ev0, c->stream));
+        CK(c, sk4_launch(a, plan, c->stream));
+        CK(c, cudaEventRecord(c->ev1, c->stream));
+        c->stats.kernel_launches += 1;
+        CK(c, cudaStreamSynchronize(c->stream));
+        *total = c->h_total[0];
+        c->stats.exact_tiles += c->h_total[1] - c->sk4_exact_seen;
+        c->sk4_exact_seen = c->h_total[1];
+        add_kernel_time(c);
+        return BLG_OK;
+    }
+    rc = prep_scratch(c, gen >= 3 ? a.status_words : a.num_tiles);
     if (rc != BLG_OK) return rc;
     a.tile_counter = static_cast<unsigned int*>(c->small.p);
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
-    if (gen == 4) {
-        a.exact_tiles = static_cast<unsigned long long*>(c->small.p) + 2;
-    }
     if (gen >= 3) {
         const long long groups = (a.num_tiles + 31) / 32;
         a.grp_acc = a.tile_status + a.num_tiles;
         a.grp_status = a.grp_acc + groups;
     }
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (gen == 1) CK(c, sk_launch(a, plan, c->stream));
-    else if (gen == 2) CK(c, sk2_launch(a, plan, c->stream));
-    else if (gen == 3) CK(c, sk3_launch(a, plan, c->stream));
-    else CK(c, sk4_launch(a, plan, c->stream));
+    if (gen == 2) CK(c, sk2_launch(a, plan, c->stream));
+    else CK(c, sk3_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -178,9 +207,7 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
 {
     KmerLaunchPlan plan;
-    const bool gen2 = c->kmer_gen != 1 || a.sync_on;            // the syncmer filter lives in the second-generation kernel only
-    if (gen2) CK(c, kmer2_plan(a, c->sm_count, &plan));
-    else CK(c, kmer_plan(a, c->sm_count, &plan));
+    CK(c, kmer2_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
     int rc = prep_scratch(c, a.num_tiles);
     if (rc != BLG_OK) return rc;
@@ -188,8 +215,7 @@ int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
     a.total = static_cast<unsigned long long*>(c->small.p) + 1;
     a.tile_status = static_cast<unsigned long long*>(c->status.p);
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (gen2) CK(c, kmer2_launch(a, plan, c->stream));
-    else CK(c, kmer_launch(a, plan, c->stream));
+    CK(c, kmer2_launch(a, plan, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches += 1;
     rc = read_total(c, total);
@@ -259,14 +285,16 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
                  const blg_params* p, blg_sk_out* out, bool with_size, bool want_hash, int* done_flag)
 {
     *done_flag = 0;
+    const bool pos32 = (p->flags & BLG_F_POS32) != 0;
+    const size_t posb = pos32 ? 4 : 8;                 // bytes per position entry
     const uint64_t nwin = hi - lo;
     const int k = p->k, m = p->m, w = k - m + 1;
-    if (nwin < (8u << 20) || c->no_pipeline) return BLG_OK;
+    if (nwin < (8u << 20)) return BLG_OK;
     int rc;
     if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
     const uint64_t cap = out->capacity > 0 ? out->capacity : estimate_records(nwin, w);
     if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
-    if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * 8)) != BLG_OK) return rc;
+    if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * posb)) != BLG_OK) return rc;
     if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
     if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
     const unsigned long long* d_offs = nullptr;
@@ -284,7 +312,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
         if (!ow) return BLG_E_NOMEM;
         h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
-        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
     }
@@ -322,7 +350,8 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         a.s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL;
         a.vec_ok = (reinterpret_cast<uintptr_t>(d_in) & 15u) == 0;
         a.value = static_cast<unsigned long long*>(c->o_value.p) + done;
-        a.mm_start = static_cast<unsigned long long*>(c->o_mm.p) + done;
+        if (pos32) { a.mm_start32 = static_cast<unsigned int*>(c->o_mm.p) + done; a.pos_base = (long long)lo; }
+        else a.mm_start = static_cast<unsigned long long*>(c->o_mm.p) + done;
         a.size = with_size ? static_cast<unsigned char*>(c->o_size.p) + done : nullptr;
         a.mm_pos = with_size ? static_cast<unsigned char*>(c->o_pos.p) + done : nullptr;
         a.hash = want_hash ? static_cast<unsigned long long*>(c->o_hash.p) + done : nullptr;
@@ -332,8 +361,8 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         if (cnt > cap - done) { overflow = true; done += cnt; break; }
         if (cnt) {
             CK(c, cudaMemcpyAsync(h.value + done, a.value, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
-            CK(c, cudaMemcpyAsync(h.mm_start + done, a.mm_start, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
-            c->stats.bytes_d2h += cnt * 16;
+            CK(c, cudaMemcpyAsync(reinterpret_cast<char*>(h.mm_start) + done * posb, static_cast<char*>(c->o_mm.p) + done * posb, cnt * posb, cudaMemcpyDeviceToHost, c->s_out));
+            c->stats.bytes_d2h += cnt * (8 + posb);
             if (with_size) {
                 CK(c, cudaMemcpyAsync(h.size + done, a.size, cnt, cudaMemcpyDeviceToHost, c->s_out));
                 CK(c, cudaMemcpyAsync(h.mm_pos + done, a.mm_pos, cnt, cudaMemcpyDeviceToHost, c->s_out));
@@ -373,6 +402,9 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const bool dev_out = (p->flags & BLG_F_DEVICE_OUTPUT) != 0;
     const bool want_hash = (p->flags & BLG_F_EMIT_HASH) != 0;
     const bool want_id = (p->flags & BLG_F_EMIT_ID) != 0;
+    const bool pos32 = (p->flags & BLG_F_POS32) != 0;
+    const size_t posb = pos32 ? 4 : 8;
+    if (pos32 && want_id) { c->err = "BLG_F_POS32 cannot be combined with BLG_F_EMIT_ID"; return BLG_E_INVALID; }
     with_size = with_size && !(p->flags & BLG_F_NO_SIZE);
     if (out->capacity > 0 && with_size && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
     if (out->capacity > 0 && want_hash && !out->hash) { c->err = "BLG_F_EMIT_HASH needs a hash array"; return BLG_E_INVALID; }
@@ -383,6 +415,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const uint64_t lo = win_begin < hi ? win_begin : hi;
     const uint64_t nwin = hi - lo;
     out->count = 0;
+    if (pos32 && nwin + (uint64_t)w > 0xFFFFFFFFull) { c->err = "BLG_F_POS32: the window range does not fit 32-bit positions"; return BLG_E_INVALID; }
     if (nwin == 0) {
         if (out->capacity == 0) { out->value = out->mm_start = out->hash = out->id = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
         c->stats.total_ms = tm.ms();
@@ -408,12 +441,17 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     a.canonical = p->canonical ? 1 : 0;
     a.s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL;
     a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
+    a.pos_base = (long long)lo;
+    auto set_pos = [&](void* ptr) {        // the position array is uint32 (relative to lo) or uint64
+        if (pos32) { a.mm_start32 = static_cast<unsigned int*>(ptr); a.mm_start = nullptr; }
+        else { a.mm_start = static_cast<unsigned long long*>(ptr); a.mm_start32 = nullptr; }
+    };
 
     uint64_t total = 0;
     if (dev_out && out->capacity > 0) {
         // caller-owned device arrays: one launch, no retry
         a.value = reinterpret_cast<unsigned long long*>(out->value);
-        a.mm_start = reinterpret_cast<unsigned long long*>(out->mm_start);
+        set_pos(out->mm_start);
         a.size = with_size ? out->size : nullptr;
         a.mm_pos = with_size ? out->mm_pos : nullptr;
         a.hash = want_hash ? reinterpret_cast<unsigned long long*>(out->hash) : nullptr;
@@ -439,19 +477,19 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
             if (!ow) return BLG_E_NOMEM;
             unsigned long long *v = nullptr, *s = nullptr, *h = nullptr, *idp = nullptr;
             unsigned char *sz = nullptr, *mp = nullptr;
-            if ((rc = alloc_owned(c, true, cap, &v, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &s, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+            if ((rc = alloc_owned(c, true, cap, &v, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, pos32 ? (cap + 1) / 2 : cap, &s, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
             if (with_size && ((rc = alloc_owned(c, true, cap, &sz, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, cap, &mp, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
             if (want_hash && (rc = alloc_owned(c, true, cap, &h, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
             if (want_id && (rc = alloc_owned(c, true, cap, &idp, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
-            a.value = v; a.mm_start = s; a.size = sz; a.mm_pos = mp; a.hash = h; d_id = idp;
+            a.value = v; set_pos(s); a.size = sz; a.mm_pos = mp; a.hash = h; d_id = idp;
         } else {
-            if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * 8)) != BLG_OK) return rc;
+            if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * posb)) != BLG_OK) return rc;
             if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
             if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
             if (want_id && (rc = ensure(c, c->o_id, cap * 8)) != BLG_OK) return rc;
             d_id = want_id ? static_cast<unsigned long long*>(c->o_id.p) : nullptr;
             a.value = static_cast<unsigned long long*>(c->o_value.p);
-            a.mm_start = static_cast<unsigned long long*>(c->o_mm.p);
+            set_pos(c->o_mm.p);
             a.size = with_size ? static_cast<unsigned char*>(c->o_size.p) : nullptr;
             a.mm_pos = with_size ? static_cast<unsigned char*>(c->o_pos.p) : nullptr;
             a.hash = want_hash ? static_cast<unsigned long long*>(c->o_hash.p) : nullptr;
@@ -469,7 +507,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (dev_out) {
         out->id = reinterpret_cast<uint64_t*>(d_id);
         out->value = reinterpret_cast<uint64_t*>(a.value);
-        out->mm_start = reinterpret_cast<uint64_t*>(a.mm_start);
+        out->mm_start = pos32 ? reinterpret_cast<uint64_t*>(a.mm_start32) : reinterpret_cast<uint64_t*>(a.mm_start);
         out->size = a.size; out->mm_pos = a.mm_pos;
         out->hash = reinterpret_cast<uint64_t*>(a.hash);
         out->owner = ow;
@@ -482,7 +520,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
         if (!ow) return BLG_E_NOMEM;
         out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
-        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         if (with_size && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, total, &out->hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
         if (want_id && (rc = alloc_owned(c, false, total, &out->id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
@@ -490,8 +528,8 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     }
     if (total) {
         CK(c, cudaMemcpyAsync(out->value, a.value, total * 8, cudaMemcpyDeviceToHost, c->stream));
-        CK(c, cudaMemcpyAsync(out->mm_start, a.mm_start, total * 8, cudaMemcpyDeviceToHost, c->stream));
-        c->stats.bytes_d2h += total * 16;
+        CK(c, cudaMemcpyAsync(out->mm_start, pos32 ? static_cast<void*>(a.mm_start32) : static_cast<void*>(a.mm_start), total * posb, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * (8 + posb);
         if (with_size) {
             CK(c, cudaMemcpyAsync(out->size, a.size, total, cudaMemcpyDeviceToHost, c->stream));
             CK(c, cudaMemcpyAsync(out->mm_pos, a.mm_pos, total, cudaMemcpyDeviceToHost, c->stream));
@@ -547,7 +585,8 @@ int blg_create(int device, blg_ctx** out)
     snprintf(c->name, sizeof(c->name), "%s", prop.name);
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
-        cudaMallocHost(reinterpret_cast<void**>(&c->h_total), 64) != cudaSuccess) {
+        cudaHostAlloc(reinterpret_cast<void**>(&c->h_total), 64, cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->d_total), c->h_total, 0) != cudaSuccess) {
         blg_destroy(c);
         return BLG_E_CUDA;
     }
@@ -556,11 +595,6 @@ int blg_create(int device, blg_ctx** out)
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
-    { const char* e = getenv("BLG_PIPE_FIRST_DIV"); if (e && atoi(e) > 0) c->pipe_first_div = atoi(e); }
-    { const char* e = getenv("BLG_PIPE_CHUNK_M"); if (e && atoi(e) > 0) c->pipe_chunk_m = atoi(e); }
-    { const char* e = getenv("BLG_NO_PIPELINE"); c->no_pipeline = (e && e[0] == '1') ? 1 : 0; }
-    { const char* e = getenv("BLG_KMER"); c->kmer_gen = (e && e[0] == '1') ? 1 : 0; }
-    { const char* e = getenv("BLG_SK"); c->sk_gen = (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 0; }
     *out = c;
     return BLG_OK;
 }
@@ -570,7 +604,7 @@ int blg_destroy(blg_ctx* c)
     if (!c) return BLG_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
+    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->sk4_status, &c->sk4_small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
                       &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
     if (c->h_total) cudaFreeHost(c->h_total);

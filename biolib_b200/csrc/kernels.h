@@ -27,6 +27,8 @@ struct SkArgs {
     int warp_smem;               // bytes of shared memory per warp (each warp owns a tile)
     unsigned long long* value;   // outputs (device); size / mm_pos / hash may be null
     unsigned long long* mm_start;
+    unsigned int* mm_start32;    // BLG_F_POS32: positions as uint32 relative to pos_base instead (mm_start is null then)
+    long long pos_base;
     unsigned char* size;
     unsigned char* mm_pos;
     unsigned long long* hash;
@@ -41,8 +43,19 @@ struct SkArgs {
     unsigned long long* grp_status;    // [groups] look-back words over groups
     // fourth-generation kernel (sk4_kernel.cu): 32-bit keys (hash bits above an index field) + exact redo on ties
     unsigned int keymask;              // ~(2^index_bits - 1)
-    unsigned long long* exact_tiles;   // optional counter: tiles that took the exact path (may be null)
+    unsigned long long* exact_tiles;   // optional counter: tiles that took the exact path (may be null); only grows
+    unsigned int epoch;                // tag of this launch's scan words (22 bits, never 0): no scratch is zeroed between launches
+    unsigned int ticket_base;          // value of *tile_counter when this launch starts (it only grows)
 };
+
+// position store of the record-emitting loops: 64-bit absolute, or 32-bit relative to pos_base (BLG_F_POS32)
+#ifdef __CUDACC__
+__device__ __forceinline__ void store_mm_start(const SkArgs& a, unsigned long long g, long long pos)
+{
+    if (a.mm_start32 != nullptr) a.mm_start32[g] = (unsigned int)(pos - a.pos_base);
+    else a.mm_start[g] = (unsigned long long)pos;
+}
+#endif
 
 struct SkLaunchPlan {
     int threads;       // w-blocks per tile (= CTA size)
@@ -50,10 +63,7 @@ struct SkLaunchPlan {
     int grid;
 };
 
-// Fills args.rb / args.nwords / args.num_tiles and the launch plan for (k, m) on a device with `sm_count` SMs.
-cudaError_t sk_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
-cudaError_t sk_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
-// second generation: same arguments, same results
+// sk2_kernel.cu: serves k - m < 5 (sparse-table window minimum); fills the launch plan for (k, m) on `sm_count` SMs
 #ifndef SK2_THREADS
 #define SK2_THREADS 128
 #endif
@@ -82,6 +92,8 @@ cudaError_t sk3_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_
 #endif
 bool sk4_supported(int k, int m);
 cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
+// tickets one launch draws from the counter: one per tile plus one per warp (the draw that tells a warp to stop)
+unsigned int sk4_ticket_draws(const SkArgs& args, const SkLaunchPlan& plan);
 cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 
 // kmer_view: every valid k-mer as (value, position), in position order.
@@ -115,9 +127,7 @@ struct KmerLaunchPlan {
     size_t smem_bytes;
     int grid;
 };
-cudaError_t kmer_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
-cudaError_t kmer_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
-// second generation (kmer2_kernel.cu): same arguments and results
+// kmer2_kernel.cu
 cudaError_t kmer2_plan(KmerArgs& args, int sm_count, KmerLaunchPlan* plan);
 cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaStream_t stream);
 

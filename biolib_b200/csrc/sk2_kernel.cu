@@ -370,7 +370,7 @@ __device__ __forceinline__ void emit_tile(const SkArgs& a, const unsigned char* 
         const u64 g = base + r;
         if (g < a.capacity) {
             a.value[g] = val;
-            a.mm_start[g] = (u64)(tbase + j);
+            store_mm_start(a, g, (long long)(tbase + j));
             if (a.size != nullptr) { a.size[g] = (u8)size; a.mm_pos[g] = (u8)(j - s0); }
             if (a.hash != nullptr) a.hash[g] = murmur3_key8(val, c.s8);
         }

@@ -496,7 +496,7 @@ __device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char*
         const u64 g = base + r;
         if (g < a.capacity) {
             a.value[g] = val;
-            a.mm_start[g] = (u64)(g0 + j);
+            store_mm_start(a, g, g0 + j);
             if (a.size != nullptr) { a.size[g] = (u8)size; a.mm_pos[g] = (u8)rel; }
             if (a.hash != nullptr) a.hash[g] = murmur3_key8_s32(val, c.s8);
         }
@@ -505,9 +505,16 @@ __device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char*
 }
 
 // ---- ordered output offset without any CTA barrier: the two-level chained scan of sk3 (tiles -> groups of 32) ------------
+// No scratch word is zeroed between launches: every word carries the launch's EPOCH (a.epoch, 22 bits, bumped by the host
+// per launch) and a word of another epoch reads as "not written yet"; tickets are drawn from a counter that only grows
+// (a.ticket_base = draws of all earlier launches: each launch draws num_tiles + number-of-warps tickets); a group's
+// arrival accumulator is reset by the warp that completes the group. The host zeroes the scratch when it allocates it
+// and when the epoch wraps.
+//   tile word  : (1 << 31 | epoch) << 32 | records of the tile
+//   group word : flag (1 = aggregate, 2 = inclusive prefix) << 62 | epoch << 40 | count (40 bits)
 constexpr int GS4 = 32;
-constexpr u64 TS_SET4 = 1ULL << 62;
 constexpr u64 ACC_ONE4 = 1ULL << 40, ACC_MASK4 = ACC_ONE4 - 1;
+constexpr u64 CNT_MASK4 = (1ULL << 40) - 1;
 
 __device__ __forceinline__ void spin_wait4(u32& spins)
 {
@@ -519,6 +526,43 @@ __device__ __forceinline__ void spin_wait4(u32& spins)
 #endif
 }
 
+__device__ __forceinline__ u32 tile_tag4(const SkArgs& a) { return 0x80000000u | a.epoch; }
+__device__ __forceinline__ u32 grp_tag4(const SkArgs& a, u32 flag) { return (flag << 22) | a.epoch; }   // compares with word >> 40
+
+// decoupled look-back over the group words; returns the exclusive prefix of group g and publishes its inclusive prefix
+__device__ __forceinline__ u64 lookback_groups4(const SkArgs& a, long long g, u64 aggregate, int lane)
+{
+    const unsigned full = 0xffffffffu;
+    u64* status = a.grp_status;
+    const u64 ep = (u64)a.epoch << 40;
+    if (g == 0) {
+        if (lane == 0) st_status(&status[0], (2ULL << 62) | ep | aggregate);
+        return 0;
+    }
+    if (lane == 0) st_status(&status[g], (1ULL << 62) | ep | aggregate);
+    const u32 t_agg = grp_tag4(a, 1), t_inc = grp_tag4(a, 2);
+    u64 excl = 0;
+    long long look = g - 1;
+    for (;;) {
+        const long long idx = look - lane;
+        u64 st = idx >= 0 ? ld_status(&status[idx]) : ((2ULL << 62) | ep);
+        u32 tag = (u32)(st >> 40);
+        while (__any_sync(full, tag != t_agg && tag != t_inc)) {
+            if (tag != t_agg && tag != t_inc) { st = ld_status(&status[idx]); tag = (u32)(st >> 40); }
+        }
+        const unsigned incl = __ballot_sync(full, tag == t_inc);
+        const int first_incl = incl ? (__ffs(incl) - 1) : 32;
+        u64 cnt = lane <= first_incl ? (st & CNT_MASK4) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(full, cnt, o);
+        excl += cnt;
+        if (incl) break;
+        look -= 32;
+    }
+    if (lane == 0) st_status(&status[g], (2ULL << 62) | ep | (excl + aggregate));
+    return excl;
+}
+
 __device__ __forceinline__ const u64* tile_base_addr4(const SkArgs& a, long long tile, int t)
 {
     const long long g = tile / GS4;
@@ -528,14 +572,20 @@ __device__ __forceinline__ const u64* tile_base_addr4(const SkArgs& a, long long
     return nullptr;
 }
 // lanes below the tile's index in its group hold the earlier tiles' counts (small), lane 31 the inclusive prefix of the
-// previous group (64-bit): one REDUX for the counts, one 64-bit broadcast
-__device__ __forceinline__ u64 tile_base_finish4(const u64* p, u64 v, int t)
+// previous group (40 bits): one REDUX for the counts, one 64-bit broadcast
+__device__ __forceinline__ u64 tile_base_finish4(const SkArgs& a, const u64* p, u64 v, int t)
 {
     if (p != nullptr) {
         u32 spins = 0;
-        if (t == 31) { while ((v >> 62) != 2) { spin_wait4(spins); v = ld_status(p); } }
-        else { while (!(v & TS_SET4)) { spin_wait4(spins); v = ld_status(p); } }
-        v &= ST_VAL;
+        if (t == 31) {
+            const u32 want = grp_tag4(a, 2);
+            while ((u32)(v >> 40) != want) { spin_wait4(spins); v = ld_status(p); }
+            v &= CNT_MASK4;
+        } else {
+            const u32 want = tile_tag4(a);
+            while ((u32)(v >> 32) != want) { spin_wait4(spins); v = ld_status(p); }
+            v &= 0xFFFFFFFFULL;
+        }
     }
     const u32 small = t == 31 ? 0u : (u32)v;
     const u32 s = __reduce_add_sync(0xffffffffu, small);
@@ -560,7 +610,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
 
     const long long num_groups = (a.num_tiles + GS4 - 1) / GS4;
     u32 tk = 0;
-    if (t == 0) tk = atomicAdd(a.tile_counter, 1u);
+    if (t == 0) tk = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
     long long tile = __shfl_sync(0xffffffffu, tk, 0);
     // computed, not yet written out: (t0, n0, b0) the newer, (t1, n1, b1) the older (KB == 3 only): tile, records, buffer set
     long long t0 = -1, t1 = -1;
@@ -585,7 +635,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
         if (have) {
             n_rec = compute_tile4<B, NB, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1);
             if (t == 0) {
-                st_status(&a.tile_status[tile], TS_SET4 | n_rec);
+                st_status(&a.tile_status[tile], ((u64)tile_tag4(a) << 32) | n_rec);
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
             }
         }
@@ -600,14 +650,18 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
             const u64 o0 = __shfl_sync(0xffffffffu, old, 0);
             if ((o0 >> 40) == expect - 1) {
                 const u64 gsum = (o0 & ACC_MASK4) + n_rec;
-                const u64 excl = lookback_exclusive(a.grp_status, g, gsum, t);
-                if (t == 0 && g == num_groups - 1) *a.total = excl + gsum;
+                if (t == 0) a.grp_acc[g] = 0;                      // nobody adds to a complete group: clean for the next launch
+                const u64 excl = lookback_groups4(a, g, gsum, t);
+                if (t == 0 && g == num_groups - 1) {
+                    a.total[0] = excl + gsum;                      // pinned host memory: no copy after the kernel
+                    if (a.exact_tiles != nullptr) a.total[1] = *reinterpret_cast<volatile unsigned long long*>(a.exact_tiles);
+                }
             }
         }
         u64 base = 0;
-        if (prev >= 0) base = tile_base_finish4(bp, bv, t);
+        if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
-        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u);
+        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
         if (prev >= 0) emit_tile4<B, NB, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;

@@ -21,11 +21,23 @@ bool pick_variant4(int k, int m, Variant4* v)
 constexpr int NB4 = 2;       // blocks per lane (sk4_device.cuh numbers record slots for two)
 
 template <int B, int NB, int LW, bool CANON, bool MW>
-cudaError_t setup4(size_t smem, int* occ)
+cudaError_t setup4_uncached(size_t smem, int* occ)
 {
     cudaError_t e = cudaFuncSetAttribute(sk4_kernel<B, NB, LW, CANON, MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, sk4_kernel<B, NB, LW, CANON, MW>, SK4_THREADS, smem);
+}
+
+// the shared-memory opt-in and the occupancy query are paid once per device and instance, not per call
+template <int B, int NB, int LW, bool CANON, bool MW>
+cudaError_t setup4(size_t smem, int* occ)
+{
+    static int cached_occ[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && cached_occ[dev] > 0) { *occ = cached_occ[dev]; return cudaSuccess; }
+    cudaError_t e = setup4_uncached<B, NB, LW, CANON, MW>(smem, occ);
+    if (e == cudaSuccess && dev >= 0 && dev < 64) cached_occ[dev] = *occ;
+    return e;
 }
 
 template <int B, int NB, int LW, bool MW>
@@ -93,6 +105,11 @@ cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
     if (grid > units) grid = units;
     plan->grid = (int)(grid < 1 ? 1 : grid);
     return cudaSuccess;
+}
+
+unsigned int sk4_ticket_draws(const SkArgs& args, const SkLaunchPlan& plan)
+{
+    return (unsigned int)((unsigned long long)args.num_tiles + (unsigned long long)plan.grid * WARPS4);
 }
 
 cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream)

@@ -370,11 +370,9 @@ def test_kmers_multi_sequence(gpu, oracle):
 
 
 @pytest.mark.parametrize("k,canon", [(31, True), (63, True), (17, False)])
-def test_kmers_many_tiles_both_generations(gpu, oracle, k, canon):
-    """Hundreds of tiles of the second-generation kernel (clean tiles, tiles with N runs, read boundaries, a ragged
-    end), against the oracle and against the first-generation kernel (BLG_KMER=1 pins it at context creation)."""
-    import os
-    import biolib_b200
+def test_kmers_many_tiles(gpu, oracle, k, canon):
+    """Hundreds of tiles of the k-mer kernel (clean tiles, tiles with N runs, read boundaries, a ragged end) against the
+    oracle."""
     rng = np.random.default_rng(900 + k)
     n = 2_000_003
     s = rand_seq(rng, n)
@@ -384,22 +382,33 @@ def test_kmers_many_tiles_both_generations(gpu, oracle, k, canon):
     offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
     offsets = offsets[offsets < n]
     offsets = np.concatenate([offsets, [n]]).astype(np.uint64)
-    os.environ["BLG_KMER"] = "1"
-    try:
-        first = biolib_b200.Context(0)
-    finally:
-        del os.environ["BLG_KMER"]
-    try:
-        for offs in (None, offsets):
-            g = gpu.kmers(s, k, canon, offsets=offs)
-            o = oracle.kmers(s, k, canon, offsets=offs)
-            f = first.kmers(s, k, canon, offsets=offs)
-            assert len(g["lo"]) == len(o["lo"]) > 1_000_000
-            for key in ("lo", "hi", "pos"):
-                assert np.array_equal(g[key], o[key]), (key, k)
-                assert np.array_equal(g[key], f[key]), (key, k)
-    finally:
-        first.close()
+    for offs in (None, offsets):
+        g = gpu.kmers(s, k, canon, offsets=offs)
+        o = oracle.kmers(s, k, canon, offsets=offs)
+        assert len(g["lo"]) == len(o["lo"]) > 1_000_000
+        for key in ("lo", "hi", "pos"):
+            assert np.array_equal(g[key], o[key]), (key, k)
+
+
+def test_kmers_device_input_small_buffers(gpu, oracle):
+    """device-resident input of 16 .. 64 KB and of exactly 2^k bytes (the next-tile prefetch of kmer2_kernel
+    used to read past such buffers); k-mers and syncmers."""
+    import torch
+    rng = np.random.default_rng(4242)
+    for n in (16_384, 20_000, 32_768, 40_961, 65_536):
+        s = rand_seq(rng, n, p_n=0.001)
+        d = torch.from_numpy(s).cuda()
+        cap = n
+        lo = torch.empty(cap, dtype=torch.int64, device="cuda"); pos = torch.empty_like(lo)
+        for canon in (False, True):
+            cnt = gpu.kmers_device(d.data_ptr(), n, 31, canon, lo.data_ptr(), 0, pos.data_ptr(), cap)
+            o = oracle.kmers(s, 31, canon)
+            assert cnt == len(o["lo"])
+            assert np.array_equal(lo[:cnt].cpu().numpy().view(np.uint64), o["lo"]) and np.array_equal(pos[:cnt].cpu().numpy().view(np.uint64), o["pos"])
+            cnt = gpu.kmers_device(d.data_ptr(), n, 31, canon, lo.data_ptr(), 0, pos.data_ptr(), cap, syncmer=(19, 0, 12))
+            o = oracle.syncmers(s, 31, 19, 0, 12, canon)
+            assert cnt == len(o["lo"])
+            assert np.array_equal(lo[:cnt].cpu().numpy().view(np.uint64), o["lo"]) and np.array_equal(pos[:cnt].cpu().numpy().view(np.uint64), o["pos"])
 
 
 def test_config1_kmer_view_1mbp(gpu, oracle):
@@ -557,3 +566,36 @@ def test_d4_window_argmin_vs_reference_extractor(gpu, oracle, k, m):
         rec = gpu.super_kmers(s, k, m, 0, False)
         km = gpu.kmers(s, k, False)
         check_d4(rec, km, np.asarray(ext.minimizer_positions(km["lo"], k, m)))
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (63, 31), (40, 9), (8, 4)])
+def test_compact_records_pos32(gpu, oracle, k, m):
+    """BLG_F_POS32: 32-bit positions relative to the range start, every kernel (sk4 / sk3 / sk2), plain and pipelined host
+    paths, whole buffer and window ranges; identical to the 64-bit layout."""
+    rng = np.random.default_rng(k * 3 + m)
+    s = rand_seq(rng, 300_000, 0.0005, 0.02)
+    for canon in (False, True):
+        a = gpu.super_kmers(s, k, m, 42, canon)
+        b = gpu.super_kmers(s, k, m, 42, canon, pos32=True)
+        for key in ("value", "hash", "mm_start", "sk_start", "size", "mm_pos"):
+            assert np.array_equal(a[key], b[key]), (key, k, m)
+    lo, hi = 100_003, 250_000
+    a = gpu.super_kmers(s, k, m, 42, True, win_range=(lo, hi))
+    b = gpu.super_kmers(s, k, m, 42, True, win_range=(lo, hi), pos32=True)
+    assert a["n"] == b["n"] > 0 and np.array_equal(a["mm_start"], b["mm_start"]) and np.array_equal(a["size"], b["size"])
+    o = oracle.super_kmers(s, k, m, 42, True)
+    sel = (o["sk_start"] >= lo) & (o["sk_start"] < hi)
+    assert np.array_equal(b["mm_start"], o["mm_start"][sel]) and np.array_equal(b["value"], o["value"][sel])
+
+
+def test_compact_records_pos32_pipelined(gpu):
+    """The chunked host path (>= 8 Mi windows) with the compact layout against the 64-bit layout."""
+    rng = np.random.default_rng(77)
+    s = rand_seq(rng, 20_000_000, 0.0001)
+    a = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False)
+    b = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False, pos32=True)
+    assert a["n"] == b["n"] > 2_000_000
+    for key in ("value", "mm_start", "size", "mm_pos"):
+        assert np.array_equal(a[key], b[key]), key
+    st = gpu.stats()
+    assert st["bytes_d2h"] < a["n"] * 14 + 4096

@@ -90,25 +90,3 @@ def test_window_ranges(gpu, oracle):
         assert np.array_equal(np.concatenate([p[key] for p in parts]), whole[key]), key
     o = oracle.super_kmers(s, k, m, 42, True)
     assert np.array_equal(whole["mm_start"], o["mm_start"]) and np.array_equal(whole["size"], o["size"])
-
-
-def test_two_generations_agree_2mbp(gpu):
-    """sk4 (default) against sk3 (BLG_SK=3 at context creation) on 2 Mbp with ties and breaks."""
-    import os
-    import biolib_b200
-    rng = np.random.default_rng(19)
-    s = rand_seq(rng, 2_000_000, p_n=0.0002)
-    s[500_000:500_600] = np.frombuffer(b"AC" * 300, np.uint8)
-    os.environ["BLG_SK"] = "3"
-    try:
-        old = biolib_b200.Context(0)
-    finally:
-        del os.environ["BLG_SK"]
-    try:
-        for k, m in ((31, 19), (21, 11)):
-            a, b = gpu.super_kmers(s, k, m, 42, True), old.super_kmers(s, k, m, 42, True)
-            assert a["n"] == b["n"]
-            for key in ("value", "mm_start", "size", "mm_pos", "hash"):
-                assert np.array_equal(a[key], b[key]), (key, k, m)
-    finally:
-        old.close()

@@ -142,21 +142,16 @@ def main():
     # ---- configs[4]: k=21 m=11, 20 000 mutated long reads (10-100 kbp), sharded by read ------------------------------
     if not only or "5" in only:
         k, m = 21, 11
-        rng = np.random.Generator(np.random.MT19937(46))
-        lens = rng.integers(10_000, 100_001, size=20_000)
-        offs_h = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        # read i = sequence_mutator(source slice i, 0.10, 0.3, 0.3) from cbegin(47 + i); every rank builds the
+        # whole batch (deterministic) and takes its read range
+        s_all, offs_h = synth.mutated_long_reads(20_000)
         a, b = shard.plan_sequences(offs_h, world)[rank]
         base, end = int(offs_h[a]), int(offs_h[b])
-        first = base // (1 << 24)
-        s = synth.generate_sharded_parallel(46 + first, end - first * (1 << 24), 1 << 24)[base - first * (1 << 24):]
-        r2 = np.random.Generator(np.random.MT19937(47 + rank))
-        mut = r2.random(s.size) < 0.10          # substitutions at the mutator's rate (its dominant event)
-        code = np.zeros(256, np.uint8); code[list(b"ACGT")] = [0, 1, 2, 3]
-        s[mut] = np.frombuffer(b"ACGT", np.uint8)[(code[s[mut]] + 1 + r2.integers(0, 3, size=int(mut.sum())).astype(np.uint8)) & 3]
+        s = s_all[base:end]
         d = torch.from_numpy(s).to(dev)
         offs = torch.from_numpy((offs_h[a:b + 1] - np.uint64(base)).view(np.int64)).to(dev)
         ms, cnt = timed(d, s.size, k, m, offs=offs)
-        report("5: minimizers+super-k-mers k=21 m=11, 20 000 long reads 10-100 kbp (10 % substitutions), sharded by read", k, m, s.size, ms, cnt,
+        report("5: minimizers+super-k-mers k=21 m=11, 20 000 long reads 10-100 kbp, sequence_mutator(0.10, 0.3, 0.3), sharded by read", k, m, s.size, ms, cnt,
                {"scaling": "strong", "reads": int(b - a)}, [s[i * 3_000_000:(i + 1) * 3_000_000].copy() for i in range(threads)] if rank == 0 else None)
         del d
 
