@@ -130,6 +130,70 @@ class Context:
             self.L.blg_free_sk_out(self.h, C.byref(out))
         return res
 
+    # ------------------------------------------------------------------ ingest
+    def pack_bases(self, seq):
+        """Host-side packer blg_pack_bases: (codes uint32[ceil(n/16)], break_start uint64[], break_len uint32[])."""
+        b = _as_bytes_array(seq)
+        codes = np.empty((b.size + 15) // 16, np.uint32)
+        cap = 1024
+        while True:
+            bs, bl = np.empty(cap, np.uint64), np.empty(cap, np.uint32)
+            nb = C.c_size_t()
+            st = self.L.blg_pack_bases(b.ctypes.data, b.size, codes.ctypes.data, bs.ctypes.data, bl.ctypes.data, cap, C.byref(nb))
+            if st == _capi.BLG_E_CAPACITY:
+                cap = nb.value
+                continue
+            self._check(st)
+            return codes, bs[:nb.value].copy(), bl[:nb.value].copy()
+
+    def super_kmers_packed(self, codes, n_bases, break_start, break_len, k, m, seed=0, canonical=False, offsets=None, want_hash=True,
+                           win_range=None, pos32=False) -> dict:
+        """blg_super_kmers_packed: 2-bit packed input (0.25 B per base over PCIe) + break intervals."""
+        codes = np.ascontiguousarray(codes, np.uint32)
+        bs, bl = np.ascontiguousarray(break_start, np.uint64), np.ascontiguousarray(break_len, np.uint32)
+        o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
+        seq = _capi.PackedSeq(codes=codes.ctypes.data, n_bases=n_bases, break_start=bs.ctypes.data if bs.size else None,
+                              break_len=bl.ctypes.data if bl.size else None, n_breaks=bs.size)
+        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_POS32 if pos32 else 0), seed=seed & (2**64 - 1))
+        out = SkOut()
+        lo, hi = (0, 2**64 - 1) if win_range is None else win_range
+        self._check(self.L.blg_super_kmers_packed(self.h, C.byref(seq), o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1,
+                                                  int(lo), int(hi), C.byref(p), C.byref(out)))
+        n = out.count
+        try:
+            if pos32:
+                base = 0 if win_range is None else min(int(win_range[0]), max(n_bases - k + 1, 0))
+                mm = _copy(out.mm_start, n, np.uint32).astype(np.uint64) + np.uint64(base)
+            else:
+                mm = _copy(out.mm_start, n, np.uint64)
+            res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=mm, size=_copy(out.size, n, np.uint8), mm_pos=_copy(out.mm_pos, n, np.uint8))
+            res["sk_start"] = res["mm_start"] - res["mm_pos"].astype(np.uint64)
+            if want_hash:
+                res["hash"] = _copy(out.hash, n, np.uint64)
+        finally:
+            self.L.blg_free_sk_out(self.h, C.byref(out))
+        return res
+
+    def parse_fastx(self, text, fmt: int = -1):
+        """blg_parse_fastx (device record splitter): FASTA / FASTQ text -> (bases uint8, seq_offsets uint64[n_seq + 1])."""
+        t = _as_bytes_array(text)
+        out = _capi.FastxOut()
+        self._check(self.L.blg_parse_fastx(self.h, t.ctypes.data, t.size, fmt, 0, C.byref(out)))
+        try:
+            return _copy(out.bases, out.n_bases, np.uint8), _copy(out.seq_offsets, out.n_seq + 1, np.uint64)
+        finally:
+            self.L.blg_free_fastx_out(self.h, C.byref(out))
+
+    def parse_fastx_device(self, text_ptr: int, n_text: int, fmt: int = -1, device_input: bool = True):
+        """Device-resident form: returns a FastxOut whose bases / seq_offsets are device pointers (free with free_fastx)."""
+        out = _capi.FastxOut()
+        flags = (F_DEVICE_INPUT if device_input else 0) | F_DEVICE_OUTPUT
+        self._check(self.L.blg_parse_fastx(self.h, C.c_void_p(text_ptr), n_text, fmt, flags, C.byref(out)))
+        return out
+
+    def free_fastx(self, out):
+        self.L.blg_free_fastx_out(self.h, C.byref(out))
+
     def minimizers(self, seq, k, m, seed=0, canonical=False, offsets=None, want_hash=True, want_id=False) -> dict:
         return self.super_kmers(seq, k, m, seed, canonical, offsets, want_hash, minimizers_only=True, want_id=want_id)
 

@@ -40,6 +40,8 @@ struct blg_ctx {
     cudaEvent_t ev_in[16] = {};
     int pipe_first_div = 4;      // first pipeline piece = a regular piece / this
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi
+    const unsigned char* staged = nullptr;  // set while a packed-input call runs: the bases are already unpacked in `in`
+    DevBuf packed, brk, fx_text, fx_scratch; // packed codes + break list of a packed-input call; FASTA/FASTQ text and parser scratch
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
     unsigned long long* h_total = nullptr;  // pinned + mapped: [0] record count, [1] cumulative exact-path tiles (sk4 writes both itself)
@@ -100,9 +102,11 @@ int place_input(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, s
     }
     int rc = check_offsets_host(offs, n_seq, n);
     if (rc != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
-    if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
-    if (n) CK(c, cudaMemcpyAsync(c->in.p, bases, n, cudaMemcpyHostToDevice, c->stream));
-    c->stats.bytes_h2d += n;
+    if (!c->staged) {
+        if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+        if (n) CK(c, cudaMemcpyAsync(c->in.p, bases, n, cudaMemcpyHostToDevice, c->stream));
+        c->stats.bytes_h2d += n;
+    }
     *d_bases = static_cast<const unsigned char*>(c->in.p);
     *d_offs = nullptr;
     if (offs) {
@@ -293,7 +297,8 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     int rc;
     if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
     const uint64_t cap = out->capacity > 0 ? out->capacity : estimate_records(nwin, w);
-    if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+    const bool staged = c->staged != nullptr;           // packed input: the bases are on the device already, nothing to upload
+    if (!staged && (rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
     if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * posb)) != BLG_OK) return rc;
     if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
     if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
@@ -330,17 +335,18 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         size_t end = i == nch - 1 ? n : (size_t)cut[i + 1] + halo;
         end = (end > n ? n : end);
         if (i < nch - 1) end = end / 16 * 16;
+        if (staged) { up[i] = n; continue; }
         if (end > sent) CK(c, cudaMemcpyAsync(d_in + sent, bases + sent, end - sent, cudaMemcpyHostToDevice, c->s_in));
         CK(c, cudaEventRecord(c->ev_in[i], c->s_in));
         sent = end > sent ? end : sent;
         up[i] = sent;
     }
-    c->stats.bytes_h2d += n;
+    if (!staged) c->stats.bytes_h2d += n;
     uint64_t done = 0;
     bool overflow = false;
     for (int i = 0; i < nch && !overflow; ++i) {
         if (cut[i + 1] <= cut[i]) continue;
-        CK(c, cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
+        if (!staged) CK(c, cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
         SkArgs a{};
         a.bases = d_in; a.buf_lo = 0; a.buf_hi = (long long)up[i];
         a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
@@ -376,7 +382,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         done += cnt;
     }
     CK(c, cudaStreamSynchronize(c->s_out));
-    CK(c, cudaStreamSynchronize(c->s_in));
+    if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
     if (overflow) {
         free_owner(ow);
         return BLG_OK;             // plain path: exact count, retry / BLG_E_CAPACITY
@@ -394,8 +400,11 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     int rc = validate_sk(c, p, out);
     if (rc != BLG_OK) return rc;
     Timer tm;
+    const uint64_t staged_h2d = c->staged ? c->stats.bytes_h2d : 0, staged_launches = c->staged ? c->stats.kernel_launches : 0;
     c->stats = blg_stats{};
     c->stats.n_bases = n;
+    c->stats.bytes_h2d = staged_h2d;
+    c->stats.kernel_launches = staged_launches;
     c->err.clear();
     CK(c, cudaSetDevice(c->device));
     const int k = p->k, m = p->m, w = k - m + 1;
@@ -604,7 +613,7 @@ int blg_destroy(blg_ctx* c)
     if (!c) return BLG_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->sk4_status, &c->sk4_small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
+    for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->packed, &c->brk, &c->fx_text, &c->fx_scratch, &c->sk4_status, &c->sk4_small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
                       &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
     if (c->h_total) cudaFreeHost(c->h_total);
@@ -673,6 +682,114 @@ int blg_minimizers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs
                    blg_sk_out* out)
 {
     return sk_common(c, bases, n, offs, n_seq, 0, ~0ULL, p, out, false);
+}
+
+int blg_super_kmers_packed(blg_ctx* c, const blg_packed_seq* seq, const uint64_t* offs, size_t n_seq, uint64_t win_begin,
+                           uint64_t win_end, const blg_params* p, blg_sk_out* out)
+{
+    if (!c || !seq || !p || !out || (seq->n_bases && !seq->codes) || (seq->n_breaks && (!seq->break_start || !seq->break_len))) return BLG_E_INVALID;
+    if (p->flags & (BLG_F_DEVICE_INPUT | BLG_F_EMIT_ID)) { c->err = "packed input: host pointers only, no BLG_F_EMIT_ID"; return BLG_E_INVALID; }
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    const size_t n = seq->n_bases, words = (n + 15) / 16;
+    int rc;
+    if ((rc = ensure(c, c->packed, words * 4 + 16)) != BLG_OK || (rc = ensure(c, c->in, words * 16 + 64)) != BLG_OK) return rc;
+    if ((rc = ensure(c, c->brk, seq->n_breaks * 12 + 16)) != BLG_OK) return rc;
+    c->stats = blg_stats{};
+    unsigned long long* d_bs = static_cast<unsigned long long*>(c->brk.p);
+    unsigned int* d_bl = reinterpret_cast<unsigned int*>(d_bs + seq->n_breaks);
+    if (words) CK(c, cudaMemcpyAsync(c->packed.p, seq->codes, words * 4, cudaMemcpyHostToDevice, c->stream));
+    if (seq->n_breaks) {
+        CK(c, cudaMemcpyAsync(d_bs, seq->break_start, seq->n_breaks * 8, cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaMemcpyAsync(d_bl, seq->break_len, seq->n_breaks * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    CK(c, unpack_launch(c->packed.p, n, d_bs, d_bl, seq->n_breaks, static_cast<unsigned char*>(c->in.p), c->stream));
+    c->stats.bytes_h2d = words * 4 + seq->n_breaks * 12;
+    c->stats.kernel_launches = seq->n_breaks ? 2 : 1;
+    c->staged = static_cast<const unsigned char*>(c->in.p);
+    rc = sk_common(c, reinterpret_cast<const char*>(c->in.p), n, offs, n_seq, win_begin, win_end, p, out, true);
+    c->staged = nullptr;
+    return rc;
+}
+
+int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uint32_t flags, blg_fastx_out* out)
+{
+    if (!c || !out || (n_text && !text) || format < -1 || format > 1) return BLG_E_INVALID;
+    c->err.clear();
+    c->stats = blg_stats{};
+    Timer tm;
+    CK(c, cudaSetDevice(c->device));
+    out->n_bases = out->n_seq = 0; out->bases = nullptr; out->seq_offsets = nullptr; out->owner = nullptr;
+    if (n_text == 0) return BLG_OK;
+    const bool dev_in = (flags & BLG_F_DEVICE_INPUT) != 0, dev_out = (flags & BLG_F_DEVICE_OUTPUT) != 0;
+    int rc;
+    const unsigned char* d_text = reinterpret_cast<const unsigned char*>(text);
+    if (!dev_in) {
+        if ((rc = ensure(c, c->fx_text, n_text + 64)) != BLG_OK) return rc;
+        CK(c, cudaMemcpyAsync(c->fx_text.p, text, n_text, cudaMemcpyHostToDevice, c->stream));
+        c->stats.bytes_h2d += n_text;
+        d_text = static_cast<const unsigned char*>(c->fx_text.p);
+    } else if (reinterpret_cast<uintptr_t>(text) & 15u) { c->err = "device text must be 16-byte aligned"; return BLG_E_INVALID; }
+    if (format < 0) {
+        char first = 0;
+        if (dev_in) CK(c, cudaMemcpy(&first, text, 1, cudaMemcpyDeviceToHost)); else first = text[0];
+        if (first == '>') format = 0; else if (first == '@') format = 1;
+        else { c->err = "text starts with neither '>' nor '@'"; return BLG_E_INVALID; }
+    }
+    if ((rc = ensure(c, c->fx_scratch, fastx_scratch_bytes(n_text) + 64)) != BLG_OK) return rc;
+    Owner* ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+    if (!ow) return BLG_E_NOMEM;
+    unsigned char* d_bases = nullptr;
+    unsigned long long* d_offs = nullptr;
+    const size_t max_seq = n_text / 2 + 2;
+    if ((rc = alloc_owned(c, true, n_text + 64, &d_bases, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, max_seq, &d_offs, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->fx_scratch.p) + fastx_scratch_bytes(n_text));
+    int launches = 0;
+    cudaError_t e = fastx_launch(d_text, n_text, format, c->fx_scratch.p, d_bases, d_offs, d_tot, c->stream, &launches);
+    if (e != cudaSuccess) { free_owner(ow); c->err = cudaGetErrorString(e); return BLG_E_CUDA; }
+    c->stats.kernel_launches += launches;
+    unsigned long long tot[2] = {0, 0}, first_off = 0;
+    if (cudaMemcpyAsync(tot, d_tot, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) { free_owner(ow); c->err = "fastx: count read-back failed"; return BLG_E_CUDA; }
+    if (tot[1] == 0 || cudaMemcpy(&first_off, d_offs, 8, cudaMemcpyDeviceToHost) != cudaSuccess || first_off != 0) {
+        free_owner(ow);
+        c->err = "text does not start with a record header";
+        return BLG_E_INVALID;
+    }
+    // close the offsets array: offsets[n_seq] = n_bases
+    if (cudaMemcpy(d_offs + tot[1], &tot[0], 8, cudaMemcpyHostToDevice) != cudaSuccess) { free_owner(ow); return BLG_E_CUDA; }
+    out->n_bases = tot[0];
+    out->n_seq = tot[1];
+    c->stats.n_bases = tot[0];
+    c->stats.n_records = tot[1];
+    if (dev_out) {
+        out->bases = reinterpret_cast<char*>(d_bases);
+        out->seq_offsets = reinterpret_cast<uint64_t*>(d_offs);
+        out->owner = ow;
+    } else {
+        Owner* hw = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        if (!hw) { free_owner(ow); return BLG_E_NOMEM; }
+        char* hb = nullptr;
+        uint64_t* ho = nullptr;
+        if ((rc = alloc_owned(c, false, (size_t)tot[0] + 1, &hb, hw, 0)) != BLG_OK || (rc = alloc_owned(c, false, (size_t)tot[1] + 1, &ho, hw, 1)) != BLG_OK) { free_owner(ow); free_owner(hw); return rc; }
+        cudaError_t e1 = cudaMemcpyAsync(hb, d_bases, tot[0], cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e2 = cudaMemcpyAsync(ho, d_offs, (tot[1] + 1) * 8, cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e3 = cudaStreamSynchronize(c->stream);
+        free_owner(ow);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { free_owner(hw); c->err = "fastx: download failed"; return BLG_E_CUDA; }
+        c->stats.bytes_d2h += tot[0] + (tot[1] + 1) * 8;
+        out->bases = hb; out->seq_offsets = ho; out->owner = hw;
+    }
+    c->stats.total_ms = tm.ms();
+    return BLG_OK;
+}
+
+void blg_free_fastx_out(blg_ctx* c, blg_fastx_out* out)
+{
+    if (!out) return;
+    if (c) cudaSetDevice(c->device);
+    if (out->owner) free_owner(static_cast<Owner*>(out->owner));
+    out->bases = nullptr; out->seq_offsets = nullptr; out->owner = nullptr; out->n_bases = out->n_seq = 0;
 }
 
 namespace {

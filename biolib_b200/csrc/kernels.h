@@ -140,6 +140,13 @@ cudaError_t record_ids_launch(const unsigned char* bases, long long n_bases, con
 // hash::minimizer_position_extractor for k-mer values held in uint64_t (k <= 32)
 cudaError_t minpos_launch(const unsigned long long* values, size_t n, int k, int m, unsigned char* out, int sm_count, cudaStream_t stream);
 
+// ingest_kernel.cu: 2-bit packed input -> ASCII; FASTA / FASTQ text -> bases + seq_offsets
+cudaError_t unpack_launch(const void* codes, size_t n_bases, const unsigned long long* break_start, const unsigned int* break_len,
+                          size_t n_breaks, unsigned char* out, cudaStream_t stream);
+size_t fastx_scratch_bytes(size_t n_text);
+cudaError_t fastx_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
+                         unsigned long long* totals, cudaStream_t stream, int* launches);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

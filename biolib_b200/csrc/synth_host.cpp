@@ -1,5 +1,5 @@
-// synth_host.cpp -- host-side workload generators of the C ABI (include/biolib_gpu.h: blg_synth_generate,
-// blg_synth_mutate). They restate, for batched buffers, the two generators the reference's benchmarks draw their inputs
+// synth_host.cpp -- host-side helpers of the C ABI (include/biolib_gpu.h): the workload generators blg_synth_generate /
+// blg_synth_mutate and the 2-bit packer blg_pack_bases (the wire format of blg_super_kmers_packed). They restate, for batched buffers, the two generators the reference's benchmarks draw their inputs
 // from:
 //   sequence::generator::nucleic<packed::uniform>::get_sequence   reference include/sequence_generator.hpp:14-23,28-43
 //   wrapper::sequence_mutator<Iterator>::const_iterator           reference include/sequence_mutator.hpp:109-169
@@ -29,6 +29,44 @@ inline int code_of(char ch)                       // constants::seq_nt4_table re
 }  // namespace
 
 extern "C" {
+
+// ASCII -> 16 bases per 32-bit word (base q at bits [2q, 2q+2)) + the intervals of bytes that are not AaCcGgTtUu
+// (constants::seq_nt4_table, reference include/constants.hpp:12-21). A code under a break is 0.
+int blg_pack_bases(const char* bases, size_t n, uint32_t* codes, uint64_t* break_start, uint32_t* break_len, size_t break_capacity,
+                   size_t* n_breaks)
+{
+    if ((n && (!bases || !codes)) || !n_breaks) return BLG_E_INVALID;
+    size_t nb = 0;
+    bool in_break = false;
+    uint64_t run_start = 0;
+    auto close_run = [&](uint64_t end) {
+        // intervals longer than 32 bits of length are split
+        uint64_t s0 = run_start;
+        while (s0 < end) {
+            const uint64_t len = end - s0 > 0xFFFFFFFFull ? 0xFFFFFFFFull : end - s0;
+            if (nb < break_capacity) { break_start[nb] = s0; break_len[nb] = (uint32_t)len; }
+            ++nb;
+            s0 += len;
+        }
+    };
+    const size_t words = (n + 15) / 16;
+    for (size_t w = 0; w < words; ++w) {
+        uint32_t word = 0;
+        const size_t lo = w * 16, hi = lo + 16 < n ? lo + 16 : n;
+        for (size_t i = lo; i < hi; ++i) {
+            const int c = code_of(bases[i]);
+            if (c > 3) { if (!in_break) { in_break = true; run_start = i; } }
+            else {
+                if (in_break) { in_break = false; close_run(i); }
+                word |= (uint32_t)c << (2 * (i - lo));
+            }
+        }
+        codes[w] = word;
+    }
+    if (in_break) close_run(n);
+    *n_breaks = nb;
+    return nb > break_capacity ? BLG_E_CAPACITY : BLG_OK;
+}
 
 int blg_synth_generate(uint64_t seed, size_t length, char* out)
 {

@@ -190,6 +190,49 @@ int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, cons
                            const blg_params* p, uint64_t threshold, blg_kmer_out* out);
 
 /*
+ * Ingest: the two input formats either side of the hot path.
+ *
+ * 2-bit packed input. H2D then moves 0.25 B per base. `codes` holds 16 bases per 32-bit little-endian word, base q of a
+ * word at bits [2q, 2q+2) with A=0 C=1 G=2 T/U=3 (the order of constants::seq_nt4_table, include/constants.hpp:12-21);
+ * ceil(n_bases / 16) words. Everything the table maps to 4 (N, IUPAC codes, ...) is listed as break intervals
+ * [break_start[i], break_start[i] + break_len[i]), sorted, disjoint; the codes under a break are ignored. Case is not kept:
+ * no output depends on it.
+ *   blg_pack_bases          host-side packer: ASCII -> codes + break intervals (BLG_E_CAPACITY with *n_breaks = the number
+ *                           needed when break_capacity is too small)
+ *   blg_super_kmers_packed  blg_super_kmers_range over packed input (host pointers); the bases are unpacked on the device
+ */
+typedef struct blg_packed_seq {
+    const uint32_t* codes;
+    size_t n_bases;
+    const uint64_t* break_start;
+    const uint32_t* break_len;
+    size_t n_breaks;
+} blg_packed_seq;
+int blg_pack_bases(const char* bases, size_t n_bases, uint32_t* codes, uint64_t* break_start, uint32_t* break_len,
+                   size_t break_capacity, size_t* n_breaks);
+int blg_super_kmers_packed(blg_ctx* ctx, const blg_packed_seq* seq, const uint64_t* seq_offsets, size_t n_seq,
+                           uint64_t win_begin, uint64_t win_end, const blg_params* p, blg_sk_out* out);
+
+/*
+ * FASTA / FASTQ text -> concatenated sequence bytes + seq_offsets (n_seq + 1 entries), i.e. the (bases, seq_offsets) pair
+ * every entry point above takes: what the reference obtains record by record from kseq_read() (tests/kseq.h:185-240, as used
+ * by tests/test_kmer_view.cpp:30-40), split on the device. format: 0 = FASTA (multi-line records), 1 = FASTQ (four lines per
+ * record), -1 = by the first byte ('>' / '@'). '\n' and '\r' are dropped; every other byte of a sequence line is kept.
+ * flags: BLG_F_DEVICE_INPUT (text is a device pointer, 16-byte aligned), BLG_F_DEVICE_OUTPUT (bases / seq_offsets stay on the
+ * device, library-owned: feed them to the entry points above with BLG_F_DEVICE_INPUT). Release with blg_free_fastx_out.
+ * BLG_E_INVALID when the text does not start with a record header.
+ */
+typedef struct blg_fastx_out {
+    uint64_t n_bases;
+    uint64_t n_seq;
+    char* bases;
+    uint64_t* seq_offsets;
+    void* owner;
+} blg_fastx_out;
+int blg_parse_fastx(blg_ctx* ctx, const char* text, size_t n_text, int format, uint32_t flags, blg_fastx_out* out);
+void blg_free_fastx_out(blg_ctx* ctx, blg_fastx_out* out);
+
+/*
  * Host-side workload generators (csrc/synth_host.cpp). They run on the CPU, as the
  * reference's own do, and feed the benchmarks / tests; nothing on the GPU path calls them.
  *   blg_synth_generate <- sequence::generator::nucleic<packed::uniform>::get_sequence(length) with uniform(seed)

@@ -173,6 +173,45 @@ class Oracle:
         self.lib.orc_generate(seed, length, out.ctypes.data)
         return out
 
+    def parse_fastx(self, text, fastq=None):
+        """Restatement of what kseq_read() yields for well-formed input (reference tests/kseq.h:185-240): FASTA = a line whose
+        first byte is '>' starts a record, every other line is sequence; FASTQ = four lines per record, the second is the
+        sequence. '\\n' / '\\r' dropped. Returns (bases uint8, offsets uint64[n_seq + 1]). Pure Python: small inputs only."""
+        t = bytes(_buf(text))
+        if fastq is None:
+            fastq = t[:1] == b"@"
+        lines = t.split(b"\n")
+        if lines and lines[-1] == b"":
+            lines.pop()
+        seqs, cur = [], None
+        if fastq:
+            for i, ln in enumerate(lines):
+                if i % 4 == 0:
+                    seqs.append(b"")
+                elif i % 4 == 1:
+                    seqs[-1] = ln.replace(b"\r", b"")
+        else:
+            for ln in lines:
+                if ln[:1] == b">":
+                    seqs.append(b"")
+                elif seqs:
+                    seqs[-1] += ln.replace(b"\r", b"")
+        offs = np.concatenate([[0], np.cumsum([len(x) for x in seqs])]).astype(np.uint64)
+        return np.frombuffer(b"".join(seqs), np.uint8).copy(), offs
+
+    def pack_bases(self, seq):
+        """2-bit wire format of blg_super_kmers_packed: (codes uint32, break_start uint64, break_len uint32)."""
+        b = np.frombuffer(bytes(_buf(seq)), np.uint8)
+        code = self.nt4_table()[b].astype(np.uint32)
+        bad = code > 3
+        c2 = np.where(bad, 0, code).astype(np.uint32)
+        pad = (-len(c2)) % 16
+        c2 = np.concatenate([c2, np.zeros(pad, np.uint32)]).reshape(-1, 16)
+        codes = (c2 << (2 * np.arange(16, dtype=np.uint32))).sum(axis=1).astype(np.uint32)
+        d = np.diff(np.concatenate([[0], bad.astype(np.int8), [0]]))
+        st, en = np.nonzero(d == 1)[0], np.nonzero(d == -1)[0]
+        return codes, st.astype(np.uint64), (en - st).astype(np.uint32)
+
     def mutate(self, seq, mutp, indelf, extp, seed):
         b = _buf(seq)
         cap = len(b) * 4 + 64
@@ -214,6 +253,8 @@ class Ref:
         L.ref_minimizer_view_literal_count.restype = C.c_size_t
         L.ref_minimizer_view_literal_count.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int]
         L.ref_generate.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
+        L.ref_kseq_parse.restype = C.c_size_t
+        L.ref_kseq_parse.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_mutate.restype = C.c_size_t
         L.ref_mutate.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_nt4_table.argtypes = [C.c_void_p]
@@ -301,6 +342,14 @@ class Ref:
     def minimizer_view_literal_count(self, seq, k, m, seed, canonical):
         b = _buf(seq)
         return int(self.lib.ref_minimizer_view_literal_count(b, len(b), k, m, seed, int(canonical)))
+
+    def kseq_parse(self, text):
+        """The reference's kseq.h executed over the text: (bases, offsets)."""
+        b = bytes(_buf(text))
+        bases = np.empty(len(b) + 1, np.uint8)
+        offs = np.empty(len(b) // 2 + 2, np.uint64)
+        n_seq = self.lib.ref_kseq_parse(b, len(b), bases.ctypes.data, offs.ctypes.data)
+        return bases[:int(offs[n_seq])].copy(), offs[:n_seq + 1].copy()
 
     def generate(self, seed, length):
         out = np.empty(length, np.uint8)

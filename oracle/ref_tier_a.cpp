@@ -51,6 +51,18 @@
 #include "sequence_generator.hpp"
 #include "sequence_mutator.hpp"
 
+// kseq.h (reference tests/kseq.h, the parser tests/test_kmer_view.cpp:30-40 reads its input with) over an in-memory reader
+struct ref_membuf { const char* p; size_t n, pos; };
+static int ref_memread(ref_membuf* b, void* dst, int want)
+{
+    const size_t left = b->n - b->pos, take = left < (size_t)want ? left : (size_t)want;
+    memcpy(dst, b->p + b->pos, take);
+    b->pos += take;
+    return (int)take;
+}
+#include "kseq.h"
+KSEQ_INIT(ref_membuf*, ref_memread)
+
 namespace {
 
 inline bool is_valid_base(unsigned char c) { return constants::seq_nt4_table[c] < 4; }
@@ -272,6 +284,23 @@ size_t ref_mutate(const char* s, size_t n, double mutp, double indelf, double ex
     if (counts) { counts[0] = rep.substitution_count; counts[1] = rep.insertion_count; counts[2] = rep.deletion_count; }
     if (total_indel_len) *total_indel_len = rep.total_indel_len;
     return o;
+}
+
+// kseq_read() until the end of the text: the sequences concatenated + their offsets (n_seq + 1 entries). Returns n_seq.
+size_t ref_kseq_parse(const char* text, size_t n, char* bases_out, uint64_t* offs_out)
+{
+    ref_membuf mb{text, n, 0};
+    kseq_t* seq = kseq_init(&mb);
+    size_t n_seq = 0;
+    uint64_t total = 0;
+    offs_out[0] = 0;
+    while (kseq_read(seq) >= 0) {
+        memcpy(bases_out + total, seq->seq.s, seq->seq.l);
+        total += seq->seq.l;
+        offs_out[++n_seq] = total;
+    }
+    kseq_destroy(seq);
+    return n_seq;
 }
 
 } // extern "C"
