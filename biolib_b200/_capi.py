@@ -21,7 +21,7 @@ EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
     "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
-    "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out",
+    "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out",
 ]
 
 
@@ -46,6 +46,12 @@ class PackedSeq(C.Structure):
 
 class FastxOut(C.Structure):
     _fields_ = [("n_bases", C.c_uint64), ("n_seq", C.c_uint64), ("bases", C.c_void_p), ("seq_offsets", C.c_void_p), ("owner", C.c_void_p)]
+
+
+class PayloadOut(C.Structure):
+    _fields_ = [("count", C.c_uint64), ("n_buckets", C.c_uint32), ("total_bases", C.c_uint64), ("n_words", C.c_size_t),
+                ("bucket_offsets", C.c_void_p), ("value", C.c_void_p), ("mm_start", C.c_void_p), ("size", C.c_void_p),
+                ("mm_pos", C.c_void_p), ("payload_start", C.c_void_p), ("words", C.c_void_p), ("owner", C.c_void_p)]
 
 
 class Stats(C.Structure):
@@ -105,6 +111,9 @@ def lib() -> C.CDLL:
     L.blg_parse_fastx.argtypes = [vp, vp, sz, C.c_int, C.c_uint32, C.POINTER(FastxOut)]
     L.blg_free_fastx_out.argtypes = [vp, C.POINTER(FastxOut)]
     L.blg_free_fastx_out.restype = None
+    L.blg_super_kmer_payloads.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.c_uint32, C.POINTER(PayloadOut)]
+    L.blg_free_payload_out.argtypes = [vp, C.POINTER(PayloadOut)]
+    L.blg_free_payload_out.restype = None
     L.blg_synth_generate.argtypes = [u64, sz, vp]
     L.blg_synth_mutate.argtypes = [vp, sz, C.c_double, C.c_double, C.c_double, u64, vp, sz, C.POINTER(sz), vp, vp]
     _lib = L

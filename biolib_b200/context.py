@@ -130,6 +130,25 @@ class Context:
             self.L.blg_free_sk_out(self.h, C.byref(out))
         return res
 
+    # ------------------------------------------------------------------ payloads
+    def super_kmer_payloads(self, seq, k: int, m: int, seed: int, canonical: bool, n_buckets: int, offsets=None) -> dict:
+        """blg_super_kmer_payloads: records grouped stably by hash % n_buckets + their bases as one 2-bit packed stream
+        (bit::packed::vector<uint64_t>(2) layout)."""
+        b = _as_bytes_array(seq)
+        o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
+        p = Params(k=k, m=m, canonical=int(canonical), flags=0, seed=seed & (2**64 - 1))
+        out = _capi.PayloadOut()
+        self._check(self.L.blg_super_kmer_payloads(self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None,
+                                                   0 if o is None else len(o) - 1, C.byref(p), n_buckets, C.byref(out)))
+        n = out.count
+        try:
+            return dict(n=n, total_bases=out.total_bases, bucket_offsets=_copy(out.bucket_offsets, n_buckets + 1, np.uint64),
+                        value=_copy(out.value, n, np.uint64), mm_start=_copy(out.mm_start, n, np.uint64), size=_copy(out.size, n, np.uint8),
+                        mm_pos=_copy(out.mm_pos, n, np.uint8), payload_start=_copy(out.payload_start, n, np.uint64),
+                        words=_copy(out.words, out.n_words, np.uint64))
+        finally:
+            self.L.blg_free_payload_out(self.h, C.byref(out))
+
     # ------------------------------------------------------------------ ingest (SURVEY 8(f) rank 4)
     def pack_bases(self, seq):
         """Host-side packer blg_pack_bases: (codes uint32[ceil(n/16)], break_start uint64[], break_len uint32[])."""

@@ -24,7 +24,7 @@ constexpr int PIPE_MAX = 16;
 
 struct Owner {
     int device_mem;  // 1: cudaFree, 0: cudaFreeHost
-    void* ptrs[6];
+    void* ptrs[8];
 };
 
 }  // namespace
@@ -314,7 +314,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     Owner* ow = nullptr;
     blg_sk_out h = *out;
     if (out->capacity == 0) {
-        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{0, {}};
         if (!ow) return BLG_E_NOMEM;
         h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
         if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
@@ -482,7 +482,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (dev_out) {
             free_owner(ow);
-            ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+            ow = new (std::nothrow) Owner{1, {}};
             if (!ow) return BLG_E_NOMEM;
             unsigned long long *v = nullptr, *s = nullptr, *h = nullptr, *idp = nullptr;
             unsigned char *sz = nullptr, *mp = nullptr;
@@ -526,7 +526,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{0, {}};
         if (!ow) return BLG_E_NOMEM;
         out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
@@ -712,6 +712,99 @@ int blg_super_kmers_packed(blg_ctx* c, const blg_packed_seq* seq, const uint64_t
     return rc;
 }
 
+int blg_super_kmer_payloads(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
+                            uint32_t n_buckets, blg_payload_out* out)
+{
+    if (!c || !p || !out) return BLG_E_INVALID;
+    if (n_buckets == 0 || n_buckets > 4096) { c->err = "need 1 <= n_buckets <= 4096"; return BLG_E_INVALID; }
+    if (p->flags & (BLG_F_EMIT_ID | BLG_F_EMIT_HASH | BLG_F_POS32 | BLG_F_NO_SIZE)) { c->err = "payloads: only BLG_F_DEVICE_INPUT / BLG_F_DEVICE_OUTPUT apply"; return BLG_E_INVALID; }
+    const bool dev_out = (p->flags & BLG_F_DEVICE_OUTPUT) != 0;
+    *out = blg_payload_out{};
+    out->n_buckets = n_buckets;
+    // 1. the records, device-resident (library-owned arrays)
+    blg_params q = *p;
+    q.flags = (p->flags & BLG_F_DEVICE_INPUT) | BLG_F_DEVICE_OUTPUT;
+    blg_sk_out rec{};
+    int rc = sk_common(c, bases, n, offs, n_seq, 0, ~0ULL, &q, &rec, true);
+    if (rc != BLG_OK) return rc;
+    Timer tm;
+    const blg_stats sk_stats = c->stats;
+    const uint64_t cnt = rec.count;
+    const int k = p->k, w = p->k - p->m + 1;
+    const unsigned char* d_bases = (p->flags & BLG_F_DEVICE_INPUT) ? reinterpret_cast<const unsigned char*>(bases) : static_cast<const unsigned char*>(c->in.p);
+    Owner* dv = new (std::nothrow) Owner{1, {}};
+    Owner* rec_owner = static_cast<Owner*>(rec.owner);
+    auto fail = [&](int code) { free_owner(dv); free_owner(rec_owner); return code; };
+    if (!dv) return fail(BLG_E_NOMEM);
+    const uint64_t max_bases = cnt * (uint64_t)(w + k - 1);
+    const size_t max_words = (size_t)(max_bases / 32 + 2);
+    unsigned long long *d_bo = nullptr, *d_v = nullptr, *d_mm = nullptr, *d_ps = nullptr, *d_words = nullptr;
+    unsigned char *d_sz = nullptr, *d_mp = nullptr;
+    if ((rc = alloc_owned(c, true, (size_t)n_buckets + 1, &d_bo, dv, 0)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_v, dv, 1)) != BLG_OK ||
+        (rc = alloc_owned(c, true, cnt, &d_mm, dv, 2)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_sz, dv, 3)) != BLG_OK ||
+        (rc = alloc_owned(c, true, cnt, &d_mp, dv, 4)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_ps, dv, 5)) != BLG_OK ||
+        (rc = alloc_owned(c, true, max_words, &d_words, dv, 6)) != BLG_OK) return fail(rc);
+    if ((rc = ensure(c, c->rank, payload_scratch_bytes(cnt, n_buckets) + 64)) != BLG_OK) return fail(rc);
+    if (cudaMemsetAsync(d_words, 0, max_words * 8, c->stream) != cudaSuccess) return fail(BLG_E_CUDA);
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + payload_scratch_bytes(cnt, n_buckets) / 8 * 8);
+    int launches = 0;
+    cudaEventRecord(c->ev0, c->stream);
+    cudaError_t e = payload_launch(d_bases, reinterpret_cast<unsigned long long*>(rec.value), reinterpret_cast<unsigned long long*>(rec.mm_start), rec.size,
+                                   rec.mm_pos, cnt, k, (unsigned long long)(uint32_t)p->seed ^ 8ULL, n_buckets, c->rank.p, d_v, d_mm, d_sz, d_mp, d_ps,
+                                   d_bo, d_words, d_tot, c->stream, &launches);
+    cudaEventRecord(c->ev1, c->stream);
+    unsigned long long tot[2] = {0, 0};
+    if (e != cudaSuccess || cudaMemcpyAsync(tot, d_tot, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "payload kernels failed"; return fail(BLG_E_CUDA); }
+    free_owner(rec_owner);
+    rec_owner = nullptr;
+    c->stats = sk_stats;
+    c->stats.kernel_launches += launches;
+    add_kernel_time(c);
+    out->count = cnt;
+    out->total_bases = tot[0];
+    out->n_words = (size_t)(tot[0] * 2 / 64 + 1);                 // bit::packed::vector::resize_data: size * bitwidth / 64 + 1
+    if (dev_out) {
+        out->bucket_offsets = reinterpret_cast<uint64_t*>(d_bo); out->value = reinterpret_cast<uint64_t*>(d_v);
+        out->mm_start = reinterpret_cast<uint64_t*>(d_mm); out->size = d_sz; out->mm_pos = d_mp;
+        out->payload_start = reinterpret_cast<uint64_t*>(d_ps); out->words = reinterpret_cast<uint64_t*>(d_words);
+        out->owner = dv;
+        c->stats.total_ms += tm.ms();
+        return BLG_OK;
+    }
+    Owner* hv = new (std::nothrow) Owner{0, {}};
+    if (!hv) return fail(BLG_E_NOMEM);
+    auto fail2 = [&](int code) { free_owner(hv); return fail(code); };
+    if ((rc = alloc_owned(c, false, (size_t)n_buckets + 1, &out->bucket_offsets, hv, 0)) != BLG_OK || (rc = alloc_owned(c, false, cnt, &out->value, hv, 1)) != BLG_OK ||
+        (rc = alloc_owned(c, false, cnt, &out->mm_start, hv, 2)) != BLG_OK || (rc = alloc_owned(c, false, cnt, &out->size, hv, 3)) != BLG_OK ||
+        (rc = alloc_owned(c, false, cnt, &out->mm_pos, hv, 4)) != BLG_OK || (rc = alloc_owned(c, false, cnt, &out->payload_start, hv, 5)) != BLG_OK ||
+        (rc = alloc_owned(c, false, out->n_words, &out->words, hv, 6)) != BLG_OK) return fail2(rc);
+    bool ok = cudaMemcpyAsync(out->bucket_offsets, d_bo, ((size_t)n_buckets + 1) * 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    if (cnt) {
+        ok = ok && cudaMemcpyAsync(out->value, d_v, cnt * 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+        ok = ok && cudaMemcpyAsync(out->mm_start, d_mm, cnt * 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+        ok = ok && cudaMemcpyAsync(out->size, d_sz, cnt, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+        ok = ok && cudaMemcpyAsync(out->mm_pos, d_mp, cnt, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+        ok = ok && cudaMemcpyAsync(out->payload_start, d_ps, cnt * 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    }
+    ok = ok && cudaMemcpyAsync(out->words, d_words, out->n_words * 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    ok = ok && cudaStreamSynchronize(c->stream) == cudaSuccess;
+    if (!ok) { c->err = "payload download failed"; return fail2(BLG_E_CUDA); }
+    c->stats.bytes_d2h += ((size_t)n_buckets + 1) * 8 + cnt * 26 + out->n_words * 8;
+    out->owner = hv;
+    free_owner(dv);
+    c->stats.total_ms += tm.ms();
+    return BLG_OK;
+}
+
+void blg_free_payload_out(blg_ctx* c, blg_payload_out* out)
+{
+    if (!out) return;
+    if (c) cudaSetDevice(c->device);
+    if (out->owner) free_owner(static_cast<Owner*>(out->owner));
+    *out = blg_payload_out{};
+}
+
 int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uint32_t flags, blg_fastx_out* out)
 {
     if (!c || !out || (n_text && !text) || format < -1 || format > 1) return BLG_E_INVALID;
@@ -737,7 +830,7 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         else { c->err = "text starts with neither '>' nor '@'"; return BLG_E_INVALID; }
     }
     if ((rc = ensure(c, c->fx_scratch, fastx_scratch_bytes(n_text) + 64)) != BLG_OK) return rc;
-    Owner* ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+    Owner* ow = new (std::nothrow) Owner{1, {}};
     if (!ow) return BLG_E_NOMEM;
     unsigned char* d_bases = nullptr;
     unsigned long long* d_offs = nullptr;
@@ -767,7 +860,7 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         out->seq_offsets = reinterpret_cast<uint64_t*>(d_offs);
         out->owner = ow;
     } else {
-        Owner* hw = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        Owner* hw = new (std::nothrow) Owner{0, {}};
         if (!hw) { free_owner(ow); return BLG_E_NOMEM; }
         char* hb = nullptr;
         uint64_t* ho = nullptr;
@@ -848,7 +941,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
     Owner* ow = nullptr;
     if (dev_out) {
-        ow = new (std::nothrow) Owner{1, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{1, {}};
         if (!ow) return BLG_E_NOMEM;
         unsigned long long *lo = nullptr, *hi = nullptr, *pos = nullptr;
         if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
@@ -876,7 +969,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+        ow = new (std::nothrow) Owner{0, {}};
         if (!ow) return BLG_E_NOMEM;
         out->value_hi = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }

@@ -147,6 +147,14 @@ size_t fastx_scratch_bytes(size_t n_text);
 cudaError_t fastx_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
                          unsigned long long* totals, cudaStream_t stream, int* launches);
 
+// payload_kernel.cu: records -> bucket-ordered records + their bases as one 2-bit packed stream
+size_t payload_scratch_bytes(unsigned long long n_records, unsigned int n_buckets);
+cudaError_t payload_launch(const unsigned char* bases, const unsigned long long* value, const unsigned long long* mm_start, const unsigned char* size,
+                           const unsigned char* mm_pos, unsigned long long n, int k, unsigned long long s8, unsigned int n_buckets, void* scratch,
+                           unsigned long long* o_value, unsigned long long* o_mm, unsigned char* o_size, unsigned char* o_pos,
+                           unsigned long long* o_pstart, unsigned long long* bucket_offsets, unsigned long long* words,
+                           unsigned long long* totals, cudaStream_t stream, int* launches);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

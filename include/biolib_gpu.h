@@ -190,6 +190,36 @@ int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, cons
                            const blg_params* p, uint64_t threshold, blg_kmer_out* out);
 
 /*
+ * Super-k-mer payloads grouped by minimizer bucket (what super-k-mers are for -- partitioned k-mer
+ * counting, de Bruijn graph construction). The records of blg_super_kmers, reordered STABLY by
+ *   bucket = hash64(value, p->seed) % n_buckets          (hash::hash64::hash, include/hash.hpp:55-59)
+ * together with the bases [sk_start, sk_start + size + k - 1) of every record appended, in that order, to one 2-bit packed
+ * stream in the layout of the reference's bit::packed::vector<uint64_t>(2) (include/packed_vector.hpp:134-160,311-318:
+ * element i in words[i / 32] at bits [62 - 2 (i % 32), 64 - 2 (i % 32)), A=0 C=1 G=2 T/U=3): n_words = total_bases * 2 / 64 + 1.
+ *   bucket_offsets[b] .. bucket_offsets[b+1]   records of bucket b   (n_buckets + 1 entries)
+ *   payload_start[i]                            index of record i's first base in the stream; it holds size[i] + k - 1 bases
+ * 1 <= n_buckets <= 4096. flags: BLG_F_DEVICE_INPUT, BLG_F_DEVICE_OUTPUT. Arrays are library-allocated (pinned host or device);
+ * release with blg_free_payload_out.
+ */
+typedef struct blg_payload_out {
+    uint64_t count;
+    uint32_t n_buckets;
+    uint64_t total_bases;
+    size_t n_words;
+    uint64_t* bucket_offsets;
+    uint64_t* value;
+    uint64_t* mm_start;
+    uint8_t* size;
+    uint8_t* mm_pos;
+    uint64_t* payload_start;
+    uint64_t* words;
+    void* owner;
+} blg_payload_out;
+int blg_super_kmer_payloads(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                            const blg_params* p, uint32_t n_buckets, blg_payload_out* out);
+void blg_free_payload_out(blg_ctx* ctx, blg_payload_out* out);
+
+/*
  * Ingest: the two input formats either side of the hot path.
  *
  * 2-bit packed input. H2D then moves 0.25 B per base. `codes` holds 16 bases per 32-bit little-endian word, base q of a

@@ -199,6 +199,29 @@ class Oracle:
         offs = np.concatenate([[0], np.cumsum([len(x) for x in seqs])]).astype(np.uint64)
         return np.frombuffer(b"".join(seqs), np.uint8).copy(), offs
 
+    def payloads(self, seq, k, m, seed, canonical, n_buckets, offsets=None):
+        """Restatement of blg_super_kmer_payloads over this oracle's records: stable grouping by hash % n_buckets, every
+        record's bases [sk_start, sk_start + size + k - 1) as 2-bit codes appended to one stream packed like
+        bit::packed::vector<uint64_t>(2) (reference include/packed_vector.hpp:134-160,311-318)."""
+        r = self.super_kmers(seq, k, m, seed, canonical, offsets=offsets)
+        b = np.frombuffer(bytes(_buf(seq)), np.uint8)
+        bucket = (r["hash"] % np.uint64(n_buckets)).astype(np.int64)
+        order = np.argsort(bucket, kind="stable")
+        res = {key: r[key][order] for key in ("value", "mm_start", "sk_start", "size")}
+        res["mm_pos"] = (res["mm_start"] - res["sk_start"]).astype(np.uint8)
+        res["bucket_offsets"] = np.concatenate([[0], np.cumsum(np.bincount(bucket, minlength=n_buckets))]).astype(np.uint64)
+        lens = res["size"].astype(np.int64) + (k - 1)
+        res["payload_start"] = (np.cumsum(lens) - lens).astype(np.uint64)
+        total = int(lens.sum())
+        idx = np.repeat(res["sk_start"].astype(np.int64), lens) + (np.arange(total) - np.repeat(np.cumsum(lens) - lens, lens))
+        codes = self.nt4_table()[b[idx]].astype(np.uint64)
+        res["codes"] = codes.astype(np.uint8)
+        words = np.zeros(total * 2 // 64 + 1, np.uint64)
+        e = np.arange(total, dtype=np.int64)
+        np.bitwise_or.at(words, e // 32, codes << (62 - 2 * (e % 32)).astype(np.uint64))
+        res["words"], res["total_bases"], res["n"] = words, total, len(order)
+        return res
+
     def pack_bases(self, seq):
         """2-bit wire format of blg_super_kmers_packed: (codes uint32, break_start uint64, break_len uint32)."""
         b = np.frombuffer(bytes(_buf(seq)), np.uint8)
@@ -253,6 +276,8 @@ class Ref:
         L.ref_minimizer_view_literal_count.restype = C.c_size_t
         L.ref_minimizer_view_literal_count.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int]
         L.ref_generate.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
+        L.ref_packed_vector_words.restype = C.c_size_t
+        L.ref_packed_vector_words.argtypes = [C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p, C.c_size_t]
         L.ref_kseq_parse.restype = C.c_size_t
         L.ref_kseq_parse.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_mutate.restype = C.c_size_t
@@ -342,6 +367,13 @@ class Ref:
     def minimizer_view_literal_count(self, seq, k, m, seed, canonical):
         b = _buf(seq)
         return int(self.lib.ref_minimizer_view_literal_count(b, len(b), k, m, seed, int(canonical)))
+
+    def packed_vector_words(self, values, bitwidth=2):
+        """bit::packed::vector<uint64_t>(bitwidth) after push_back of every value: its underlying words."""
+        v = np.ascontiguousarray(values, np.uint8)
+        out = np.zeros(v.size * bitwidth // 64 + 2, np.uint64)
+        nw = self.lib.ref_packed_vector_words(v.ctypes.data, v.size, bitwidth, out.ctypes.data, out.size)
+        return out[:nw].copy()
 
     def kseq_parse(self, text):
         """The reference's kseq.h executed over the text: (bases, offsets)."""

@@ -50,6 +50,7 @@
 #undef private
 #include "sequence_generator.hpp"
 #include "sequence_mutator.hpp"
+#include "packed_vector.hpp"
 
 // kseq.h (reference tests/kseq.h, the parser tests/test_kmer_view.cpp:30-40 reads its input with) over an in-memory reader
 struct ref_membuf { const char* p; size_t n, pos; };
@@ -284,6 +285,16 @@ size_t ref_mutate(const char* s, size_t n, double mutp, double indelf, double ex
     if (counts) { counts[0] = rep.substitution_count; counts[1] = rep.insertion_count; counts[2] = rep.deletion_count; }
     if (total_indel_len) *total_indel_len = rep.total_indel_len;
     return o;
+}
+
+// bit::packed::vector<uint64_t>(bitwidth): push_back every value, return the underlying words (include/packed_vector.hpp:134-160)
+size_t ref_packed_vector_words(const uint8_t* values, size_t n, unsigned bitwidth, uint64_t* out_words, size_t out_cap)
+{
+    bit::packed::vector<uint64_t> pv(bitwidth);
+    for (size_t i = 0; i < n; ++i) pv.push_back(values[i]);
+    const size_t nw = pv.underlying_size();
+    for (size_t i = 0; i < nw && i < out_cap; ++i) out_words[i] = pv.data()[i];
+    return nw;
 }
 
 // kseq_read() until the end of the text: the sequences concatenated + their offsets (n_seq + 1 entries). Returns n_seq.
