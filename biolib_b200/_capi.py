@@ -16,12 +16,13 @@ CSRC = os.path.join(HERE, "csrc")
 
 BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOMEM = range(6)
 F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID, F_POS32 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
+F_REF_DROP_LAST = 0x40
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
     "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
-    "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out",
+    "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out", "blg_sorted_unique_kmers", "blg_kmer_jaccard",
 ]
 
 
@@ -52,6 +53,10 @@ class PayloadOut(C.Structure):
     _fields_ = [("count", C.c_uint64), ("n_buckets", C.c_uint32), ("total_bases", C.c_uint64), ("n_words", C.c_size_t),
                 ("bucket_offsets", C.c_void_p), ("value", C.c_void_p), ("mm_start", C.c_void_p), ("size", C.c_void_p),
                 ("mm_pos", C.c_void_p), ("payload_start", C.c_void_p), ("words", C.c_void_p), ("owner", C.c_void_p)]
+
+
+class JaccardOut(C.Structure):
+    _fields_ = [("intersection", C.c_uint64), ("union_size", C.c_uint64), ("size1", C.c_uint64), ("size2", C.c_uint64)]
 
 
 class Stats(C.Structure):
@@ -114,6 +119,8 @@ def lib() -> C.CDLL:
     L.blg_super_kmer_payloads.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.c_uint32, C.POINTER(PayloadOut)]
     L.blg_free_payload_out.argtypes = [vp, C.POINTER(PayloadOut)]
     L.blg_free_payload_out.restype = None
+    L.blg_sorted_unique_kmers.argtypes = [vp, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(KmerOut)]
+    L.blg_kmer_jaccard.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, sz, C.POINTER(Params), C.POINTER(JaccardOut)]
     L.blg_synth_generate.argtypes = [u64, sz, vp]
     L.blg_synth_mutate.argtypes = [vp, sz, C.c_double, C.c_double, C.c_double, u64, vp, sz, C.POINTER(sz), vp, vp]
     _lib = L

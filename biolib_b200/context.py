@@ -130,6 +130,32 @@ class Context:
             self.L.blg_free_sk_out(self.h, C.byref(out))
         return res
 
+    # ------------------------------------------------------------------ sort / unique / Jaccard
+    def sorted_unique_kmers(self, seq, k: int, canonical: bool = False, offsets=None, drop_last: bool = False) -> np.ndarray:
+        """blg_sorted_unique_kmers: the distinct k-mer values in increasing order (external_memory_vector + ordered_unique_sampler)."""
+        b = _as_bytes_array(seq)
+        o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
+        p = Params(k=k, m=0, canonical=int(canonical), flags=_capi.F_REF_DROP_LAST if drop_last else 0, seed=0)
+        out = KmerOut()
+        self._check(self.L.blg_sorted_unique_kmers(self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None,
+                                                   0 if o is None else len(o) - 1, C.byref(p), C.byref(out)))
+        try:
+            return _copy(out.value_lo, out.count, np.uint64)
+        finally:
+            self.L.blg_free_kmer_out(self.h, C.byref(out))
+
+    def kmer_jaccard(self, seq1, seq2, k: int, canonical: bool = False, offsets1=None, offsets2=None, drop_last: bool = False):
+        """blg_kmer_jaccard: (intersection, union, size1, size2) of the two distinct k-mer sets (algorithm::jaccard)."""
+        b1, b2 = _as_bytes_array(seq1), _as_bytes_array(seq2)
+        o1 = None if offsets1 is None else np.ascontiguousarray(offsets1, dtype=np.uint64)
+        o2 = None if offsets2 is None else np.ascontiguousarray(offsets2, dtype=np.uint64)
+        p = Params(k=k, m=0, canonical=int(canonical), flags=_capi.F_REF_DROP_LAST if drop_last else 0, seed=0)
+        out = _capi.JaccardOut()
+        self._check(self.L.blg_kmer_jaccard(self.h, b1.ctypes.data, b1.size, o1.ctypes.data if o1 is not None else None, 0 if o1 is None else len(o1) - 1,
+                                            b2.ctypes.data, b2.size, o2.ctypes.data if o2 is not None else None, 0 if o2 is None else len(o2) - 1,
+                                            C.byref(p), C.byref(out)))
+        return out.intersection, out.union_size, out.size1, out.size2
+
     # ------------------------------------------------------------------ payloads (SURVEY 8(f) rank 2)
     def super_kmer_payloads(self, seq, k: int, m: int, seed: int, canonical: bool, n_buckets: int, offsets=None) -> dict:
         """blg_super_kmer_payloads: records grouped stably by hash % n_buckets + their bases as one 2-bit packed stream

@@ -1006,6 +1006,140 @@ int blg_hash_sampled_kmers(blg_ctx* c, const char* bases, size_t n, const uint64
     return kmers_common(c, bases, n, offs, n_seq, p, -1, -1, out, &threshold);
 }
 
+namespace {
+// distinct k-mer values of one input, sorted, in a fresh device array (*d_out, owned by *ow slot 0); *count = their number
+int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p, Owner** ow_out,
+                         unsigned long long** d_out, uint64_t* count, blg_stats* acc)
+{
+    *ow_out = nullptr; *d_out = nullptr; *count = 0;
+    if (p->k == 0 || p->k > 32) { c->err = "sorted / unique / Jaccard: need 1 <= k <= 32 (64-bit k-mer values)"; return BLG_E_INVALID; }
+    blg_params q = *p;
+    q.flags = (p->flags & BLG_F_DEVICE_INPUT) | BLG_F_DEVICE_OUTPUT;
+    blg_kmer_out km{};
+    int rc = kmers_common(c, bases, n, offs, n_seq, &q, -1, -1, &km);
+    if (rc != BLG_OK) return rc;
+    acc->bytes_h2d += c->stats.bytes_h2d; acc->kernel_launches += c->stats.kernel_launches; acc->kernel_ms += c->stats.kernel_ms; acc->n_bases += n;
+    Owner* kow = static_cast<Owner*>(km.owner);
+    uint64_t cnt = km.count;
+    Owner* ow = new (std::nothrow) Owner{1, {}};
+    auto fail = [&](int code) { free_owner(ow); free_owner(kow); return code; };
+    if (!ow) return fail(BLG_E_NOMEM);
+    if (cnt == 0) { free_owner(kow); *ow_out = ow; return BLG_OK; }
+    unsigned long long *d_tmp = nullptr, *d_flags = nullptr, *d_uniq = nullptr;
+    if ((rc = alloc_owned(c, true, cnt, &d_uniq, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_tmp, ow, 1)) != BLG_OK ||
+        (rc = alloc_owned(c, true, cnt, &d_flags, ow, 2)) != BLG_OK) return fail(rc);
+    if ((rc = ensure(c, c->rank, sort_scratch_bytes(cnt) + 64)) != BLG_OK) return fail(rc);
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(cnt) / 8 * 8);
+    unsigned long long* vals = reinterpret_cast<unsigned long long*>(km.value_lo);
+    int launches = 0;
+    cudaEventRecord(c->ev0, c->stream);
+    if (p->flags & BLG_F_REF_DROP_LAST) {
+        const unsigned long long* d_offs = (p->flags & BLG_F_DEVICE_INPUT) ? reinterpret_cast<const unsigned long long*>(offs)
+                                                                            : static_cast<const unsigned long long*>(offs ? c->offs.p : nullptr);
+        if (drop_last_kmers(vals, reinterpret_cast<unsigned long long*>(km.position), cnt, p->k, d_offs, n_seq, n, d_flags, c->rank.p, d_tmp, d_tot,
+                            c->stream, &launches) != cudaSuccess) return fail(BLG_E_CUDA);
+        unsigned long long kept = 0;
+        if (cudaMemcpyAsync(&kept, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) return fail(BLG_E_CUDA);
+        cnt = kept;
+    }
+    unsigned long long uniq = 0;
+    if (cnt) {
+        if (radix_sort_u64(vals, d_tmp, cnt, 2 * p->k, c->rank.p, c->stream, &launches) != cudaSuccess ||
+            unique_sorted_u64(vals, cnt, d_flags, c->rank.p, d_uniq, d_tot, c->stream, &launches) != cudaSuccess) return fail(BLG_E_CUDA);
+        cudaEventRecord(c->ev1, c->stream);
+        if (cudaMemcpyAsync(&uniq, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) {
+            c->err = "sort / unique failed"; return fail(BLG_E_CUDA);
+        }
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) acc->kernel_ms += ms;
+    }
+    acc->kernel_launches += launches;
+    free_owner(kow);
+    // keep only the result array
+    cudaFree(ow->ptrs[1]); ow->ptrs[1] = nullptr;
+    cudaFree(ow->ptrs[2]); ow->ptrs[2] = nullptr;
+    *ow_out = ow; *d_out = d_uniq; *count = uniq;
+    return BLG_OK;
+}
+}  // namespace
+
+int blg_sorted_unique_kmers(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p, blg_kmer_out* out)
+{
+    if (!c || !p || !out) return BLG_E_INVALID;
+    Timer tm;
+    blg_stats acc{};
+    Owner* ow = nullptr;
+    unsigned long long* d = nullptr;
+    uint64_t cnt = 0;
+    int rc = sorted_unique_device(c, bases, n, offs, n_seq, p, &ow, &d, &cnt, &acc);
+    if (rc != BLG_OK) return rc;
+    out->count = cnt; out->value_hi = nullptr; out->position = nullptr;
+    if (p->flags & BLG_F_DEVICE_OUTPUT) { out->value_lo = reinterpret_cast<uint64_t*>(d); out->owner = ow; }
+    else {
+        Owner* hw = new (std::nothrow) Owner{0, {}};
+        if (!hw) { free_owner(ow); return BLG_E_NOMEM; }
+        if ((rc = alloc_owned(c, false, cnt, &out->value_lo, hw, 0)) != BLG_OK) { free_owner(ow); free_owner(hw); return rc; }
+        if (cnt && (cudaMemcpyAsync(out->value_lo, d, cnt * 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess)) {
+            free_owner(ow); free_owner(hw); return BLG_E_CUDA;
+        }
+        acc.bytes_d2h += cnt * 8;
+        free_owner(ow);
+        out->owner = hw;
+    }
+    acc.n_records = cnt;
+    acc.total_ms = tm.ms();
+    c->stats = acc;
+    return BLG_OK;
+}
+
+int blg_kmer_jaccard(blg_ctx* c, const char* b1, size_t n1, const uint64_t* o1, size_t s1, const char* b2, size_t n2, const uint64_t* o2, size_t s2,
+                     const blg_params* p, blg_jaccard_out* out)
+{
+    if (!c || !p || !out) return BLG_E_INVALID;
+    Timer tm;
+    blg_stats acc{};
+    *out = blg_jaccard_out{};
+    Owner *w1 = nullptr, *w2 = nullptr;
+    unsigned long long *d1 = nullptr, *d2 = nullptr;
+    uint64_t c1 = 0, c2 = 0;
+    int rc = sorted_unique_device(c, b1, n1, o1, s1, p, &w1, &d1, &c1, &acc);
+    if (rc != BLG_OK) return rc;
+    if ((rc = sorted_unique_device(c, b2, n2, o2, s2, p, &w2, &d2, &c2, &acc)) != BLG_OK) { free_owner(w1); return rc; }
+    // |A u B| = distinct values of the concatenation of the two distinct lists; |A n B| = |A| + |B| - |A u B|
+    const uint64_t tot = c1 + c2;
+    uint64_t uni = 0;
+    if (tot) {
+        Owner* ow = new (std::nothrow) Owner{1, {}};
+        auto fail = [&](int code) { free_owner(ow); free_owner(w1); free_owner(w2); return code; };
+        if (!ow) return fail(BLG_E_NOMEM);
+        unsigned long long *cat = nullptr, *tmp = nullptr, *flags = nullptr, *uq = nullptr;
+        if ((rc = alloc_owned(c, true, tot, &cat, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, tot, &tmp, ow, 1)) != BLG_OK ||
+            (rc = alloc_owned(c, true, tot, &flags, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, tot, &uq, ow, 3)) != BLG_OK) return fail(rc);
+        if ((rc = ensure(c, c->rank, sort_scratch_bytes(tot) + 64)) != BLG_OK) return fail(rc);
+        unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(tot) / 8 * 8);
+        int launches = 0;
+        cudaEventRecord(c->ev0, c->stream);
+        bool ok = (c1 == 0 || cudaMemcpyAsync(cat, d1, c1 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess) &&
+                  (c2 == 0 || cudaMemcpyAsync(cat + c1, d2, c2 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess);
+        ok = ok && radix_sort_u64(cat, tmp, tot, 2 * p->k, c->rank.p, c->stream, &launches) == cudaSuccess;
+        ok = ok && unique_sorted_u64(cat, tot, flags, c->rank.p, uq, d_tot, c->stream, &launches) == cudaSuccess;
+        cudaEventRecord(c->ev1, c->stream);
+        unsigned long long u = 0;
+        ok = ok && cudaMemcpyAsync(&u, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
+        if (!ok) { c->err = "jaccard merge failed"; return fail(BLG_E_CUDA); }
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) acc.kernel_ms += ms;
+        acc.kernel_launches += launches;
+        uni = u;
+        free_owner(ow);
+    }
+    free_owner(w1); free_owner(w2);
+    out->size1 = c1; out->size2 = c2; out->union_size = uni; out->intersection = c1 + c2 - uni;
+    acc.total_ms = tm.ms();
+    c->stats = acc;
+    return BLG_OK;
+}
+
 int blg_hash64(blg_ctx* c, const uint64_t* values, size_t n, uint64_t seed, uint32_t flags, uint64_t* out)
 {
     if (!c || (n && (!values || !out))) return BLG_E_INVALID;

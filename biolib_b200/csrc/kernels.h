@@ -155,6 +155,17 @@ cudaError_t payload_launch(const unsigned char* bases, const unsigned long long*
                            unsigned long long* o_pstart, unsigned long long* bucket_offsets, unsigned long long* words,
                            unsigned long long* totals, cudaStream_t stream, int* launches);
 
+// sort_kernel.cu: radix sort / adjacent unique of 64-bit k-mer values (the reference's sorted external-memory vector +
+// ordered_unique_sampler), the K1 drop-last filter of kmer_view
+size_t sort_scratch_bytes(unsigned long long n);
+cudaError_t radix_sort_u64(unsigned long long* keys, unsigned long long* tmp, unsigned long long n, int bits, void* scratch, cudaStream_t stream,
+                           int* launches);
+cudaError_t unique_sorted_u64(const unsigned long long* keys, unsigned long long n, unsigned long long* flags, void* scratch, unsigned long long* out,
+                              unsigned long long* d_total, cudaStream_t stream, int* launches);
+cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long* pos, unsigned long long n, int k, const unsigned long long* offs,
+                            unsigned long long n_seq, unsigned long long n_bases, unsigned long long* flags, void* scratch, unsigned long long* tmp,
+                            unsigned long long* d_total, cudaStream_t stream, int* launches);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

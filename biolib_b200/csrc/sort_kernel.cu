@@ -1,0 +1,222 @@
+// sort_kernel.cu -- the downstream pipeline of the reference's tests/test_jaccard.cpp:55-130 on the device:
+//
+//   emem::external_memory_vector<kmer_t>  (sorted runs + k-way merge = the k-mer values in sorted order,
+//                                          reference include/external_memory_vector.hpp:186-196,244-251,320-341)
+//   sampler::ordered_unique_sampler       (adjacent duplicates collapsed, include/ordered_unique_sampler.hpp:116-130)
+//   algorithm::jaccard                    (merge of two sorted distinct streams: intersection / union / sizes, include/jaccard.hpp:8-38)
+//
+// as an LSD radix sort of the 64-bit k-mer values (8 bits per pass, only the ceil(2k / 8) passes the values can differ in), an
+// adjacent-unique compaction, and |A n B| = |A| + |B| - |distinct(A u B)| from a third sort of the two distinct lists.
+//
+// One radix pass = per-tile digit histograms -> bucket-major exclusive scan -> stable scatter. Stability inside a tile comes
+// from warp match (rank among the lanes of a warp with the same digit) + per-warp digit counts summed in warp order.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace blg {
+
+namespace {
+
+constexpr int RS_THREADS = 256, RS_WARPS = RS_THREADS / 32, RS_CHUNKS = 16, RS_TILE = RS_THREADS * RS_CHUNKS, RS_BINS = 256;
+
+__global__ void __launch_bounds__(RS_THREADS) rs_count(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, u64* __restrict__ M)
+{
+    __shared__ u32 hist[RS_BINS];
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const u64 base = (u64)blockIdx.x * RS_TILE;
+#pragma unroll 4
+    for (int c = 0; c < RS_CHUNKS; ++c) {
+        const u64 i = base + (u64)c * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&hist[(u32)(__ldg(keys + i) >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    M[(u64)threadIdx.x * n_tiles + blockIdx.x] = hist[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
+                                                         u64* __restrict__ out)
+{
+    __shared__ u32 cnt[RS_BINS];                   // keys of this tile already placed, per digit
+    __shared__ u32 wcnt[RS_WARPS][RS_BINS];        // this chunk: keys per (warp, digit)
+    __shared__ u32 woff[RS_WARPS][RS_BINS];        // this chunk: first slot of (warp, digit) inside the tile's digit group
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    cnt[tid] = 0;
+    const u64 base = (u64)blockIdx.x * RS_TILE;
+    const u64 mybase = M[(u64)tid * n_tiles + blockIdx.x];     // thread tid keeps digit tid's global offset
+    __shared__ u64 gbase[RS_BINS];
+    gbase[tid] = mybase;
+    for (int c = 0; c < RS_CHUNKS; ++c) {
+#pragma unroll
+        for (int j = lane; j < RS_BINS; j += 32) wcnt[warp][j] = 0;
+        __syncwarp();
+        const u64 i = base + (u64)c * RS_THREADS + tid;
+        const bool have = i < n;
+        u64 key = 0;
+        u32 d = 0x100u + (u32)lane;                // lanes without a key match nobody
+        if (have) { key = __ldg(keys + i); d = (u32)(key >> shift) & 255u; }
+        const u32 peers = __match_any_sync(0xffffffffu, d);
+        const u32 rank = __popc(peers & ((1u << lane) - 1u));
+        if (have && rank == 0) wcnt[warp][d] = __popc(peers);
+        __syncthreads();
+        {
+            u32 run = cnt[tid];
+#pragma unroll
+            for (int w = 0; w < RS_WARPS; ++w) { const u32 x = wcnt[w][tid]; woff[w][tid] = run; run += x; }
+            cnt[tid] = run;
+        }
+        __syncthreads();
+        if (have) out[gbase[d] + woff[warp][d] + rank] = key;
+    }
+}
+
+// ---- u64 exclusive scan (same three-kernel scheme as payload_kernel.cu) ---------------------------------------------------
+constexpr int SC_THREADS = 256, SC_PER = 8, SC_BLOCK = SC_THREADS * SC_PER;
+
+__global__ void __launch_bounds__(SC_THREADS) ss_sums(const u64* __restrict__ a, u64 n, u64* __restrict__ sums)
+{
+    __shared__ u64 s[SC_THREADS / 32];
+    const u64 base = (u64)blockIdx.x * SC_BLOCK + (u64)threadIdx.x * SC_PER;
+    u64 t = 0;
+#pragma unroll
+    for (int i = 0; i < SC_PER; ++i) if (base + i < n) t += a[base + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) { u64 x = 0; for (int w = 0; w < SC_THREADS / 32; ++w) x += s[w]; sums[blockIdx.x] = x; }
+}
+__global__ void __launch_bounds__(1024) ss_scan_sums(u64* __restrict__ sums, u64 n_blocks, u64* __restrict__ total)
+{
+    __shared__ u64 s[1024];
+    const int tid = threadIdx.x;
+    const u64 per = (n_blocks + 1023) / 1024;
+    const u64 lo = min(n_blocks, (u64)tid * per), hi = min(n_blocks, lo + per);
+    u64 t = 0;
+    for (u64 i = lo; i < hi; ++i) t += sums[i];
+    s[tid] = t;
+    __syncthreads();
+    if (tid == 0) { u64 r = 0; for (int i = 0; i < 1024; ++i) { const u64 x = s[i]; s[i] = r; r += x; } if (total) *total = r; }
+    __syncthreads();
+    u64 r = s[tid];
+    for (u64 i = lo; i < hi; ++i) { const u64 x = sums[i]; sums[i] = r; r += x; }
+}
+__global__ void __launch_bounds__(SC_THREADS) ss_apply(u64* __restrict__ a, u64 n, const u64* __restrict__ sums)
+{
+    __shared__ u64 s[SC_THREADS];
+    const u64 base = (u64)blockIdx.x * SC_BLOCK + (u64)threadIdx.x * SC_PER;
+    u64 v[SC_PER], t = 0;
+#pragma unroll
+    for (int i = 0; i < SC_PER; ++i) { v[i] = base + i < n ? a[base + i] : 0; t += v[i]; }
+    s[threadIdx.x] = t;
+    __syncthreads();
+    u64 r = sums[blockIdx.x];
+    for (int j = 0; j < (int)threadIdx.x; ++j) r += s[j];
+#pragma unroll
+    for (int i = 0; i < SC_PER; ++i) { if (base + i < n) a[base + i] = r; r += v[i]; }
+}
+cudaError_t ss_scan(u64* a, u64 n, u64* sums, u64* total, cudaStream_t stream)
+{
+    if (n == 0) return total ? cudaMemsetAsync(total, 0, 8, stream) : cudaSuccess;
+    const u64 nb = (n + SC_BLOCK - 1) / SC_BLOCK;
+    ss_sums<<<(unsigned)nb, SC_THREADS, 0, stream>>>(a, n, sums);
+    ss_scan_sums<<<1, 1024, 0, stream>>>(sums, nb, total);
+    ss_apply<<<(unsigned)nb, SC_THREADS, 0, stream>>>(a, n, sums);
+    return cudaGetLastError();
+}
+
+// ---- adjacent unique / generic keep-compaction ---------------------------------------------------------------------------------
+__global__ void uq_flags(const u64* __restrict__ k, u64 n, u64* __restrict__ f)
+{
+    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (i < n) f[i] = (i == 0 || k[i] != k[i - 1]) ? 1 : 0;
+}
+// kmer_view's end test drops the k-mer that ends with the last byte of its sequence: keep[i] = 0 for those
+__global__ void k1_flags(const u64* __restrict__ pos, u64 n, int k, const u64* __restrict__ offs, u64 n_seq, u64 n_bases, u64* __restrict__ f)
+{
+    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 end = pos[i] + (u64)k;
+    u64 seq_end = n_bases;
+    if (offs != nullptr) {
+        u64 lo = 0, hi = n_seq;                    // first sequence boundary offs[q] (q >= 1) that is >= end
+        while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (offs[mid + 1] < end) lo = mid + 1; else hi = mid; }
+        seq_end = lo < n_seq ? offs[lo + 1] : n_bases;
+    }
+    f[i] = end == seq_end ? 0 : 1;
+}
+// f_excl = exclusive scan of 0/1 flags, *total = their sum (device): element i is kept iff the scan steps at i
+__global__ void compact_by_flags(const u64* __restrict__ k, const u64* __restrict__ f_excl, u64 n, const u64* __restrict__ total, u64* __restrict__ out)
+{
+    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 here = f_excl[i], next = i + 1 < n ? f_excl[i + 1] : *total;
+    if (next != here) out[here] = k[i];
+}
+
+}  // namespace
+
+size_t sort_scratch_bytes(unsigned long long n)
+{
+    const u64 n_tiles = (n + RS_TILE - 1) / RS_TILE + 1;
+    const u64 m = n_tiles * RS_BINS;
+    const u64 big = m > n ? m : n;
+    return (size_t)((m + (big + SC_BLOCK - 1) / SC_BLOCK + 16) * 8 + 256);
+}
+
+// In-place sort of keys[0, n) using tmp[0, n) as the second buffer; bits = number of low bits the keys can differ in.
+cudaError_t radix_sort_u64(unsigned long long* keys, unsigned long long* tmp, unsigned long long n, int bits, void* scratch, cudaStream_t stream,
+                           int* launches)
+{
+    if (n <= 1) return cudaSuccess;
+    const u64 n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    const u64 m = n_tiles * RS_BINS;
+    u64* M = static_cast<u64*>(scratch);
+    u64* sums = M + m;
+    u64 *src = keys, *dst = tmp;
+    const int passes = (bits + 7) / 8;
+    for (int p = 0; p < passes; ++p) {
+        rs_count<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(src, n, 8 * p, n_tiles, M);
+        cudaError_t e = ss_scan(M, m, sums, nullptr, stream);
+        if (e != cudaSuccess) return e;
+        rs_scatter<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(src, n, 8 * p, n_tiles, M, dst);
+        u64* t = src; src = dst; dst = t;
+        *launches += 5;
+    }
+    if (src != keys) { cudaError_t e = cudaMemcpyAsync(keys, src, n * 8, cudaMemcpyDeviceToDevice, stream); if (e != cudaSuccess) return e; }
+    return cudaGetLastError();
+}
+
+// keys sorted -> distinct keys in out (may not alias keys); *d_total (device) = their number. flags: n entries of scratch.
+cudaError_t unique_sorted_u64(const unsigned long long* keys, unsigned long long n, unsigned long long* flags, void* scratch, unsigned long long* out,
+                              unsigned long long* d_total, cudaStream_t stream, int* launches)
+{
+    if (n == 0) return cudaMemsetAsync(d_total, 0, 8, stream);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    uq_flags<<<grid, 256, 0, stream>>>(keys, n, flags);
+    u64* sums = static_cast<u64*>(scratch);
+    cudaError_t e = ss_scan(flags, n, sums, d_total, stream);
+    if (e != cudaSuccess) return e;
+    compact_by_flags<<<grid, 256, 0, stream>>>(keys, flags, n, d_total, out);
+    *launches += 5;
+    return cudaGetLastError();
+}
+
+// keep the k-mers that kmer_view yields (drop the last k-mer of every sequence that ends in a valid base): compacts `values` in place
+// through tmp; *d_total = kept
+cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long* pos, unsigned long long n, int k, const unsigned long long* offs,
+                            unsigned long long n_seq, unsigned long long n_bases, unsigned long long* flags, void* scratch, unsigned long long* tmp,
+                            unsigned long long* d_total, cudaStream_t stream, int* launches)
+{
+    if (n == 0) return cudaMemsetAsync(d_total, 0, 8, stream);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    k1_flags<<<grid, 256, 0, stream>>>(pos, n, k, offs, n_seq, n_bases, flags);
+    cudaError_t e = ss_scan(flags, n, static_cast<u64*>(scratch), d_total, stream);
+    if (e != cudaSuccess) return e;
+    compact_by_flags<<<grid, 256, 0, stream>>>(values, flags, n, d_total, tmp);
+    e = cudaMemcpyAsync(values, tmp, n * 8, cudaMemcpyDeviceToDevice, stream);
+    *launches += 5;
+    return e != cudaSuccess ? e : cudaGetLastError();
+}
+
+}  // namespace blg

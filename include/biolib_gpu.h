@@ -56,6 +56,8 @@ typedef enum blg_status {
 #define BLG_F_POS32         0x20u /* compact records: out->mm_start points at uint32_t entries holding mm_start - win_begin (range
                                    * form; mm_start itself for the whole-buffer calls). 14 instead of 18 bytes per record over PCIe.
                                    * BLG_E_INVALID when a position could exceed 2^32 - 1; not combinable with BLG_F_EMIT_ID */
+#define BLG_F_REF_DROP_LAST 0x40u /* blg_sorted_unique_kmers / blg_kmer_jaccard: leave out the last k-mer of every sequence that ends in
+                                   * a valid base, as iterating the reference's kmer_view does (include/kmer_view.hpp:57) */
 #define BLG_F_EMIT_ID       0x10u /* also fill out->id (minimizer_context_t::id; one extra pass over the bases) */
 
 typedef struct blg_params {
@@ -188,6 +190,26 @@ int blg_syncmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t
  */
 int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
                            const blg_params* p, uint64_t threshold, blg_kmer_out* out);
+
+/*
+ * The reference's one downstream pipeline (tests/test_jaccard.cpp:55-130) on the device, k <= 32:
+ *   blg_sorted_unique_kmers  kmer_view values -> emem::external_memory_vector (sorted, include/external_memory_vector.hpp:186-196,
+ *                            320-341) -> sampler::ordered_unique_sampler (include/ordered_unique_sampler.hpp:116-130): the distinct
+ *                            k-mer values of the input in increasing order, in out->value_lo (position / value_hi stay NULL)
+ *   blg_kmer_jaccard         that for two inputs + algorithm::jaccard (include/jaccard.hpp:8-38): {intersection, union, size1, size2}
+ * p->k, p->canonical, p->flags (BLG_F_DEVICE_INPUT, BLG_F_DEVICE_OUTPUT for the sorted list, BLG_F_REF_DROP_LAST) apply.
+ */
+typedef struct blg_jaccard_out {
+    uint64_t intersection;
+    uint64_t union_size;
+    uint64_t size1;
+    uint64_t size2;
+} blg_jaccard_out;
+int blg_sorted_unique_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, const uint64_t* seq_offsets, size_t n_seq,
+                            const blg_params* p, blg_kmer_out* out);
+int blg_kmer_jaccard(blg_ctx* ctx, const char* bases1, size_t n1, const uint64_t* seq_offsets1, size_t n_seq1,
+                     const char* bases2, size_t n2, const uint64_t* seq_offsets2, size_t n_seq2, const blg_params* p,
+                     blg_jaccard_out* out);
 
 /*
  * Super-k-mer payloads grouped by minimizer bucket (what super-k-mers are for -- partitioned k-mer

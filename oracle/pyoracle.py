@@ -199,6 +199,23 @@ class Oracle:
         offs = np.concatenate([[0], np.cumsum([len(x) for x in seqs])]).astype(np.uint64)
         return np.frombuffer(b"".join(seqs), np.uint8).copy(), offs
 
+    def sorted_unique_kmers(self, seq, k, canonical, offsets=None, drop_last=False):
+        """Restatement of test_jaccard's vector -> sort -> ordered_unique_sampler: distinct k-mer values in increasing order.
+        drop_last: leave out the last k-mer of every sequence that ends in a valid base (kmer_view's K1)."""
+        r = self.kmers(seq, k, canonical, offsets=offsets)
+        lo, pos = r["lo"], r["pos"].astype(np.int64)
+        if drop_last:
+            n = len(_buf(seq))
+            ends = np.array([n], np.int64) if offsets is None else np.asarray(offsets, np.int64)[1:]
+            lo = lo[~np.isin(pos + k, ends)]
+        return np.unique(lo)
+
+    def jaccard(self, seq1, seq2, k, canonical, offsets1=None, offsets2=None, drop_last=False):
+        a = self.sorted_unique_kmers(seq1, k, canonical, offsets1, drop_last)
+        b = self.sorted_unique_kmers(seq2, k, canonical, offsets2, drop_last)
+        inter = int(np.intersect1d(a, b, assume_unique=True).size)
+        return inter, int(a.size + b.size - inter), int(a.size), int(b.size)
+
     def payloads(self, seq, k, m, seed, canonical, n_buckets, offsets=None):
         """Restatement of blg_super_kmer_payloads over this oracle's records: stable grouping by hash % n_buckets, every
         record's bases [sk_start, sk_start + size + k - 1) as 2-bit codes appended to one stream packed like
@@ -276,6 +293,9 @@ class Ref:
         L.ref_minimizer_view_literal_count.restype = C.c_size_t
         L.ref_minimizer_view_literal_count.argtypes = [C.c_char_p, C.c_size_t, C.c_uint, C.c_uint, C.c_uint64, C.c_int]
         L.ref_generate.argtypes = [C.c_uint64, C.c_size_t, C.c_void_p]
+        L.ref_jaccard_sorted.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ref_ordered_unique.restype = C.c_size_t
+        L.ref_ordered_unique.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         L.ref_packed_vector_words.restype = C.c_size_t
         L.ref_packed_vector_words.argtypes = [C.c_void_p, C.c_size_t, C.c_uint, C.c_void_p, C.c_size_t]
         L.ref_kseq_parse.restype = C.c_size_t
@@ -367,6 +387,29 @@ class Ref:
     def minimizer_view_literal_count(self, seq, k, m, seed, canonical):
         b = _buf(seq)
         return int(self.lib.ref_minimizer_view_literal_count(b, len(b), k, m, seed, int(canonical)))
+
+    def kmer_values(self, seq, k, canonical, offsets=None):
+        """What tests/test_jaccard.cpp:61-66 pushes into its vector: the present values of kmer_view, sequence by sequence."""
+        b = np.frombuffer(bytes(_buf(seq)), np.uint8)
+        offs = [0, b.size] if offsets is None else [int(x) for x in offsets]
+        parts = []
+        for a, e in zip(offs[:-1], offs[1:]):
+            r = self.kmer_stream(b[a:e], k, canonical)
+            parts.append(r["lo"][r["has"] == 1])
+        return np.concatenate(parts) if parts else np.zeros(0, np.uint64)
+
+    def ordered_unique(self, sorted_values):
+        v = np.ascontiguousarray(sorted_values, np.uint64)
+        out = np.empty(max(v.size, 1), np.uint64)
+        n = self.lib.ref_ordered_unique(v.ctypes.data, v.size, out.ctypes.data)
+        return out[:n].copy()
+
+    def jaccard_sorted(self, a, b):
+        """ordered_unique_sampler + algorithm::jaccard over two sorted lists: (intersection, union, size1, size2)."""
+        a, b = np.ascontiguousarray(a, np.uint64), np.ascontiguousarray(b, np.uint64)
+        out = np.zeros(4, np.uint64)
+        self.lib.ref_jaccard_sorted(a.ctypes.data, a.size, b.ctypes.data, b.size, out.ctypes.data)
+        return tuple(int(x) for x in out)
 
     def packed_vector_words(self, values, bitwidth=2):
         """bit::packed::vector<uint64_t>(bitwidth) after push_back of every value: its underlying words."""

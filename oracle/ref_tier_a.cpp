@@ -51,6 +51,10 @@
 #include "sequence_generator.hpp"
 #include "sequence_mutator.hpp"
 #include "packed_vector.hpp"
+#include <mutex>
+#include <tuple>
+#include "ordered_unique_sampler.hpp"
+#include "jaccard.hpp"
 
 // kseq.h (reference tests/kseq.h, the parser tests/test_kmer_view.cpp:30-40 reads its input with) over an in-memory reader
 struct ref_membuf { const char* p; size_t n, pos; };
@@ -285,6 +289,27 @@ size_t ref_mutate(const char* s, size_t n, double mutp, double indelf, double ex
     if (counts) { counts[0] = rep.substitution_count; counts[1] = rep.insertion_count; counts[2] = rep.deletion_count; }
     if (total_indel_len) *total_indel_len = rep.total_indel_len;
     return o;
+}
+
+// sampler::ordered_unique_sampler over two SORTED value lists + algorithm::jaccard, verbatim (include/ordered_unique_sampler.hpp:116-130,
+// include/jaccard.hpp:8-38; tests/test_jaccard.cpp:97-130 is the same loop): out = {intersection, union, size1, size2}
+void ref_jaccard_sorted(const uint64_t* a, size_t na, const uint64_t* b, size_t nb, uint64_t out[4])
+{
+    const std::vector<uint64_t> va(a, a + na), vb(b, b + nb);      // the sampler wants class-type iterators (Iterator::value_type)
+    sampler::ordered_unique_sampler ua(va.cbegin(), va.cend());
+    sampler::ordered_unique_sampler ub(vb.cbegin(), vb.cend());
+    auto [inter, uni, s1, s2] = algorithm::jaccard(ua.cbegin(), ua.cend(), ub.cbegin(), ub.cend());
+    out[0] = inter; out[1] = uni; out[2] = s1; out[3] = s2;
+}
+
+// the distinct values of a sorted list as ordered_unique_sampler yields them
+size_t ref_ordered_unique(const uint64_t* a, size_t na, uint64_t* out)
+{
+    const std::vector<uint64_t> va(a, a + na);
+    sampler::ordered_unique_sampler ua(va.cbegin(), va.cend());
+    size_t n = 0;
+    for (auto it = ua.cbegin(); it != ua.cend(); ++it) out[n++] = *it;
+    return n;
 }
 
 // bit::packed::vector<uint64_t>(bitwidth): push_back every value, return the underlying words (include/packed_vector.hpp:134-160)
