@@ -7,6 +7,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/biolib_gpu.h"
 #include "kernels.h"
@@ -23,8 +24,37 @@ struct DevBuf {
 constexpr int PIPE_MAX = 16;
 
 struct Owner {
-    int device_mem;  // 1: cudaFree, 0: cudaFreeHost
+    int device_mem;  // 1: device memory, 0: pinned host memory
     void* ptrs[8];
+    size_t bytes[8];
+    blg_ctx* ctx;    // blocks go back to this context's pool
+};
+
+// Result arrays are handed out per call and given back through blg_free_*: cudaMallocHost / cudaMalloc of hundreds of MB cost
+// more than the kernels (measured: 150 ms of a 210 ms shim call), so freed blocks are kept per context and reused.
+struct BlockPool {
+    struct Block { void* p; size_t bytes; };
+    std::vector<Block> free_blocks;
+    size_t cached = 0, limit = 0;
+    void* take(size_t bytes, size_t* got)
+    {
+        int best = -1;
+        for (int i = 0; i < (int)free_blocks.size(); ++i)
+            if (free_blocks[i].bytes >= bytes && free_blocks[i].bytes <= 2 * bytes + (1u << 20) && (best < 0 || free_blocks[i].bytes < free_blocks[best].bytes)) best = i;
+        if (best < 0) return nullptr;
+        void* p = free_blocks[best].p;
+        *got = free_blocks[best].bytes;
+        cached -= *got;
+        free_blocks.erase(free_blocks.begin() + best);
+        return p;
+    }
+    bool give(void* p, size_t bytes)
+    {
+        if (cached + bytes > limit) return false;
+        free_blocks.push_back({p, bytes});
+        cached += bytes;
+        return true;
+    }
 };
 
 }  // namespace
@@ -51,6 +81,7 @@ struct blg_ctx {
     long long sk4_cap_tiles = 0;            // roles inside sk4_status are fixed per allocation: tiles | group accumulators | group words
     unsigned int sk4_epoch = 0, sk4_tickets = 0;
     unsigned long long sk4_exact_seen = 0;
+    BlockPool pool_dev, pool_pinned;         // result arrays given back through blg_free_* (limits set in blg_create)
     std::string err;
     blg_stats stats{};
 };
@@ -262,11 +293,22 @@ uint64_t estimate_records(uint64_t nwin, int w)
 template <typename T>
 int alloc_owned(blg_ctx* c, bool device_mem, size_t count, T** out, Owner* ow, int slot)
 {
-    void* p = nullptr;
-    const size_t bytes = (count ? count : 1) * sizeof(T);
-    if (device_mem) CK(c, cudaMalloc(&p, bytes));
-    else CK(c, cudaMallocHost(&p, bytes));
+    size_t bytes = ((count ? count : 1) * sizeof(T) + 255) / 256 * 256;
+    BlockPool& pool = device_mem ? c->pool_dev : c->pool_pinned;
+    void* p = pool.take(bytes, &bytes);
+    if (!p) {
+        cudaError_t e = device_mem ? cudaMalloc(&p, bytes) : cudaMallocHost(&p, bytes);
+        if (e == cudaErrorMemoryAllocation) {                 // give the cached blocks back to the driver and try once more
+            cudaGetLastError();
+            for (auto& b : pool.free_blocks) { if (device_mem) cudaFree(b.p); else cudaFreeHost(b.p); }
+            pool.free_blocks.clear(); pool.cached = 0;
+            e = device_mem ? cudaMalloc(&p, bytes) : cudaMallocHost(&p, bytes);
+        }
+        CK(c, e);
+    }
     ow->ptrs[slot] = p;
+    ow->bytes[slot] = bytes;
+    ow->ctx = c;
     *out = static_cast<T*>(p);
     return BLG_OK;
 }
@@ -274,8 +316,13 @@ int alloc_owned(blg_ctx* c, bool device_mem, size_t count, T** out, Owner* ow, i
 void free_owner(Owner* ow)
 {
     if (!ow) return;
-    for (void* p : ow->ptrs)
-        if (p) { if (ow->device_mem) cudaFree(p); else cudaFreeHost(p); }
+    for (int i = 0; i < 8; ++i) {
+        void* p = ow->ptrs[i];
+        if (!p) continue;
+        BlockPool* pool = ow->ctx ? (ow->device_mem ? &ow->ctx->pool_dev : &ow->ctx->pool_pinned) : nullptr;
+        if (pool && pool->give(p, ow->bytes[i])) continue;
+        if (ow->device_mem) cudaFree(p); else cudaFreeHost(p);
+    }
     delete ow;
 }
 
@@ -285,10 +332,13 @@ void free_owner(Owner* ow)
 // (blg_super_kmers_range semantics), so the concatenated output is the single-launch output.
 // Returns BLG_OK with *done_flag = 1 when it produced the result, 0 when the caller should take the plain path
 // (small input, id output, or the record estimate was too small).
+int run_ids(blg_ctx* c, const SkArgs& a, uint64_t total, unsigned long long* d_id);
+
 int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t lo, uint64_t hi,
                  const blg_params* p, blg_sk_out* out, bool with_size, bool want_hash, int* done_flag)
 {
     *done_flag = 0;
+    const bool want_id = (p->flags & BLG_F_EMIT_ID) != 0;
     const bool pos32 = (p->flags & BLG_F_POS32) != 0;
     const size_t posb = pos32 ? 4 : 8;                 // bytes per position entry
     const uint64_t nwin = hi - lo;
@@ -302,6 +352,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * posb)) != BLG_OK) return rc;
     if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
     if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
+    if (want_id && (rc = ensure(c, c->o_id, cap * 8)) != BLG_OK) return rc;
     const unsigned long long* d_offs = nullptr;
     if (offs) {
         const size_t ob = (n_seq + 1) * sizeof(uint64_t);
@@ -314,12 +365,13 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     Owner* ow = nullptr;
     blg_sk_out h = *out;
     if (out->capacity == 0) {
-        ow = new (std::nothrow) Owner{0, {}};
+        ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
         if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
+        if (want_id && (rc = alloc_owned(c, false, cap, &h.id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
     }
     int nch = (int)(nwin / ((uint64_t)c->pipe_chunk_m << 20));
     nch = nch < 2 ? 2 : (nch > PIPE_MAX ? PIPE_MAX : nch);
@@ -381,6 +433,18 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         }
         done += cnt;
     }
+    if (want_id && !overflow && done) {
+        // minimizer_context_t::id: one rank-directory pass over the whole input once every chunk is in, then one more download
+        SkArgs a{};
+        a.bases = d_in; a.buf_lo = 0; a.buf_hi = (long long)n;
+        a.seq_offsets = d_offs; a.n_seq = (long long)n_seq; a.m = m;
+        a.mm_start = static_cast<unsigned long long*>(c->o_mm.p);
+        if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
+        if ((rc = run_ids(c, a, done, static_cast<unsigned long long*>(c->o_id.p))) != BLG_OK) { free_owner(ow); return rc; }
+        CK(c, cudaMemcpyAsync(h.id, c->o_id.p, done * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->stats.bytes_d2h += done * 8;
+    }
     CK(c, cudaStreamSynchronize(c->s_out));
     if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
     if (overflow) {
@@ -431,7 +495,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         return BLG_OK;
     }
 
-    if (!(p->flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT)) && !want_id) {
+    if (!(p->flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT))) {
         int produced = 0;
         if ((rc = sk_pipelined(c, bases, n, offs, n_seq, lo, hi, p, out, with_size, want_hash, &produced)) != BLG_OK) return rc;
         if (produced) { c->stats.total_ms = tm.ms(); return BLG_OK; }
@@ -482,7 +546,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (dev_out) {
             free_owner(ow);
-            ow = new (std::nothrow) Owner{1, {}};
+            ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
             if (!ow) return BLG_E_NOMEM;
             unsigned long long *v = nullptr, *s = nullptr, *h = nullptr, *idp = nullptr;
             unsigned char *sz = nullptr, *mp = nullptr;
@@ -526,7 +590,7 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {}};
+        ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
@@ -600,6 +664,8 @@ int blg_create(int device, blg_ctx** out)
         return BLG_E_CUDA;
     }
     c->stream = c->own_stream;
+    c->pool_dev.limit = (size_t)24 << 30;        // B200: 180 GB of HBM
+    c->pool_pinned.limit = (size_t)2 << 30;
     bool ok = cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
@@ -616,6 +682,8 @@ int blg_destroy(blg_ctx* c)
     for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->packed, &c->brk, &c->fx_text, &c->fx_scratch, &c->sk4_status, &c->sk4_small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
                       &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
         if (b->p) cudaFree(b->p);
+    for (auto& b : c->pool_dev.free_blocks) cudaFree(b.p);
+    for (auto& b : c->pool_pinned.free_blocks) cudaFreeHost(b.p);
     if (c->h_total) cudaFreeHost(c->h_total);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -732,7 +800,7 @@ int blg_super_kmer_payloads(blg_ctx* c, const char* bases, size_t n, const uint6
     const uint64_t cnt = rec.count;
     const int k = p->k, w = p->k - p->m + 1;
     const unsigned char* d_bases = (p->flags & BLG_F_DEVICE_INPUT) ? reinterpret_cast<const unsigned char*>(bases) : static_cast<const unsigned char*>(c->in.p);
-    Owner* dv = new (std::nothrow) Owner{1, {}};
+    Owner* dv = new (std::nothrow) Owner{1, {}, {}, nullptr};
     Owner* rec_owner = static_cast<Owner*>(rec.owner);
     auto fail = [&](int code) { free_owner(dv); free_owner(rec_owner); return code; };
     if (!dv) return fail(BLG_E_NOMEM);
@@ -772,7 +840,7 @@ int blg_super_kmer_payloads(blg_ctx* c, const char* bases, size_t n, const uint6
         c->stats.total_ms += tm.ms();
         return BLG_OK;
     }
-    Owner* hv = new (std::nothrow) Owner{0, {}};
+    Owner* hv = new (std::nothrow) Owner{0, {}, {}, nullptr};
     if (!hv) return fail(BLG_E_NOMEM);
     auto fail2 = [&](int code) { free_owner(hv); return fail(code); };
     if ((rc = alloc_owned(c, false, (size_t)n_buckets + 1, &out->bucket_offsets, hv, 0)) != BLG_OK || (rc = alloc_owned(c, false, cnt, &out->value, hv, 1)) != BLG_OK ||
@@ -830,21 +898,23 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         else { c->err = "text starts with neither '>' nor '@'"; return BLG_E_INVALID; }
     }
     if ((rc = ensure(c, c->fx_scratch, fastx_scratch_bytes(n_text) + 64)) != BLG_OK) return rc;
-    Owner* ow = new (std::nothrow) Owner{1, {}};
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->fx_scratch.p) + fastx_scratch_bytes(n_text));
+    int launches = 0;
+    cudaError_t e = fastx_count_launch(d_text, n_text, format, c->fx_scratch.p, d_tot, c->stream, &launches);
+    unsigned long long tot[2] = {0, 0};
+    if (e != cudaSuccess || cudaMemcpyAsync(tot, d_tot, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "fastx: counting passes failed"; return BLG_E_CUDA; }
+    if (tot[1] == 0) { c->err = "text does not start with a record header"; return BLG_E_INVALID; }
+    Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
     if (!ow) return BLG_E_NOMEM;
     unsigned char* d_bases = nullptr;
     unsigned long long* d_offs = nullptr;
-    const size_t max_seq = n_text / 2 + 2;
-    if ((rc = alloc_owned(c, true, n_text + 64, &d_bases, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, max_seq, &d_offs, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
-    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->fx_scratch.p) + fastx_scratch_bytes(n_text));
-    int launches = 0;
-    cudaError_t e = fastx_launch(d_text, n_text, format, c->fx_scratch.p, d_bases, d_offs, d_tot, c->stream, &launches);
+    if ((rc = alloc_owned(c, true, (size_t)tot[0] + 64, &d_bases, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, (size_t)tot[1] + 1, &d_offs, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+    e = fastx_emit_launch(d_text, n_text, format, c->fx_scratch.p, d_bases, d_offs, c->stream, &launches);
     if (e != cudaSuccess) { free_owner(ow); c->err = cudaGetErrorString(e); return BLG_E_CUDA; }
     c->stats.kernel_launches += launches;
-    unsigned long long tot[2] = {0, 0}, first_off = 0;
-    if (cudaMemcpyAsync(tot, d_tot, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
-        cudaStreamSynchronize(c->stream) != cudaSuccess) { free_owner(ow); c->err = "fastx: count read-back failed"; return BLG_E_CUDA; }
-    if (tot[1] == 0 || cudaMemcpy(&first_off, d_offs, 8, cudaMemcpyDeviceToHost) != cudaSuccess || first_off != 0) {
+    unsigned long long first_off = 1;
+    if (cudaMemcpyAsync(&first_off, d_offs, 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess || first_off != 0) {
         free_owner(ow);
         c->err = "text does not start with a record header";
         return BLG_E_INVALID;
@@ -860,7 +930,7 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         out->seq_offsets = reinterpret_cast<uint64_t*>(d_offs);
         out->owner = ow;
     } else {
-        Owner* hw = new (std::nothrow) Owner{0, {}};
+        Owner* hw = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!hw) { free_owner(ow); return BLG_E_NOMEM; }
         char* hb = nullptr;
         uint64_t* ho = nullptr;
@@ -941,7 +1011,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (!dev_out && out->capacity > 0 && out->capacity < cap) cap = out->capacity;
     Owner* ow = nullptr;
     if (dev_out) {
-        ow = new (std::nothrow) Owner{1, {}};
+        ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         unsigned long long *lo = nullptr, *hi = nullptr, *pos = nullptr;
         if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
@@ -969,7 +1039,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (out->capacity > 0) {
         if (total > out->capacity) { c->stats.total_ms = tm.ms(); c->err = "output capacity too small"; return BLG_E_CAPACITY; }
     } else {
-        ow = new (std::nothrow) Owner{0, {}};
+        ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         out->value_hi = nullptr;
         if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
@@ -1021,7 +1091,7 @@ int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t
     acc->bytes_h2d += c->stats.bytes_h2d; acc->kernel_launches += c->stats.kernel_launches; acc->kernel_ms += c->stats.kernel_ms; acc->n_bases += n;
     Owner* kow = static_cast<Owner*>(km.owner);
     uint64_t cnt = km.count;
-    Owner* ow = new (std::nothrow) Owner{1, {}};
+    Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
     auto fail = [&](int code) { free_owner(ow); free_owner(kow); return code; };
     if (!ow) return fail(BLG_E_NOMEM);
     if (cnt == 0) { free_owner(kow); *ow_out = ow; return BLG_OK; }
@@ -1056,8 +1126,10 @@ int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t
     acc->kernel_launches += launches;
     free_owner(kow);
     // keep only the result array
-    cudaFree(ow->ptrs[1]); ow->ptrs[1] = nullptr;
-    cudaFree(ow->ptrs[2]); ow->ptrs[2] = nullptr;
+    for (int i = 1; i <= 2; ++i) {
+        if (!c->pool_dev.give(ow->ptrs[i], ow->bytes[i])) cudaFree(ow->ptrs[i]);
+        ow->ptrs[i] = nullptr;
+    }
     *ow_out = ow; *d_out = d_uniq; *count = uniq;
     return BLG_OK;
 }
@@ -1076,7 +1148,7 @@ int blg_sorted_unique_kmers(blg_ctx* c, const char* bases, size_t n, const uint6
     out->count = cnt; out->value_hi = nullptr; out->position = nullptr;
     if (p->flags & BLG_F_DEVICE_OUTPUT) { out->value_lo = reinterpret_cast<uint64_t*>(d); out->owner = ow; }
     else {
-        Owner* hw = new (std::nothrow) Owner{0, {}};
+        Owner* hw = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!hw) { free_owner(ow); return BLG_E_NOMEM; }
         if ((rc = alloc_owned(c, false, cnt, &out->value_lo, hw, 0)) != BLG_OK) { free_owner(ow); free_owner(hw); return rc; }
         if (cnt && (cudaMemcpyAsync(out->value_lo, d, cnt * 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess)) {
@@ -1109,7 +1181,7 @@ int blg_kmer_jaccard(blg_ctx* c, const char* b1, size_t n1, const uint64_t* o1, 
     const uint64_t tot = c1 + c2;
     uint64_t uni = 0;
     if (tot) {
-        Owner* ow = new (std::nothrow) Owner{1, {}};
+        Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
         auto fail = [&](int code) { free_owner(ow); free_owner(w1); free_owner(w2); return code; };
         if (!ow) return fail(BLG_E_NOMEM);
         unsigned long long *cat = nullptr, *tmp = nullptr, *flags = nullptr, *uq = nullptr;

@@ -276,10 +276,11 @@ size_t fastx_scratch_bytes(size_t n_text)
     return (nb * (sizeof(FxSummary) + sizeof(u32) + 2 * sizeof(u64)) + 511) / 256 * 256;
 }
 
-// bases must hold n_text bytes, offsets n_text / 2 + 2 entries at most (the caller sizes them from the text: a record needs at
-// least two bytes); totals[0] = kept bytes, totals[1] = records (device, read back by the caller)
-cudaError_t fastx_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
-                         unsigned long long* totals, cudaStream_t stream, int* launches)
+// Two stages, so that the caller can size the outputs exactly: fastx_count_launch runs passes 1-2 and the scans and leaves
+// totals[0] = kept bytes, totals[1] = records on the device; fastx_emit_launch (same scratch, untouched in between) scatters
+// into bases (totals[0] bytes) and offsets (totals[1] entries; the caller appends the closing entry).
+cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned long long* totals, cudaStream_t stream,
+                               int* launches)
 {
     const size_t nb = (n_text + FX_BLOCK - 1) / FX_BLOCK;
     *launches = 0;
@@ -293,12 +294,26 @@ cudaError_t fastx_launch(const unsigned char* text, size_t n_text, int fastq, vo
     fx_scan1<<<1, 32, 0, stream>>>(sum, nb, fastq, text, n_text, entry);
     fx_pass2<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts);
     fx_scan2<<<1, 1024, 0, stream>>>(keep, starts, nb);
-    fx_pass3<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets);
-    *launches = 5;
+    *launches = 4;
     cudaError_t e = cudaMemcpyAsync(totals, keep + nb, 8, cudaMemcpyDeviceToDevice, stream);
     if (e != cudaSuccess) return e;
     e = cudaMemcpyAsync(totals + 1, starts + nb, 8, cudaMemcpyDeviceToDevice, stream);
     if (e != cudaSuccess) return e;
+    return cudaGetLastError();
+}
+
+cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
+                              cudaStream_t stream, int* launches)
+{
+    const size_t nb = (n_text + FX_BLOCK - 1) / FX_BLOCK;
+    if (nb == 0) return cudaSuccess;
+    char* p = static_cast<char*>(scratch);
+    u64* keep = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
+    u64* starts = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
+    p += nb * sizeof(FxSummary);
+    u32* entry = reinterpret_cast<u32*>(p);
+    fx_pass3<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets);
+    *launches += 1;
     return cudaGetLastError();
 }
 

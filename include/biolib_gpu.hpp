@@ -32,6 +32,7 @@
 #include <cstdint>
 #include <cstdlib>
 #include <iterator>
+#include <limits>
 #include <memory>
 #include <optional>
 #include <stdexcept>
@@ -314,6 +315,54 @@ class syncmer_sampler
         std::vector<value_type> records;
 };
 
+// ------------------------------------------------------------------------------------------------ hash_sampler
+// sampler::hash_sampler<Iterator, HashFunctionFamily>(start, stop, hash, seed, sampling_rate) (reference include/hash_sampler.hpp:73-78,
+// selection rule :138-141: keep iff hash(value, seed) < threshold, threshold = (hash_type)(rate * max)) with the filter fused into
+// the k-mer kernel (blg_hash_sampled_kmers). The reference's sampler walks an iterator over k-mer VALUES; here [start, stop) is
+// the character range the k-mers come from, so k (and canonical) follow the reference's five arguments. The reference's own
+// template also works unchanged over gpu::kmer_view iterators with hash::hash64. Records are kmer_context_t (value, position,
+// id = ordinal among the sampled k-mers); the last k-mer of an input that ends in a valid base is dropped.
+template <class Iterator, typename HashFunctionFamily>
+class hash_sampler
+{
+    static_assert(std::is_same<HashFunctionFamily, ::hash::hash64>::value, "the device path implements hash::hash64 only");
+    public:
+        using value_type = kmer_context_t<uint64_t>;
+        using const_iterator = typename std::vector<value_type>::const_iterator;
+        hash_sampler(Iterator const& start, Iterator const& stop, HashFunctionFamily const& /*hash*/, uint64_t seed, double sampling_rate,
+                     uint8_t k, bool canonical = false)
+            : srate(sampling_rate)
+        {
+            if (srate > 1 or srate < 0) throw std::invalid_argument("[hash_sampler] Invalid sampling rate");       // hash_sampler.hpp:76
+            // hash_sampler.hpp:77 computes static_cast<uint64_t>(srate * max); for rate 1.0 that cast is out of range (undefined
+            // behaviour in the reference): the largest threshold is used there
+            const double prod = srate * static_cast<double>(std::numeric_limits<uint64_t>::max());
+            threshold = prod >= 18446744073709551615.0 ? std::numeric_limits<uint64_t>::max() : static_cast<uint64_t>(prod);
+            const std::size_t n = detail::range_length(start, stop);
+            char const* s = detail::contiguous_begin(start, n);
+            context& c = context::thread_default();
+            blg_params p{};
+            p.k = k; p.canonical = canonical ? 1 : 0; p.seed = seed;
+            blg_kmer_out o{};
+            c.check(blg_hash_sampled_kmers(c.get(), s, n, nullptr, 0, &p, threshold, &o), "blg_hash_sampled_kmers");
+            detail::out_guard<blg_kmer_out, void (*)(blg_ctx*, blg_kmer_out*)> g{c, o, blg_free_kmer_out};
+            uint64_t cnt = o.count;
+            if (cnt > 0 && o.position[cnt - 1] + k == n) --cnt;                                                       // K1
+            records.reserve(cnt);
+            for (uint64_t i = 0; i < cnt; ++i) records.push_back(value_type{o.value_lo[i], static_cast<std::size_t>(o.position[i]), static_cast<std::size_t>(i)});
+        }
+        const_iterator cbegin() const { return records.cbegin(); }
+        const_iterator cend() const { return records.cend(); }
+        const_iterator begin() const { return cbegin(); }
+        const_iterator end() const { return cend(); }
+        double get_sampling_rate() const { return srate; }
+        uint64_t get_threshold() const { return threshold; }
+    private:
+        double srate;
+        uint64_t threshold;
+        std::vector<value_type> records;
+};
+
 // ------------------------------------------------------------------------------------------------ minimizer_view
 template <typename MinimizerType>
 struct minimizer_context_t {     // layout of minimizer_view::const_iterator::minimizer_context_t (minimizer_view.hpp:21-25)
@@ -324,30 +373,35 @@ struct minimizer_context_t {     // layout of minimizer_view::const_iterator::mi
 
 namespace detail {
 
-// shared by minimizer_view and super_kmer_view: one blg_super_kmers call, records kept as SoA host copies
+// shared by minimizer_view and super_kmer_view: ONE blg_super_kmers / blg_minimizers call; the library's own (pinned) result
+// arrays are kept as they are -- structure of arrays -- and an iterator builds its record when it is dereferenced, so
+// nothing is copied record by record. Inputs of 8 Mi k-mers and more take the library's chunked path (upload, kernel and
+// record download overlap), ids included.
 template <typename MinimizerType>
 struct sk_records {
-    std::vector<minimizer_context_t<MinimizerType>> mm;
-    std::vector<uint8_t> mm_pos, size;
+    static_assert(std::is_same<MinimizerType, uint64_t>::value, "MinimizerType must be uint64_t (m <= 32)");
+    blg_sk_out o{};
+    context* ctx = nullptr;
 
+    sk_records() = default;
+    sk_records(sk_records const&) = delete;
+    sk_records& operator=(sk_records const&) = delete;
+    ~sk_records() { if (ctx) blg_free_sk_out(ctx->get(), &o); }
+
+    std::size_t size() const noexcept { return static_cast<std::size_t>(o.count); }
+    minimizer_context_t<MinimizerType> minimizer(std::size_t i) const noexcept
+    {
+        return minimizer_context_t<MinimizerType>{o.value[i], static_cast<std::size_t>(o.mm_start[i] + 1),     // D7: 1-based start
+                                                  static_cast<std::size_t>(o.id ? o.id[i] : i)};
+    }
     void run(char const* s, std::size_t n, uint8_t k, uint8_t m, uint64_t seed, bool canon, bool with_size)
     {
-        static_assert(std::is_same<MinimizerType, uint64_t>::value, "MinimizerType must be uint64_t (m <= 32)");
         context& c = context::thread_default();
         blg_params p{};
         p.k = k; p.m = m; p.canonical = canon ? 1 : 0; p.seed = seed; p.flags = BLG_F_EMIT_ID;
-        blg_sk_out o{};
         const int st = with_size ? blg_super_kmers(c.get(), s, n, nullptr, 0, &p, &o) : blg_minimizers(c.get(), s, n, nullptr, 0, &p, &o);
+        ctx = &c;
         c.check(st, with_size ? "blg_super_kmers" : "blg_minimizers");
-        out_guard<blg_sk_out, void (*)(blg_ctx*, blg_sk_out*)> g{c, o, blg_free_sk_out};
-        mm.resize(o.count);
-        for (uint64_t i = 0; i < o.count; ++i)
-            mm[i] = minimizer_context_t<MinimizerType>{o.value[i], static_cast<std::size_t>(o.mm_start[i] + 1),
-                                                       static_cast<std::size_t>(o.id ? o.id[i] : i)};
-        if (with_size) {
-            mm_pos.assign(o.mm_pos, o.mm_pos + o.count);
-            size.assign(o.size, o.size + o.count);
-        }
     }
 };
 
@@ -367,15 +421,17 @@ class minimizer_view
                 using value_type = minimizer_context_t<MinimizerType>;
                 using pointer = value_type const*;
                 using reference = value_type const&;
-                const_iterator(minimizer_view const* v, std::size_t i) : parent(v), idx(i) {}
-                value_type const& operator*() const noexcept { return parent->rec.mm[idx]; }   // by reference (:34)
-                const_iterator const& operator++() { ++idx; return *this; }
-                const_iterator operator++(int) { auto r = *this; ++idx; return r; }
+                const_iterator(minimizer_view const* v, std::size_t i) : parent(v), idx(i) { load(); }
+                value_type const& operator*() const noexcept { return current; }               // by reference (:34)
+                const_iterator const& operator++() { ++idx; load(); return *this; }
+                const_iterator operator++(int) { auto r = *this; ++idx; load(); return r; }
                 friend bool operator==(const_iterator const& a, const_iterator const& b) { return a.parent == b.parent && a.idx == b.idx; }
                 friend bool operator!=(const_iterator const& a, const_iterator const& b) { return !(a == b); }
             private:
                 minimizer_view const* parent;
                 std::size_t idx;
+                value_type current{};
+                void load() { if (idx < parent->rec.size()) current = parent->rec.minimizer(idx); }
         };
 
         minimizer_view(Iterator start, Iterator stop, uint8_t k, uint8_t m, uint64_t seed, bool canonical = false)
@@ -384,7 +440,7 @@ class minimizer_view
             if (2u * klen > 8 * sizeof(KmerType)) throw std::invalid_argument("[biolib::gpu::minimizer_view] k does not fit KmerType");
         }
         const_iterator cbegin() const { run(); return const_iterator(this, 0); }
-        const_iterator cend() const { run(); return const_iterator(this, rec.mm.size()); }
+        const_iterator cend() const { run(); return const_iterator(this, rec.size()); }
         const_iterator begin() const { return cbegin(); }
         const_iterator end() const { return cend(); }
         uint8_t get_k() const noexcept { return klen; }
@@ -454,7 +510,7 @@ class super_kmer_view
                 value_type current_sk;
                 void load()
                 {
-                    if (idx < parent->rec.mm.size()) current_sk = value_type{parent->rec.mm[idx], parent->rec.mm_pos[idx], parent->rec.size[idx]};
+                    if (idx < parent->rec.size()) current_sk = value_type{parent->rec.minimizer(idx), parent->rec.o.mm_pos[idx], parent->rec.o.size[idx]};
                 }
         };
 
@@ -468,7 +524,7 @@ class super_kmer_view
         super_kmer_view(std::string const& contig, uint8_t k, uint8_t m, bool canonical = false, uint64_t seed = 0)
             : super_kmer_view(contig.data(), contig.size(), k, m, canonical, seed) {}
         const_iterator cbegin() const { run(); return const_iterator(this, 0); }
-        const_iterator cend() const { run(); return const_iterator(this, rec.mm.size()); }
+        const_iterator cend() const { run(); return const_iterator(this, rec.size()); }
         const_iterator begin() const { return cbegin(); }
         const_iterator end() const { return cend(); }
         uint8_t get_k() const noexcept { return klen; }

@@ -469,6 +469,7 @@ def test_minimizer_ids(gpu, oracle, k, m):
 
 CPP_DRIVER = r"""
 #include "biolib_gpu.hpp"
+namespace hash { class hash64 {}; }   // the reference's include/hash.hpp:45 defines it; the shim only needs the tag
 #include <cstdio>
 #include <fstream>
 #include <iterator>
@@ -504,6 +505,13 @@ int main(int argc, char** argv) {
         biolib::gpu::syncmer_sampler<std::string::const_iterator> sy(s.cbegin(), s.cend(), ex, 0, k - m, canon);
         if (sy.get_offsets() != std::make_pair<uint16_t, uint16_t>(0, k - m)) return 7;
         for (auto const& r : sy) std::printf("Y %llu %zu\n", (unsigned long long)*r.value, r.position);
+    }
+    if (k <= 32) {
+        biolib::gpu::hash_sampler<std::string::const_iterator, hash::hash64> hs(s.cbegin(), s.cend(), hash::hash64(), 42, 0.25, k, canon);
+        if (hs.get_sampling_rate() != 0.25) return 8;
+        for (auto const& r : hs) std::printf("H %llu %zu %zu\n", (unsigned long long)*r.value, r.position, r.id);
+        try { biolib::gpu::hash_sampler<std::string::const_iterator, hash::hash64> bad(s.cbegin(), s.cend(), hash::hash64(), 42, 1.5, k); return 9; }
+        catch (std::invalid_argument const&) {}
     }
     try { biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> bad(s, 3, 4); bad.cbegin(); return 4; }
     catch (std::invalid_argument const&) {}
@@ -546,6 +554,12 @@ def test_cpp_shim_views(gpu, oracle, tmp_path):
             Y = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("Y ")]
             sy = oracle.syncmer_stream(seq, k, m, 0, k - m, canon)
             assert Y == list(zip(sy["lo"].tolist(), sy["pos"].tolist())), (seq[:20], k, m, canon)
+            H = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("H ")]
+            if k <= 32:
+                thr = gpu.hash_sampler_threshold(0.25)
+                valid = ks["has"] == 1                                              # kmer_view's stream already applies K1
+                keep = np.array([oracle.hash64(int(v), 42) < thr for v in ks["lo"][valid]], dtype=bool)
+                assert H == list(zip(ks["lo"][valid][keep].tolist(), ks["pos"][valid][keep].tolist(), range(int(keep.sum())))), (seq[:20], k, canon)
             X = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("X ")]
             xv = np.array([v for v, _ in X], dtype=np.uint64)
             assert [p for _, p in X] == oracle.minimizer_positions(xv, k, m).tolist() if len(X) else True
