@@ -38,6 +38,27 @@ BLG_HD uint32_t blg_pack4(uint32_t x)
     return code8 | (bad8 << 8);
 }
 
+// The two halves of blg_pack4 on their own, for the fused kernels' fast path (most 16-base words hold valid letters only):
+//   blg_codes4  the four 2-bit codes gathered into bits 0..7 (meaningful for valid bytes)
+//   blg_bad4    a word whose byte q is non-zero iff base q is not one of AaCcGgTtUu -- exact, 9 logic operations: after folding
+//               the case (y = x & 0xDF) the valid bytes are 0x41 0x43 0x47 (bit 4 clear) and 0x54 0x55 (bit 4 set), i.e.
+//                 bits 7,6,5,3 read 0,1,0,0                         (y ^ 0x40) & 0xE8 == 0
+//                 g = b2 & !b1 must equal b4                        A (001) C (011) G (111): g = 0;  T (100) U (101): g = 1
+//                 b4 | b0                                           the A/C/G row needs bit 0
+BLG_HD uint32_t blg_codes4(uint32_t x)
+{
+    const uint32_t t = ((x >> 1) ^ (x >> 2)) & 0x03030303u;
+    return (t * 0x01041040u) >> 24;
+}
+BLG_HD uint32_t blg_bad4(uint32_t x)
+{
+    const uint32_t y = x & 0xDFDFDFDFu;
+    const uint32_t s1 = y >> 1, s2 = y >> 2, s4 = y >> 4;
+    const uint32_t frame = (y ^ 0x40404040u) & 0xE8E8E8E8u;
+    const uint32_t g = s2 & ~s1;
+    return frame | (((g ^ s4) | ~(s4 | y)) & 0x01010101u);
+}
+
 // Sixteen bases: four 32-bit words (w[0] = first four bases) -> 32 bits of codes, 32 bits of flags.
 BLG_HD void blg_pack16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t* codes, uint32_t* flags)
 {

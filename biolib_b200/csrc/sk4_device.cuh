@@ -75,7 +75,29 @@ __device__ __forceinline__ u32 make_key(u32 h, u32 mask, u32 idx)
     return k;
 }
 
-// murmur3_key8 with a 32-bit s8 (the seed is 32 bits wide, hash.hpp:50): the high words of both `^= s8` / `+= s8` vanish
+// murmur3_key8 with a 32-bit s8 (the seed is 32 bits wide, hash.hpp:50): the high words of both `^= s8` / `+= s8` vanish.
+// SK4_FMA_SHIFT_MASK (development): bit n set = the n-th of the six `h ^= h >> 33` steps takes its shift from IMAD.HI on the
+// FMA pipe (hi * 2^31 >> 32) instead of SHF on the ALU pipe, the busier of the two in this kernel.
+#ifndef SK4_FMA_SHIFT_MASK
+#define SK4_FMA_SHIFT_MASK 0
+#endif
+template <int SITE>
+__device__ __forceinline__ u64 xorshift33_site(u64 h)
+{
+    if ((SK4_FMA_SHIFT_MASK >> SITE) & 1) {
+        u32 hi = (u32)(h >> 32), lo = (u32)h, sh;
+        asm("mul.hi.u32 %0, %1, 0x80000000;" : "=r"(sh) : "r"(hi));
+        return ((u64)hi << 32) | (lo ^ sh);
+    }
+    return h ^ (h >> 33);
+}
+template <int SITE0>
+__device__ __forceinline__ u64 fmix64_site(u64 h)
+{
+    h = xorshift33_site<SITE0>(h); h *= 0xff51afd7ed558ccdULL;
+    h = xorshift33_site<SITE0 + 1>(h); h *= 0xc4ceb9fe1a85ec53ULL;
+    return xorshift33_site<SITE0 + 2>(h);
+}
 __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
 {
     u64 k1 = key * 0x87c37b91114253d5ULL;
@@ -84,7 +106,7 @@ __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
     u64 h1 = k1 ^ (u64)s8;
     u64 h2 = (u64)s8;
     h1 += h2; h2 += h1;
-    h1 = fmix64(h1); h2 = fmix64(h2);
+    h1 = fmix64_site<0>(h1); h2 = fmix64_site<3>(h2);
     return h1 + h2;
 }
 
@@ -256,8 +278,14 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
                         if (q < 4) w0 |= sh; else if (q < 8) w1 |= sh; else if (q < 12) w2 |= sh; else w3 |= sh;
                     }
                 }
-                blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
-                anybad |= (bad != 0);
+                // fast path: codes + one exact "any byte invalid" word; the per-base bits only where a word has a bad byte
+                if ((blg_bad4(w0) | blg_bad4(w1) | blg_bad4(w2) | blg_bad4(w3)) == 0u) {
+                    codes = blg_codes4(w0) | (blg_codes4(w1) << 8) | (blg_codes4(w2) << 16) | (blg_codes4(w3) << 24);
+                    bad = 0;
+                } else {
+                    blg_pack16_bits(w0, w1, w2, w3, &codes, &bad);
+                    anybad = 1;
+                }
             }
             if (wi < G::NWORDS + 3) {
                 CW[wi] = ~codes;
@@ -328,9 +356,18 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
             wv[q] = __byte_perm(__byte_perm(m0, m1, 0x0040), __byte_perm(m2, m3, 0x0040), 0x5410);
         }
         *reinterpret_cast<uint4*>(IDXB + t * 32 + nbp * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        // change bits inside the block, four windows per step on the packed bytes: two windows of one block have the same
+        // minimizer iff their (next-block bit, index) fields are equal. Byte i against byte i+1: x = low five bits of the xor;
+        // (x + 0x7F) & 0x80 flags a non-zero byte; the multiply gathers the four flags into the top nibble.
         u32 d = 0;
 #pragma unroll
-        for (int i = 0; i + 1 < B; ++i) d |= (u32)(mvb[i + 1] != mvb[i]) << i;
+        for (int q = 0; q < (B + 3) / 4; ++q) {
+            const u32 nxt = __funnelshift_r(wv[q], q + 1 < 4 ? wv[q + 1] : 0u, 8);
+            const u32 x = (wv[q] ^ nxt) & 0x1F1F1F1Fu;
+            const u32 nz = (x + 0x7F7F7F7Fu) & 0x80808080u;
+            d |= ((nz * 0x00204081u) >> 28) << (4 * q);
+        }
+        d &= (1u << (B - 1)) - 1u;                     // bit B-1 (this block's last window against the next block's first) is the caller's
         // the previous block's last window against this block's first: the same position reads +16 from there
         if (nbp > 0) dif |= (u32)(mvb[0] + 16u != mv_last) << (nbp * B - 1);
         else mv_first = mvb[0];

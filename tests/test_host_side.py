@@ -44,7 +44,10 @@ def test_nt4_swar_exhaustive(tmp_path, oracle):
         "  /* the byte under test in `lane`, the other three lanes filled with every class of neighbour */\n"
         "  static const unsigned char fill[6] = {'A','t',0x00,0xFF,'N','G'};\n"
         "  for (int f = 0; f < 6; ++f) { unsigned x = 0; for (int q = 0; q < 4; ++q) x |= (unsigned)(q == lane ? b : fill[(f + q) % 6]) << (8*q);\n"
-        "    unsigned r = blg_pack4(x); printf(\"%u %d %u %u\\n\", b, lane, (r >> (2*lane)) & 3u, (r >> (8 + 2*lane)) & 3u); } }\n"
+        "    unsigned r = blg_pack4(x); printf(\"%u %d %u %u\\n\", b, lane, (r >> (2*lane)) & 3u, (r >> (8 + 2*lane)) & 3u);\n"
+        "    /* the split forms of the fused kernels' fast path must say the same */\n"
+        "    unsigned fb = ((blg_bad4(x) >> (8*lane)) & 0xFFu) != 0, fc = (blg_codes4(x) >> (2*lane)) & 3u;\n"
+        "    if (fb != ((r >> (8 + 2*lane)) & 1u) || (!fb && fc != ((r >> (2*lane)) & 3u))) { printf(\"SPLIT MISMATCH %u %d\\n\", b, lane); return 1; } } }\n"
         "  unsigned c, fl; blg_pack16(0x54474341u /*ACGT*/, 0x7567634Eu /*Ncgu*/, 0x41414141u, 0x0A3E4155u /*UA>\\n*/, &c, &fl);\n"
         "  printf(\"P16 %u %u\\n\", c, fl); return 0; }\n")
     exe = tmp_path / "swar"

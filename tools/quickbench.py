@@ -57,6 +57,7 @@ def main():
     count = 0
     for i in range(3 + args.steps):
         flush.zero_()
+        torch.cuda.synchronize()      # an event recorded while the flush still runs time-stamps early on this driver (bench.py DeviceRun)
         count = ctx.super_kmers_device(d_bases.data_ptr(), args.n, args.k, args.m, 42, bool(args.canon), d_value.data_ptr(),
                                        d_mm.data_ptr(), d_size.data_ptr(), d_pos.data_ptr(), cap,
                                        d_offsets=offs_d.data_ptr() if offs_d is not None else 0, n_seq=n_seq)
