@@ -361,17 +361,22 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         c->stats.bytes_h2d += ob;
         d_offs = static_cast<const unsigned long long*>(c->offs.p);
     }
-    // library-allocated host arrays are sized by the estimate; an overflow falls back to the plain path
+    // library-allocated host arrays are sized by the estimate; an overflow falls back to the plain path. The guard gives them
+    // back (after draining the two side streams) on every early return below.
     Owner* ow = nullptr;
+    struct Guard {
+        blg_ctx* c; Owner** ow; bool armed;
+        ~Guard() { if (armed) { cudaStreamSynchronize(c->s_in); cudaStreamSynchronize(c->s_out); cudaStreamSynchronize(c->stream); free_owner(*ow); *ow = nullptr; } }
+    } guard{c, &ow, true};
     blg_sk_out h = *out;
     if (out->capacity == 0) {
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
-        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
-        if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
-        if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
-        if (want_id && (rc = alloc_owned(c, false, cap, &h.id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) return rc;
+        if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) return rc;
+        if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) return rc;
+        if (want_id && (rc = alloc_owned(c, false, cap, &h.id, ow, 5)) != BLG_OK) return rc;
     }
     int nch = (int)(nwin / ((uint64_t)c->pipe_chunk_m << 20));
     nch = nch < 2 ? 2 : (nch > PIPE_MAX ? PIPE_MAX : nch);
@@ -415,7 +420,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         a.hash = want_hash ? static_cast<unsigned long long*>(c->o_hash.p) + done : nullptr;
         a.capacity = cap - done;
         uint64_t cnt = 0;
-        if ((rc = run_sk_once(c, a, &cnt)) != BLG_OK) { free_owner(ow); return rc; }   // returns after the kernel: count is known
+        if ((rc = run_sk_once(c, a, &cnt)) != BLG_OK) return rc;   // returns after the kernel: count is known
         if (cnt > cap - done) { overflow = true; done += cnt; break; }
         if (cnt) {
             CK(c, cudaMemcpyAsync(h.value + done, a.value, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
@@ -440,17 +445,15 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         a.seq_offsets = d_offs; a.n_seq = (long long)n_seq; a.m = m;
         a.mm_start = static_cast<unsigned long long*>(c->o_mm.p);
         if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
-        if ((rc = run_ids(c, a, done, static_cast<unsigned long long*>(c->o_id.p))) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = run_ids(c, a, done, static_cast<unsigned long long*>(c->o_id.p))) != BLG_OK) return rc;
         CK(c, cudaMemcpyAsync(h.id, c->o_id.p, done * 8, cudaMemcpyDeviceToHost, c->stream));
         CK(c, cudaStreamSynchronize(c->stream));
         c->stats.bytes_d2h += done * 8;
     }
     CK(c, cudaStreamSynchronize(c->s_out));
     if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
-    if (overflow) {
-        free_owner(ow);
-        return BLG_OK;             // plain path: exact count, retry / BLG_E_CAPACITY
-    }
+    if (overflow) return BLG_OK;   // plain path: exact count, retry / BLG_E_CAPACITY (the guard releases the arrays)
+    guard.armed = false;
     if (out->capacity == 0) { *out = h; out->owner = ow; out->capacity = 0; }
     out->count = done;
     c->stats.n_records = done;
@@ -650,7 +653,7 @@ int blg_create(int device, blg_ctx** out)
     if (cudaSetDevice(device) != cudaSuccess) return BLG_E_CUDA;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return BLG_E_CUDA;
-    if (prop.major != 10) return BLG_E_UNSUPPORTED;  // built for sm_100a only
+    if (prop.major != 10) return BLG_E_CUDA;         // built for sm_100a only: any other device is "no usable device" (biolib_gpu.h)
     blg_ctx* c = new (std::nothrow) blg_ctx();
     if (!c) return BLG_E_NOMEM;
     c->device = device;

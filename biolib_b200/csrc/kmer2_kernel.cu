@@ -31,6 +31,13 @@
 //                1.64 ms per 100 Mbp at k=31 m=19 canonical (profiles/r01_s30_syncmer_bench_v3.txt)
 //   sync_on = 2  sampler::hash_sampler (include/hash_sampler.hpp:138-141; blg_hash_sampled_kmers): hash64(value, seed) <
 //                threshold, on the ordinary tiles. 0.62 ms per 100 Mbp (profiles/r01_s30_hash_sampler_bench.txt)
+// Staging of the next tile's ASCII bytes: one bulk async copy per tile (cp.async.bulk global -> shared, completion on an mbarrier:
+// UBLKCP in SASS) instead of one LDG.128 per thread held in registers across the write-out of the previous tile. Measured on
+// B200, k=31 canonical, 100 Mbp: 0.3174 -> 0.3108 ms (81.8 % -> 83.5 % of the measured HBM copy peak), bit-identical
+// (profiles/r02_r_kmer2_tma_staging.txt). -DK2_NO_TMA restores the register prefetch.
+#ifndef K2_NO_TMA
+#define K2_TMA 1
+#endif
 #include "common.cuh"
 #include "kernels.h"
 
@@ -81,7 +88,33 @@ struct K2Smem {
     u64 base[2];
     int next;
     int seqdirty[2];
+#ifdef K2_TMA
+    // staging experiment: the next tile's ASCII bytes arrive by ONE bulk async copy (cp.async.bulk,
+    // completion on an mbarrier) instead of one LDG.128 per thread held in registers across the write-out of the previous tile
+    alignas(16) unsigned char raw[(S == K2S_SYNC || S == K2S_SYNC_FWD) ? 16 : K2Geo<S>::NW * 16];   // the syncmer tiles keep the register prefetch
+    alignas(8) unsigned long long mbar;
+#endif
 };
+
+#ifdef K2_TMA
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, u32 bytes, unsigned long long* b)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, u32 phase)
+{
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}"
+                 ::"r"(smem_u32(b)), "r"(phase) : "memory");
+}
+#endif
 
 __device__ __forceinline__ u32 pairrev32_k(u32 x)
 {
@@ -203,6 +236,10 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
     constexpr int NV = WIDE ? 4 : 2;
     const int wp = warp * (32 * K2S);                               // first start of this warp, tile-local
 
+#ifdef K2_TMA
+    if (tid == 0) mbar_init(&sm.mbar, 1);
+    u32 tma_phase = 0;
+#endif
     if (tid == 0) sm.next = (int)atomicAdd(a.tile_counter, 1u);
     __syncthreads();
     long long tile = (unsigned)sm.next;                             // the tile staged in this iteration
@@ -242,6 +279,9 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
             if (is_scan && lane == 0) sm.next = (int)atomicAdd(a.tile_counter, 1u);
             // ---- stage: ASCII -> two packed streams + bad bits --------------------------------------------------------
             if (!is_scan) {
+#ifdef K2_TMA
+                if (have_pre) { mbar_wait(&sm.mbar, tma_phase); tma_phase ^= 1u; }
+#endif
 #pragma unroll
                 for (int it = 0; it < (K2WORDS + K2T - 1) / K2T; ++it) {
                     const int wi = tid + it * K2T;
@@ -250,10 +290,18 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                     if (wi < K2NW) {
                         const long long P = A0 + 16LL * wi;
                         u32 w0, w1, w2, w3;
+#ifdef K2_TMA
+                        if (have_pre) {
+                            const uint4 v = reinterpret_cast<const uint4*>(sm.raw)[wi];
+                            w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+                        } else if
+#else
                         if (have_pre && it < 2) {
                             const uint4 v = it == 0 ? pre0 : pre1;
                             w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
-                        } else if (a.vec_ok && P >= a.buf_lo && P + 16 <= a.buf_hi) {
+                        } else if
+#endif
+ (a.vec_ok && P >= a.buf_lo && P + 16 <= a.buf_hi) {
                             const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P - a.buf_lo)));
                             w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
                         } else {
@@ -402,10 +450,17 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
                 const long long nlo = a.win_lo + next_tile * (long long)K2TILE;
                 const long long P0 = (nlo & ~15LL) - a.buf_lo;
                 have_pre = next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * K2NW <= a.buf_hi - a.buf_lo;
+#ifdef K2_TMA
+                if (SYNC) have_pre = false;
+#endif
+#ifdef K2_TMA
+                if (have_pre && tid == 0) bulk_load(sm.raw, a.bases + P0, (u32)(16 * K2NW), &sm.mbar);
+#else
                 if (have_pre) {
                     if (tid < K2NW) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + tid);   // K2NW < K2T for the small tiles
                     if (K2T + tid < K2NW) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + K2T + tid);
                 }
+#endif
             }
             // ---- write out the previous tile: its offset was resolved by the scan warp during the previous iteration ----
             if (have_prev) {
