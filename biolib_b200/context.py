@@ -254,7 +254,9 @@ class Context:
 
     @staticmethod
     def hash_sampler_threshold(sampling_rate: float) -> int:
-        """hash_sampler's constructor (reference include/hash_sampler.hpp:76-77): same check, same double product."""
+        """hash_sampler's constructor (reference include/hash_sampler.hpp:76-77): same check, same double product. At rate 1.0
+        the reference's cast of 2^64 to uint64_t is out of range (undefined behaviour; 0 with g++ -O2 here, i.e. nothing kept):
+        this helper clamps to 2^64 - 1 instead -- a deliberate divergence."""
         if sampling_rate > 1 or sampling_rate < 0:
             raise ValueError("[hash_sampler] Invalid sampling rate")
         return min(int(sampling_rate * float(2**64 - 1)), 2**64 - 1)

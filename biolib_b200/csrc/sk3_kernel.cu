@@ -1,7 +1,6 @@
 // sk3_kernel.cu -- host side of the third-generation fused minimizer / super-k-mer kernel (device code and the
 // description of the scheme: sk3_device.cuh): which form serves a (k, m), the launch geometry, the launch.
 //
-//   tuned form    (k - m = 2 B = 32, compile-time geometry)     k=63 m=31 (BASELINE config 4), compiled here
 //   general form  (k - m = q B + r, q and r launch arguments)   every other (k, m) with k - m >= 5, compiled one block
 //                                                               size per translation unit in sk3_gen{16,12,8,6}.cu
 #include "sk3_device.cuh"
@@ -21,8 +20,7 @@ bool pick_variant(int k, int m, Variant* v)
 {
     const int d = k - m;
     if (m < 1 || m > 32 || k > 64) return false;
-    // the tuned forms for k - m = 12 and 10 (configs 2, 3, 5) were superseded by sk4_kernel.cu
-    if (d == 32 && m >= 17 && m <= 32) { *v = {16, 2, 3, 1, 0, 0, 0}; return true; }   // k=63 m=31 (config 4)
+    // the tuned forms (k - m = 12, 10, 32: configs 2 - 5) were superseded by sk4_kernel.cu: only the general form is left
     const int B = d >= 15 ? 16 : d >= 11 ? 12 : d >= 7 ? 8 : d >= 5 ? 6 : 0;
     if (B == 0) return false;                                                            // w <= 5: sk2
     const int q = d / B, r = d % B;
@@ -81,7 +79,7 @@ cudaError_t sk3_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan)
         else if (v.B == 8) e = sk3_gen8_setup(v.LW, canon, &smem, &occ);
         else e = sk3_gen6_setup(v.LW, canon, &smem, &occ);
     }
-    else { R = Geo<16, 2>::R; smem = smem3<16, 2>(); e = setup3c<16, 2, 3, true>(canon, smem, &occ); }
+    else return cudaErrorInvalidValue;
     if (e != cudaSuccess) return e;
     args.R = R;
     args.org = args.win_lo;
@@ -109,7 +107,7 @@ cudaError_t sk3_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_
         else if (v.B == 8) sk3_gen8_launch(v.LW, canon, args, plan, stream);
         else sk3_gen6_launch(v.LW, canon, args, plan, stream);
     }
-    else launch3c<16, 2, 3, true>(canon, args, plan, stream);
+    else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 

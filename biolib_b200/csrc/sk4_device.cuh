@@ -20,6 +20,9 @@
 // A warp owns a tile end to end and never meets another warp at a barrier, as in sk3: tiles come from a ticket counter,
 // the ordered output offset from the two-level chained scan, records are written KB-1 tiles after they were computed.
 #pragma once
+#ifdef SK4_TIE_DEBUG
+#include <cstdio>
+#endif
 #include "common.cuh"
 #include "kernels.h"
 
@@ -31,11 +34,13 @@ constexpr int NT4 = 32;
 constexpr int WARPS4 = SK4_THREADS / 32;
 constexpr int PADF4 = 3;     // zero words in front of the big-endian stream
 
-template <int B, int NB>
+template <int B, int NB, int Q = 1>
 struct Geo4 {
+    // Q: a window is suffix-of-own-block + (Q-1 whole blocks) + prefix-of-block-(b+Q): w = Q B + 1 (Q = 1: k-m = 12, 10; Q = 2: k-m = 32)
     static constexpr int L = NB * B;                    // starts per lane (its span), <= 32
     static constexpr int S = NT4 * L;                   // m-mer starts hashed per tile
-    static constexpr int OWN = NT4 * NB - 3;            // blocks 1 .. 32 NB - 3 own record starts (w = B + 1)
+    static constexpr int OWN = NT4 * NB - 1 - 2 * Q;    // blocks 1 .. 32 NB - 1 - 2Q own record starts: a record reaches Q blocks
+                                                        // further, and those windows Q blocks beyond that
     static constexpr int R = OWN * B;                   // new windows per tile
     static constexpr int NWORDS = S / 16 + 3;           // staged 16-base words: 15 (alignment) + S + 32 (m - 1) bases
     static constexpr int NROW = (NWORDS + 8) / 2 + 2;   // u32 words of the packed bad-byte / sequence-start bit rows
@@ -44,8 +49,9 @@ struct Geo4 {
     static constexpr int OFF_BAD = 0;                               // u32 [NROW]   bit x: base a0 + x is not ACGTU
     static constexpr int OFF_SEQ = OFF_BAD + NROW * 4;              // u32 [NROW]   bit x: a sequence starts at a0 + x
     static constexpr int OFF_FLAG = OFF_SEQ + NROW * 4;             // int [4]
-    static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;    // uint4 [BQ * 32 + 1]  prefix keys of each lane's block 0
-    static constexpr int OFF_BUF = OFF_P + (BQ * 32 + 1) * 16;
+    static constexpr int PBLK = Q == 1 ? 1 : NB;                    // blocks per lane whose prefix keys another lane reads
+    static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;    // uint4 [PBLK][BQ][32] (+1)  prefix keys, [block][quad][lane]
+    static constexpr int OFF_BUF = OFF_P + (PBLK * BQ * 32 + 1) * 16;
     // per buffer set (tile i is written out while tiles i+1, i+2 are computed)
     static constexpr int BUF_CW = 0;                                // u32 [NWORDS + 3]  complemented codes, little-endian
     static constexpr int BUF_EW = BUF_CW + (NWORDS + 3) * 4;        // u32 [PADF4 + NWORDS + 3]  codes, big-endian words
@@ -56,7 +62,7 @@ struct Geo4 {
 #ifdef SK4_KB
     static constexpr int KB = SK4_KB;
 #else
-    static constexpr int KB = 3;
+    static constexpr int KB = Q == 1 ? 3 : 2;                       // Q = 2: three sets would leave 12 warps per SM
 #endif
     static constexpr int WARP_BYTES = (OFF_BUF + KB * BUF_BYTES + 127) / 128 * 128;
 };
@@ -171,35 +177,42 @@ __device__ __forceinline__ u64 mmer_from_smem(const u32* CW, const u32* EW, int 
 // case -- one equal pair of m-mers in a tile, e.g. reverse-complement neighbours at small m -- adds a fraction of a
 // tile's time, and a tile full of ties (low-complexity sequence) about four tile times. Overwrites the argmin bytes
 // of the redone windows in IDXB; the caller rebuilds its change bits from IDXB afterwards (change_bits_from_idx4).
-template <int B, int NB, bool CANON, bool MW>
+template <int B, int NB, int Q, bool CANON, bool MW>
 __device__ __noinline__ void redo_windows4(const u32* CW, const u32* EW, unsigned char* IDXB, TileConst4 c, int o, int t, u32 flagged)
 {
-    constexpr int L = NB * B, W = B + 1, S = 32 * L, NU = 33 - W, UNITS = (S + NU - 1) / NU;
+    constexpr int L = NB * B, W = Q * B + 1, S = 32 * L;
+    constexpr int H = W <= 17 ? 1 : 2;                 // m-mer starts hashed per lane and unit
+    constexpr int NU = 32 * H - W + 1, UNITS = (S + NU - 1) / NU;
     static_assert(UNITS <= 64, "unit mask is 64 bits");
-    // units to redo: those that overlap [L f - B, L f + L) of a flagged lane f
+    // units to redo: those that overlap [L f - Q B, L f + L) of a flagged lane f (the lanes whose blocks read f's prefix keys)
     u64 todo = 0;
     for (u32 fm = flagged; fm; fm &= fm - 1) {
         const int f = __ffs((int)fm) - 1;
-        int lo = L * f - B, hi = L * f + L;
+        int lo = L * f - Q * B, hi = L * f + L;
         lo = lo < 0 ? 0 : lo;
         const int u0 = lo / NU, u1 = (hi - 1) / NU;
         for (int u = u0; u <= u1 && u < UNITS; ++u) todo |= 1ULL << u;
     }
     for (; todo; todo &= todo - 1) {
         const int s = (__ffsll((long long)todo) - 1) * NU;
-        const u64 h = murmur3_key8_s32(mmer_from_smem<CANON, MW>(CW, EW, o + s + t, c), c.s8);
-        u64 best = h;
-        int bd = 0;
+        u64 h[H];
 #pragma unroll
+        for (int q = 0; q < H; ++q) h[q] = murmur3_key8_s32(mmer_from_smem<CANON, MW>(CW, EW, o + s + 32 * q + t, c), c.s8);
+        u64 best = h[0];
+        int bd = 0;
+#pragma unroll 4
         for (int d = 1; d < W; ++d) {
-            const u64 hd = __shfl_down_sync(0xffffffffu, h, d);
+            const int src = t + d;                     // hash of start s + t + d: lane src & 31 of h[src >> 5]
+            u64 hd = __shfl_sync(0xffffffffu, h[0], src & 31);
+            if (H == 2) { const u64 h1 = __shfl_sync(0xffffffffu, h[H - 1], src & 31); if (src >= 32) hd = h1; }
             if (hd < best) { best = hd; bd = d; }
         }
         const int ws = s + t;                          // this lane's window
         if (t < NU && ws < S) {
             const int gb = ws / B, i = ws - gb * B;    // block of the tile (= lane * NB + block in lane), window in block
-            const int pb = i + bd;                      // minimizer start relative to the block's first start
-            IDXB[gb * 16 + i] = (unsigned char)(pb < B ? pb : (16 | (pb - B)));
+            const int pb = i + bd;                      // minimizer start relative to the block's first start: up to Q blocks on
+            const int pv = pb / B;
+            IDXB[gb * 16 + i] = (unsigned char)((pv << 4) | (pb - pv * B));
         }
     }
     __syncwarp();
@@ -222,8 +235,8 @@ __device__ __forceinline__ u32 change_bits_from_idx4(const unsigned char* IDXB, 
     for (int j = 0; j <= L; ++j) {
         // position of window j's minimizer relative to the lane's first start (window L = the next lane's window 0)
         const int nb = j / B, i = j - nb * B;
-        const int byt = j < L ? (int)((wv[4 * nb + (i >> 2)] >> (8 * (i & 3))) & 31u) : (n0 & 31);
-        const int pos = nb * B + (byt & 15) + ((byt & 16) ? B : 0);
+        const int byt = j < L ? (int)((wv[4 * nb + (i >> 2)] >> (8 * (i & 3))) & 63u) : (n0 & 63);
+        const int pos = nb * B + (byt & 15) + ((byt >> 4) & 3) * B;
         if (j > 0) dif |= (u32)(pos != pcur) << (j - 1);
         pcur = pos;
     }
@@ -231,11 +244,12 @@ __device__ __forceinline__ u32 change_bits_from_idx4(const unsigned char* IDXB, 
 }
 
 // Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
-template <int B, int NB, int LW, bool CANON, bool MW>
+template <int B, int NB, int Q, int LW, bool CANON, bool MW>
 __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
-                                             bool have_pre, uint4 pre0, uint4 pre1)
+                                             bool have_pre, const uint4 (&pre)[3])
 {
-    using G = Geo4<B, NB>;
+    using G = Geo4<B, NB, Q>;
+    static_assert(G::NWORDS <= 3 * NT4, "three prefetch registers per lane");
     constexpr int L = G::L;
     constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
     const long long g0 = a.org + tile * (long long)G::R - B;     // global position of local start 0 (block 0 = left margin)
@@ -263,7 +277,7 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
                 const long long P16 = a0 + 16LL * wi;
                 u32 w0, w1, w2, w3;
                 if (have_pre) {
-                    const uint4 v = wi < NT4 ? pre0 : pre1;
+                    const uint4 v = wi < NT4 ? pre[0] : wi < 2 * NT4 ? pre[1] : pre[2];
                     w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
                 } else if (a.vec_ok && P16 >= a.buf_lo && P16 + 16 <= a.buf_hi) {
                     const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P16 - a.buf_lo)));
@@ -328,25 +342,48 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
 
     // ---- the lane's blocks, left to right (a ROLLED loop: the unrolled body of one block is what the instruction cache holds).
     // Iteration nb hashes block nb -- one 32-bit key per m-mer start (hash bits above the index INSIDE the block), running
-    // prefix minimum pk[] -- and then finishes the windows of block nb-1: suffix minimum of its own keys combined with
-    // pk[] (a window is suffix-of-own-block + prefix-of-next-block). Keys that come from the next block enter with +16, so
-    // the low byte of a window's minimum says where it is: bits 0-3 index in its block, bit 4 = next block.
-    constexpr u32 MB = (1u << B) - 1u;
+    // prefix minimum pk[] -- and, for Q = 1, finishes the windows of block nb-1: suffix minimum of its own keys combined with
+    // pk[] (a window is suffix-of-own-block + [Q-1 whole blocks] + prefix-of-block-(b+Q)). Keys that come from a later block
+    // enter with +16 per block, so the low byte of a window's minimum says where it is: bits 0-3 index in its block, bits 4-5
+    // how many blocks further on.
+    constexpr u32 MB = B >= 32 ? 0xFFFFFFFFu : ((1u << B) - 1u);
     u32 tacc = 0xFFFFFFFFu;                    // min over all compares of (right key - left key): below 32 <=> a hash-part tie
+#ifdef SK4_TIE_DEBUG
+    u32 dbg_seed = 0xFFFFFFFFu, dbg_suf = 0xFFFFFFFFu, dbg_cmb = 0xFFFFFFFFu, dbg_pre = 0xFFFFFFFFu;
+#endif
     u32 dif = 0;                               // bit j: windows j and j+1 of the span have different minimizer positions
-    u32 ks_prev[B];
+    u32 ks_prev[B], ks_prev2[B];               // keys of the last and (Q = 2) the last but one hashed block
+    u32 full_prev = 0;                         // minimum key of the last hashed block (Q = 2)
     u32 mv_first = 0, mv_last = 0;
-    // windows of one block: own keys kk[] (suffix side) and the next block's prefix keys np[]; returns the block's change
-    // bits (bit i: windows i, i+1; bit B-1 is set by the caller) and stores the argmin bytes
-    auto finish_block = [&](const u32 (&kk)[B], const u32 (&np)[G::BQ * 4], int nbp) -> u32 {
+    // windows of one block: own keys kk[] (suffix side), for Q = 2 the minimum key of the block after it, and the prefix keys
+    // np[] of the block Q further on; returns the block's change bits (bit i: windows i, i+1; bit B-1 is set by the caller)
+    // and stores the argmin bytes
+    auto finish_block = [&](const u32 (&kk)[B], u32 fullkey, const u32 (&np)[G::BQ * 4], int nbp) -> u32 {
         u32 mvb[B];
         u32 sm = 0;
 #pragma unroll
         for (int i = B - 1; i >= 0; --i) {
-            if (i == B - 1) sm = kk[i];
-            else { tacc = min(tacc, sm - kk[i]); sm = min(kk[i], sm); }
-            tacc = min(tacc, sm - np[i]);              // equal hash parts: own index i.. minus next-block index ..i, in [0, B)
-            mvb[i] = min(np[i] + 16u, sm);
+            if (i == B - 1) {
+                if (Q == 1) sm = kk[i];
+                else {
+                    sm = fullkey + 16u; tacc = min(tacc, sm - kk[i]);
+#ifdef SK4_TIE_DEBUG
+                    dbg_seed = min(dbg_seed, sm - kk[i]);
+#endif
+                    sm = min(kk[i], sm);
+                }
+            } else {
+                tacc = min(tacc, sm - kk[i]);
+#ifdef SK4_TIE_DEBUG
+                dbg_suf = min(dbg_suf, sm - kk[i]);
+#endif
+                sm = min(kk[i], sm);
+            }
+#ifdef SK4_TIE_DEBUG
+            dbg_cmb = min(dbg_cmb, sm - np[i]);
+#endif
+            tacc = min(tacc, sm - np[i]);              // equal hash parts: what sm holds lies left of what np holds: a small difference >= 0
+            mvb[i] = min(np[i] + 16u * Q, sm);
         }
         u32 wv[4] = {0, 0, 0, 0};
 #pragma unroll
@@ -357,13 +394,13 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         }
         *reinterpret_cast<uint4*>(IDXB + t * 32 + nbp * 16) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
         // change bits inside the block, four windows per step on the packed bytes: two windows of one block have the same
-        // minimizer iff their (next-block bit, index) fields are equal. Byte i against byte i+1: x = low five bits of the xor;
+        // minimizer iff their (blocks-further-on, index) fields are equal. Byte i against byte i+1: x = low six bits of the xor;
         // (x + 0x7F) & 0x80 flags a non-zero byte; the multiply gathers the four flags into the top nibble.
         u32 d = 0;
 #pragma unroll
         for (int q = 0; q < (B + 3) / 4; ++q) {
             const u32 nxt = __funnelshift_r(wv[q], q + 1 < 4 ? wv[q + 1] : 0u, 8);
-            const u32 x = (wv[q] ^ nxt) & 0x1F1F1F1Fu;
+            const u32 x = (wv[q] ^ nxt) & 0x3F3F3F3Fu;
             const u32 nz = (x + 0x7F7F7F7Fu) & 0x80808080u;
             d |= ((nz * 0x00204081u) >> 28) << (4 * q);
         }
@@ -419,22 +456,28 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
             const u32 hh = (u32)(murmur3_key8_s32(val, c.s8) >> 32);
             ks[i] = make_key(hh, c.keymask, (u32)i);
             if (i == 0) pm = ks[i];
-            else { tacc = min(tacc, ks[i] - pm); pm = min(pm, ks[i]); }
+            else {
+                tacc = min(tacc, ks[i] - pm);
+#ifdef SK4_TIE_DEBUG
+                dbg_pre = min(dbg_pre, ks[i] - pm);
+#endif
+                pm = min(pm, ks[i]);
+            }
             pk[i] = pm;
         }
 #pragma unroll
         for (int i = B; i < G::BQ * 4; ++i) pk[i] = 0;
-        if (nb == 0) {
+        if (nb < G::PBLK) {
 #pragma unroll
-            for (int q = 0; q < G::BQ; ++q) P[q * 32 + t] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-        } else {
-            dif |= finish_block(ks_prev, pk, nb - 1) << ((nb - 1) * B);
+            for (int q = 0; q < G::BQ; ++q) P[(nb * G::BQ + q) * 32 + t] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
+        if (Q == 1 && nb >= 1) dif |= finish_block(ks_prev, 0u, pk, nb - 1) << ((nb - 1) * B);
 #pragma unroll
-        for (int i = 0; i < B; ++i) ks_prev[i] = ks[i];
+        for (int i = 0; i < B; ++i) { ks_prev2[i] = ks_prev[i]; ks_prev[i] = ks[i]; }
+        full_prev = pm;
     }
     __syncwarp();
-    {
+    if (Q == 1) {
         // the last block: its next block is the next lane's block 0
         u32 np[G::BQ * 4];
 #pragma unroll
@@ -442,16 +485,47 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
             const uint4 e = P[q * 32 + t + 1];
             np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
         }
-        dif |= finish_block(ks_prev, np, NB - 1) << ((NB - 1) * B);
+        dif |= finish_block(ks_prev, 0u, np, NB - 1) << ((NB - 1) * B);
+    } else {
+        // Q = 2, two blocks per lane: block 0 = own suffix + own block 1 + the next lane's block-0 prefix; block 1 = own suffix +
+        // the next lane's block 0 + its block-1 prefix
+        static_assert(Q == 1 || NB == 2, "Q = 2 is written for two blocks per lane");
+        u32 np[G::BQ * 4];
+#pragma unroll
+        for (int q = 0; q < G::BQ; ++q) {
+            const uint4 e = P[q * 32 + t + 1];
+            np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
+        }
+        const u32 next_full0 = np[B - 1];
+        dif |= finish_block(ks_prev2, full_prev, np, 0);
+#pragma unroll
+        for (int q = 0; q < G::BQ; ++q) {
+            const uint4 e = P[(G::BQ + q) * 32 + t + 1];
+            np[4 * q] = e.x; np[4 * q + 1] = e.y; np[4 * q + 2] = e.z; np[4 * q + 3] = e.w;
+        }
+        dif |= finish_block(ks_prev, next_full0, np, 1) << B;
+    }
+    {
         const u32 nv0 = __shfl_down_sync(0xffffffffu, mv_first, 1);
         dif |= (u32)(nv0 + 16u != mv_last) << (L - 1);
     }
 #ifndef SK4_NO_EXACT     // timing experiments only: without the redo a tile with ties may be wrong
     {
-        const u32 flagged = __ballot_sync(0xffffffffu, tacc < 32u && V != 0u);
+        // Q = 2: lane 31 holds the last two margin blocks; no owned record reaches its windows, and what it reads as "next lane"
+        // is other lanes' keys (a seed and a prefix entry can be the same key there): it never asks for a redo
+        const u32 flagged = __ballot_sync(0xffffffffu, tacc < 32u && V != 0u && (Q == 1 || t < 31));
+#ifdef SK4_TIE_DEBUG
+        if (tacc < 32u && V != 0u) {
+            if (dbg_seed < 32u) atomicAdd(a.exact_tiles + 1, 1ULL);
+            if (dbg_suf < 32u) atomicAdd(a.exact_tiles + 2, 1ULL);
+            if (dbg_cmb < 32u) atomicAdd(a.exact_tiles + 3, 1ULL);
+            if (dbg_pre < 32u) atomicAdd(a.exact_tiles + 4, 1ULL);
+            if (dbg_cmb < 32u || dbg_seed < 32u) printf("tile %lld lane %d seed %u suf %u cmb %u pre %u V %x\n", tile, t, dbg_seed, dbg_suf, dbg_cmb, dbg_pre, V);
+        }
+#endif
         if (flagged) {
             __syncwarp();
-            redo_windows4<B, NB, CANON, MW>(CW, EW, IDXB, c, o, t, flagged);
+            redo_windows4<B, NB, Q, CANON, MW>(CW, EW, IDXB, c, o, t, flagged);
             dif = change_bits_from_idx4<B, NB>(IDXB, t);
             if (t == 0 && a.exact_tiles != nullptr) atomicAdd(a.exact_tiles, 1ULL);
         }
@@ -486,8 +560,9 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
     {
         // a record start is named by its slot in IDXB: lane << 5 | block-in-lane << 4 | window-in-block
         static_assert(NB == 2 && B <= 16, "slot numbering assumes two blocks of at most 16 windows per lane");
+        static_assert(Q == 1 || Q == 2, "a window spans Q + 1 blocks");
         unsigned short* rp = REC + (incl - cnt);
-        u32 sm = (start & MB) | ((start >> B) << 16);
+        u32 sm = B == 16 ? start : ((start & MB) | ((start >> B) << 16));
         const u32 tag = (u32)t << 5;
         while (sm) {
             const int i = __ffs((int)sm) - 1;
@@ -500,11 +575,11 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
 }
 
 // Record-parallel output of a finished tile from buffer set b: `n_rec` records, the first one at global index `base`.
-template <int B, int NB, bool CANON, bool MW>
+template <int B, int NB, int Q, bool CANON, bool MW>
 __device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
                                            u32 n_rec, u64 base)
 {
-    using G = Geo4<B, NB>;
+    using G = Geo4<B, NB, Q>;
     constexpr int L = G::L;
     const long long g0 = a.org + tile * (long long)G::R - B;
     const int o = (int)(g0 - (g0 & ~15LL));
@@ -518,8 +593,8 @@ __device__ __forceinline__ void emit_tile4(const SkArgs& a, const unsigned char*
         const u32 rec = REC[r];
         const int t0 = (int)(rec >> 5), nb0 = (int)((rec >> 4) & 1u), i0 = (int)(rec & 15u);
         const int j0 = nb0 * B + i0;                            // the window's offset in its lane's span
-        const int byt = IDXB[rec];                              // bits 0-3: index in the block, bit 4: the NEXT block
-        const int rel = (byt & 15) + ((byt & 16) ? B : 0) - i0; // mm_pos
+        const int byt = IDXB[rec];                              // bits 0-3: index in its block, bits 4-5: how many blocks further on
+        const int rel = (byt & 15) + ((byt >> 4) & 3) * B - i0; // mm_pos
         const int j = L * t0 + j0 + rel;                        // local m-mer start
         // size: distance to the first record-end bit at or after the start, at most w
         int size;
@@ -632,10 +707,10 @@ __device__ __forceinline__ u64 tile_base_finish4(const SkArgs& a, const u64* p, 
 
 }  // namespace
 
-template <int B, int NB, int LW, bool CANON, bool MW>
-__global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const SkArgs a)
+template <int B, int NB, int Q, int LW, bool CANON, bool MW>
+__global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_kernel(const SkArgs a)
 {
-    using G = Geo4<B, NB>;
+    using G = Geo4<B, NB, Q>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
@@ -654,7 +729,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
     u32 n0 = 0, n1 = 0;
     int b0 = 0, b1 = 0;
     bool have_pre = false;
-    uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
+    uint4 pre[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
     int b = 0;                          // buffer set of the tile computed in this iteration
     // Every warp runs on its own: compute tile i, publish its count, write out tile i-(KB-1) from its buffer set.
     // A ticket is taken only when nothing can block any more before that tile is published (a warp that waits for a
@@ -670,7 +745,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
         u32 n_rec = 0;
         u64 old = 0;
         if (have) {
-            n_rec = compute_tile4<B, NB, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre0, pre1);
+            n_rec = compute_tile4<B, NB, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre);
             if (t == 0) {
                 st_status(&a.tile_status[tile], ((u64)tile_tag4(a) << 32) | n_rec);
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
@@ -699,7 +774,7 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
         if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
-        if (prev >= 0) emit_tile4<B, NB, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
+        if (prev >= 0) emit_tile4<B, NB, Q, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
@@ -707,8 +782,9 @@ __global__ void __launch_bounds__(SK4_THREADS, SK4_MIN_BLOCKS) sk4_kernel(const 
             const long long P0 = (ng0 & ~15LL) - a.buf_lo;
             if (next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
                 have_pre = true;
-                if (t < G::NWORDS) pre0 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + t);
-                if (G::NWORDS > NT4 && t < G::NWORDS - NT4) pre1 = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + NT4 + t);
+#pragma unroll
+                for (int q = 0; q < 3; ++q)
+                    if (G::NWORDS > q * NT4 && t < G::NWORDS - q * NT4) pre[q] = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + q * NT4 + t);
             }
         }
         // queue: drop what was written, push what was computed

@@ -167,3 +167,13 @@ def test_synth_mutator_matches_reference(oracle):
     assert offs[0] == 0 and offs[-1] == bases.size and len(offs) == 7 and set(np.unique(bases).tolist()) <= set(b"ACGT")
     b2, o2 = synth.mutated_long_reads(6, lo=500, hi=900, threads=1)
     assert np.array_equal(bases, b2) and np.array_equal(offs, o2)
+
+
+def test_hash_sampler_threshold_rate_one_is_clamped():
+    """rate 1.0 is outside the reference's defined domain (uint64 cast of 2^64); we keep everything."""
+    from biolib_b200.context import Context
+    assert Context.hash_sampler_threshold(1.0) == 2**64 - 1
+    assert Context.hash_sampler_threshold(0.0) == 0
+    assert Context.hash_sampler_threshold(0.5) == int(0.5 * float(2**64 - 1))
+    with pytest.raises(ValueError):
+        Context.hash_sampler_threshold(1.5)
