@@ -8,7 +8,8 @@ per GPU 100 Mbp of the reference generator's stream (BASELINE configs[1]). With 
 GPU) rank r owns windows [r*100M, (r+1)*100M) of one N*100 Mbp genome built from shards uniform(42 + shard), plus
 the k+w-2 halo from the next shard: weak scaling, no data-path collective, one NCCL all-reduce of the counts.
 
-  value         Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream, max over ranks
+  value         Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream around each step (the K steps
+                are enqueued with BLG_F_ASYNC, the record count is collected after the timed region), max over ranks
   e2e           the same call with HOST (pinned) buffers and the compact record layout (BLG_F_POS32, 14 B per record):
                 H2D of the bases and D2H of the records inside the timing; e2e_records18 = the default 18-byte layout
   roofline      algorithmic bytes (1 B/base + 18 B/record) / kernel time vs the measured HBM copy peak
@@ -237,8 +238,7 @@ def bind_to_gpu_numa_node(local: int) -> str:
 
 class DeviceRun:
     """Device-resident runs of blg_super_kmers_range for one (k, m): output arrays sized once, kernel time from the
-    library's CUDA events with the stream idle at launch (an event recorded while the previous operation still runs can
-    time-stamp early on this driver: measured 45 us on the L2 flush), L2 flushed between runs."""
+    library's CUDA events with the device idle at launch, L2 flushed between runs."""
 
     def __init__(self, torch, ctx, dev, flush, k, m):
         self.torch, self.ctx, self.dev, self.flush, self.k, self.m = torch, ctx, dev, flush, k, m
@@ -251,11 +251,11 @@ class DeviceRun:
             self.sz = t.empty(cap, dtype=t.uint8, device=self.dev); self.ps = t.empty(cap, dtype=t.uint8, device=self.dev)
             self.cap = cap
 
-    def call(self, d_bases, n, win=None, offs=None):
+    def call(self, d_bases, n, win=None, offs=None, async_call=False):
         n_seq = 0 if offs is None else offs.numel() - 1
         return self.ctx.super_kmers_device(d_bases.data_ptr(), n, self.k, self.m, SEED, CANON, self.v.data_ptr(), self.mm.data_ptr(),
                                            self.sz.data_ptr(), self.ps.data_ptr(), self.cap, win_range=win,
-                                           d_offsets=offs.data_ptr() if offs is not None else 0, n_seq=n_seq)
+                                           d_offsets=offs.data_ptr() if offs is not None else 0, n_seq=n_seq, async_call=async_call)
 
     def kernel_ms(self, d_bases, n, win=None, offs=None, reps=5, warm=1):
         """(median kernel ms, record count)"""
@@ -380,7 +380,11 @@ def run_gpu(args):
 
     d_bases = torch.from_numpy(bases_h).to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    stream = torch.cuda.current_stream()
+    # a stream of our own: torch's default stream is the legacy stream 0, which blg_set_stream reads as "the context's own
+    # stream" -- flush, events and kernels must share one real stream to be ordered
+    torch.cuda.synchronize()
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     main_run = DeviceRun(torch, ctx, dev, flush, K, M)
     main_run.ensure(cap)
@@ -406,12 +410,14 @@ def run_gpu(args):
     for s, e in ev:
         flush.zero_()           # L2 flush between timed iterations (outside the event pair)
         s.record(stream)
-        count = step_device()
+        main_run.call(d_bases, n, win=(win_lo, win_hi), async_call=True)   # BLG_F_ASYNC: enqueue only, as a pipeline would
         e.record(stream)
-        exact_tiles = ctx.stats()["exact_tiles"]
     barrier()
     sampler.stop_flag = True
     sampler.join()
+    count_async = ctx.async_count()                                            # the last step's record count, after the fact
+    assert count_async == count, (count_async, count)
+    exact_tiles = ctx.stats()["exact_tiles"] // max(args.steps, 1)
     step_ms = sum(s.elapsed_time(e) for s, e in ev) / args.steps
     kernel_ms, count_k = main_run.kernel_ms(d_bases, n, win=(win_lo, win_hi), reps=min(max(args.steps, 3), 10))
     assert count_k == count

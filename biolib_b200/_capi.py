@@ -17,10 +17,11 @@ CSRC = os.path.join(HERE, "csrc")
 BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOMEM = range(6)
 F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID, F_POS32 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
 F_REF_DROP_LAST = 0x40
+F_ASYNC = 0x80
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
-    "blg_last_stats", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
+    "blg_last_stats", "blg_async_count", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
     "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out", "blg_sorted_unique_kmers", "blg_kmer_jaccard",
 ]
@@ -96,6 +97,7 @@ def lib() -> C.CDLL:
     L.blg_last_error.restype = C.c_char_p
     L.blg_last_error.argtypes = [vp]
     L.blg_last_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.blg_async_count.argtypes = [vp, C.POINTER(u64)]
     L.blg_device_info.argtypes = [vp, C.POINTER(C.c_int), C.c_char_p, sz]
     L.blg_minimizer_positions.argtypes = [vp, vp, sz, C.c_uint8, C.c_uint8, C.c_uint32, vp]
     L.blg_host_alloc.argtypes = [vp, sz, C.POINTER(vp)]

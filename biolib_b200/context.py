@@ -275,9 +275,10 @@ class Context:
     # ------------------------------------------------------------------ device resident (raw pointers)
     def super_kmers_device(self, d_bases: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, d_value: int,
                            d_mm_start: int, d_size: int, d_mm_pos: int, capacity: int, d_offsets: int = 0, n_seq: int = 0,
-                           win_range=None, d_hash: int = 0) -> int:
-        """Everything already in HBM: enqueue on the context stream, return the record count."""
-        flags = F_DEVICE_INPUT | F_DEVICE_OUTPUT | (F_EMIT_HASH if d_hash else 0)
+                           win_range=None, d_hash: int = 0, async_call: bool = False) -> int:
+        """Everything already in HBM: enqueue on the context stream, return the record count (0 with async_call: the kernel is
+        only enqueued, collect the count with async_count())."""
+        flags = F_DEVICE_INPUT | F_DEVICE_OUTPUT | (F_EMIT_HASH if d_hash else 0) | (_capi.F_ASYNC if async_call else 0)
         if not d_size:
             flags |= _capi.F_NO_SIZE
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
@@ -288,6 +289,12 @@ class Context:
                                           int(lo), int(hi), C.byref(p), C.byref(out))
         self._check(st)
         return out.count
+
+    def async_count(self) -> int:
+        """blg_async_count: wait for the context's stream, records of the last async call."""
+        n = C.c_uint64()
+        self._check(self.L.blg_async_count(self.h, C.byref(n)))
+        return n.value
 
     def super_kmers_raw(self, bases_ptr: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, value_ptr: int,
                         mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int, flags: int = 0,

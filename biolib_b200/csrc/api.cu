@@ -70,6 +70,8 @@ struct blg_ctx {
     cudaEvent_t ev_in[16] = {};
     int pipe_first_div = 4;      // first pipeline piece = a regular piece / this
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi
+    bool async_call = false;                 // BLG_F_ASYNC: run_sk_once only enqueues
+    uint64_t async_capacity = 0;
     const unsigned char* staged = nullptr;  // set while a packed-input call runs: the bases are already unpacked in `in`
     DevBuf packed, brk, fx_text, fx_scratch; // packed codes + break list of a packed-input call; FASTA/FASTQ text and parser scratch
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
@@ -212,6 +214,7 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
         CK(c, sk4_launch(a, plan, c->stream));
         CK(c, cudaEventRecord(c->ev1, c->stream));
         c->stats.kernel_launches += 1;
+        if (c->async_call) { *total = 0; c->async_capacity = a.capacity; return BLG_OK; }   // blg_async_count() collects
         CK(c, cudaStreamSynchronize(c->stream));
         *total = c->h_total[0];
         c->stats.exact_tiles += c->h_total[1] - c->sk4_exact_seen;
@@ -524,6 +527,9 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     };
 
     uint64_t total = 0;
+    c->async_call = (p->flags & BLG_F_ASYNC) != 0 && dev_out && (p->flags & BLG_F_DEVICE_INPUT) && out->capacity > 0 && !want_id &&
+                    sk4_supported(k, m);
+    struct AsyncOff { blg_ctx* c; ~AsyncOff() { c->async_call = false; } } async_off{c};
     if (dev_out && out->capacity > 0) {
         // caller-owned device arrays: one launch, no retry
         a.value = reinterpret_cast<unsigned long long*>(out->value);
@@ -706,6 +712,20 @@ int blg_set_stream(blg_ctx* c, void* s)
 }
 
 const char* blg_last_error(blg_ctx* c) { return c ? c->err.c_str() : "no context"; }
+
+int blg_async_count(blg_ctx* c, uint64_t* count)
+{
+    if (!c || !count) return BLG_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    *count = c->h_total[0];
+    c->stats.n_records = c->h_total[0];
+    c->stats.exact_tiles = c->h_total[1] - c->sk4_exact_seen;     // of every launch since the last collected one
+    c->sk4_exact_seen = c->h_total[1];
+    add_kernel_time(c);
+    if (c->async_capacity && *count > c->async_capacity) { c->err = "output capacity too small"; return BLG_E_CAPACITY; }
+    return BLG_OK;
+}
 
 int blg_last_stats(blg_ctx* c, blg_stats* out)
 {

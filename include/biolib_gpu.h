@@ -58,6 +58,9 @@ typedef enum blg_status {
                                    * BLG_E_INVALID when a position could exceed 2^32 - 1; not combinable with BLG_F_EMIT_ID */
 #define BLG_F_REF_DROP_LAST 0x40u /* blg_sorted_unique_kmers / blg_kmer_jaccard: leave out the last k-mer of every sequence that ends in
                                    * a valid base, as iterating the reference's kmer_view does (include/kmer_view.hpp:57) */
+#define BLG_F_ASYNC         0x80u /* with BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT and caller arrays: only enqueue the kernel on the context's
+                                   * stream and return; out->count stays 0. The record count (and a BLG_E_CAPACITY verdict) comes from
+                                   * blg_async_count(), which waits for the stream. Several calls may be in flight; the count is the last one's */
 #define BLG_F_EMIT_ID       0x10u /* also fill out->id (minimizer_context_t::id; one extra pass over the bases) */
 
 typedef struct blg_params {
@@ -124,7 +127,8 @@ typedef struct blg_ctx blg_ctx;
 /* context: one GPU, one stream; not thread-safe (one context per host thread / GPU) */
 int blg_create(int device, blg_ctx** out);
 int blg_destroy(blg_ctx* ctx);
-/* Run on a caller stream (cudaStream_t passed as void*); NULL restores the context's own stream.
+/* Run on a caller stream (cudaStream_t passed as void*); NULL (which is also the value of the legacy default stream 0: use a
+ * created stream) restores the context's own non-blocking stream.
  * Device-resident calls (BLG_F_DEVICE_INPUT|BLG_F_DEVICE_OUTPUT with caller arrays) then only
  * enqueue work and one 8-byte count read-back. */
 int blg_set_stream(blg_ctx* ctx, void* cuda_stream);
@@ -132,6 +136,8 @@ int blg_abi_version(void);
 const char* blg_strerror(int status);
 const char* blg_last_error(blg_ctx* ctx);
 int blg_last_stats(blg_ctx* ctx, blg_stats* out);
+/* waits for the context's stream; *count = records of the last BLG_F_ASYNC call (BLG_E_CAPACITY if they exceeded its capacity) */
+int blg_async_count(blg_ctx* ctx, uint64_t* count);
 /* number of SMs / device name of the context's GPU (for sizing and reports) */
 int blg_device_info(blg_ctx* ctx, int* sm_count, char* name, size_t name_len);
 

@@ -27,6 +27,7 @@ def main():
 
     dev = torch.device("cuda", 0)
     ctx = biolib_b200.Context(0)
+    torch.cuda.set_stream(torch.cuda.Stream())   # not the legacy stream 0 (blg_set_stream reads 0 as "the context's own stream")
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     n = args.n
     vals = torch.randint(0, 2**62, (n,), dtype=torch.int64, device=dev)

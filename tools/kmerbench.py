@@ -59,6 +59,7 @@ def main():
     d_hi = torch.empty(cap if wide else 1, dtype=torch.int64, device=dev)
     d_pos = torch.empty(cap if args.pos else 1, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    torch.cuda.set_stream(torch.cuda.Stream())   # not the legacy stream 0 (blg_set_stream reads 0 as "the context's own stream")
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ms, count = [], 0
     for i in range(3 + args.steps):

@@ -52,6 +52,7 @@ def main():
     d_size = torch.empty(cap, dtype=torch.uint8, device=dev)
     d_pos = torch.empty(cap, dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    torch.cuda.set_stream(torch.cuda.Stream())   # not the legacy stream 0 (blg_set_stream reads 0 as "the context's own stream")
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ms = []
     count = 0

@@ -57,6 +57,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     ctx = biolib_b200.Context(local)
+    torch.cuda.set_stream(torch.cuda.Stream())   # not the legacy stream 0 (blg_set_stream reads 0 as "the context's own stream")
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     only = set(sys.argv[1:])

@@ -15,6 +15,7 @@ d_value = torch.empty(cap, dtype=torch.int64, device=dev); d_mm = torch.empty(ca
 d_size = torch.empty(cap, dtype=torch.uint8, device=dev); d_pos = torch.empty(cap, dtype=torch.uint8, device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 dummy = torch.zeros(1024, device=dev)
+torch.cuda.set_stream(torch.cuda.Stream())
 stream = torch.cuda.current_stream()
 ctx.set_stream(stream.cuda_stream)
 for mode in ("plain", "dummy_after_flush", "sync_after_flush", "noflush"):
