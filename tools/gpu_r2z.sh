@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+python tools/run_configs.py > gpurun_out/r2z_configs_n1.jsonl 2> gpurun_out/r2z_configs_n1.err
+cut -c1-420 gpurun_out/r2z_configs_n1.jsonl
+python tools/quickbench.py --k 31 --m 19 --steps 3 > gpurun_out/r2z_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:sk4_kernel -s 2 -c 1 -o gpurun_out/r2z_sk4 python tools/quickbench.py --k 31 --m 19 --steps 3 > gpurun_out/r2z_ncu.log 2>&1
+tail -n 2 gpurun_out/r2z_ncu.log
