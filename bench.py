@@ -10,8 +10,9 @@ the k+w-2 halo from the next shard: weak scaling, no data-path collective, one N
 
   value         Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream around each step (the K steps
                 are enqueued with BLG_F_ASYNC, the record count is collected after the timed region), max over ranks
-  e2e           the same call with HOST (pinned) buffers and the compact record layout (BLG_F_POS32, 14 B per record):
-                H2D of the bases and D2H of the records inside the timing; e2e_records18 = the default 18-byte layout
+  e2e           the same call with HOST (pinned) buffers and the smallest record layout (BLG_F_RUNS, 10 B per record + a run
+                list): H2D of the bases and D2H of the records inside the timing; e2e_compact14 = BLG_F_POS32 (14 B),
+                e2e_records18 = the default 18-byte layout
   roofline      algorithmic bytes (1 B/base + 18 B/record) / kernel time vs the measured HBM copy peak
   roofline_int  why the HBM fraction is what it is: executed instructions per base and pipe utilisation (from the committed
                 ncu capture, with its git sha), hashes per second of this run against the hash rate the machine sustains
@@ -430,10 +431,13 @@ def run_gpu(args):
     hp_in = ctx.host_alloc(n)
     np_from_ptr(hp_in, n, np.uint8)[:] = bases_h
     hp = [ctx.host_alloc(cap * 8), ctx.host_alloc(cap * 8), ctx.host_alloc(cap), ctx.host_alloc(cap)]
+    run_cap = cap // 64 + 65536
+    hp_runs = [ctx.host_alloc(run_cap * 8), ctx.host_alloc(run_cap * 8)]
     e2e = {}
-    for name, flags in (("records18", 0), ("compact14", _capi.F_POS32)):
+    for name, flags in (("records18", 0), ("compact14", _capi.F_POS32), ("runs10", _capi.F_RUNS)):
         def step_host():
-            return ctx.super_kmers_raw(hp_in, n, K, M, SEED, CANON, hp[0], hp[1], hp[2], hp[3], cap, flags=flags, win_range=(win_lo, win_hi))
+            return ctx.super_kmers_raw(hp_in, n, K, M, SEED, CANON, hp[0], hp[1], hp[2], hp[3], cap, flags=flags, win_range=(win_lo, win_hi),
+                                       run_ptrs=hp_runs if flags & _capi.F_RUNS else None, run_capacity=run_cap if flags & _capi.F_RUNS else 0)
         for _ in range(2):
             c2 = step_host()
         assert c2 == count, (c2, count)
@@ -447,20 +451,26 @@ def run_gpu(args):
         # parity of the host path: same records as the device-resident run (checksums over what landed in host memory)
         hv = np_from_ptr(hp[0], cap * 8, np.uint64)[:count]
         assert int(hv.sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
-        pos = np_from_ptr(hp[1], cap * 8, np.uint32 if flags else np.uint64)[:count].astype(np.uint64) + np.uint64(win_lo if flags else 0)
+        if flags & _capi.F_RUNS:
+            from biolib_b200.context import expand_runs
+            nr = ctx.last_n_runs
+            pos = expand_runs(np_from_ptr(hp_runs[0], run_cap * 8, np.uint64)[:nr], np_from_ptr(hp_runs[1], run_cap * 8, np.uint64)[:nr],
+                              np_from_ptr(hp[2], cap, np.uint8)[:count], np_from_ptr(hp[3], cap, np.uint8)[:count])
+        else:
+            pos = np_from_ptr(hp[1], cap * 8, np.uint32 if flags else np.uint64)[:count].astype(np.uint64) + np.uint64(win_lo if flags else 0)
         assert int(pos.sum(dtype=np.uint64)) == int(d_mm[:count].sum().item()) & (2**64 - 1)
-    for p in [hp_in] + hp:
+    for p in [hp_in] + hp + hp_runs:
         ctx.host_free(p)
 
     ctx.set_stream(stream.cuda_stream)
     extras = None if args.no_extra else run_extras(torch, dist, ctx, dev, flush, world, rank)
 
-    t = torch.tensor([step_ms, e2e["compact14"][0], kernel_ms, e2e["records18"][0]], dtype=torch.float64, device=dev)
+    t = torch.tensor([step_ms, e2e["runs10"][0], kernel_ms, e2e["records18"][0], e2e["compact14"][0]], dtype=torch.float64, device=dev)
     cnt = torch.tensor([count, nwin, exact_tiles], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)   # the path's only collective: per-GPU counts
-    step_ms, e2e_ms, kernel_ms, e2e18_ms = t.tolist()
+    step_ms, e2e_ms, kernel_ms, e2e18_ms, e2e14_ms = t.tolist()
     total_records, total_win, total_exact = cnt.tolist()
     total_bases = SHARD * world
 
@@ -479,9 +489,12 @@ def run_gpu(args):
                                    "uniform(42+shard) (BASELINE configs[1])",
                        "k": K, "m": M, "bases_per_gpu": SHARD, "records": total_records, "kmers": total_win,
                        "l2": "256 MiB flush write between timed steps", "sharding": f"chunk+halo x{world}",
-                       "host": numa, "e2e_layout": "BLG_F_POS32: value u64 + 32-bit position relative to the range start + size u8 + mm_pos u8"},
-            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["compact14"][1]),
-                    "d2h_bytes_per_step": int(e2e["compact14"][2]), "steps": e2e_steps, "ms_per_step": e2e_ms},
+                       "host": numa, "e2e_layout": "BLG_F_RUNS: value u64 + size u8 + mm_pos u8 per record, plus (first record, start) per run of contiguous "
+                                     "super-k-mers; positions follow by adding sizes, as in the reference's own sequential view"},
+            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["runs10"][1]),
+                    "d2h_bytes_per_step": int(e2e["runs10"][2]), "steps": e2e_steps, "ms_per_step": e2e_ms},
+            "e2e_compact14": {"value": total_bases / (e2e14_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["compact14"][1]),
+                              "d2h_bytes_per_step": int(e2e["compact14"][2]), "ms_per_step": e2e14_ms},
             "e2e_records18": {"value": total_bases / (e2e18_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["records18"][1]),
                               "d2h_bytes_per_step": int(e2e["records18"][2]), "ms_per_step": e2e18_ms},
             "gpu_launches": args.steps,

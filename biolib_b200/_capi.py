@@ -18,6 +18,7 @@ BLG_OK, BLG_E_INVALID, BLG_E_UNSUPPORTED, BLG_E_CAPACITY, BLG_E_CUDA, BLG_E_NOME
 F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID, F_POS32 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
 F_REF_DROP_LAST = 0x40
 F_ASYNC = 0x80
+F_RUNS = 0x100
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
@@ -39,7 +40,8 @@ class KmerOut(C.Structure):
 
 class SkOut(C.Structure):
     _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value", C.c_void_p), ("mm_start", C.c_void_p),
-                ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("id", C.c_void_p), ("owner", C.c_void_p)]
+                ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("id", C.c_void_p), ("owner", C.c_void_p),
+                ("n_runs", C.c_uint64), ("run_capacity", C.c_uint64), ("run_first_record", C.c_void_p), ("run_start", C.c_void_p)]
 
 
 class PackedSeq(C.Structure):

@@ -94,13 +94,13 @@ class Context:
         return res
 
     def super_kmers(self, seq, k: int, m: int, seed: int = 0, canonical: bool = False, offsets=None, want_hash=True,
-                    win_range=None, minimizers_only=False, want_id=False, pos32=False) -> dict:
+                    win_range=None, minimizers_only=False, want_id=False, pos32=False, runs=False) -> dict:
         """pos32: ask for the compact record layout (BLG_F_POS32: 32-bit positions relative to the range start); the
         returned mm_start / sk_start are widened back to absolute uint64 so that both layouts compare equal."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0) | (_capi.F_POS32 if pos32 else 0),
-                   seed=seed & (2**64 - 1))
+        p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0) | (_capi.F_POS32 if pos32 else 0) |
+                   (_capi.F_RUNS if runs else 0), seed=seed & (2**64 - 1))
         out = SkOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1)
         if win_range is not None:
@@ -112,12 +112,18 @@ class Context:
         self._check(st)
         n = out.count
         try:
-            if pos32:
+            if runs:
+                # BLG_F_RUNS: no positions came back; rebuild them from the run list (what a streaming consumer does on the fly)
+                rf, rs = _copy(out.run_first_record, out.n_runs, np.uint64), _copy(out.run_start, out.n_runs, np.uint64)
+                mm = expand_runs(rf, rs, _copy(out.size, n, np.uint8), _copy(out.mm_pos, n, np.uint8))
+            elif pos32:
                 base = 0 if win_range is None else min(int(win_range[0]), max(b.size - k + 1, 0))
                 mm = _copy(out.mm_start, n, np.uint32).astype(np.uint64) + np.uint64(base)
             else:
                 mm = _copy(out.mm_start, n, np.uint64)
             res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=mm)
+            if runs:
+                res["n_runs"] = int(out.n_runs)
             if not minimizers_only:
                 res["size"] = _copy(out.size, n, np.uint8)
                 res["mm_pos"] = _copy(out.mm_pos, n, np.uint8)
@@ -298,14 +304,17 @@ class Context:
 
     def super_kmers_raw(self, bases_ptr: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, value_ptr: int,
                         mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int, flags: int = 0,
-                        offsets_ptr: int = 0, n_seq: int = 0, win_range=None) -> int:
-        """Raw-pointer call with caller-owned arrays (host pointers unless the DEVICE flags are set)."""
+                        offsets_ptr: int = 0, n_seq: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0) -> int:
+        """Raw-pointer call with caller-owned arrays (host pointers unless the DEVICE flags are set). With F_RUNS pass
+        run_ptrs=(first_record_ptr, start_ptr) and run_capacity; the number of runs is left in self.last_n_runs."""
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
-        out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr, size=size_ptr or None,
-                    mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None)
+        out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr or None, size=size_ptr or None,
+                    mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None, n_runs=0, run_capacity=run_capacity,
+                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None)
         lo, hi = (0, 2**64 - 1) if win_range is None else win_range
         self._check(self.L.blg_super_kmers_range(self.h, C.c_void_p(bases_ptr), n_bases, C.c_void_p(offsets_ptr or 0), n_seq,
                                                  int(lo), int(hi), C.byref(p), C.byref(out)))
+        self.last_n_runs = int(out.n_runs)
         return out.count
 
     def host_alloc(self, nbytes: int) -> int:
@@ -329,6 +338,19 @@ class Context:
         else:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         return out.count
+
+
+def expand_runs(run_first_record, run_start, size, mm_pos) -> np.ndarray:
+    """mm_start of every record from the BLG_F_RUNS outputs: inside a run every record starts where the previous one ended."""
+    n = len(size)
+    if n == 0:
+        return np.zeros(0, np.uint64)
+    sz = size.astype(np.int64)
+    before = np.cumsum(sz) - sz                                   # bases (k-mer starts) consumed before record r, over all records
+    run_of = np.searchsorted(run_first_record.astype(np.int64), np.arange(n), side="right") - 1
+    first = run_first_record.astype(np.int64)[run_of]
+    sk = run_start.astype(np.int64)[run_of] + before - before[first]
+    return (sk + mm_pos.astype(np.int64)).astype(np.uint64)
 
 
 def _copy(ptr, n, dtype) -> np.ndarray:

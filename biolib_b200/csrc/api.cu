@@ -281,7 +281,7 @@ int validate_sk(blg_ctx* c, const blg_params* p, const blg_sk_out* out)
         c->err = "need 1 <= m <= min(k, 32) and k <= 64";
         return BLG_E_INVALID;
     }
-    if (out->capacity > 0 && (!out->value || !out->mm_start)) { c->err = "capacity > 0 needs value and mm_start arrays"; return BLG_E_INVALID; }
+    if (out->capacity > 0 && (!out->value || (!out->mm_start && !(p->flags & BLG_F_RUNS)))) { c->err = "capacity > 0 needs value and mm_start arrays"; return BLG_E_INVALID; }
     return BLG_OK;
 }
 
@@ -337,11 +337,41 @@ void free_owner(Owner* ow)
 // (small input, id output, or the record estimate was too small).
 int run_ids(blg_ctx* c, const SkArgs& a, uint64_t total, unsigned long long* d_id);
 
+// BLG_F_RUNS: the run list of `total` device-resident records -> host arrays of `out` (library- or caller-owned)
+int emit_runs(blg_ctx* c, const unsigned long long* d_mm, const unsigned char* d_pos, const unsigned char* d_size, uint64_t total, blg_sk_out* out,
+              Owner* ow)
+{
+    out->n_runs = 0;
+    if (total == 0) return BLG_OK;
+    int rc = ensure(c, c->rank, runs_scratch_bytes(total) + 64);
+    if (rc != BLG_OK) return rc;
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + runs_scratch_bytes(total) / 8 * 8);
+    unsigned long long *d_first = nullptr, *d_start = nullptr, nr = 0;
+    int launches = 0;
+    CK(c, runs_launch(d_mm, d_pos, d_size, total, c->rank.p, &d_first, &d_start, d_tot, c->stream, &launches));
+    c->stats.kernel_launches += launches;
+    CK(c, cudaMemcpyAsync(&nr, d_tot, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    out->n_runs = nr;
+    if (ow) {
+        if ((rc = alloc_owned(c, false, nr, &out->run_first_record, ow, 6)) != BLG_OK || (rc = alloc_owned(c, false, nr, &out->run_start, ow, 7)) != BLG_OK) return rc;
+    } else if (nr > out->run_capacity || !out->run_first_record || !out->run_start) {
+        c->err = "run arrays too small (out->n_runs holds the required size)";
+        return BLG_E_CAPACITY;
+    }
+    CK(c, cudaMemcpyAsync(out->run_first_record, d_first, nr * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaMemcpyAsync(out->run_start, d_start, nr * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    c->stats.bytes_d2h += nr * 16 + 8;
+    return BLG_OK;
+}
+
 int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t lo, uint64_t hi,
                  const blg_params* p, blg_sk_out* out, bool with_size, bool want_hash, int* done_flag)
 {
     *done_flag = 0;
     const bool want_id = (p->flags & BLG_F_EMIT_ID) != 0;
+    const bool runs = (p->flags & BLG_F_RUNS) != 0;       // positions stay on the device; the run list is downloaded at the end
     const bool pos32 = (p->flags & BLG_F_POS32) != 0;
     const size_t posb = pos32 ? 4 : 8;                 // bytes per position entry
     const uint64_t nwin = hi - lo;
@@ -376,7 +406,9 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
-        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) return rc;
+        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK) return rc;
+        h.mm_start = nullptr;
+        if (!runs && (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) return rc;
         if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) return rc;
         if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) return rc;
         if (want_id && (rc = alloc_owned(c, false, cap, &h.id, ow, 5)) != BLG_OK) return rc;
@@ -427,8 +459,8 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         if (cnt > cap - done) { overflow = true; done += cnt; break; }
         if (cnt) {
             CK(c, cudaMemcpyAsync(h.value + done, a.value, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
-            CK(c, cudaMemcpyAsync(reinterpret_cast<char*>(h.mm_start) + done * posb, static_cast<char*>(c->o_mm.p) + done * posb, cnt * posb, cudaMemcpyDeviceToHost, c->s_out));
-            c->stats.bytes_d2h += cnt * (8 + posb);
+            if (!runs) CK(c, cudaMemcpyAsync(reinterpret_cast<char*>(h.mm_start) + done * posb, static_cast<char*>(c->o_mm.p) + done * posb, cnt * posb, cudaMemcpyDeviceToHost, c->s_out));
+            c->stats.bytes_d2h += cnt * (8 + (runs ? 0 : posb));
             if (with_size) {
                 CK(c, cudaMemcpyAsync(h.size + done, a.size, cnt, cudaMemcpyDeviceToHost, c->s_out));
                 CK(c, cudaMemcpyAsync(h.mm_pos + done, a.mm_pos, cnt, cudaMemcpyDeviceToHost, c->s_out));
@@ -453,10 +485,18 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         CK(c, cudaStreamSynchronize(c->stream));
         c->stats.bytes_d2h += done * 8;
     }
+    if (runs && !overflow) {
+        if ((rc = emit_runs(c, static_cast<unsigned long long*>(c->o_mm.p), static_cast<unsigned char*>(c->o_pos.p), static_cast<unsigned char*>(c->o_size.p),
+                            done, &h, out->capacity == 0 ? ow : nullptr)) != BLG_OK) {
+            if (rc == BLG_E_CAPACITY) { out->n_runs = h.n_runs; out->count = done; }
+            return rc;
+        }
+    }
     CK(c, cudaStreamSynchronize(c->s_out));
     if (!staged) CK(c, cudaStreamSynchronize(c->s_in));
     if (overflow) return BLG_OK;   // plain path: exact count, retry / BLG_E_CAPACITY (the guard releases the arrays)
     guard.armed = false;
+    if (runs) { out->n_runs = h.n_runs; out->run_first_record = h.run_first_record; out->run_start = h.run_start; }
     if (out->capacity == 0) { *out = h; out->owner = ow; out->capacity = 0; }
     out->count = done;
     c->stats.n_records = done;
@@ -484,6 +524,8 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const bool pos32 = (p->flags & BLG_F_POS32) != 0;
     const size_t posb = pos32 ? 4 : 8;
     if (pos32 && want_id) { c->err = "BLG_F_POS32 cannot be combined with BLG_F_EMIT_ID"; return BLG_E_INVALID; }
+    const bool runs = (p->flags & BLG_F_RUNS) != 0;
+    if (runs && (dev_out || pos32 || !with_size || (p->flags & BLG_F_NO_SIZE))) { c->err = "BLG_F_RUNS: host output of the super-k-mer calls only, without BLG_F_POS32"; return BLG_E_INVALID; }
     with_size = with_size && !(p->flags & BLG_F_NO_SIZE);
     if (out->capacity > 0 && with_size && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
     if (out->capacity > 0 && want_hash && !out->hash) { c->err = "BLG_F_EMIT_HASH needs a hash array"; return BLG_E_INVALID; }
@@ -602,7 +644,9 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
-        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK) { free_owner(ow); return rc; }
+        out->mm_start = nullptr;
+        if (!runs && (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         if (with_size && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, total, &out->hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
         if (want_id && (rc = alloc_owned(c, false, total, &out->id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
@@ -610,8 +654,8 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     }
     if (total) {
         CK(c, cudaMemcpyAsync(out->value, a.value, total * 8, cudaMemcpyDeviceToHost, c->stream));
-        CK(c, cudaMemcpyAsync(out->mm_start, pos32 ? static_cast<void*>(a.mm_start32) : static_cast<void*>(a.mm_start), total * posb, cudaMemcpyDeviceToHost, c->stream));
-        c->stats.bytes_d2h += total * (8 + posb);
+        if (!runs) CK(c, cudaMemcpyAsync(out->mm_start, pos32 ? static_cast<void*>(a.mm_start32) : static_cast<void*>(a.mm_start), total * posb, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * (8 + (runs ? 0 : posb));
         if (with_size) {
             CK(c, cudaMemcpyAsync(out->size, a.size, total, cudaMemcpyDeviceToHost, c->stream));
             CK(c, cudaMemcpyAsync(out->mm_pos, a.mm_pos, total, cudaMemcpyDeviceToHost, c->stream));
@@ -626,6 +670,10 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
             c->stats.bytes_d2h += total * 8;
         }
         CK(c, cudaStreamSynchronize(c->stream));
+        if (runs && (rc = emit_runs(c, a.mm_start, a.mm_pos, a.size, total, out, out->capacity == 0 ? ow : nullptr)) != BLG_OK) {
+            if (out->capacity == 0) { free_owner(ow); out->owner = nullptr; }
+            return rc;
+        }
     }
     c->stats.total_ms = tm.ms();
     return BLG_OK;
@@ -1299,6 +1347,8 @@ void blg_free_sk_out(blg_ctx* c, blg_sk_out* out)
         free_owner(static_cast<Owner*>(out->owner));
         out->value = out->mm_start = out->hash = out->id = nullptr;
         out->size = out->mm_pos = nullptr;
+        out->run_first_record = out->run_start = nullptr;
+        out->n_runs = 0;
         out->owner = nullptr;
         out->count = 0;
     }

@@ -168,6 +168,11 @@ cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long
                             unsigned long long n_seq, unsigned long long n_bases, unsigned long long* flags, void* scratch, unsigned long long* tmp,
                             unsigned long long* d_total, cudaStream_t stream, int* launches);
 
+// BLG_F_RUNS: the maximal runs of records in which every record starts where the previous one ended
+size_t runs_scratch_bytes(unsigned long long n);
+cudaError_t runs_launch(const unsigned long long* mm_start, const unsigned char* mm_pos, const unsigned char* size, unsigned long long n, void* scratch,
+                        unsigned long long** first, unsigned long long** start, unsigned long long* d_total, cudaStream_t stream, int* launches);
+
 cudaError_t hash64_launch(const unsigned long long* in, unsigned long long* out, size_t n, unsigned long long s8,
                           cudaStream_t stream);
 

@@ -154,7 +154,44 @@ __global__ void compact_by_flags(const u64* __restrict__ k, const u64* __restric
     if (next != here) out[here] = k[i];
 }
 
+// ---- runs of consecutive super-k-mers (BLG_F_RUNS): record r opens a run iff it does not start where r-1 ended ----------------
+__global__ void run_flags(const u64* __restrict__ mm_start, const u8* __restrict__ mm_pos, const u8* __restrict__ size, u64 n, u64* __restrict__ f)
+{
+    const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const u64 sk = mm_start[r] - mm_pos[r];
+    f[r] = (r == 0 || sk != mm_start[r - 1] - mm_pos[r - 1] + size[r - 1]) ? 1 : 0;
+}
+__global__ void run_scatter(const u64* __restrict__ mm_start, const u8* __restrict__ mm_pos, const u64* __restrict__ f_excl, u64 n,
+                            const u64* __restrict__ total, u64* __restrict__ first, u64* __restrict__ start)
+{
+    const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const u64 here = f_excl[r], next = r + 1 < n ? f_excl[r + 1] : *total;
+    if (next != here) { first[here] = r; start[here] = mm_start[r] - mm_pos[r]; }
+}
+
 }  // namespace
+
+size_t runs_scratch_bytes(unsigned long long n) { return (size_t)((3 * n + (n + SC_BLOCK - 1) / SC_BLOCK + 16) * 8 + 256); }
+
+// scratch: [flags n][first n][start n][sums]; *d_total (device) = number of runs; first / start are returned as pointers into scratch
+cudaError_t runs_launch(const unsigned long long* mm_start, const unsigned char* mm_pos, const unsigned char* size, unsigned long long n, void* scratch,
+                        unsigned long long** first, unsigned long long** start, unsigned long long* d_total, cudaStream_t stream, int* launches)
+{
+    u64* flags = static_cast<u64*>(scratch);
+    *first = flags + n;
+    *start = flags + 2 * n;
+    u64* sums = flags + 3 * n;
+    if (n == 0) return cudaMemsetAsync(d_total, 0, 8, stream);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    run_flags<<<grid, 256, 0, stream>>>(mm_start, mm_pos, size, n, flags);
+    cudaError_t e = ss_scan(flags, n, sums, d_total, stream);
+    if (e != cudaSuccess) return e;
+    run_scatter<<<grid, 256, 0, stream>>>(mm_start, mm_pos, flags, n, d_total, *first, *start);
+    *launches += 5;
+    return cudaGetLastError();
+}
 
 size_t sort_scratch_bytes(unsigned long long n)
 {

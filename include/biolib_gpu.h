@@ -61,6 +61,12 @@ typedef enum blg_status {
 #define BLG_F_ASYNC         0x80u /* with BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT and caller arrays: only enqueue the kernel on the context's
                                    * stream and return; out->count stays 0. The record count (and a BLG_E_CAPACITY verdict) comes from
                                    * blg_async_count(), which waits for the stream. Several calls may be in flight; the count is the last one's */
+#define BLG_F_RUNS          0x100u /* smallest records over PCIe (host output of the super-k-mer calls): mm_start is NOT returned (out->mm_start stays
+                                    * NULL / untouched); instead the records come with the list of RUNS -- maximal stretches of records in which
+                                    * every record starts where the previous one ended (one run for a sequence without breaks):
+                                    *   run_first_record[j]  index of the first record of run j      run_start[j]  its sk_start
+                                    * so that sk_start[r] = run_start[j] + sum of size[run_first_record[j] .. r), mm_start = sk_start + mm_pos.
+                                    * 10 instead of 18 bytes per record. With caller arrays set run_capacity and the two run arrays. */
 #define BLG_F_EMIT_ID       0x10u /* also fill out->id (minimizer_context_t::id; one extra pass over the bases) */
 
 typedef struct blg_params {
@@ -109,6 +115,11 @@ typedef struct blg_sk_out {
     uint64_t* hash;
     uint64_t* id;       /* only with BLG_F_EMIT_ID: ordinal of the minimizer's m-mer among the valid m-mers of its sequence */
     void* owner;
+    /* only with BLG_F_RUNS */
+    uint64_t n_runs;            /* out (required size on BLG_E_CAPACITY) */
+    uint64_t run_capacity;      /* in, with caller arrays */
+    uint64_t* run_first_record;
+    uint64_t* run_start;
 } blg_sk_out;
 
 typedef struct blg_stats {

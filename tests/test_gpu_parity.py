@@ -613,3 +613,36 @@ def test_compact_records_pos32_pipelined(gpu):
         assert np.array_equal(a[key], b[key]), key
     st = gpu.stats()
     assert st["bytes_d2h"] < a["n"] * 14 + 4096
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (63, 31), (40, 9), (8, 4)])
+def test_runs_layout(gpu, oracle, k, m):
+    """BLG_F_RUNS: 10-byte records + the run list; positions rebuilt from the runs equal the 64-bit layout (plain host path)."""
+    rng = np.random.default_rng(k * 5 + m)
+    s = rand_seq(rng, 200_000, 0.0008, 0.02)
+    lens = rng.integers(0, 3000, size=120)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    offs = np.concatenate([offs[offs < s.size], [s.size]]).astype(np.uint64)
+    for canon in (False, True):
+        for o in (None, offs):
+            a = gpu.super_kmers(s, k, m, 42, canon, offsets=o, want_hash=False)
+            b = gpu.super_kmers(s, k, m, 42, canon, offsets=o, want_hash=False, runs=True)
+            assert a["n"] == b["n"] and 0 < b["n_runs"] <= b["n"]
+            for key in ("value", "mm_start", "sk_start", "size", "mm_pos"):
+                assert np.array_equal(a[key], b[key]), (key, k, m)
+    clean = rand_seq(rng, 50_000)
+    assert gpu.super_kmers(clean, k, m, 42, True, want_hash=False, runs=True)["n_runs"] == 1
+    assert gpu.super_kmers(np.zeros(0, np.uint8), k, m, 42, True, want_hash=False, runs=True)["n"] == 0
+
+
+def test_runs_layout_pipelined(gpu):
+    """The chunked host path with BLG_F_RUNS: 10 bytes per record over PCIe."""
+    rng = np.random.default_rng(78)
+    s = rand_seq(rng, 20_000_000, 0.00005)
+    a = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False)
+    b = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False, runs=True)
+    st = gpu.stats()
+    assert a["n"] == b["n"] > 2_000_000 and b["n_runs"] > 100
+    for key in ("value", "mm_start", "size", "mm_pos"):
+        assert np.array_equal(a[key], b[key]), key
+    assert st["bytes_d2h"] < a["n"] * 10 + b["n_runs"] * 16 + 4096
