@@ -36,6 +36,7 @@ struct BlockPool {
     struct Block { void* p; size_t bytes; };
     std::vector<Block> free_blocks;
     size_t cached = 0, limit = 0;
+    bool device = false;
     void* take(size_t bytes, size_t* got)
     {
         int best = -1;
@@ -48,9 +49,15 @@ struct BlockPool {
         free_blocks.erase(free_blocks.begin() + best);
         return p;
     }
+    // keeps the block unless it is larger than the whole pool; the blocks that have been lying here longest make room for it
     bool give(void* p, size_t bytes)
     {
-        if (cached + bytes > limit) return false;
+        if (bytes > limit) return false;
+        while (cached + bytes > limit && !free_blocks.empty()) {
+            if (device) cudaFree(free_blocks.front().p); else cudaFreeHost(free_blocks.front().p);
+            cached -= free_blocks.front().bytes;
+            free_blocks.erase(free_blocks.begin());
+        }
         free_blocks.push_back({p, bytes});
         cached += bytes;
         return true;
@@ -68,6 +75,7 @@ struct blg_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;   // upload / download streams of the pipelined host path
     cudaEvent_t ev_in[16] = {};
+    cudaEvent_t ev_dl[2] = {};                      // k-mer pipeline: the download of the piece that used device buffer b is done
     int pipe_first_div = 4;      // first pipeline piece = a regular piece / this
     int pipe_chunk_m = 12;       // k-mer starts per pipeline chunk, in Mi
     bool async_call = false;                 // BLG_F_ASYNC: run_sk_once only enqueues
@@ -722,10 +730,12 @@ int blg_create(int device, blg_ctx** out)
     }
     c->stream = c->own_stream;
     c->pool_dev.limit = (size_t)24 << 30;        // B200: 180 GB of HBM
+    c->pool_dev.device = true;
     c->pool_pinned.limit = (size_t)2 << 30;
     bool ok = cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreateWithFlags(&c->ev_dl[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
     *out = c;
     return BLG_OK;
@@ -746,6 +756,7 @@ int blg_destroy(blg_ctx* c)
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     for (cudaEvent_t e : c->ev_in) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_dl) if (e) cudaEventDestroy(e);
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_out) cudaStreamDestroy(c->s_out);
     delete c;
@@ -1027,6 +1038,109 @@ void blg_free_fastx_out(blg_ctx* c, blg_fastx_out* out)
 }
 
 namespace {
+// Host input, host output, 8 Mi k-mer starts or more: pieces of pipe_chunk_m Mi starts whose upload (s_in), kernel (stream) and
+// record download (s_out) overlap. Two device piece buffers alternate, so the device holds two pieces of output rather than
+// one record slot per k-mer start of the whole input. `est` sizes library-owned host arrays; when a piece does not fit what
+// is left of them (or of the caller's capacity) *done_flag stays 0 and the caller takes the plain path, which knows the count.
+int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const KmerArgs& proto, uint64_t est,
+                    blg_kmer_out* out, int* done_flag)
+{
+    *done_flag = 0;
+    const int k = proto.k;
+    const bool wide = k > 32;
+    const uint64_t nwin = n - (size_t)k + 1;
+    if (nwin < (8u << 20) || c->staged) return BLG_OK;
+    int rc;
+    if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
+    const uint64_t cap = out->capacity > 0 ? out->capacity : est;
+    int nch = (int)(nwin / ((uint64_t)c->pipe_chunk_m << 20));
+    nch = nch < 2 ? 2 : (nch > PIPE_MAX ? PIPE_MAX : nch);
+    uint64_t cut[PIPE_MAX + 1];
+    size_t up[PIPE_MAX + 1];
+    const uint64_t first = nwin / nch / (uint64_t)c->pipe_first_div;
+    uint64_t piece = 0;
+    for (int i = 0; i <= nch; ++i) {
+        cut[i] = i == nch ? nwin : i == 0 ? 0 : (first + (nwin - first) * (uint64_t)(i - 1) / (nch - 1)) / 16 * 16;
+        if (i && cut[i] - cut[i - 1] > piece) piece = cut[i] - cut[i - 1];
+    }
+    if ((rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+    if ((rc = ensure(c, c->o_lo, 2 * piece * 8)) != BLG_OK || (rc = ensure(c, c->o_position, 2 * piece * 8)) != BLG_OK) return rc;
+    if (wide && (rc = ensure(c, c->o_hi, 2 * piece * 8)) != BLG_OK) return rc;
+    const unsigned long long* d_offs = nullptr;
+    if (offs) {
+        const size_t ob = (n_seq + 1) * sizeof(uint64_t);
+        if ((rc = ensure(c, c->offs, ob)) != BLG_OK) return rc;
+        CK(c, cudaMemcpyAsync(c->offs.p, offs, ob, cudaMemcpyHostToDevice, c->stream));
+        c->stats.bytes_h2d += ob;
+        d_offs = static_cast<const unsigned long long*>(c->offs.p);
+    }
+    Owner* ow = nullptr;
+    struct Guard {
+        blg_ctx* c; Owner** ow; bool armed;
+        ~Guard() { if (armed) { cudaStreamSynchronize(c->s_in); cudaStreamSynchronize(c->s_out); cudaStreamSynchronize(c->stream); free_owner(*ow); *ow = nullptr; } }
+    } guard{c, &ow, true};
+    blg_kmer_out h = *out;
+    if (out->capacity == 0) {
+        ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
+        if (!ow) return BLG_E_NOMEM;
+        h.value_hi = nullptr;
+        if ((rc = alloc_owned(c, false, cap, &h.value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.position, ow, 2)) != BLG_OK) return rc;
+        if (wide && (rc = alloc_owned(c, false, cap, &h.value_hi, ow, 1)) != BLG_OK) return rc;
+    }
+    unsigned char* d_in = static_cast<unsigned char*>(c->in.p);
+    const size_t halo = (size_t)k + 64;
+    size_t sent = 0;
+    for (int i = 0; i < nch; ++i) {
+        size_t end = i == nch - 1 ? n : (size_t)cut[i + 1] + halo;
+        end = end > n ? n : end;
+        if (i < nch - 1) end = end / 16 * 16;
+        if (end > sent) CK(c, cudaMemcpyAsync(d_in + sent, bases + sent, end - sent, cudaMemcpyHostToDevice, c->s_in));
+        CK(c, cudaEventRecord(c->ev_in[i], c->s_in));
+        sent = end > sent ? end : sent;
+        up[i] = sent;
+    }
+    c->stats.bytes_h2d += n;
+    uint64_t done = 0;
+    bool overflow = false;
+    int used[2] = {0, 0};
+    for (int i = 0, b = 0; i < nch; ++i) {
+        if (cut[i + 1] <= cut[i]) continue;
+        CK(c, cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
+        if (used[b]) CK(c, cudaStreamWaitEvent(c->stream, c->ev_dl[b], 0));    // the piece before last has left this buffer
+        KmerArgs a = proto;
+        a.bases = d_in; a.buf_lo = 0; a.buf_hi = (long long)up[i];
+        a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
+        a.win_lo = (long long)cut[i]; a.win_hi = (long long)cut[i + 1];
+        a.vec_ok = (reinterpret_cast<uintptr_t>(d_in) & 15u) == 0;
+        a.value_lo = static_cast<unsigned long long*>(c->o_lo.p) + (size_t)b * piece;
+        a.value_hi = wide ? static_cast<unsigned long long*>(c->o_hi.p) + (size_t)b * piece : nullptr;
+        a.position = static_cast<unsigned long long*>(c->o_position.p) + (size_t)b * piece;
+        a.capacity = piece;
+        uint64_t cnt = 0;
+        if ((rc = run_kmer_once(c, a, &cnt)) != BLG_OK) return rc;      // returns after the kernel: the count is known
+        if (cnt > cap - done) { overflow = true; break; }
+        if (cnt) {
+            CK(c, cudaMemcpyAsync(h.value_lo + done, a.value_lo, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+            if (wide) CK(c, cudaMemcpyAsync(h.value_hi + done, a.value_hi, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+            if (h.position) CK(c, cudaMemcpyAsync(h.position + done, a.position, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
+            c->stats.bytes_d2h += cnt * ((wide ? 16 : 8) + (h.position ? 8 : 0));
+            CK(c, cudaEventRecord(c->ev_dl[b], c->s_out));
+            used[b] = 1;
+            b ^= 1;
+        }
+        done += cnt;
+    }
+    CK(c, cudaStreamSynchronize(c->s_out));
+    CK(c, cudaStreamSynchronize(c->s_in));
+    if (overflow) return BLG_OK;       // the guard gives library arrays back; the plain path reports the exact count
+    guard.armed = false;
+    if (out->capacity == 0) { *out = h; out->owner = ow; out->capacity = 0; }
+    out->count = done;
+    c->stats.n_records = done;
+    *done_flag = 1;
+    return BLG_OK;
+}
+
 // sync_s < 0: every valid k-mer (blg_kmers); else the closed-syncmer filter with m-mers of p->m bases (blg_syncmers);
 // threshold != nullptr: the hash-threshold filter (blg_hash_sampled_kmers)
 int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
@@ -1053,17 +1167,27 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         return BLG_OK;
     }
     int rc;
+    KmerArgs a{};
+    a.k = k; a.canonical = p->canonical ? 1 : 0;
+    if (sync_s >= 0) { a.sync_on = 1; a.sync_m = p->m; a.sync_s = sync_s; a.sync_e = sync_e; }
+    if (threshold) { a.sync_on = 2; a.samp_s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL; a.samp_threshold = *threshold; }
+    if (!(p->flags & (BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT))) {
+        // expected number of kept k-mers (+25 % and a constant): every start; two window offsets out of k - m + 1; the sampled fraction
+        uint64_t est = nwin;
+        if (sync_s >= 0) est = (uint64_t)((double)nwin * (sync_s == sync_e ? 1.0 : 2.0) / (double)(k - p->m + 1) * 1.25) + 65536;
+        if (threshold) est = (uint64_t)((double)nwin * ((double)*threshold / 18446744073709551616.0) * 1.25) + 65536;
+        if (est > nwin) est = nwin;
+        int produced = 0;
+        if ((rc = kmers_pipelined(c, bases, n, offs, n_seq, a, est, out, &produced)) != BLG_OK) return rc;
+        if (produced) { c->stats.total_ms = tm.ms(); return BLG_OK; }
+    }
     const unsigned char* d_bases = nullptr;
     const unsigned long long* d_offs = nullptr;
     if ((rc = place_input(c, bases, n, offs, n_seq, p->flags, &d_bases, &d_offs)) != BLG_OK) return rc;
-    KmerArgs a{};
     a.bases = d_bases; a.buf_lo = 0; a.buf_hi = (long long)n;
     a.seq_offsets = d_offs; a.n_seq = (long long)n_seq;
     a.win_lo = 0; a.win_hi = (long long)nwin;
-    a.k = k; a.canonical = p->canonical ? 1 : 0;
     a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
-    if (sync_s >= 0) { a.sync_on = 1; a.sync_m = p->m; a.sync_s = sync_s; a.sync_e = sync_e; }
-    if (threshold) { a.sync_on = 2; a.samp_s8 = (unsigned long long)(uint32_t)p->seed ^ 8ULL; a.samp_threshold = *threshold; }
     uint64_t total = 0;
     if (dev_out && out->capacity > 0) {
         a.value_lo = reinterpret_cast<unsigned long long*>(out->value_lo);
@@ -1235,6 +1359,42 @@ int blg_sorted_unique_kmers(blg_ctx* c, const char* bases, size_t n, const uint6
     return BLG_OK;
 }
 
+namespace {
+// |A u B| of two sorted distinct device lists = distinct values of their concatenation (|A n B| = |A| + |B| - |A u B|): one more sort
+int union_of_sorted(blg_ctx* c, const unsigned long long* d1, uint64_t c1, const unsigned long long* d2, uint64_t c2, int bits, uint64_t* uni_out,
+                    blg_stats* acc)
+{
+    *uni_out = 0;
+    const uint64_t tot = c1 + c2;
+    if (tot == 0) return BLG_OK;
+    int rc;
+    Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
+    auto fail = [&](int code) { free_owner(ow); return code; };
+    if (!ow) return BLG_E_NOMEM;
+    unsigned long long *cat = nullptr, *tmp = nullptr, *flags = nullptr, *uq = nullptr;
+    if ((rc = alloc_owned(c, true, tot, &cat, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, tot, &tmp, ow, 1)) != BLG_OK ||
+        (rc = alloc_owned(c, true, tot, &flags, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, tot, &uq, ow, 3)) != BLG_OK) return fail(rc);
+    if ((rc = ensure(c, c->rank, sort_scratch_bytes(tot) + 64)) != BLG_OK) return fail(rc);
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(tot) / 8 * 8);
+    int launches = 0;
+    cudaEventRecord(c->ev0, c->stream);
+    bool ok = (c1 == 0 || cudaMemcpyAsync(cat, d1, c1 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess) &&
+              (c2 == 0 || cudaMemcpyAsync(cat + c1, d2, c2 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess);
+    ok = ok && radix_sort_u64(cat, tmp, tot, bits, c->rank.p, c->stream, &launches) == cudaSuccess;
+    ok = ok && unique_sorted_u64(cat, tot, flags, c->rank.p, uq, d_tot, c->stream, &launches) == cudaSuccess;
+    cudaEventRecord(c->ev1, c->stream);
+    unsigned long long u = 0;
+    ok = ok && cudaMemcpyAsync(&u, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
+    if (!ok) { c->err = "jaccard merge failed"; return fail(BLG_E_CUDA); }
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) acc->kernel_ms += ms;
+    acc->kernel_launches += launches;
+    *uni_out = u;
+    free_owner(ow);
+    return BLG_OK;
+}
+}  // namespace
+
 int blg_kmer_jaccard(blg_ctx* c, const char* b1, size_t n1, const uint64_t* o1, size_t s1, const char* b2, size_t n2, const uint64_t* o2, size_t s2,
                      const blg_params* p, blg_jaccard_out* out)
 {
@@ -1248,38 +1408,84 @@ int blg_kmer_jaccard(blg_ctx* c, const char* b1, size_t n1, const uint64_t* o1, 
     int rc = sorted_unique_device(c, b1, n1, o1, s1, p, &w1, &d1, &c1, &acc);
     if (rc != BLG_OK) return rc;
     if ((rc = sorted_unique_device(c, b2, n2, o2, s2, p, &w2, &d2, &c2, &acc)) != BLG_OK) { free_owner(w1); return rc; }
-    // |A u B| = distinct values of the concatenation of the two distinct lists; |A n B| = |A| + |B| - |A u B|
-    const uint64_t tot = c1 + c2;
     uint64_t uni = 0;
-    if (tot) {
-        Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
-        auto fail = [&](int code) { free_owner(ow); free_owner(w1); free_owner(w2); return code; };
-        if (!ow) return fail(BLG_E_NOMEM);
-        unsigned long long *cat = nullptr, *tmp = nullptr, *flags = nullptr, *uq = nullptr;
-        if ((rc = alloc_owned(c, true, tot, &cat, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, tot, &tmp, ow, 1)) != BLG_OK ||
-            (rc = alloc_owned(c, true, tot, &flags, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, tot, &uq, ow, 3)) != BLG_OK) return fail(rc);
-        if ((rc = ensure(c, c->rank, sort_scratch_bytes(tot) + 64)) != BLG_OK) return fail(rc);
-        unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(tot) / 8 * 8);
-        int launches = 0;
-        cudaEventRecord(c->ev0, c->stream);
-        bool ok = (c1 == 0 || cudaMemcpyAsync(cat, d1, c1 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess) &&
-                  (c2 == 0 || cudaMemcpyAsync(cat + c1, d2, c2 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess);
-        ok = ok && radix_sort_u64(cat, tmp, tot, 2 * p->k, c->rank.p, c->stream, &launches) == cudaSuccess;
-        ok = ok && unique_sorted_u64(cat, tot, flags, c->rank.p, uq, d_tot, c->stream, &launches) == cudaSuccess;
-        cudaEventRecord(c->ev1, c->stream);
-        unsigned long long u = 0;
-        ok = ok && cudaMemcpyAsync(&u, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
-        if (!ok) { c->err = "jaccard merge failed"; return fail(BLG_E_CUDA); }
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) acc.kernel_ms += ms;
-        acc.kernel_launches += launches;
-        uni = u;
-        free_owner(ow);
-    }
+    if ((rc = union_of_sorted(c, d1, c1, d2, c2, 2 * p->k, &uni, &acc)) != BLG_OK) { free_owner(w1); free_owner(w2); return rc; }
     free_owner(w1); free_owner(w2);
     out->size1 = c1; out->size2 = c2; out->union_size = uni; out->intersection = c1 + c2 - uni;
     acc.total_ms = tm.ms();
     c->stats = acc;
+    return BLG_OK;
+}
+
+// ---- device-resident building blocks of the multi-GPU form of the sort / unique / Jaccard row (biolib_b200/multi_gpu.py) ----------------
+int blg_sort_unique_u64(blg_ctx* c, uint64_t* d_keys, size_t n, int key_bits, uint64_t* count)
+{
+    if (!c || !count || (n && !d_keys) || key_bits < 1 || key_bits > 64) return BLG_E_INVALID;
+    Timer tm;
+    c->stats = blg_stats{};
+    c->err.clear();
+    *count = 0;
+    CK(c, cudaSetDevice(c->device));
+    if (n == 0) return BLG_OK;
+    int rc;
+    Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
+    auto fail = [&](int code) { free_owner(ow); return code; };
+    if (!ow) return BLG_E_NOMEM;
+    unsigned long long *tmp = nullptr, *flags = nullptr, *uq = nullptr;
+    if ((rc = alloc_owned(c, true, n, &tmp, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, n, &flags, ow, 1)) != BLG_OK ||
+        (rc = alloc_owned(c, true, n, &uq, ow, 2)) != BLG_OK) return fail(rc);
+    if ((rc = ensure(c, c->rank, sort_scratch_bytes(n) + 64)) != BLG_OK) return fail(rc);
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(n) / 8 * 8);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(d_keys);
+    int launches = 0;
+    cudaEventRecord(c->ev0, c->stream);
+    bool ok = radix_sort_u64(keys, tmp, n, key_bits, c->rank.p, c->stream, &launches) == cudaSuccess;
+    ok = ok && unique_sorted_u64(keys, n, flags, c->rank.p, uq, d_tot, c->stream, &launches) == cudaSuccess;
+    cudaEventRecord(c->ev1, c->stream);
+    unsigned long long u = 0;
+    ok = ok && cudaMemcpyAsync(&u, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
+    ok = ok && (u == 0 || cudaMemcpyAsync(keys, uq, u * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess) && cudaStreamSynchronize(c->stream) == cudaSuccess;
+    if (!ok) { c->err = "sort / unique failed"; return fail(BLG_E_CUDA); }
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.kernel_ms = ms;
+    c->stats.kernel_launches = launches;
+    c->stats.n_records = u;
+    free_owner(ow);
+    *count = u;
+    c->stats.total_ms = tm.ms();
+    return BLG_OK;
+}
+
+int blg_sorted_sets_jaccard(blg_ctx* c, const uint64_t* d_a, size_t na, const uint64_t* d_b, size_t nb, int key_bits, blg_jaccard_out* out)
+{
+    if (!c || !out || (na && !d_a) || (nb && !d_b) || key_bits < 1 || key_bits > 64) return BLG_E_INVALID;
+    Timer tm;
+    blg_stats acc{};
+    c->err.clear();
+    *out = blg_jaccard_out{};
+    CK(c, cudaSetDevice(c->device));
+    uint64_t uni = 0;
+    int rc = union_of_sorted(c, reinterpret_cast<const unsigned long long*>(d_a), na, reinterpret_cast<const unsigned long long*>(d_b), nb, key_bits, &uni, &acc);
+    if (rc != BLG_OK) return rc;
+    out->size1 = na; out->size2 = nb; out->union_size = uni; out->intersection = na + nb - uni;
+    acc.total_ms = tm.ms();
+    c->stats = acc;
+    return BLG_OK;
+}
+
+int blg_lower_bound_u64(blg_ctx* c, const uint64_t* d_sorted, size_t n, const uint64_t* queries, size_t nq, uint64_t* out_index)
+{
+    if (!c || (n && !d_sorted) || (nq && (!queries || !out_index))) return BLG_E_INVALID;
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    if (nq == 0) return BLG_OK;
+    int rc = ensure(c, c->rank, 2 * nq * 8);
+    if (rc != BLG_OK) return rc;
+    unsigned long long* d_q = static_cast<unsigned long long*>(c->rank.p);
+    CK(c, cudaMemcpyAsync(d_q, queries, nq * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(c, lower_bound_u64(reinterpret_cast<const unsigned long long*>(d_sorted), n, d_q, nq, d_q + nq, c->stream));
+    CK(c, cudaMemcpyAsync(out_index, d_q + nq, nq * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
     return BLG_OK;
 }
 

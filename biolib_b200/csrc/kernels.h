@@ -168,6 +168,9 @@ cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long
                             unsigned long long n_seq, unsigned long long n_bases, unsigned long long* flags, void* scratch, unsigned long long* tmp,
                             unsigned long long* d_total, cudaStream_t stream, int* launches);
 
+cudaError_t lower_bound_u64(const unsigned long long* keys, unsigned long long n, const unsigned long long* d_queries, unsigned long long nq,
+                            unsigned long long* d_out, cudaStream_t stream);
+
 // BLG_F_RUNS: the maximal runs of records in which every record starts where the previous one ended
 size_t runs_scratch_bytes(unsigned long long n);
 cudaError_t runs_launch(const unsigned long long* mm_start, const unsigned char* mm_pos, const unsigned char* size, unsigned long long n, void* scratch,

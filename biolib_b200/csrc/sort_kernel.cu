@@ -256,4 +256,26 @@ cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long
     return e != cudaSuccess ? e : cudaGetLastError();
 }
 
+// index of the first key >= q[i] in a sorted array, one thread per query (the split points of a key-range partition: a handful of queries)
+__global__ void lower_bound_kernel(const u64* __restrict__ keys, u64 n, const u64* __restrict__ q, u64 nq, u64* __restrict__ out)
+{
+    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const u64 v = q[i];
+    u64 lo = 0, hi = n;
+    while (lo < hi) {
+        const u64 mid = lo + (hi - lo) / 2;
+        if (keys[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    out[i] = lo;
+}
+
+cudaError_t lower_bound_u64(const unsigned long long* keys, unsigned long long n, const unsigned long long* d_queries, unsigned long long nq,
+                            unsigned long long* d_out, cudaStream_t stream)
+{
+    if (nq == 0) return cudaSuccess;
+    lower_bound_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, stream>>>(keys, n, d_queries, nq, d_out);
+    return cudaGetLastError();
+}
+
 }  // namespace blg

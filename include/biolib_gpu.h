@@ -229,6 +229,21 @@ int blg_kmer_jaccard(blg_ctx* ctx, const char* bases1, size_t n1, const uint64_t
                      blg_jaccard_out* out);
 
 /*
+ * The same row across several GPUs (SURVEY.md 8(e) + 8(f) rank 3; biolib_b200/multi_gpu.py drives it, one process per GPU): every
+ * rank extracts, sorts and deduplicates its share of the input (blg_sorted_unique_kmers with BLG_F_DEVICE_OUTPUT), the ranks agree on
+ * key-range splitters, exchange the ranges (one all-to-all over NVLink: the path's one real exchange step), and each rank merges what it
+ * received. These are the device-resident pieces of that, all on the context's stream, all pointers device pointers unless stated:
+ *   blg_sort_unique_u64      d_keys[0, n) -> sorted distinct keys in d_keys[0, *count) (in place). key_bits = number of low bits the
+ *                            keys can differ in (2k for k-mer values)
+ *   blg_sorted_sets_jaccard  algorithm::jaccard (include/jaccard.hpp:8-38) of two sorted distinct lists
+ *   blg_lower_bound_u64      for each of nq HOST queries the index of the first key >= it in the sorted device array (HOST out_index):
+ *                            where a rank's sorted list is cut for the exchange
+ */
+int blg_sort_unique_u64(blg_ctx* ctx, uint64_t* d_keys, size_t n, int key_bits, uint64_t* count);
+int blg_sorted_sets_jaccard(blg_ctx* ctx, const uint64_t* d_a, size_t na, const uint64_t* d_b, size_t nb, int key_bits, blg_jaccard_out* out);
+int blg_lower_bound_u64(blg_ctx* ctx, const uint64_t* d_sorted, size_t n, const uint64_t* queries, size_t nq, uint64_t* out_index);
+
+/*
  * Super-k-mer payloads grouped by minimizer bucket (what super-k-mers are for -- partitioned k-mer
  * counting, de Bruijn graph construction). The records of blg_super_kmers, reordered STABLY by
  *   bucket = hash64(value, p->seed) % n_buckets          (hash::hash64::hash, include/hash.hpp:55-59)

@@ -646,3 +646,36 @@ def test_runs_layout_pipelined(gpu):
     for key in ("value", "mm_start", "size", "mm_pos"):
         assert np.array_equal(a[key], b[key]), key
     assert st["bytes_d2h"] < a["n"] * 10 + b["n_runs"] * 16 + 4096
+
+
+@pytest.mark.parametrize("k,canon,multi", [(31, True, False), (63, True, True), (21, False, True)])
+def test_kmers_pipelined_host_path(gpu, oracle, k, canon, multi):
+    """blg_kmers / blg_syncmers / blg_hash_sampled_kmers above 8 Mi k-mer starts: upload, kernel and download overlap piece by
+    piece through two alternating device buffers; the result equals the oracle's (and the small-input path's) records."""
+    import biolib_b200
+    from biolib_b200 import synth
+    n = 30_000_000
+    s = synth.generate(79 + k, n).copy()
+    rng = np.random.default_rng(k)
+    for p_ in rng.integers(0, n - 100, 300):
+        s[p_:p_ + int(rng.integers(1, 40))] = ord("N")
+    offs = None
+    if multi:
+        offs = np.concatenate([[0], np.sort(rng.choice(np.arange(1, n), size=2000, replace=False)), [n]]).astype(np.uint64)
+    g = gpu.kmers(s, k, canon, offsets=offs)
+    st = gpu.stats()
+    assert st["kernel_launches"] >= 2 and st["bytes_h2d"] >= n
+    o = oracle.kmers(s, k, canon, offsets=offs)
+    assert len(g["lo"]) == len(o["lo"])
+    for key in ("lo", "hi", "pos"):
+        assert np.array_equal(g[key], o[key]), key
+    if k <= 32:
+        m = k - 12
+        gs = gpu.syncmers(s, k, m, 0, k - m, canon, offsets=offs)
+        assert gpu.stats()["kernel_launches"] >= 2
+        os_ = oracle.syncmers(s, k, m, 0, k - m, canon, offsets=offs)
+        assert np.array_equal(gs["lo"], os_["lo"]) and np.array_equal(gs["pos"], os_["pos"])
+        thr = gpu.hash_sampler_threshold(0.05)
+        gh = gpu.hash_sampled_kmers(s, k, 42, 0.05, canon, offsets=offs)
+        oh = oracle.hash_sampled_kmers(s, k, 42, thr, canon, offsets=offs)
+        assert np.array_equal(gh["lo"], oh["lo"]) and np.array_equal(gh["pos"], oh["pos"])

@@ -70,6 +70,31 @@ def main():
     out["packed_input_e2e"] = {"bases": n, "ascii_ms": dt_a * 1e3, "packed_ms": dt_p * 1e3, "ascii_h2d": st_a["bytes_h2d"], "packed_h2d": st_p["bytes_h2d"],
                                "d2h": st_p["bytes_d2h"], "note": "pageable numpy buffers, library-allocated pinned outputs, incl. the Python copy of the results"}
 
+    # ---- the k-mer entry points end to end: pinned host bases in, library-owned pinned (value, position) arrays out
+    hp = ctx.host_alloc(n)
+    np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(n,))[:] = s
+    pk = biolib_b200.context.Params(k=31, m=19, canonical=1, flags=0, seed=42)
+
+    def kmer_call(which):
+        o = _capi.KmerOut()
+        if which == "kmers":
+            st = ctx.L.blg_kmers(ctx.h, hp, n, None, 0, C.byref(pk), C.byref(o))
+        elif which == "syncmers":
+            st = ctx.L.blg_syncmers(ctx.h, hp, n, None, 0, C.byref(pk), 0, 12, C.byref(o))
+        else:
+            st = ctx.L.blg_hash_sampled_kmers(ctx.h, hp, n, None, 0, C.byref(pk), ctx.hash_sampler_threshold(0.1), C.byref(o))
+        assert st == 0, st
+        cnt = o.count
+        ctx.L.blg_free_kmer_out(ctx.h, C.byref(o))
+        return cnt
+    for which in ("kmers", "syncmers", "hash_sampled"):
+        kmer_call(which)
+        dt, cnt = timed(lambda: kmer_call(which))
+        st = ctx.stats()
+        out[which + "_e2e_k31"] = {"bases": n, "records": int(cnt), "ms": dt * 1e3, "Gbases_per_s": n / dt / 1e9, "h2d": st["bytes_h2d"], "d2h": st["bytes_d2h"],
+                                   "kernel_ms_all": st["kernel_ms"], "kernel_launches": st["kernel_launches"]}
+    ctx.host_free(hp)
+
     # ---- payloads, device output
     p = biolib_b200.context.Params(k=31, m=19, canonical=1, flags=_capi.F_DEVICE_INPUT | _capi.F_DEVICE_OUTPUT, seed=42)
     d_s = torch.from_numpy(s).cuda()
