@@ -353,6 +353,31 @@ def run_extras(torch, dist, ctx, dev, flush, world, rank):
     out["config3_reads150_nruns"] = {"scaling": "strong", "n_gpus": world, "bases": bases, "records": rec, "kernel_ms_max_over_ranks": ms,
                                      "Gbases_per_s": bases / ms / 1e6, "reads": batches * per_batch,
                                      "note": "32 batches of 1 M reads (4.8 Gbp) of the 100 M-read configuration, 32 / N batches per rank"}
+    del run
+    torch.cuda.empty_cache()
+    # ---- the reference's downstream pipeline (tests/test_jaccard.cpp: k-mers -> sort -> unique -> Jaccard) over two related genomes of
+    # 200 Mbp, cut over the ranks by k-mer start: local sort + unique, all-to-all by key range over NVLink, merge, per-range Jaccard
+    from biolib_b200 import multi_gpu as mg
+    n, k = 200_000_000, 31
+    lo, hi = mg.kmer_chunk(n, k, world, rank)
+    s1, s2 = synth.related_genomes_slice(lo, hi)
+    d1, d2 = torch.from_numpy(s1).to(dev), torch.from_numpy(s2).to(dev)
+    ops = mg.CudaKmerOps(ctx, torch, dev)
+    best, res = None, None
+    for _ in range(3):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        res = mg.distributed_jaccard(ops, dist if world > 1 else None, d1, d2, k, True)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) * 1e3
+        best = dt if best is None else min(best, dt)
+    ms, _, _ = reduce(best, 0, 0)
+    out["jaccard_k31_two_200mbp_genomes"] = {"scaling": "strong", "n_gpus": world, "kmers": 2 * (n - k + 1), "ms_max_over_ranks": ms,
+                                             "G_kmers_per_s": 2 * (n - k + 1) / ms / 1e6, "intersection": res["intersection"], "union": res["union"],
+                                             "bytes_over_nvlink": res["bytes_exchanged"],
+                                             "timing": "wall clock around the whole call (extraction, sorts, splitter agreement, all-to-all, merge, all-reduce), best of 3"}
     return out
 
 

@@ -111,9 +111,16 @@ class CudaKmerOps:
         return self.torch.tensor(list(values), dtype=self.torch.int64, device=self.device)
 
 
+def _world(dist, group=None) -> int:
+    """dist = None (or an uninitialised torch.distributed) means a single process: every step degenerates to the local one."""
+    return dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
+
+
 def agree_on_splitters(ops, dist, sorted_lists, group=None) -> np.ndarray:
     """Step 2: a regular sample of every rank's sorted lists -> the same world - 1 splitters on every rank."""
-    world = dist.get_world_size(group)
+    world = _world(dist, group)
+    if world == 1:
+        return np.zeros(0, np.uint64)
     mine = np.concatenate([ops.sample(t, sample_positions(len(t))) for t in sorted_lists]) if sorted_lists else np.zeros(0, np.uint64)
     gathered = [None] * world
     dist.all_gather_object(gathered, mine, group=group)
@@ -123,8 +130,11 @@ def agree_on_splitters(ops, dist, sorted_lists, group=None) -> np.ndarray:
 def exchange_by_key_range(ops, dist, local_sorted, splitters: np.ndarray, bits: int, group=None):
     """Steps 3 and 4 for one set: cut at the splitters, all-to-all, merge. Returns (this rank's key range of the global distinct
     set as a sorted tensor, keys sent, keys received)."""
-    world = dist.get_world_size(group)
+    world = _world(dist, group)
     n = len(local_sorted)
+    if world == 1:
+        return local_sorted, 0, 0                      # one rank owns every key: its sorted distinct list is the result
+    rank = dist.get_rank(group)
     cuts = np.concatenate([[0], ops.lower_bound(local_sorted, splitters), [n]]).astype(np.int64)
     send = np.diff(cuts)
     assert send.min() >= 0 and int(send.sum()) == n
@@ -134,7 +144,8 @@ def exchange_by_key_range(ops, dist, local_sorted, splitters: np.ndarray, bits: 
     recv = [int(x) for x in recv_t.tolist()]
     inbox = ops.empty(sum(recv))
     dist.all_to_all_single(inbox, local_sorted, recv, [int(x) for x in send], group=group)   # the keys themselves
-    return ops.sort_unique(inbox, bits), n, sum(recv)
+    # keys that crossed a link: everything but the piece a rank keeps for itself
+    return ops.sort_unique(inbox, bits), n - int(send[rank]), sum(recv) - recv[rank]
 
 
 def distributed_sorted_unique(ops, dist, bases, k: int, canonical: bool, offsets=None, group=None):
@@ -145,7 +156,8 @@ def distributed_sorted_unique(ops, dist, bases, k: int, canonical: bool, offsets
     spl = agree_on_splitters(ops, dist, [local], group)
     part, sent, received = exchange_by_key_range(ops, dist, local, spl, bits, group)
     tot = ops.counts_tensor([len(part)])
-    dist.all_reduce(tot, op=dist.ReduceOp.SUM, group=group)
+    if _world(dist, group) > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM, group=group)
     return {"part": part, "total": int(tot[0]), "splitters": spl, "sent": sent, "received": received, "local_distinct": len(local)}
 
 
@@ -159,7 +171,8 @@ def distributed_jaccard(ops, dist, bases1, bases2, k: int, canonical: bool, offs
     pb, sb, rb = exchange_by_key_range(ops, dist, b, spl, bits, group)
     inter, union, n1, n2 = ops.set_sizes(pa, pb, bits)
     t = ops.counts_tensor([inter, union, n1, n2, sa + sb, ra + rb])
-    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    if _world(dist, group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
     inter, union, n1, n2, sent, received = (int(x) for x in t.tolist())
     return {"intersection": inter, "union": union, "size1": n1, "size2": n2, "jaccard": inter / union if union else 0.0,
             "keys_exchanged": sent, "keys_received": received, "bytes_exchanged": 8 * sent}

@@ -128,3 +128,20 @@ def mutated_long_reads(n_reads: int, seed_len: int = 46, seed_src: int = 46, see
         reads = list(ex.map(lambda i: mutate(src[starts[i]:starts[i + 1]], mutp, indelf, extp, seed_mut0 + i), range(n_reads)))
     offs = np.concatenate([[0], np.cumsum([r.size for r in reads])]).astype(np.uint64)
     return (np.concatenate(reads) if reads else np.zeros(0, np.uint8)), offs
+
+
+def related_genomes_slice(lo: int, hi: int, seed_base: int = 71, sub_rate: float = 0.02, shard_len: int = 1 << 24):
+    """Bases [lo, hi) of two related synthetic genomes: the first is the generator's stream in shards uniform(seed_base + i)
+    of shard_len bases, the second is the first with `sub_rate` random substitutions. Both the shards and the substitutions
+    are seeded per shard, so any slice of them is the same bytes however the genome is cut over ranks (the Jaccard
+    benchmark's input)."""
+    first = lo // shard_len
+    s1 = generate_sharded_parallel(seed_base + first, hi - first * shard_len, shard_len)[lo - first * shard_len:]
+    s2 = s1.copy()
+    for sh in range(first, (hi + shard_len - 1) // shard_len):
+        g = np.random.default_rng(5000 + seed_base + sh)
+        mut = np.flatnonzero(g.random(shard_len) < sub_rate) + sh * shard_len
+        sub = g.choice(np.frombuffer(b"ACGT", np.uint8), size=mut.size)
+        keep = (mut >= lo) & (mut < hi)
+        s2[mut[keep] - lo] = sub[keep]
+    return s1, s2

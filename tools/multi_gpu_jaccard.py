@@ -41,20 +41,7 @@ def main():
     ops = mg.CudaKmerOps(ctx, torch, dev)
 
     n, k = a.bases, a.k
-    shard_len = 1 << 24
-
-    def make_inputs(lo, hi):
-        """bases [lo, hi) of the two genomes: the same bytes whatever N (generator shards and substitutions are seeded per 16 Mbp shard)"""
-        first = lo // shard_len
-        s1 = synth.generate_sharded_parallel(71 + first, hi - first * shard_len, shard_len)[lo - first * shard_len:]
-        s2 = s1.copy()
-        for sh in range(first, (hi + shard_len - 1) // shard_len):
-            g = np.random.default_rng(5000 + sh)
-            mut = np.flatnonzero(g.random(shard_len) < 0.02) + sh * shard_len
-            sub = g.choice(np.frombuffer(b"ACGT", np.uint8), size=mut.size)
-            keep = (mut >= lo) & (mut < hi)
-            s2[mut[keep] - lo] = sub[keep]
-        return s1, s2
+    make_inputs = synth.related_genomes_slice
 
     lo, hi = mg.kmer_chunk(n, k, world, rank)
     s1, s2 = make_inputs(lo, hi)
