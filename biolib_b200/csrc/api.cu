@@ -192,8 +192,9 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
     SkLaunchPlan plan;
     // one kernel per (k, m): sk4 for the benchmark families (k - m = 12, 10), the general form of sk3 for every other
     // k - m >= 5, sk2 below that
-    const int gen = sk4_supported(a.k, a.m) ? 4 : sk3_supported(a.k, a.m) ? 3 : 2;
-    if (gen == 4) CK(c, sk4_plan(a, c->sm_count, &plan));
+    const int gen = a.sync_on || sk4_supported(a.k, a.m) ? 4 : sk3_supported(a.k, a.m) ? 3 : 2;
+    if (a.sync_on) CK(c, sy4_plan(a, c->sm_count, &plan));
+    else if (gen == 4) CK(c, sk4_plan(a, c->sm_count, &plan));
     else if (gen == 2) CK(c, sk2_plan(a, c->sm_count, &plan));
     else CK(c, sk3_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }
@@ -219,7 +220,7 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
         a.ticket_base = c->sk4_tickets;
         c->sk4_tickets += sk4_ticket_draws(a, plan);
         CK(c, cudaEventRecord(c->ev0, c->stream));
-        CK(c, sk4_launch(a, plan, c->stream));
+        if (a.sync_on) CK(c, sy4_launch(a, plan, c->stream)); else CK(c, sk4_launch(a, plan, c->stream));
         CK(c, cudaEventRecord(c->ev1, c->stream));
         c->stats.kernel_launches += 1;
         if (c->async_call) { *total = 0; c->async_capacity = a.capacity; return BLG_OK; }   // blg_async_count() collects
@@ -252,6 +253,18 @@ int run_sk_once(blg_ctx* c, SkArgs& a, uint64_t* total)
 
 int run_kmer_once(blg_ctx* c, KmerArgs& a, uint64_t* total)
 {
+    if (a.sync_on == 1 && sy4_supported(a.k, a.sync_m)) {
+        // closed syncmers with k - m = 12 or 10: the filter in the sk4 frame (sy4_kernel.cu); kmer2_kernel<.., SYNC> has the rest
+        SkArgs s{};
+        s.bases = a.bases; s.buf_lo = a.buf_lo; s.buf_hi = a.buf_hi;
+        s.seq_offsets = a.seq_offsets; s.n_seq = a.n_seq;
+        s.win_lo = a.win_lo; s.win_hi = a.win_hi;
+        s.k = a.k; s.m = a.sync_m; s.w = a.k - a.sync_m + 1;
+        s.canonical = a.canonical; s.s8 = 8ULL; s.vec_ok = a.vec_ok;         // minimizer_position_extractor hashes with seed 0
+        s.value = a.value_lo; s.mm_start = a.position; s.capacity = a.capacity;
+        s.sync_on = 1; s.sync_s = a.sync_s; s.sync_e = a.sync_e;
+        return run_sk_once(c, s, total);
+    }
     KmerLaunchPlan plan;
     CK(c, kmer2_plan(a, c->sm_count, &plan));
     if (a.num_tiles == 0) { *total = 0; return BLG_OK; }

@@ -46,6 +46,8 @@ struct SkArgs {
     unsigned long long* exact_tiles;   // optional counter: tiles that took the exact path (may be null); only grows
     unsigned int epoch;                // tag of this launch's scan words (22 bits, never 0): no scratch is zeroed between launches
     unsigned int ticket_base;          // value of *tile_counter when this launch starts (it only grows)
+    // syncmer filter in the sk4 frame (sy4_kernel.cu): value = kept k-mer values, mm_start = their positions (may be null)
+    int sync_on, sync_s, sync_e;
 };
 
 // position store of the record-emitting loops: 64-bit absolute, or 32-bit relative to pos_base (BLG_F_POS32)
@@ -95,6 +97,12 @@ cudaError_t sk4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
 // tickets one launch draws from the counter: one per tile plus one per warp (the draw that tells a warp to stop)
 unsigned int sk4_ticket_draws(const SkArgs& args, const SkLaunchPlan& plan);
 cudaError_t sk4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
+
+// sy4_kernel.cu: closed syncmers (blg_syncmers) for k - m = 12 or 10, k <= 32, in the same frame: sk4's 32-bit-key window minimum once per
+// strand, keep bits from the packed argmin bytes. Uses sk4's scan scratch and ticket protocol (sk4_ticket_draws applies).
+bool sy4_supported(int k, int m);
+cudaError_t sy4_plan(SkArgs& args, int sm_count, SkLaunchPlan* plan);
+cudaError_t sy4_launch(const SkArgs& args, const SkLaunchPlan& plan, cudaStream_t stream);
 
 // kmer_view: every valid k-mer as (value, position), in position order.
 struct KmerArgs {

@@ -20,9 +20,6 @@
 // A warp owns a tile end to end and never meets another warp at a barrier, as in sk3: tiles come from a ticket counter,
 // the ordered output offset from the two-level chained scan, records are written KB-1 tiles after they were computed.
 #pragma once
-#ifdef SK4_TIE_DEBUG
-#include <cstdio>
-#endif
 #include "common.cuh"
 #include "kernels.h"
 
@@ -34,9 +31,10 @@ constexpr int NT4 = 32;
 constexpr int WARPS4 = SK4_THREADS / 32;
 constexpr int PADF4 = 3;     // zero words in front of the big-endian stream
 
-template <int B, int NB, int Q = 1>
+template <int B, int NB, int Q = 1, int NP = 1>
 struct Geo4 {
     // Q: a window is suffix-of-own-block + (Q-1 whole blocks) + prefix-of-block-(b+Q): w = Q B + 1 (Q = 1: k-m = 12, 10; Q = 2: k-m = 32)
+    static constexpr int B_ = B;
     static constexpr int L = NB * B;                    // starts per lane (its span), <= 32
     static constexpr int S = NT4 * L;                   // m-mer starts hashed per tile
     static constexpr int OWN = NT4 * NB - 1 - 2 * Q;    // blocks 1 .. 32 NB - 1 - 2Q own record starts: a record reaches Q blocks
@@ -51,7 +49,8 @@ struct Geo4 {
     static constexpr int OFF_FLAG = OFF_SEQ + NROW * 4;             // int [4]
     static constexpr int PBLK = Q == 1 ? 1 : NB;                    // blocks per lane whose prefix keys another lane reads
     static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;    // uint4 [PBLK][BQ][32] (+1)  prefix keys, [block][quad][lane]
-    static constexpr int OFF_BUF = OFF_P + (PBLK * BQ * 32 + 1) * 16;
+    static constexpr int OFF_IDX2 = OFF_P + NP * (PBLK * BQ * 32 + 1) * 16;   // NP = 2 (syncmers, both strands): a second row of prefix keys
+    static constexpr int OFF_BUF = OFF_IDX2 + (NP - 1) * 32 * 32;               // and of argmin bytes, u8 [32][2][16]
     // per buffer set (tile i is written out while tiles i+1, i+2 are computed)
     static constexpr int BUF_CW = 0;                                // u32 [NWORDS + 3]  complemented codes, little-endian
     static constexpr int BUF_EW = BUF_CW + (NWORDS + 3) * 4;        // u32 [PADF4 + NWORDS + 3]  codes, big-endian words
@@ -82,27 +81,13 @@ __device__ __forceinline__ u32 make_key(u32 h, u32 mask, u32 idx)
 }
 
 // murmur3_key8 with a 32-bit s8 (the seed is 32 bits wide, hash.hpp:50): the high words of both `^= s8` / `+= s8` vanish.
-// SK4_FMA_SHIFT_MASK (development): bit n set = the n-th of the six `h ^= h >> 33` steps takes its shift from IMAD.HI on the
-// FMA pipe (hi * 2^31 >> 32) instead of SHF on the ALU pipe, the busier of the two in this kernel.
-#ifndef SK4_FMA_SHIFT_MASK
-#define SK4_FMA_SHIFT_MASK 0
-#endif
-template <int SITE>
-__device__ __forceinline__ u64 xorshift33_site(u64 h)
+// (Taking the six `h >> 33` shifts from IMAD.HI on the FMA pipe instead of SHF on the ALU pipe was measured: slower at 1, 2 and 4
+// converted sites, profiles/r02_q_fma_shift_variants.txt.)
+__device__ __forceinline__ u64 fmix64_4(u64 h)
 {
-    if ((SK4_FMA_SHIFT_MASK >> SITE) & 1) {
-        u32 hi = (u32)(h >> 32), lo = (u32)h, sh;
-        asm("mul.hi.u32 %0, %1, 0x80000000;" : "=r"(sh) : "r"(hi));
-        return ((u64)hi << 32) | (lo ^ sh);
-    }
+    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL;
+    h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL;
     return h ^ (h >> 33);
-}
-template <int SITE0>
-__device__ __forceinline__ u64 fmix64_site(u64 h)
-{
-    h = xorshift33_site<SITE0>(h); h *= 0xff51afd7ed558ccdULL;
-    h = xorshift33_site<SITE0 + 1>(h); h *= 0xc4ceb9fe1a85ec53ULL;
-    return xorshift33_site<SITE0 + 2>(h);
 }
 __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
 {
@@ -112,7 +97,7 @@ __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
     u64 h1 = k1 ^ (u64)s8;
     u64 h2 = (u64)s8;
     h1 += h2; h2 += h1;
-    h1 = fmix64_site<0>(h1); h2 = fmix64_site<3>(h2);
+    h1 = fmix64_4(h1); h2 = fmix64_4(h2);
     return h1 + h2;
 }
 
@@ -243,29 +228,54 @@ __device__ __forceinline__ u32 change_bits_from_idx4(const unsigned char* IDXB, 
     return dif;
 }
 
-// Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
-template <int B, int NB, int Q, int LW, bool CANON, bool MW>
-__device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
-                                             bool have_pre, const uint4 (&pre)[3])
+// The lane's selected windows (bit j of `start`: window j of its span) -> their slots in REC, in tile order: a window is named by
+// its slot in the argmin array, lane << 5 | block-in-lane << 4 | window-in-block. Returns the tile's count.
+template <int B>
+__device__ __forceinline__ u32 record_slots4(unsigned short* REC, u32 start, int t)
 {
-    using G = Geo4<B, NB, Q>;
+    static_assert(B <= 16, "slot numbering assumes two blocks of at most 16 windows per lane");
+    constexpr u32 MB = B >= 32 ? 0xFFFFFFFFu : ((1u << B) - 1u);
+    const u32 cnt = __popc(start);
+    u32 incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (t >= d) incl += v;
+    }
+    unsigned short* rp = REC + (incl - cnt);
+    u32 sm = B == 16 ? start : ((start & MB) | ((start >> B) << 16));
+    const u32 tag = (u32)t << 5;
+    while (sm) {
+        const int i = __ffs((int)sm) - 1;
+        sm &= sm - 1;
+        *rp++ = (unsigned short)(tag | (u32)i);
+    }
+    __syncwarp();
+    return __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// Stage one tile into buffer set b: ASCII -> the two packed streams + bad-byte bits + sequence-start bits. Returns the valid mask
+// of the lane's L windows (bit j: the k-mer at the lane's start j has k good bases of one sequence); *o_out = offset of local start 0
+// from the 16-base boundary the staged range begins at.
+template <int B, int NB, int Q, int NP>
+__device__ __forceinline__ u32 stage_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
+                                           bool have_pre, const uint4 (&pre)[3], int* o_out)
+{
+    using G = Geo4<B, NB, Q, NP>;
     static_assert(G::NWORDS <= 3 * NT4, "three prefetch registers per lane");
     constexpr int L = G::L;
     constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
     const long long g0 = a.org + tile * (long long)G::R - B;     // global position of local start 0 (block 0 = left margin)
     const long long a0 = g0 & ~15LL;                              // staged range starts on a 16-base boundary
     const int o = (int)(g0 - a0);
+    *o_out = o;
     unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
     u32* BAD = reinterpret_cast<u32*>(wsm + G::OFF_BAD);
     u32* SEQ = reinterpret_cast<u32*>(wsm + G::OFF_SEQ);
     int* FLAG = reinterpret_cast<int*>(wsm + G::OFF_FLAG);
-    uint4* P = reinterpret_cast<uint4*>(wsm + G::OFF_P);
     u32* CW = reinterpret_cast<u32*>(buf + G::BUF_CW);
     u32* EW = reinterpret_cast<u32*>(buf + G::BUF_EW);
-    unsigned char* IDXB = buf + G::BUF_IDX;
     u32* EBW = reinterpret_cast<u32*>(buf + G::BUF_EBW);
-    unsigned short* REC = reinterpret_cast<unsigned short*>(buf + G::BUF_REC);
-
     // ---- stage: ASCII -> packed streams + bad-byte bits -----------------------------------------------------------
     int anybad = 0;
     {
@@ -339,6 +349,28 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         if (seqdirty && c.k > 1) inv |= or_span_bits4<L>(SEQ, x0, c.k - 1, 1);
         V = ~inv & ML;
     }
+    return V;
+}
+
+// Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
+template <int B, int NB, int Q, int LW, bool CANON, bool MW>
+__device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
+                                             bool have_pre, const uint4 (&pre)[3])
+{
+    using G = Geo4<B, NB, Q>;
+    constexpr int L = G::L;
+    constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
+    const long long g0 = a.org + tile * (long long)G::R - B;
+    int o;
+    const u32 V = stage_tile4<B, NB, Q, 1>(a, wsm, c, b, tile, t, have_pre, pre, &o);
+    unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
+    uint4* P = reinterpret_cast<uint4*>(wsm + G::OFF_P);
+    u32* CW = reinterpret_cast<u32*>(buf + G::BUF_CW);
+    u32* EW = reinterpret_cast<u32*>(buf + G::BUF_EW);
+    unsigned char* IDXB = buf + G::BUF_IDX;
+    u32* EBW = reinterpret_cast<u32*>(buf + G::BUF_EBW);
+    unsigned short* REC = reinterpret_cast<unsigned short*>(buf + G::BUF_REC);
+    const int x0 = o + L * t;                                  // base index of this lane's first start, from the staged range's start
 
     // ---- the lane's blocks, left to right (a ROLLED loop: the unrolled body of one block is what the instruction cache holds).
     // Iteration nb hashes block nb -- one 32-bit key per m-mer start (hash bits above the index INSIDE the block), running
@@ -346,11 +378,7 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
     // pk[] (a window is suffix-of-own-block + [Q-1 whole blocks] + prefix-of-block-(b+Q)). Keys that come from a later block
     // enter with +16 per block, so the low byte of a window's minimum says where it is: bits 0-3 index in its block, bits 4-5
     // how many blocks further on.
-    constexpr u32 MB = B >= 32 ? 0xFFFFFFFFu : ((1u << B) - 1u);
     u32 tacc = 0xFFFFFFFFu;                    // min over all compares of (right key - left key): below 32 <=> a hash-part tie
-#ifdef SK4_TIE_DEBUG
-    u32 dbg_seed = 0xFFFFFFFFu, dbg_suf = 0xFFFFFFFFu, dbg_cmb = 0xFFFFFFFFu, dbg_pre = 0xFFFFFFFFu;
-#endif
     u32 dif = 0;                               // bit j: windows j and j+1 of the span have different minimizer positions
     u32 ks_prev[B], ks_prev2[B];               // keys of the last and (Q = 2) the last but one hashed block
     u32 full_prev = 0;                         // minimum key of the last hashed block (Q = 2)
@@ -367,21 +395,12 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
                 if (Q == 1) sm = kk[i];
                 else {
                     sm = fullkey + 16u; tacc = min(tacc, sm - kk[i]);
-#ifdef SK4_TIE_DEBUG
-                    dbg_seed = min(dbg_seed, sm - kk[i]);
-#endif
                     sm = min(kk[i], sm);
                 }
             } else {
                 tacc = min(tacc, sm - kk[i]);
-#ifdef SK4_TIE_DEBUG
-                dbg_suf = min(dbg_suf, sm - kk[i]);
-#endif
                 sm = min(kk[i], sm);
             }
-#ifdef SK4_TIE_DEBUG
-            dbg_cmb = min(dbg_cmb, sm - np[i]);
-#endif
             tacc = min(tacc, sm - np[i]);              // equal hash parts: what sm holds lies left of what np holds: a small difference >= 0
             mvb[i] = min(np[i] + 16u * Q, sm);
         }
@@ -458,9 +477,6 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
             if (i == 0) pm = ks[i];
             else {
                 tacc = min(tacc, ks[i] - pm);
-#ifdef SK4_TIE_DEBUG
-                dbg_pre = min(dbg_pre, ks[i] - pm);
-#endif
                 pm = min(pm, ks[i]);
             }
             pk[i] = pm;
@@ -514,15 +530,6 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         // Q = 2: lane 31 holds the last two margin blocks; no owned record reaches its windows, and what it reads as "next lane"
         // is other lanes' keys (a seed and a prefix entry can be the same key there): it never asks for a redo
         const u32 flagged = __ballot_sync(0xffffffffu, tacc < 32u && V != 0u && (Q == 1 || t < 31));
-#ifdef SK4_TIE_DEBUG
-        if (tacc < 32u && V != 0u) {
-            if (dbg_seed < 32u) atomicAdd(a.exact_tiles + 1, 1ULL);
-            if (dbg_suf < 32u) atomicAdd(a.exact_tiles + 2, 1ULL);
-            if (dbg_cmb < 32u) atomicAdd(a.exact_tiles + 3, 1ULL);
-            if (dbg_pre < 32u) atomicAdd(a.exact_tiles + 4, 1ULL);
-            if (dbg_cmb < 32u || dbg_seed < 32u) printf("tile %lld lane %d seed %u suf %u cmb %u pre %u V %x\n", tile, t, dbg_seed, dbg_suf, dbg_cmb, dbg_pre, V);
-        }
-#endif
         if (flagged) {
             __syncwarp();
             redo_windows4<B, NB, Q, CANON, MW>(CW, EW, IDXB, c, o, t, flagged);
@@ -550,28 +557,7 @@ __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm
         const u32 him = hi_j >= 32 ? 0xFFFFFFFFu : ((1u << hi_j) - 1u);
         start &= lom & him;
     }
-    const u32 cnt = __popc(start);
-    u32 incl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const u32 v = __shfl_up_sync(0xffffffffu, incl, d);
-        if (t >= d) incl += v;
-    }
-    {
-        // a record start is named by its slot in IDXB: lane << 5 | block-in-lane << 4 | window-in-block
-        static_assert(NB == 2 && B <= 16, "slot numbering assumes two blocks of at most 16 windows per lane");
-        static_assert(Q == 1 || Q == 2, "a window spans Q + 1 blocks");
-        unsigned short* rp = REC + (incl - cnt);
-        u32 sm = B == 16 ? start : ((start & MB) | ((start >> B) << 16));
-        const u32 tag = (u32)t << 5;
-        while (sm) {
-            const int i = __ffs((int)sm) - 1;
-            sm &= sm - 1;
-            *rp++ = (unsigned short)(tag | (u32)i);
-        }
-    }
-    __syncwarp();
-    return __shfl_sync(0xffffffffu, incl, 31);
+    return record_slots4<B>(REC, start, t);
 }
 
 // Record-parallel output of a finished tile from buffer set b: `n_rec` records, the first one at global index `base`.
@@ -705,21 +691,13 @@ __device__ __forceinline__ u64 tile_base_finish4(const SkArgs& a, const u64* p, 
     return g + s;
 }
 
-}  // namespace
-
-template <int B, int NB, int Q, int LW, bool CANON, bool MW>
-__global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_kernel(const SkArgs a)
+// The loop every warp runs on its own: compute tile i (`compute(b, tile, have_pre, pre)` -> its record count), publish the count,
+// write out tile i-(KB-1) from its buffer set (`emit(b, tile, n_rec, base)`). A ticket is taken only when nothing can block any
+// more before that tile is published (a warp that waits for a prefix while it holds an uncomputed tile stalls that tile's group,
+// the groups behind it, and so itself: convoys).
+template <class G, class ComputeF, class EmitF>
+__device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF compute, EmitF emit)
 {
-    using G = Geo4<B, NB, Q>;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
-
-    TileConst4 c;
-    c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = (u32)a.s8; c.keymask = a.keymask;
-    c.maskhi = MW ? (c.m == 32 ? 0xFFFFFFFFu : ((1u << (2 * c.m - 32)) - 1u)) : 0u;
-    c.masklo = MW ? 0xFFFFFFFFu : (c.m == 16 ? 0xFFFFFFFFu : ((1u << (2 * c.m)) - 1u));
-
     const long long num_groups = (a.num_tiles + GS4 - 1) / GS4;
     u32 tk = 0;
     if (t == 0) tk = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
@@ -731,9 +709,6 @@ __global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_
     bool have_pre = false;
     uint4 pre[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
     int b = 0;                          // buffer set of the tile computed in this iteration
-    // Every warp runs on its own: compute tile i, publish its count, write out tile i-(KB-1) from its buffer set.
-    // A ticket is taken only when nothing can block any more before that tile is published (a warp that waits for a
-    // prefix while it holds an uncomputed tile stalls that tile's group, the groups behind it, and so itself: convoys).
     for (;;) {
         const bool have = tile < a.num_tiles;
         // the tile to write out now: the older pending one once two are queued, or whatever is left when draining
@@ -745,7 +720,7 @@ __global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_
         u32 n_rec = 0;
         u64 old = 0;
         if (have) {
-            n_rec = compute_tile4<B, NB, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre);
+            n_rec = compute(b, tile, have_pre, pre);
             if (t == 0) {
                 st_status(&a.tile_status[tile], ((u64)tile_tag4(a) << 32) | n_rec);
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
@@ -774,11 +749,11 @@ __global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_
         if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
-        if (prev >= 0) emit_tile4<B, NB, Q, CANON, MW>(a, wsm, c, pb, prev, t, prev_n, base);
+        if (prev >= 0) emit(pb, prev, prev_n, base);
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
-            const long long ng0 = a.org + next_tile * (long long)G::R - B;
+            const long long ng0 = a.org + next_tile * (long long)G::R - G::B_;
             const long long P0 = (ng0 & ~15LL) - a.buf_lo;
             if (next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
                 have_pre = true;
@@ -795,6 +770,30 @@ __global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_
         tile = next_tile;
         b = (b + 1) % G::KB;
     }
+}
+
+__device__ __forceinline__ TileConst4 tile_const4(const SkArgs& a, bool mw)
+{
+    TileConst4 c;
+    c.w = a.w; c.m = a.m; c.k = a.k; c.s8 = (u32)a.s8; c.keymask = a.keymask;
+    c.maskhi = mw ? (c.m == 32 ? 0xFFFFFFFFu : ((1u << (2 * c.m - 32)) - 1u)) : 0u;
+    c.masklo = mw ? 0xFFFFFFFFu : (c.m == 16 ? 0xFFFFFFFFu : ((1u << (2 * c.m)) - 1u));
+    return c;
+}
+
+}  // namespace
+
+template <int B, int NB, int Q, int LW, bool CANON, bool MW>
+__global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_kernel(const SkArgs a)
+{
+    using G = Geo4<B, NB, Q>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
+    const TileConst4 c = tile_const4(a, MW);
+    tile_loop4<G>(a, t,
+                  [&](int b, long long tile, bool have_pre, const uint4 (&pre)[3]) { return compute_tile4<B, NB, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre); },
+                  [&](int b, long long tile, u32 n_rec, u64 base) { emit_tile4<B, NB, Q, CANON, MW>(a, wsm, c, b, tile, t, n_rec, base); });
 }
 
 }  // namespace blg

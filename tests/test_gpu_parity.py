@@ -679,3 +679,30 @@ def test_kmers_pipelined_host_path(gpu, oracle, k, canon, multi):
         gh = gpu.hash_sampled_kmers(s, k, 42, 0.05, canon, offsets=offs)
         oh = oracle.hash_sampled_kmers(s, k, 42, thr, canon, offsets=offs)
         assert np.array_equal(gh["lo"], oh["lo"]) and np.array_equal(gh["pos"], oh["pos"])
+
+
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (32, 20), (32, 22), (11, 1), (13, 1), (15, 5), (16, 4), (17, 7), (28, 16), (29, 17), (27, 17)])
+def test_syncmers_sk4_frame(gpu, oracle, k, m):
+    """k - m = 12 or 10: the syncmer filter in the sk4 frame (sy4_kernel.cu), every word-width variant, both strands, arbitrary offset
+    pairs, ties (low complexity: the exact redo of both rows), N runs, many sequences, k < 16 (full strand compare)."""
+    rng = np.random.default_rng(7000 + 100 * k + m)
+    w = k - m + 1
+    s = rand_seq(rng, 400_000, 0.0005, 0.03)
+    s[5000:9000] = ord("A")
+    s[20000:24000] = np.frombuffer(b"AT" * 2000, np.uint8)            # reverse-complement palindromes: strands tie
+    s[30000:33000] = np.frombuffer(b"ACG" * 1000, np.uint8)
+    lens = rng.integers(0, 2500, size=300)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    offs = np.concatenate([offs[offs < s.size], [s.size]]).astype(np.uint64)
+    for canon in (True, False):
+        for soff, eoff in ((0, w - 1), (3, 7), (w - 1, w - 1), (w, 0), (w + 5, w + 9)):
+            for o in (None, offs):
+                g = gpu.syncmers(s, k, m, soff, eoff, canon, offsets=o)
+                r = oracle.syncmers(s, k, m, soff, eoff, canon, offsets=o)
+                assert len(g["lo"]) == len(r["lo"]), (k, m, canon, soff, eoff, o is not None)
+                assert np.array_equal(g["lo"], r["lo"]) and np.array_equal(g["pos"], r["pos"]), (k, m, canon, soff, eoff)
+    for n in (0, k - 1, k, k + 1, 700, 733, 1500):
+        t = rand_seq(rng, n)
+        g = gpu.syncmers(t, k, m, 0, w - 1, True)
+        r = oracle.syncmers(t, k, m, 0, w - 1, True)
+        assert np.array_equal(g["lo"], r["lo"]) and np.array_equal(g["pos"], r["pos"]), (k, m, n)
