@@ -321,8 +321,9 @@ __device__ __forceinline__ void emit_sync4(const SkArgs& a, const unsigned char*
 
 }  // namespace
 
+// forward-only input: one row, 96 registers, 5 CTAs per SM as sk4; canonical input: two rows (and their shared memory), 4 CTAs
 template <int B, int NB, int LW, bool CANON, bool MW>
-__global__ void __launch_bounds__(SK4_THREADS, 4) sy4_kernel(const SkArgs a)
+__global__ void __launch_bounds__(SK4_THREADS, CANON ? 4 : SK4_MIN_BLOCKS) sy4_kernel(const SkArgs a)
 {
     using G = Geo4<B, NB, 1, CANON ? 2 : 1>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
