@@ -1157,8 +1157,9 @@ int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* off
 // sync_s < 0: every valid k-mer (blg_kmers); else the closed-syncmer filter with m-mers of p->m bases (blg_syncmers);
 // threshold != nullptr: the hash-threshold filter (blg_hash_sampled_kmers)
 int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const blg_params* p,
-                 int sync_s, int sync_e, blg_kmer_out* out, const uint64_t* threshold = nullptr)
+                 int sync_s, int sync_e, blg_kmer_out* out, const uint64_t* threshold = nullptr, bool want_pos = true)
 {
+    // want_pos = false (internal callers that only sort the values): library-owned device output without the position array
     if (!c || !p || !out) return BLG_E_INVALID;
     if (p->k == 0 || p->k > 64) { c->err = "need 1 <= k <= 64"; return BLG_E_INVALID; }
     if (sync_s >= 0 && (p->k > 32 || p->m == 0 || p->m > p->k)) { c->err = "syncmers need 1 <= m <= k <= 32"; return BLG_E_INVALID; }
@@ -1222,7 +1223,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
         unsigned long long *lo = nullptr, *hi = nullptr, *pos = nullptr;
-        if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
+        if ((rc = alloc_owned(c, true, cap, &lo, ow, 0)) != BLG_OK || (want_pos && (rc = alloc_owned(c, true, cap, &pos, ow, 2)) != BLG_OK)) { free_owner(ow); return rc; }
         if (wide && (rc = alloc_owned(c, true, cap, &hi, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         a.value_lo = lo; a.value_hi = hi; a.position = pos;
     } else {
@@ -1294,7 +1295,7 @@ int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t
     blg_params q = *p;
     q.flags = (p->flags & BLG_F_DEVICE_INPUT) | BLG_F_DEVICE_OUTPUT;
     blg_kmer_out km{};
-    int rc = kmers_common(c, bases, n, offs, n_seq, &q, -1, -1, &km);
+    int rc = kmers_common(c, bases, n, offs, n_seq, &q, -1, -1, &km, nullptr, (p->flags & BLG_F_REF_DROP_LAST) != 0);
     if (rc != BLG_OK) return rc;
     acc->bytes_h2d += c->stats.bytes_h2d; acc->kernel_launches += c->stats.kernel_launches; acc->kernel_ms += c->stats.kernel_ms; acc->n_bases += n;
     Owner* kow = static_cast<Owner*>(km.owner);
@@ -1304,8 +1305,8 @@ int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t
     if (!ow) return fail(BLG_E_NOMEM);
     if (cnt == 0) { free_owner(kow); *ow_out = ow; return BLG_OK; }
     unsigned long long *d_tmp = nullptr, *d_flags = nullptr, *d_uniq = nullptr;
-    if ((rc = alloc_owned(c, true, cnt, &d_uniq, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_tmp, ow, 1)) != BLG_OK ||
-        (rc = alloc_owned(c, true, cnt, &d_flags, ow, 2)) != BLG_OK) return fail(rc);
+    if ((rc = alloc_owned(c, true, cnt, &d_uniq, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, cnt, &d_tmp, ow, 1)) != BLG_OK) return fail(rc);
+    if ((p->flags & BLG_F_REF_DROP_LAST) && (rc = alloc_owned(c, true, cnt, &d_flags, ow, 2)) != BLG_OK) return fail(rc);   // the K1 filter's keep flags
     if ((rc = ensure(c, c->rank, sort_scratch_bytes(cnt) + 64)) != BLG_OK) return fail(rc);
     unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(cnt) / 8 * 8);
     unsigned long long* vals = reinterpret_cast<unsigned long long*>(km.value_lo);
@@ -1335,6 +1336,7 @@ int sorted_unique_device(blg_ctx* c, const char* bases, size_t n, const uint64_t
     free_owner(kow);
     // keep only the result array
     for (int i = 1; i <= 2; ++i) {
+        if (!ow->ptrs[i]) continue;
         if (!c->pool_dev.give(ow->ptrs[i], ow->bytes[i])) cudaFree(ow->ptrs[i]);
         ow->ptrs[i] = nullptr;
     }
@@ -1373,37 +1375,25 @@ int blg_sorted_unique_kmers(blg_ctx* c, const char* bases, size_t n, const uint6
 }
 
 namespace {
-// |A u B| of two sorted distinct device lists = distinct values of their concatenation (|A n B| = |A| + |B| - |A u B|): one more sort
-int union_of_sorted(blg_ctx* c, const unsigned long long* d1, uint64_t c1, const unsigned long long* d2, uint64_t c2, int bits, uint64_t* uni_out,
+// |A u B| of two sorted distinct device lists = |A| + |B| - |A n B|; the intersection is counted by looking one list up in the other
+int union_of_sorted(blg_ctx* c, const unsigned long long* d1, uint64_t c1, const unsigned long long* d2, uint64_t c2, int /*bits*/, uint64_t* uni_out,
                     blg_stats* acc)
 {
-    *uni_out = 0;
-    const uint64_t tot = c1 + c2;
-    if (tot == 0) return BLG_OK;
-    int rc;
-    Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
-    auto fail = [&](int code) { free_owner(ow); return code; };
-    if (!ow) return BLG_E_NOMEM;
-    unsigned long long *cat = nullptr, *tmp = nullptr, *flags = nullptr, *uq = nullptr;
-    if ((rc = alloc_owned(c, true, tot, &cat, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, tot, &tmp, ow, 1)) != BLG_OK ||
-        (rc = alloc_owned(c, true, tot, &flags, ow, 2)) != BLG_OK || (rc = alloc_owned(c, true, tot, &uq, ow, 3)) != BLG_OK) return fail(rc);
-    if ((rc = ensure(c, c->rank, sort_scratch_bytes(tot) + 64)) != BLG_OK) return fail(rc);
-    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(tot) / 8 * 8);
-    int launches = 0;
+    *uni_out = c1 + c2;
+    if (c1 == 0 || c2 == 0) return BLG_OK;
+    int rc = ensure(c, c->small, 64);
+    if (rc != BLG_OK) return rc;
+    unsigned long long* d_cnt = static_cast<unsigned long long*>(c->small.p) + 4;
+    unsigned long long inter = 0;
     cudaEventRecord(c->ev0, c->stream);
-    bool ok = (c1 == 0 || cudaMemcpyAsync(cat, d1, c1 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess) &&
-              (c2 == 0 || cudaMemcpyAsync(cat + c1, d2, c2 * 8, cudaMemcpyDeviceToDevice, c->stream) == cudaSuccess);
-    ok = ok && radix_sort_u64(cat, tmp, tot, bits, c->rank.p, c->stream, &launches) == cudaSuccess;
-    ok = ok && unique_sorted_u64(cat, tot, flags, c->rank.p, uq, d_tot, c->stream, &launches) == cudaSuccess;
+    bool ok = intersect_count_u64(d1, c1, d2, c2, d_cnt, c->stream) == cudaSuccess;
     cudaEventRecord(c->ev1, c->stream);
-    unsigned long long u = 0;
-    ok = ok && cudaMemcpyAsync(&u, d_tot, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
-    if (!ok) { c->err = "jaccard merge failed"; return fail(BLG_E_CUDA); }
+    ok = ok && cudaMemcpyAsync(&inter, d_cnt, 8, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess && cudaStreamSynchronize(c->stream) == cudaSuccess;
+    if (!ok) { c->err = "jaccard merge failed"; return BLG_E_CUDA; }
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) acc->kernel_ms += ms;
-    acc->kernel_launches += launches;
-    *uni_out = u;
-    free_owner(ow);
+    acc->kernel_launches += 1;
+    *uni_out = c1 + c2 - inter;
     return BLG_OK;
 }
 }  // namespace
@@ -1445,8 +1435,7 @@ int blg_sort_unique_u64(blg_ctx* c, uint64_t* d_keys, size_t n, int key_bits, ui
     auto fail = [&](int code) { free_owner(ow); return code; };
     if (!ow) return BLG_E_NOMEM;
     unsigned long long *tmp = nullptr, *flags = nullptr, *uq = nullptr;
-    if ((rc = alloc_owned(c, true, n, &tmp, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, n, &flags, ow, 1)) != BLG_OK ||
-        (rc = alloc_owned(c, true, n, &uq, ow, 2)) != BLG_OK) return fail(rc);
+    if ((rc = alloc_owned(c, true, n, &tmp, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, n, &uq, ow, 2)) != BLG_OK) return fail(rc);
     if ((rc = ensure(c, c->rank, sort_scratch_bytes(n) + 64)) != BLG_OK) return fail(rc);
     unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(n) / 8 * 8);
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(d_keys);
@@ -1483,6 +1472,34 @@ int blg_sorted_sets_jaccard(blg_ctx* c, const uint64_t* d_a, size_t na, const ui
     out->size1 = na; out->size2 = nb; out->union_size = uni; out->intersection = na + nb - uni;
     acc.total_ms = tm.ms();
     c->stats = acc;
+    return BLG_OK;
+}
+
+int blg_partition_by_top_byte(blg_ctx* c, const uint64_t* d_keys, size_t n, int key_bits, uint64_t* d_out, uint64_t* bin_counts)
+{
+    if (!c || !bin_counts || (n && (!d_keys || !d_out)) || key_bits < 1 || key_bits > 64) return BLG_E_INVALID;
+    Timer tm;
+    c->stats = blg_stats{};
+    c->err.clear();
+    CK(c, cudaSetDevice(c->device));
+    for (int i = 0; i < 256; ++i) bin_counts[i] = 0;
+    if (n == 0) return BLG_OK;
+    int rc = ensure(c, c->rank, sort_scratch_bytes(n) + 64 + 257 * 8);
+    if (rc != BLG_OK) return rc;
+    unsigned long long* d_start = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + sort_scratch_bytes(n) / 8 * 8 + 64);
+    unsigned long long start[257];
+    int launches = 0;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, partition_by_digit_u64(reinterpret_cast<const unsigned long long*>(d_keys), reinterpret_cast<unsigned long long*>(d_out), n,
+                                 key_bits > 8 ? key_bits - 8 : 0, c->rank.p, d_start, c->stream, &launches));
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    CK(c, cudaMemcpyAsync(start, d_start, sizeof(start), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 256; ++i) bin_counts[i] = start[i + 1] - start[i];
+    add_kernel_time(c);
+    c->stats.kernel_launches = launches;
+    c->stats.n_records = n;
+    c->stats.total_ms = tm.ms();
     return BLG_OK;
 }
 

@@ -176,6 +176,10 @@ cudaError_t drop_last_kmers(unsigned long long* values, const unsigned long long
                             unsigned long long n_seq, unsigned long long n_bases, unsigned long long* flags, void* scratch, unsigned long long* tmp,
                             unsigned long long* d_total, cudaStream_t stream, int* launches);
 
+cudaError_t partition_by_digit_u64(const unsigned long long* keys, unsigned long long* out, unsigned long long n, int shift, void* scratch,
+                                   unsigned long long* bin_start, cudaStream_t stream, int* launches);
+cudaError_t intersect_count_u64(const unsigned long long* a, unsigned long long na, const unsigned long long* b, unsigned long long nb,
+                                unsigned long long* d_count, cudaStream_t stream);
 cudaError_t lower_bound_u64(const unsigned long long* keys, unsigned long long n, const unsigned long long* d_queries, unsigned long long nq,
                             unsigned long long* d_out, cudaStream_t stream);
 

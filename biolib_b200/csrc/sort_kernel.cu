@@ -6,10 +6,10 @@
 //   algorithm::jaccard                    (merge of two sorted distinct streams: intersection / union / sizes, include/jaccard.hpp:8-38)
 //
 // as an LSD radix sort of the 64-bit k-mer values (8 bits per pass, only the ceil(2k / 8) passes the values can differ in), an
-// adjacent-unique compaction, and |A n B| = |A| + |B| - |distinct(A u B)| from a third sort of the two distinct lists.
+// adjacent-unique compaction, and |A n B| by looking the shorter distinct list up in the longer one (binary searches narrowed per block).
 //
-// One radix pass = per-tile digit histograms -> bucket-major exclusive scan -> stable scatter. Stability inside a tile comes
-// from warp match (rank among the lanes of a warp with the same digit) + per-warp digit counts summed in warp order.
+// One radix pass = per-tile digit histograms -> bucket-major exclusive scan -> stable scatter (rs_scatter: warp-private ranking,
+// tile reordered in shared memory, coalesced writes).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -34,39 +34,76 @@ __global__ void __launch_bounds__(RS_THREADS) rs_count(const u64* __restrict__ k
     M[(u64)threadIdx.x * n_tiles + blockIdx.x] = hist[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
+// Stable scatter of one tile. Ranking is warp-private (warp w owns keys [512 w, 512 w + 512) of the tile and walks them 32 at a
+// time: rank = keys of the same digit seen by this warp so far + rank among the lanes of this round, from a warp match), so the
+// only block barriers are the three between the phases; the tile is then put in digit order in shared memory and written out with
+// consecutive threads on consecutive addresses of each digit's run.
+__global__ void __launch_bounds__(RS_THREADS, 3) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
                                                          u64* __restrict__ out)
 {
-    __shared__ u32 cnt[RS_BINS];                   // keys of this tile already placed, per digit
-    __shared__ u32 wcnt[RS_WARPS][RS_BINS];        // this chunk: keys per (warp, digit)
-    __shared__ u32 woff[RS_WARPS][RS_BINS];        // this chunk: first slot of (warp, digit) inside the tile's digit group
+    __shared__ u64 skeys[RS_TILE];                 // the tile in digit order
+    __shared__ u32 whist[RS_WARPS][RS_BINS];       // keys per (warp, digit), then: first slot of (warp, digit) inside the tile's digit group
+    __shared__ u32 dstart[RS_BINS];                // first slot of a digit's group inside the tile
+    __shared__ u64 gbase[RS_BINS];                 // global slot of the group's first key minus dstart
+    __shared__ u32 wtot[RS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    cnt[tid] = 0;
     const u64 base = (u64)blockIdx.x * RS_TILE;
-    const u64 mybase = M[(u64)tid * n_tiles + blockIdx.x];     // thread tid keeps digit tid's global offset
-    __shared__ u64 gbase[RS_BINS];
-    gbase[tid] = mybase;
-    for (int c = 0; c < RS_CHUNKS; ++c) {
+    const u32 tile_n = (u32)min((u64)RS_TILE, n - base);
 #pragma unroll
-        for (int j = lane; j < RS_BINS; j += 32) wcnt[warp][j] = 0;
-        __syncwarp();
-        const u64 i = base + (u64)c * RS_THREADS + tid;
-        const bool have = i < n;
-        u64 key = 0;
-        u32 d = 0x100u + (u32)lane;                // lanes without a key match nobody
-        if (have) { key = __ldg(keys + i); d = (u32)(key >> shift) & 255u; }
+    for (int w = 0; w < RS_WARPS; ++w) whist[w][tid] = 0;
+    __syncthreads();
+    u64 key[RS_CHUNKS];
+    u32 rnk2[RS_CHUNKS / 2];                       // ranks inside the warp's segment (< 512), two per register
+    const u32 seg = (u32)warp * (RS_TILE / RS_WARPS);
+#pragma unroll
+    for (int r = 0; r < RS_CHUNKS; ++r) {
+        const u32 li = seg + (u32)r * 32u + (u32)lane;
+        const bool have = li < tile_n;
+        key[r] = have ? __ldg(keys + base + li) : 0;
+        const u32 d = have ? ((u32)(key[r] >> shift) & 255u) : (0x100u + (u32)lane);     // lanes without a key match nobody
         const u32 peers = __match_any_sync(0xffffffffu, d);
-        const u32 rank = __popc(peers & ((1u << lane) - 1u));
-        if (have && rank == 0) wcnt[warp][d] = __popc(peers);
-        __syncthreads();
-        {
-            u32 run = cnt[tid];
+        const u32 lr = __popc(peers & ((1u << lane) - 1u));
+        const u32 prev = have ? whist[warp][d] : 0u;
+        if (r & 1) rnk2[r >> 1] |= (prev + lr) << 16; else rnk2[r >> 1] = prev + lr;
+        __syncwarp();
+        if (have && lr == 0) whist[warp][d] = prev + __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        // digit tid: counts of the warps -> their first slots; tile count -> exclusive scan over the digits
+        u32 run = 0;
 #pragma unroll
-            for (int w = 0; w < RS_WARPS; ++w) { const u32 x = wcnt[w][tid]; woff[w][tid] = run; run += x; }
-            cnt[tid] = run;
-        }
+        for (int w = 0; w < RS_WARPS; ++w) { const u32 x = whist[w][tid]; whist[w][tid] = run; run += x; }
+        u32 incl = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        if (lane == 31) wtot[warp] = incl;
         __syncthreads();
-        if (have) out[gbase[d] + woff[warp][d] + rank] = key;
+        u32 before = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) before += w < warp ? wtot[w] : 0u;
+        const u32 ds = before + incl - run;
+        dstart[tid] = ds;
+        gbase[tid] = M[(u64)tid * n_tiles + blockIdx.x] - ds;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_CHUNKS; ++r) {
+        const u32 li = seg + (u32)r * 32u + (u32)lane;
+        if (li < tile_n) {
+            const u32 d = (u32)(key[r] >> shift) & 255u;
+            skeys[dstart[d] + whist[warp][d] + ((rnk2[r >> 1] >> (16 * (r & 1))) & 0xFFFFu)] = key[r];
+        }
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int j = 0; j < RS_CHUNKS; ++j) {
+        const u32 idx = (u32)j * RS_THREADS + (u32)tid;
+        if (idx < tile_n) {
+            const u64 k = skeys[idx];
+            out[gbase[(u32)(k >> shift) & 255u] + idx] = k;
+        }
     }
 }
 
@@ -125,12 +162,44 @@ cudaError_t ss_scan(u64* a, u64 n, u64* sums, u64* total, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-// ---- adjacent unique / generic keep-compaction ---------------------------------------------------------------------------------
-__global__ void uq_flags(const u64* __restrict__ k, u64 n, u64* __restrict__ f)
+// ---- adjacent unique in two passes over the keys: per-block counts of run starts, then (after a scan of the few block counts)
+// each block recomputes its flags and writes its distinct keys behind those of the blocks before it
+constexpr int UQ_THREADS = 256, UQ_PER = 8, UQ_TILE = UQ_THREADS * UQ_PER;
+template <bool WRITE>
+__global__ void __launch_bounds__(UQ_THREADS) uq_tile(const u64* __restrict__ k, u64 n, u64* __restrict__ block_counts, u64* __restrict__ out)
 {
-    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
-    if (i < n) f[i] = (i == 0 || k[i] != k[i - 1]) ? 1 : 0;
+    __shared__ u32 wsum[UQ_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u64 i0 = (u64)blockIdx.x * UQ_TILE + (u64)tid * UQ_PER;
+    u64 v[UQ_PER];
+    u64 prev = i0 > 0 && i0 <= n ? k[i0 - 1] : 0;
+    u32 flags = 0;
+#pragma unroll
+    for (int j = 0; j < UQ_PER; ++j) {
+        const u64 i = i0 + j;
+        v[j] = i < n ? k[i] : 0;
+        if (i < n && (i == 0 || v[j] != prev)) flags |= 1u << j;
+        prev = v[j];
+    }
+    const u32 cnt = __popc(flags);
+    u32 incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += x; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    u32 before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < UQ_THREADS / 32; ++w) { before += w < warp ? wsum[w] : 0u; total += wsum[w]; }
+    if (!WRITE) {
+        if (tid == 0) block_counts[blockIdx.x] = total;
+        return;
+    }
+    u64 o = block_counts[blockIdx.x] + before + incl - cnt;     // block_counts: exclusive scan by now
+#pragma unroll
+    for (int j = 0; j < UQ_PER; ++j) if (flags & (1u << j)) out[o++] = v[j];
 }
+
+// ---- adjacent unique / generic keep-compaction ---------------------------------------------------------------------------------
 // kmer_view's end test drops the k-mer that ends with the last byte of its sequence: keep[i] = 0 for those
 __global__ void k1_flags(const u64* __restrict__ pos, u64 n, int k, const u64* __restrict__ offs, u64 n_seq, u64 n_bases, u64* __restrict__ f)
 {
@@ -169,6 +238,54 @@ __global__ void run_scatter(const u64* __restrict__ mm_start, const u8* __restri
     if (r >= n) return;
     const u64 here = f_excl[r], next = r + 1 < n ? f_excl[r + 1] : *total;
     if (next != here) { first[here] = r; start[here] = mm_start[r] - mm_pos[r]; }
+}
+
+// |A n B| of two sorted distinct arrays (algorithm::jaccard's merge, include/jaccard.hpp:8-38, as a count): a block takes 2048
+// consecutive keys of A, narrows B to the range those keys can fall in (two binary searches), and every key is looked up in that
+// range -- a dozen steps that stay in L1 -- instead of sorting the concatenation of the two lists a third time.
+constexpr int IX_THREADS = 256, IX_PER = 8, IX_TILE = IX_THREADS * IX_PER;
+__global__ void __launch_bounds__(IX_THREADS) intersect_count_kernel(const u64* __restrict__ a, u64 na, const u64* __restrict__ b, u64 nb,
+                                                                     unsigned long long* __restrict__ count)
+{
+    __shared__ u64 range[2];
+    __shared__ u32 wsum[IX_THREADS / 32];
+    const u64 base = (u64)blockIdx.x * IX_TILE;
+    const u64 last = min(base + IX_TILE, na) - 1;
+    if (threadIdx.x < 2) {
+        const u64 v = threadIdx.x == 0 ? a[base] : a[last];
+        u64 lo = 0, hi = nb;                               // thread 0: first b >= a[base]; thread 1: first b > a[last]
+        while (lo < hi) {
+            const u64 mid = lo + (hi - lo) / 2;
+            const u64 x = b[mid];
+            if (threadIdx.x == 0 ? x < v : x <= v) lo = mid + 1; else hi = mid;
+        }
+        range[threadIdx.x] = lo;
+    }
+    __syncthreads();
+    const u64 blo = range[0], bhi = range[1];
+    u32 hits = 0;
+#pragma unroll
+    for (int c = 0; c < IX_PER; ++c) {
+        const u64 i = base + (u64)c * IX_THREADS + threadIdx.x;
+        if (i < na && bhi > blo) {
+            const u64 v = a[i];
+            u64 lo = blo, hi = bhi;
+            while (lo < hi) {
+                const u64 mid = lo + (hi - lo) / 2;
+                if (b[mid] < v) lo = mid + 1; else hi = mid;
+            }
+            hits += (lo < bhi && b[lo] == v) ? 1u : 0u;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) hits += __shfl_xor_sync(0xffffffffu, hits, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = hits;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u32 t = 0;
+        for (int w = 0; w < IX_THREADS / 32; ++w) t += wsum[w];
+        if (t) atomicAdd(count, (unsigned long long)t);
+    }
 }
 
 }  // namespace
@@ -224,17 +341,18 @@ cudaError_t radix_sort_u64(unsigned long long* keys, unsigned long long* tmp, un
     return cudaGetLastError();
 }
 
-// keys sorted -> distinct keys in out (may not alias keys); *d_total (device) = their number. flags: n entries of scratch.
-cudaError_t unique_sorted_u64(const unsigned long long* keys, unsigned long long n, unsigned long long* flags, void* scratch, unsigned long long* out,
+// keys sorted -> distinct keys in out (may not alias keys); *d_total (device) = their number. scratch: sort_scratch_bytes(n).
+cudaError_t unique_sorted_u64(const unsigned long long* keys, unsigned long long n, unsigned long long* /*flags*/, void* scratch, unsigned long long* out,
                               unsigned long long* d_total, cudaStream_t stream, int* launches)
 {
     if (n == 0) return cudaMemsetAsync(d_total, 0, 8, stream);
-    const unsigned grid = (unsigned)((n + 255) / 256);
-    uq_flags<<<grid, 256, 0, stream>>>(keys, n, flags);
-    u64* sums = static_cast<u64*>(scratch);
-    cudaError_t e = ss_scan(flags, n, sums, d_total, stream);
+    const u64 nb = (n + UQ_TILE - 1) / UQ_TILE;
+    u64* counts = static_cast<u64*>(scratch);
+    u64* sums = counts + nb;
+    uq_tile<false><<<(unsigned)nb, UQ_THREADS, 0, stream>>>(keys, n, counts, nullptr);
+    cudaError_t e = ss_scan(counts, nb, sums, d_total, stream);
     if (e != cudaSuccess) return e;
-    compact_by_flags<<<grid, 256, 0, stream>>>(keys, flags, n, d_total, out);
+    uq_tile<true><<<(unsigned)nb, UQ_THREADS, 0, stream>>>(keys, n, counts, out);
     *launches += 5;
     return cudaGetLastError();
 }
@@ -275,6 +393,37 @@ cudaError_t lower_bound_u64(const unsigned long long* keys, unsigned long long n
 {
     if (nq == 0) return cudaSuccess;
     lower_bound_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, stream>>>(keys, n, d_queries, nq, d_out);
+    return cudaGetLastError();
+}
+
+// *d_count (device) = |A n B| for two sorted arrays of distinct keys
+cudaError_t intersect_count_u64(const unsigned long long* a, unsigned long long na, const unsigned long long* b, unsigned long long nb,
+                                unsigned long long* d_count, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(d_count, 0, 8, stream);
+    if (e != cudaSuccess || na == 0 || nb == 0) return e;
+    if (na > nb) { const unsigned long long* t = a; a = b; b = t; const unsigned long long tn = na; na = nb; nb = tn; }   // look the shorter list up in the longer
+    intersect_count_kernel<<<(unsigned)((na + IX_TILE - 1) / IX_TILE), IX_THREADS, 0, stream>>>(a, na, b, nb, d_count);
+    return cudaGetLastError();
+}
+
+// One stable scatter by the digit (key >> shift) & 255 (the partition step of the multi-GPU sort: keys grouped by their top byte,
+// order inside a group kept). bin_start (device, 257 entries) = first slot of every digit's group, bin_start[256] = n.
+cudaError_t partition_by_digit_u64(const unsigned long long* keys, unsigned long long* out, unsigned long long n, int shift, void* scratch,
+                                   unsigned long long* bin_start, cudaStream_t stream, int* launches)
+{
+    if (n == 0) return cudaMemsetAsync(bin_start, 0, 257 * 8, stream);
+    const u64 n_tiles = (n + RS_TILE - 1) / RS_TILE;
+    const u64 m = n_tiles * RS_BINS;
+    u64* M = static_cast<u64*>(scratch);
+    u64* sums = M + m;
+    rs_count<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(keys, n, shift, n_tiles, M);
+    cudaError_t e = ss_scan(M, m, sums, bin_start + 256, stream);          // total = n lands in bin_start[256]
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpy2DAsync(bin_start, 8, M, n_tiles * 8, 8, 256, cudaMemcpyDeviceToDevice, stream);   // M[d][0]: where digit d starts
+    if (e != cudaSuccess) return e;
+    rs_scatter<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(keys, n, shift, n_tiles, M, out);
+    *launches += 5;
     return cudaGetLastError();
 }
 

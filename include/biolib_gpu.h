@@ -236,11 +236,15 @@ int blg_kmer_jaccard(blg_ctx* ctx, const char* bases1, size_t n1, const uint64_t
  *   blg_sort_unique_u64      d_keys[0, n) -> sorted distinct keys in d_keys[0, *count) (in place). key_bits = number of low bits the
  *                            keys can differ in (2k for k-mer values)
  *   blg_sorted_sets_jaccard  algorithm::jaccard (include/jaccard.hpp:8-38) of two sorted distinct lists
+ *   blg_partition_by_top_byte  d_keys[0, n) -> d_out grouped (stably) by their top byte, (key >> (key_bits - 8)) & 255, groups in increasing
+ *                            order; bin_counts (HOST, 256 entries) = keys per group. The partition step when the keys are exchanged
+ *                            BEFORE they are sorted: a rank's share of the key space is a range of groups, i.e. a contiguous piece of d_out
  *   blg_lower_bound_u64      for each of nq HOST queries the index of the first key >= it in the sorted device array (HOST out_index):
  *                            where a rank's sorted list is cut for the exchange
  */
 int blg_sort_unique_u64(blg_ctx* ctx, uint64_t* d_keys, size_t n, int key_bits, uint64_t* count);
 int blg_sorted_sets_jaccard(blg_ctx* ctx, const uint64_t* d_a, size_t na, const uint64_t* d_b, size_t nb, int key_bits, blg_jaccard_out* out);
+int blg_partition_by_top_byte(blg_ctx* ctx, const uint64_t* d_keys, size_t n, int key_bits, uint64_t* d_out, uint64_t* bin_counts);
 int blg_lower_bound_u64(blg_ctx* ctx, const uint64_t* d_sorted, size_t n, const uint64_t* queries, size_t nq, uint64_t* out_index);
 
 /*

@@ -43,6 +43,14 @@ class NumpyKmerOps:
     def local_sorted_unique(self, bases, k, canonical, offsets=None):
         return self._t(self.oracle.sorted_unique_kmers(bases, k, canonical, offsets))
 
+    def local_kmers(self, bases, k, canonical, offsets=None):
+        return self._t(self.oracle.kmers(bases, k, canonical, offsets=offsets)["lo"])
+
+    def partition(self, keys, bits):
+        u = self._u(keys)
+        top = ((u >> np.uint64(max(bits - 8, 0))) & np.uint64(255)).astype(np.int64)
+        return self._t(u[np.argsort(top, kind="stable")]), np.bincount(top, minlength=256).astype(np.uint64)
+
     def sample(self, keys, idx):
         return self._u(keys)[np.asarray(idx, np.int64)].copy()
 
@@ -74,7 +82,7 @@ def _inputs(n, seed):
     return a, b
 
 
-def _worker(rank, world, port, backend, n, q):
+def _worker(rank, world, port, backend, n, strategy, q):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import torch
@@ -98,8 +106,8 @@ def _worker(rank, world, port, backend, n, q):
     try:
         a, b = _inputs(n, 31)
         la, ha = mg.kmer_chunk(n, K, world, rank)
-        ja = mg.distributed_jaccard(ops, dist, a[la:ha], b[la:ha], K, True)
-        su = mg.distributed_sorted_unique(ops, dist, a[la:ha], K, True)
+        ja = mg.distributed_jaccard(ops, dist, a[la:ha], b[la:ha], K, True, strategy=strategy)
+        su = mg.distributed_sorted_unique(ops, dist, a[la:ha], K, True, strategy=strategy)
         part = su["part"].cpu().numpy().view(np.uint64)
         parts = [None] * world
         dist.all_gather_object(parts, part)
@@ -117,12 +125,12 @@ def _worker(rank, world, port, backend, n, q):
             ctx.close()
 
 
-def _run(world, backend, n):
+def _run(world, backend, n, strategy="partition"):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, n, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, n, strategy, q)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -131,9 +139,9 @@ def _run(world, backend, n):
     return q.get(timeout=5)
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_key_range_exchange_over_gloo(world):
-    r = _run(world, "gloo", 60_000)
+@pytest.mark.parametrize("world,strategy", [(2, "partition"), (3, "partition"), (2, "sorted"), (3, "sorted")])
+def test_key_range_exchange_over_gloo(world, strategy):
+    r = _run(world, "gloo", 60_000, strategy)
     assert r["jaccard_ok"] and r["unique_ok"] and r["total_ok"], r
     assert r["want"][0] > 1000 and r["exchanged"] > 0
     # the splitters balance the ranges: no rank holds more than twice its share
@@ -152,13 +160,37 @@ def test_splitters_and_chunks():
     assert list(s) == [3, 5, 8] and len(mg.choose_splitters(np.zeros(0, np.uint64), 3)) == 2
     assert len(mg.choose_splitters(np.arange(4, dtype=np.uint64), 1)) == 0
     assert list(mg.sample_positions(10, 4)) == [0, 2, 5, 7] and len(mg.sample_positions(3)) == 3 and len(mg.sample_positions(0)) == 0
+    c = np.zeros(256, np.uint64)
+    c[10:20] = 100
+    b = mg.deal_groups(c, 4)
+    assert b[0] == 0 and b[-1] == 256 and all(x <= y for x, y in zip(b, b[1:]))
+    assert [int(c[b[r]:b[r + 1]].sum()) for r in range(4)] in ([300, 200, 300, 200], [200, 300, 200, 300], [300, 200, 200, 300], [300, 300, 200, 200])
+    assert list(mg.deal_groups(np.zeros(256, np.uint64), 3)) == [0, 256, 256, 256] and list(mg.deal_groups(c, 1)) == [0, 256]
 
 
 @pytest.mark.gpu
-def test_product_ops_one_rank_nccl():
-    """CudaKmerOps through the same driver functions (one NCCL rank: the exchange is a copy to itself) against the oracle."""
-    r = _run(1, "nccl", 3_000_000)
+@pytest.mark.parametrize("strategy", ["partition", "sorted"])
+def test_product_ops_one_rank_nccl(strategy):
+    """CudaKmerOps through the same driver functions in a one-rank NCCL group against the oracle."""
+    r = _run(1, "nccl", 3_000_000, strategy)
     assert r["jaccard_ok"] and r["unique_ok"] and r["total_ok"], r
+
+
+@pytest.mark.gpu
+def test_partition_by_top_byte(gpu):
+    """blg_partition_by_top_byte: a stable grouping by (key >> (bits - 8)) & 255 and the group sizes."""
+    import ctypes as C
+    import torch
+    rng = np.random.default_rng(11)
+    for n, bits in ((0, 62), (1, 62), (5000, 62), (1_000_003, 62), (300_000, 20), (70_000, 6), (4096 * 3, 64)):
+        keys = rng.integers(0, 2**bits if bits < 64 else 2**64, size=n, dtype=np.uint64)
+        t = torch.from_numpy(keys.view(np.int64).copy()).cuda()
+        out = torch.empty_like(t)
+        counts = np.zeros(256, np.uint64)
+        gpu._check(gpu.L.blg_partition_by_top_byte(gpu.h, C.c_void_p(t.data_ptr()), n, bits, C.c_void_p(out.data_ptr()), counts.ctypes.data))
+        top = ((keys >> np.uint64(max(bits - 8, 0))) & np.uint64(255)).astype(np.int64)
+        assert np.array_equal(counts, np.bincount(top, minlength=256).astype(np.uint64)), (n, bits)
+        assert np.array_equal(out.cpu().numpy().view(np.uint64), keys[np.argsort(top, kind="stable")]), (n, bits)
 
 
 @pytest.mark.gpu

@@ -6,7 +6,8 @@
 
 Two inputs of --bases bases (the second = the first with 2 % substitutions), each cut into N chunks of k-mer starts (+ k - 1 bases);
 rank r holds chunk r of both. Timed (wall clock between barriers + device synchronise, max over ranks): local extraction + sort +
-unique, the splitter agreement, the two all-to-alls by key range, the merge, the per-range Jaccard and the final all-reduce.
+unique, the agreement on key ranges, the two all-to-alls, the merge, the per-range Jaccard and the final all-reduce (both strategies of
+biolib_b200/multi_gpu.py).
 Rank 0 then runs blg_kmer_jaccard over the whole inputs on its GPU alone and compares the four counters.
 """
 import argparse
@@ -25,6 +26,7 @@ def main():
     ap.add_argument("--bases", type=int, default=200_000_000)
     ap.add_argument("--k", type=int, default=31)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--strategy", default="partition", help="partition (exchange, then sort once) or sorted (sort, exchange distinct keys, merge)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -56,7 +58,7 @@ def main():
     for _ in range(a.reps + 1):
         barrier()
         t0 = time.perf_counter()
-        res = mg.distributed_jaccard(ops, dist, d1, d2, k, True)
+        res = mg.distributed_jaccard(ops, dist, d1, d2, k, True, strategy=a.strategy)
         barrier()
         times.append(time.perf_counter() - t0)
     t = torch.tensor([min(times[1:])], dtype=torch.float64, device=dev)
