@@ -112,19 +112,48 @@ __global__ void __launch_bounds__(FX_THREADS) fx_pass1(const unsigned char* __re
     }
 }
 
-// scan 1 (one CTA, sequential: a few hundred thousand blocks at most): entry state of every block
-__global__ void fx_scan1(const FxSummary* __restrict__ sum, size_t n_blocks, int fastq, const unsigned char* __restrict__ text, size_t n,
-                         u32* __restrict__ entry)
+// scan 1 (one CTA of 1024 threads): entry state of every block. The carried state is associative -- FASTQ: the line count mod 4
+// (a sum); FASTA: the state after the last newline seen so far ("last defined value") -- so every thread summarises a contiguous
+// run of blocks, the 1024 summaries are scanned in shared memory, and every thread walks its run again to write the entries.
+__global__ void __launch_bounds__(1024) fx_scan1(const FxSummary* __restrict__ sum, size_t n_blocks, int fastq, const unsigned char* __restrict__ text,
+                                                 size_t n, u32* __restrict__ entry)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    u32 state = fastq ? 0u : (n > 0 && text[0] == '>' ? 1u : 0u);     // the first line starts at byte 0
+    __shared__ u64 s_lines[1024];
+    __shared__ u32 s_state[1024];                  // FASTA: state after the run's last newline, 3 = the run holds no newline
+    const int tid = threadIdx.x;
+    const size_t per = (n_blocks + 1023) / 1024;
+    const size_t lo = min(n_blocks, (size_t)tid * per), hi = min(n_blocks, lo + per);
     u64 lines = 0;
-    for (size_t b = 0; b < n_blocks; ++b) {
-        const u32 e = state;
-        entry[b] = e;
-        if (fastq) { lines += sum[b].nl; state = (u32)(lines & 3u); }
-        else if (sum[b].nl > 0) state = sum[b].last_state;
-        else state = e;
+    u32 st = 3u;
+    for (size_t b = lo; b < hi; ++b) {
+        const FxSummary x = sum[b];
+        lines += x.nl;
+        if (x.nl > 0) st = x.last_state;
+    }
+    s_lines[tid] = lines;
+    s_state[tid] = st;
+    __syncthreads();
+    if (tid == 0) {
+        // exclusive scan over the 1024 run summaries (shared memory only)
+        u64 acc = 0;
+        u32 state = fastq ? 0u : (n > 0 && text[0] == '>' ? 1u : 0u);     // the first line starts at byte 0
+        for (int i = 0; i < 1024; ++i) {
+            const u64 l = s_lines[i];
+            const u32 t = s_state[i];
+            s_lines[i] = acc;
+            s_state[i] = state;
+            acc += l;
+            if (t != 3u) state = t;
+        }
+    }
+    __syncthreads();
+    u64 acc = s_lines[tid];
+    u32 state = fastq ? (u32)(acc & 3u) : s_state[tid];
+    for (size_t b = lo; b < hi; ++b) {
+        entry[b] = state;
+        const FxSummary x = sum[b];
+        if (fastq) { acc += x.nl; state = (u32)(acc & 3u); }
+        else if (x.nl > 0) state = x.last_state;
     }
 }
 
@@ -291,7 +320,7 @@ cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fas
     FxSummary* sum = reinterpret_cast<FxSummary*>(p); p += nb * sizeof(FxSummary);
     u32* entry = reinterpret_cast<u32*>(p);
     fx_pass1<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, sum);
-    fx_scan1<<<1, 32, 0, stream>>>(sum, nb, fastq, text, n_text, entry);
+    fx_scan1<<<1, 1024, 0, stream>>>(sum, nb, fastq, text, n_text, entry);
     fx_pass2<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts);
     fx_scan2<<<1, 1024, 0, stream>>>(keep, starts, nb);
     *launches = 4;

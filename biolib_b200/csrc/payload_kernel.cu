@@ -11,11 +11,12 @@
 // Passes (all record-parallel, the records being device-resident output of the fused kernel):
 //   count    tiles of 2048 records: per-tile bucket histogram in shared memory -> matrix M[bucket][tile]
 //   scan     exclusive prefix sum of M in bucket-major order: where every (bucket, tile) group starts
-//   scatter  same tiles; the rank of a record inside its group comes from warp match + an ordered walk over the warps of a
-//            chunk, so the order is the stream order; writes the reordered record arrays and every record's payload length
+//   scatter  same tiles; the rank of a record inside its group comes from ballots (lanes of a warp with the same bucket) and a
+//            packed per-warp counter per bucket, so the order is the stream order; writes the reordered record arrays and every
+//            record's payload length
 //   scan     exclusive prefix sum of the lengths: the payload start of every record in the packed stream
-//   pack     one thread per record: gather its ASCII bases, code them, OR them into the stream (a record shares its first
-//            and last word with its neighbours: atomicOr there, plain stores in between)
+//   pack     one thread per record: its ASCII bases as aligned 8-byte words, eight bases -> sixteen stream bits at a time, ORed into
+//            the stream (a record shares its first and last word with its neighbours: atomicOr there, plain stores in between)
 #include "common.cuh"
 #include "kernels.h"
 
@@ -93,14 +94,27 @@ __global__ void __launch_bounds__(SC_THREADS) sc_apply(u64* __restrict__ a, u64 
     for (int i = 0; i < SC_PER; ++i) { if (base + i < n) a[base + i] = r; r += v[i]; }
 }
 
+__device__ __forceinline__ u32 sum_bytes8(unsigned long long x)
+{
+    unsigned long long t = (x & 0x00FF00FF00FF00FFULL) + ((x >> 8) & 0x00FF00FF00FF00FFULL);
+    t = (t & 0x0000FFFF0000FFFFULL) + ((t >> 16) & 0x0000FFFF0000FFFFULL);
+    return (u32)(t & 0xFFFFFFFFULL) + (u32)(t >> 32);
+}
+
 // ---- scatter: stable rank inside (bucket, tile) ---------------------------------------------------------------------------
+// A chunk is 256 consecutive records, 32 per warp. Lanes of a warp with the same bucket are found with ballots over the bucket's
+// bits; the leader of every such group adds its size into byte `warp` of a packed 64-bit counter of the bucket (a group has at most
+// 32 members, a byte holds it): after one barrier the bytes below `warp` are the records of earlier warps of the chunk, all eight
+// the chunk's total. Three barriers per chunk instead of one per warp.
 __global__ void __launch_bounds__(PL_THREADS) pl_scatter(const u64* __restrict__ value, const u64* __restrict__ mm_start, const u8* __restrict__ size,
-                                                         const u8* __restrict__ mm_pos, u64 n, u64 s8, u32 n_buckets, u64 n_tiles, int k,
+                                                         const u8* __restrict__ mm_pos, u64 n, u64 s8, u32 n_buckets, int bucket_bits, u64 n_tiles, int k,
                                                          const u64* __restrict__ M, u64* __restrict__ o_value, u64* __restrict__ o_mm,
                                                          u8* __restrict__ o_size, u8* __restrict__ o_pos, u64* __restrict__ o_len)
 {
-    extern __shared__ u32 cnt[];                 // records of this tile already placed, per bucket
-    for (u32 b = threadIdx.x; b < n_buckets; b += PL_THREADS) cnt[b] = 0;
+    extern __shared__ u64 pl_smem[];
+    unsigned long long* pk = reinterpret_cast<unsigned long long*>(pl_smem);   // [n_buckets] this chunk: records per warp, one byte each
+    u32* cnt = reinterpret_cast<u32*>(pl_smem + n_buckets);                     // [n_buckets] records of this tile already placed
+    for (u32 b = threadIdx.x; b < n_buckets; b += PL_THREADS) { cnt[b] = 0; pk[b] = 0; }
     __syncthreads();
     const u64 base = (u64)blockIdx.x * PL_TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -108,17 +122,28 @@ __global__ void __launch_bounds__(PL_THREADS) pl_scatter(const u64* __restrict__
         const u64 r = base + (u64)c * PL_THREADS + threadIdx.x;
         const bool have = r < n;
         u64 v = 0;
-        u32 b = 0xFFFFFFFFu;                      // lanes without a record match among themselves only
+        u32 b = 0;
         if (have) { v = __ldg(value + r); b = bucket_of(v, s8, n_buckets); }
-        const u32 peers = __match_any_sync(0xffffffffu, b);
-        const int leader = __ffs((int)peers) - 1;
-        const u32 rank_in_warp = __popc(peers & ((1u << lane) - 1u));
-        u32 first = 0;
-        for (int w = 0; w < PL_THREADS / 32; ++w) {          // the warps of a chunk take their slots in order: stream order
-            if (warp == w && have && lane == leader) { first = cnt[b]; cnt[b] = first + __popc(peers); }
-            __syncthreads();
+        u32 peers = __ballot_sync(0xffffffffu, have);
+        for (int bit = 0; bit < bucket_bits; ++bit) {
+            const u32 x = __ballot_sync(0xffffffffu, (b >> bit) & 1u);
+            peers &= ((b >> bit) & 1u) ? x : ~x;
         }
-        first = __shfl_sync(0xffffffffu, first, leader);
+        const u32 rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        const bool leader = have && rank_in_warp == 0;
+        if (leader) atomicAdd(&pk[b], (unsigned long long)__popc(peers) << (8 * warp));
+        __syncthreads();
+        u32 first = 0, chunk_total = 0;
+        bool closes = false;
+        if (have) {
+            const unsigned long long packed = pk[b];
+            const unsigned long long below = packed & ((1ULL << (8 * warp)) - 1ULL);
+            first = cnt[b] + sum_bytes8(below);
+            chunk_total = sum_bytes8(packed);
+            closes = leader && below == 0;         // the first warp of the chunk that holds this bucket closes it after the barrier
+        }
+        __syncthreads();
+        if (closes) { cnt[b] += chunk_total; pk[b] = 0; }
         if (have) {
             const u64 dst = M[(u64)b * n_tiles + blockIdx.x] + first + rank_in_warp;
             const u8 sz = size[r];
@@ -128,6 +153,7 @@ __global__ void __launch_bounds__(PL_THREADS) pl_scatter(const u64* __restrict__
             o_pos[dst] = mm_pos[r];
             o_len[dst] = (u64)sz + (u64)(k - 1);
         }
+        __syncthreads();
     }
 }
 
@@ -140,32 +166,50 @@ __global__ void pl_bucket_offsets(const u64* __restrict__ M, u64 n_tiles, u32 n_
 }
 
 // ---- pack: one thread per (reordered) record ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) pl_pack(const unsigned char* __restrict__ bases, const u64* __restrict__ mm_start, const u8* __restrict__ mm_pos,
-                                               const u64* __restrict__ pstart, const u64* __restrict__ plen_unused, const u8* __restrict__ size, int k,
-                                               u64 n, u64* __restrict__ words)
+// The record's bases are read as aligned 8-byte words (the granule that holds a valid byte is always readable), eight bases become
+// sixteen stream bits at a time (SWAR codes, then the pairs reversed so that the first base is on top), and are shifted into the
+// 64-bit words of the stream.
+__device__ __forceinline__ u32 codes8_msb_first(u64 w)
 {
-    (void)plen_unused;
+    const u32 c = blg_codes4((u32)w) | (blg_codes4((u32)(w >> 32)) << 8);      // base i at bits [2i, 2i+2)
+    const u32 r = __brev(c) >> 16;                                               // base i at bits [14-2i, 16-2i), the two bits of a pair swapped
+    return ((r >> 1) & 0x5555u) | ((r & 0x5555u) << 1);
+}
+
+__global__ void __launch_bounds__(256) pl_pack(const unsigned char* __restrict__ bases, const u64* __restrict__ mm_start, const u8* __restrict__ mm_pos,
+                                               const u64* __restrict__ pstart, const u8* __restrict__ size, int k, u64 n, u64* __restrict__ words)
+{
     const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
     if (r >= n) return;
-    const u64 src = mm_start[r] - mm_pos[r];            // sk_start
-    const int len = (int)size[r] + k - 1;
-    u64 e = pstart[r];                                    // element index in the packed stream
-    u64 acc = 0;                                          // bits of the current word, already in place
+    const unsigned char* p = bases + (mm_start[r] - mm_pos[r]);       // first base of the super-k-mer
+    int left = (int)size[r] + k - 1;                                     // bases to go
+    u64 e = pstart[r];                                                   // element index in the packed stream
     u64 wi = e >> 5;
+    int pos = (int)(e & 31);                                             // elements already in word wi
+    u64 acc = 0;
     bool first_word = true;
-    for (int i = 0; i < len; ++i, ++e) {
-        const u32 c = bases[src + i];
-        const u64 code = ((c >> 1) ^ (c >> 2)) & 3u;     // A 0, C 1, G 2, T/U 3 for the ten valid letters (nt4_swar.h); records hold valid bases only
-        acc |= code << (62 - 2 * (int)(e & 31));
-        if ((e & 31) == 31) {
+    int skip = (int)(reinterpret_cast<uintptr_t>(p) & 7u);               // bytes of the first aligned word that lie before the record
+    const u64* q = reinterpret_cast<const u64*>(p - skip);
+    while (left > 0) {
+        u32 chunk = codes8_msb_first(__ldg(q++));
+        int nb = 8 - skip;
+        chunk = (chunk << (2 * skip)) & 0xFFFFu;
+        skip = 0;
+        if (nb > left) nb = left;
+        chunk &= 0xFFFFu << (16 - 2 * nb);                               // codes of bytes behind the record out
+        const u64 val = (u64)chunk << 48;                                // first base in the top two bits
+        acc |= val >> (2 * pos);
+        if (pos + nb >= 32) {
             if (first_word) atomicOr(reinterpret_cast<unsigned long long*>(words + wi), acc);   // shared with the previous record
             else words[wi] = acc;
             first_word = false;
-            acc = 0;
             ++wi;
-        }
+            acc = pos == 32 - nb ? 0 : val << (2 * (32 - pos));           // what did not fit
+            pos = pos + nb - 32;
+        } else pos += nb;
+        left -= nb;
     }
-    if ((e & 31) != 0) atomicOr(reinterpret_cast<unsigned long long*>(words + wi), acc);          // shared with the next record
+    if (pos != 0) atomicOr(reinterpret_cast<unsigned long long*>(words + wi), acc);              // shared with the next record
 }
 
 cudaError_t scan_u64(u64* a, u64 n, u64* sums, u64* total, cudaStream_t stream)
@@ -211,11 +255,13 @@ cudaError_t payload_launch(const unsigned char* bases, const unsigned long long*
     cudaError_t e = scan_u64(M, m, sums, totals + 1, stream);
     if (e != cudaSuccess) return e;
     pl_bucket_offsets<<<(n_buckets + 1 + 255) / 256, 256, 0, stream>>>(M, n_tiles, n_buckets, n, bucket_offsets);
-    pl_scatter<<<(unsigned)n_tiles, PL_THREADS, smem, stream>>>(value, mm_start, size, mm_pos, n, s8, n_buckets, n_tiles, k, M, o_value, o_mm, o_size,
+    int bucket_bits = 0;
+    while ((1u << bucket_bits) < n_buckets) ++bucket_bits;
+    pl_scatter<<<(unsigned)n_tiles, PL_THREADS, (size_t)n_buckets * 12, stream>>>(value, mm_start, size, mm_pos, n, s8, n_buckets, bucket_bits, n_tiles, k, M, o_value, o_mm, o_size,
                                                                   o_pos, o_pstart);
     e = scan_u64(o_pstart, n, sums, totals, stream);
     if (e != cudaSuccess) return e;
-    pl_pack<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(bases, o_mm, o_pos, o_pstart, nullptr, o_size, k, n, words);
+    pl_pack<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(bases, o_mm, o_pos, o_pstart, o_size, k, n, words);
     *launches = 10;
     return cudaGetLastError();
 }

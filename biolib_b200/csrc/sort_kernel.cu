@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_count(const u64* __restrict__ k
 }
 
 // Stable scatter of one tile. Ranking is warp-private (warp w owns keys [512 w, 512 w + 512) of the tile and walks them 32 at a
-// time: rank = keys of the same digit seen by this warp so far + rank among the lanes of this round, from a warp match), so the
+// time: rank = keys of the same digit seen by this warp so far + rank among the lanes of this round, from ballots), so the
 // only block barriers are the three between the phases; the tile is then put in digit order in shared memory and written out with
 // consecutive threads on consecutive addresses of each digit's run.
 __global__ void __launch_bounds__(RS_THREADS, 3) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
@@ -60,8 +60,14 @@ __global__ void __launch_bounds__(RS_THREADS, 3) rs_scatter(const u64* __restric
         const u32 li = seg + (u32)r * 32u + (u32)lane;
         const bool have = li < tile_n;
         key[r] = have ? __ldg(keys + base + li) : 0;
-        const u32 d = have ? ((u32)(key[r] >> shift) & 255u) : (0x100u + (u32)lane);     // lanes without a key match nobody
-        const u32 peers = __match_any_sync(0xffffffffu, d);
+        const u32 d = (u32)(key[r] >> shift) & 255u;
+        // lanes of this round with the same digit: eight ballots (a warp match walks the distinct values one by one, ~30 of them here)
+        u32 peers = __ballot_sync(0xffffffffu, have);
+#pragma unroll
+        for (int bit = 0; bit < 8; ++bit) {
+            const u32 v = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+            peers &= ((d >> bit) & 1u) ? v : ~v;
+        }
         const u32 lr = __popc(peers & ((1u << lane) - 1u));
         const u32 prev = have ? whist[warp][d] : 0u;
         if (r & 1) rnk2[r >> 1] |= (prev + lr) << 16; else rnk2[r >> 1] = prev + lr;
