@@ -8,8 +8,8 @@
 // as an LSD radix sort of the 64-bit k-mer values (8 bits per pass, only the ceil(2k / 8) passes the values can differ in), an
 // adjacent-unique compaction, and |A n B| by looking the shorter distinct list up in the longer one (binary searches narrowed per block).
 //
-// One radix pass = per-tile digit histograms -> bucket-major exclusive scan -> stable scatter (rs_scatter: warp-private ranking,
-// tile reordered in shared memory, coalesced writes).
+// One radix pass = per-tile digit histograms -> bucket-major exclusive scan -> stable scatter (rs_scatter: persistent CTAs, tiles
+// staged by bulk async copies, warp-private ranking, tile reordered in shared memory, coalesced writes).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -34,83 +34,157 @@ __global__ void __launch_bounds__(RS_THREADS) rs_count(const u64* __restrict__ k
     M[(u64)threadIdx.x * n_tiles + blockIdx.x] = hist[threadIdx.x];
 }
 
-// Stable scatter of one tile. Ranking is warp-private (warp w owns keys [512 w, 512 w + 512) of the tile and walks them 32 at a
-// time: rank = keys of the same digit seen by this warp so far + rank among the lanes of this round, from ballots), so the
-// only block barriers are the three between the phases; the tile is then put in digit order in shared memory and written out with
-// consecutive threads on consecutive addresses of each digit's run.
-__global__ void __launch_bounds__(RS_THREADS, 3) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
-                                                         u64* __restrict__ out)
+// Stable scatter, persistent: a CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ... The next tile's 32 KB of keys arrive by ONE
+// bulk async copy (cp.async.bulk global -> shared, completion on an mbarrier; UBLKCP in SASS) while the current tile is ranked,
+// reordered and written, so no warp ever waits for a key load (the first version loaded 16 keys per thread up front and then sat
+// in long-scoreboard stalls for half of its time: DRAM 24 % busy). Ranking is warp-private (warp w owns keys [512 w, 512 w + 512)
+// of the tile and walks them 32 at a time: rank = keys of the same digit seen by this warp so far + rank among the lanes of this
+// round, from eight ballots), so the only block barriers are those between the phases; the tile is put in digit order in shared
+// memory and written out with consecutive threads on consecutive addresses of each digit's run.
+struct RsSmem {
+    alignas(16) u64 in[2][RS_TILE];                // the tile as it arrives (double buffered)
+    u64 skeys[RS_TILE];                            // the tile in digit order
+    u64 gbase[RS_BINS];                            // global slot of a digit group's first key minus dstart
+    u32 whist[RS_WARPS][RS_BINS];                  // keys per (warp, digit), then: first slot of (warp, digit) inside the tile's digit group
+    u32 dstart[RS_BINS];                           // first slot of a digit's group inside the tile
+    u32 wtot[RS_WARPS];
+    alignas(8) unsigned long long mbar[2];
+};
+
+__device__ __forceinline__ u32 rs_smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void rs_mbar_init(unsigned long long* b, int count)
 {
-    __shared__ u64 skeys[RS_TILE];                 // the tile in digit order
-    __shared__ u32 whist[RS_WARPS][RS_BINS];       // keys per (warp, digit), then: first slot of (warp, digit) inside the tile's digit group
-    __shared__ u32 dstart[RS_BINS];                // first slot of a digit's group inside the tile
-    __shared__ u64 gbase[RS_BINS];                 // global slot of the group's first key minus dstart
-    __shared__ u32 wtot[RS_WARPS];
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rs_smem_u32(b)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void rs_bulk_load(void* dst, const void* src, u32 bytes, unsigned long long* b)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rs_smem_u32(b)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(rs_smem_u32(dst)), "l"(src), "r"(bytes), "r"(rs_smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void rs_mbar_wait(unsigned long long* b, u32 phase)
+{
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}"
+                 ::"r"(rs_smem_u32(b)), "r"(phase) : "memory");
+}
+
+__global__ void __launch_bounds__(RS_THREADS, 2) rs_scatter(const u64* __restrict__ keys, u64 n, int shift, u64 n_tiles, const u64* __restrict__ M,
+                                                            u64* __restrict__ out)
+{
+    extern __shared__ __align__(16) unsigned char rs_raw[];
+    RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const u64 base = (u64)blockIdx.x * RS_TILE;
-    const u32 tile_n = (u32)min((u64)RS_TILE, n - base);
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) whist[w][tid] = 0;
+    const bool bulk_ok = (reinterpret_cast<uintptr_t>(keys) & 15u) == 0;     // bulk copies want 16-byte aligned addresses and sizes
+    if (tid == 0) { rs_mbar_init(&sm.mbar[0], 1); rs_mbar_init(&sm.mbar[1], 1); }
     __syncthreads();
-    u64 key[RS_CHUNKS];
-    u32 rnk2[RS_CHUNKS / 2];                       // ranks inside the warp's segment (< 512), two per register
-    const u32 seg = (u32)warp * (RS_TILE / RS_WARPS);
-#pragma unroll
-    for (int r = 0; r < RS_CHUNKS; ++r) {
-        const u32 li = seg + (u32)r * 32u + (u32)lane;
-        const bool have = li < tile_n;
-        key[r] = have ? __ldg(keys + base + li) : 0;
-        const u32 d = (u32)(key[r] >> shift) & 255u;
-        // lanes of this round with the same digit: eight ballots (a warp match walks the distinct values one by one, ~30 of them here)
-        u32 peers = __ballot_sync(0xffffffffu, have);
-#pragma unroll
-        for (int bit = 0; bit < 8; ++bit) {
-            const u32 v = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
-            peers &= ((d >> bit) & 1u) ? v : ~v;
+    // a full tile of an aligned array comes by bulk copy; the last, partial tile (or an unaligned array) by ordinary loads
+    auto stage = [&](u64 tile, int buf) -> bool {
+        const u64 base = tile * RS_TILE;
+        if (bulk_ok && base + RS_TILE <= n) {
+            if (tid == 0) rs_bulk_load(sm.in[buf], keys + base, RS_TILE * 8, &sm.mbar[buf]);
+            return true;
         }
-        const u32 lr = __popc(peers & ((1u << lane) - 1u));
-        const u32 prev = have ? whist[warp][d] : 0u;
-        if (r & 1) rnk2[r >> 1] |= (prev + lr) << 16; else rnk2[r >> 1] = prev + lr;
-        __syncwarp();
-        if (have && lr == 0) whist[warp][d] = prev + __popc(peers);
-        __syncwarp();
-    }
-    __syncthreads();
-    {
-        // digit tid: counts of the warps -> their first slots; tile count -> exclusive scan over the digits
-        u32 run = 0;
+        const u32 cnt = (u32)min((u64)RS_TILE, n - base);
+        for (u32 i = tid; i < cnt; i += RS_THREADS) sm.in[buf][i] = __ldg(keys + base + i);
+        return false;
+    };
+    u64 tile = blockIdx.x;
+    if (tile >= n_tiles) return;
+    bool cur_bulk = stage(tile, 0);
+    u32 ph[2] = {0u, 0u};
+    for (int it = 0; tile < n_tiles; ++it, tile += gridDim.x) {
+        const int buf = it & 1;
+        const u64 next = tile + gridDim.x;
+        bool next_bulk = false;
+        if (next < n_tiles) next_bulk = stage(next, buf ^ 1);       // in[buf ^ 1] was last read before the barrier that ended the previous iteration
+        if (cur_bulk) { rs_mbar_wait(&sm.mbar[buf], ph[buf]); ph[buf] ^= 1u; }
+        const u64 base = tile * RS_TILE;
+        const u32 tile_n = (u32)min((u64)RS_TILE, n - base);
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; ++w) { const u32 x = whist[w][tid]; whist[w][tid] = run; run += x; }
-        u32 incl = run;
+        for (int w = 0; w < RS_WARPS; ++w) sm.whist[w][tid] = 0;
+        __syncthreads();                                            // also: the ordinary loads of stage() are visible
+        const u64* in = sm.in[buf];
+        u32 rnk2[RS_CHUNKS / 2];                                    // ranks inside the warp's segment (< 512), two per register
+        const u32 seg = (u32)warp * (RS_TILE / RS_WARPS);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
-        if (lane == 31) wtot[warp] = incl;
+        for (int r = 0; r < RS_CHUNKS; ++r) {
+            const u32 li = seg + (u32)r * 32u + (u32)lane;
+            const bool have = li < tile_n;
+            const u32 d = have ? ((u32)(in[li] >> shift) & 255u) : 0u;
+            u32 peers = __ballot_sync(0xffffffffu, have);
+#pragma unroll
+            for (int bit = 0; bit < 8; ++bit) {
+                const u32 v = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+                peers &= ((d >> bit) & 1u) ? v : ~v;
+            }
+            const u32 lr = __popc(peers & ((1u << lane) - 1u));
+            const u32 prev = have ? sm.whist[warp][d] : 0u;
+            if (r & 1) rnk2[r >> 1] |= (prev + lr) << 16; else rnk2[r >> 1] = prev + lr;
+            __syncwarp();
+            if (have && lr == 0) sm.whist[warp][d] = prev + __popc(peers);
+            __syncwarp();
+        }
         __syncthreads();
-        u32 before = 0;
+        {
+            // digit tid: counts of the warps -> their first slots; tile count -> exclusive scan over the digits
+            u32 run = 0;
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; ++w) before += w < warp ? wtot[w] : 0u;
-        const u32 ds = before + incl - run;
-        dstart[tid] = ds;
-        gbase[tid] = M[(u64)tid * n_tiles + blockIdx.x] - ds;
-    }
-    __syncthreads();
+            for (int w = 0; w < RS_WARPS; ++w) { const u32 x = sm.whist[w][tid]; sm.whist[w][tid] = run; run += x; }
+            u32 incl = run;
 #pragma unroll
-    for (int r = 0; r < RS_CHUNKS; ++r) {
-        const u32 li = seg + (u32)r * 32u + (u32)lane;
-        if (li < tile_n) {
-            const u32 d = (u32)(key[r] >> shift) & 255u;
-            skeys[dstart[d] + whist[warp][d] + ((rnk2[r >> 1] >> (16 * (r & 1))) & 0xFFFFu)] = key[r];
+            for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+            if (lane == 31) sm.wtot[warp] = incl;
+            __syncthreads();
+            u32 before = 0;
+#pragma unroll
+            for (int w = 0; w < RS_WARPS; ++w) before += w < warp ? sm.wtot[w] : 0u;
+            const u32 ds = before + incl - run;
+            sm.dstart[tid] = ds;
+            sm.gbase[tid] = M[(u64)tid * n_tiles + tile] - ds;
         }
-    }
-    __syncthreads();
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < RS_CHUNKS; ++r) {
+            const u32 li = seg + (u32)r * 32u + (u32)lane;
+            if (li < tile_n) {
+                const u64 key = in[li];
+                const u32 d = (u32)(key >> shift) & 255u;
+                sm.skeys[sm.dstart[d] + sm.whist[warp][d] + ((rnk2[r >> 1] >> (16 * (r & 1))) & 0xFFFFu)] = key;
+            }
+        }
+        __syncthreads();
 #pragma unroll 4
-    for (int j = 0; j < RS_CHUNKS; ++j) {
-        const u32 idx = (u32)j * RS_THREADS + (u32)tid;
-        if (idx < tile_n) {
-            const u64 k = skeys[idx];
-            out[gbase[(u32)(k >> shift) & 255u] + idx] = k;
+        for (int j = 0; j < RS_CHUNKS; ++j) {
+            const u32 idx = (u32)j * RS_THREADS + (u32)tid;
+            if (idx < tile_n) {
+                const u64 k = sm.skeys[idx];
+                out[sm.gbase[(u32)(k >> shift) & 255u] + idx] = k;
+            }
         }
+        __syncthreads();                                            // skeys / whist / in[buf] are free again
+        cur_bulk = next_bulk;
     }
+}
+
+// the scatter's launch: persistent grid of 2 CTAs per SM (107 KB of shared memory each)
+cudaError_t rs_scatter_launch(const u64* keys, u64 n, int shift, u64 n_tiles, const u64* M, u64* out, cudaStream_t stream)
+{
+    static int grid_cap[64] = {0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (grid_cap[dev] == 0) {
+        int sms = 0, occ = 0;
+        if ((e = cudaFuncSetAttribute(rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem))) != cudaSuccess) return e;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rs_scatter, RS_THREADS, sizeof(RsSmem))) != cudaSuccess) return e;
+        grid_cap[dev] = sms * (occ < 1 ? 1 : occ);
+    }
+    const unsigned grid = (unsigned)(n_tiles < (u64)grid_cap[dev] ? n_tiles : (u64)grid_cap[dev]);
+    rs_scatter<<<grid, RS_THREADS, sizeof(RsSmem), stream>>>(keys, n, shift, n_tiles, M, out);
+    return cudaGetLastError();
 }
 
 // ---- u64 exclusive scan (same three-kernel scheme as payload_kernel.cu) ---------------------------------------------------
@@ -339,7 +413,7 @@ cudaError_t radix_sort_u64(unsigned long long* keys, unsigned long long* tmp, un
         rs_count<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(src, n, 8 * p, n_tiles, M);
         cudaError_t e = ss_scan(M, m, sums, nullptr, stream);
         if (e != cudaSuccess) return e;
-        rs_scatter<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(src, n, 8 * p, n_tiles, M, dst);
+        if ((e = rs_scatter_launch(src, n, 8 * p, n_tiles, M, dst, stream)) != cudaSuccess) return e;
         u64* t = src; src = dst; dst = t;
         *launches += 5;
     }
@@ -428,7 +502,7 @@ cudaError_t partition_by_digit_u64(const unsigned long long* keys, unsigned long
     if (e != cudaSuccess) return e;
     e = cudaMemcpy2DAsync(bin_start, 8, M, n_tiles * 8, 8, 256, cudaMemcpyDeviceToDevice, stream);   // M[d][0]: where digit d starts
     if (e != cudaSuccess) return e;
-    rs_scatter<<<(unsigned)n_tiles, RS_THREADS, 0, stream>>>(keys, n, shift, n_tiles, M, out);
+    if ((e = rs_scatter_launch(keys, n, shift, n_tiles, M, out, stream)) != cudaSuccess) return e;
     *launches += 5;
     return cudaGetLastError();
 }
