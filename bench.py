@@ -355,6 +355,29 @@ def run_extras(torch, dist, ctx, dev, flush, world, rank):
                                      "note": "32 batches of 1 M reads (4.8 Gbp) of the 100 M-read configuration, 32 / N batches per rank"}
     del run
     torch.cuda.empty_cache()
+    # ---- the other views of the path on this rank's 100 Mbp shard, device-resident: kmer_view (the HBM-bound kernel) and the closed
+    # syncmer filter (every rank runs its own shard: weak scaling, like the headline)
+    peak, _ = load_peaks()
+    bases_h, _, _ = build_rank_input(rank, world)
+    nb = min(bases_h.size, SHARD)
+    d = torch.from_numpy(bases_h[:nb]).to(dev)
+    d_lo = torch.empty(nb, dtype=torch.int64, device=dev)
+    d_pos = torch.empty(nb, dtype=torch.int64, device=dev)
+    for name, kw in (("kmer_view_k31", {}), ("syncmers_k31_m19", {"syncmer": (19, 0, 12)})):
+        ms, cnt = [], 0
+        for i in range(4):
+            flush.zero_()
+            torch.cuda.synchronize()
+            cnt = ctx.kmers_device(d.data_ptr(), nb, 31, True, d_lo.data_ptr(), 0, d_pos.data_ptr(), nb, **kw)
+            if i:
+                ms.append(ctx.stats()["kernel_ms"])
+        t, rec, bases = reduce(float(np.median(ms)), cnt, nb)
+        algo = (nb + 16 * cnt) / 1e9
+        out[name] = {"scaling": "weak", "n_gpus": world, "bases": bases, "records": rec, "kernel_ms_max_over_ranks": t, "Gbases_per_s": bases / t / 1e6,
+                     "achieved_GBps_per_gpu": algo / (float(np.median(ms)) * 1e-3), "frac_of_hbm_peak": algo / (float(np.median(ms)) * 1e-3) / peak,
+                     "algorithmic_bytes": "1 B per base + 16 B per (kept) k-mer"}
+    del d, d_lo, d_pos
+    torch.cuda.empty_cache()
     # ---- the reference's downstream pipeline (tests/test_jaccard.cpp: k-mers -> sort -> unique -> Jaccard) over two related genomes of
     # 200 Mbp, cut over the ranks by k-mer start: local sort + unique, all-to-all by key range over NVLink, merge, per-range Jaccard
     from biolib_b200 import multi_gpu as mg

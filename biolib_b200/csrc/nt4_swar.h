@@ -6,7 +6,7 @@
 //   code = ((c >> 1) ^ (c >> 2)) & 3   ->  A0 C1 G2 T3 (and U3),
 // and validity is decided exactly (only the ten letters above are valid), so '@', 'E', 'W' ...
 // which alias a code are flagged bad. Plain C++ (no CUDA types) so that the same function is
-// compiled for the device and checked exhaustively on the host by tests/test_nt4_swar.py.
+// compiled for the device and checked exhaustively on the host by tests/test_host_side.py::test_nt4_swar_exhaustive.
 #ifndef BIOLIB_B200_NT4_SWAR_H
 #define BIOLIB_B200_NT4_SWAR_H
 
