@@ -912,7 +912,7 @@ int blg_super_kmer_payloads(blg_ctx* c, const char* bases, size_t n, const uint6
     unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + payload_scratch_bytes(cnt, n_buckets) / 8 * 8);
     int launches = 0;
     cudaEventRecord(c->ev0, c->stream);
-    cudaError_t e = payload_launch(d_bases, reinterpret_cast<unsigned long long*>(rec.value), reinterpret_cast<unsigned long long*>(rec.mm_start), rec.size,
+    cudaError_t e = payload_launch(d_bases, (unsigned long long)n, reinterpret_cast<unsigned long long*>(rec.value), reinterpret_cast<unsigned long long*>(rec.mm_start), rec.size,
                                    rec.mm_pos, cnt, k, (unsigned long long)(uint32_t)p->seed ^ 8ULL, n_buckets, c->rank.p, d_v, d_mm, d_sz, d_mp, d_ps,
                                    d_bo, d_words, d_tot, c->stream, &launches);
     cudaEventRecord(c->ev1, c->stream);

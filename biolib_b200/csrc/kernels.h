@@ -159,7 +159,7 @@ cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fast
 
 // payload_kernel.cu: records -> bucket-ordered records + their bases as one 2-bit packed stream
 size_t payload_scratch_bytes(unsigned long long n_records, unsigned int n_buckets);
-cudaError_t payload_launch(const unsigned char* bases, const unsigned long long* value, const unsigned long long* mm_start, const unsigned char* size,
+cudaError_t payload_launch(const unsigned char* bases, unsigned long long n_bases, const unsigned long long* value, const unsigned long long* mm_start, const unsigned char* size,
                            const unsigned char* mm_pos, unsigned long long n, int k, unsigned long long s8, unsigned int n_buckets, void* scratch,
                            unsigned long long* o_value, unsigned long long* o_mm, unsigned char* o_size, unsigned char* o_pos,
                            unsigned long long* o_pstart, unsigned long long* bucket_offsets, unsigned long long* words,

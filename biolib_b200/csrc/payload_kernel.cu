@@ -177,10 +177,12 @@ __device__ __forceinline__ u32 codes8_msb_first(u64 w)
 }
 
 __global__ void __launch_bounds__(256) pl_pack(const unsigned char* __restrict__ bases, const u64* __restrict__ mm_start, const u8* __restrict__ mm_pos,
-                                               const u64* __restrict__ pstart, const u8* __restrict__ size, int k, u64 n, u64* __restrict__ words)
+                                               const u64* __restrict__ pstart, const u8* __restrict__ size, int k, u64 n, u64 n_bases,
+                                               u64* __restrict__ words)
 {
     const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
     if (r >= n) return;
+    const unsigned char* const buf_end = bases + n_bases;
     const unsigned char* p = bases + (mm_start[r] - mm_pos[r]);       // first base of the super-k-mer
     int left = (int)size[r] + k - 1;                                     // bases to go
     u64 e = pstart[r];                                                   // element index in the packed stream
@@ -191,7 +193,17 @@ __global__ void __launch_bounds__(256) pl_pack(const unsigned char* __restrict__
     int skip = (int)(reinterpret_cast<uintptr_t>(p) & 7u);               // bytes of the first aligned word that lie before the record
     const u64* q = reinterpret_cast<const u64*>(p - skip);
     while (left > 0) {
-        u32 chunk = codes8_msb_first(__ldg(q++));
+        // an aligned word that sticks out of the buffer (its first or last few bytes) is put together byte by byte
+        const unsigned char* g = reinterpret_cast<const unsigned char*>(q);
+        u64 w8;
+        if (g >= bases && g + 8 <= buf_end) w8 = __ldg(q);
+        else {
+            w8 = 0;
+#pragma unroll 1
+            for (int i = 0; i < 8; ++i) if (g + i >= bases && g + i < buf_end) w8 |= (u64)g[i] << (8 * i);
+        }
+        ++q;
+        u32 chunk = codes8_msb_first(w8);
         int nb = 8 - skip;
         chunk = (chunk << (2 * skip)) & 0xFFFFu;
         skip = 0;
@@ -234,7 +246,7 @@ size_t payload_scratch_bytes(unsigned long long n_records, unsigned int n_bucket
 
 // All pointers device. words must be zeroed by the caller ((total bases * 2) / 64 + 1 entries, total bases <= n (w + k - 1)).
 // o_pstart doubles as the length array before its scan. totals[0] = payload bases.
-cudaError_t payload_launch(const unsigned char* bases, const unsigned long long* value, const unsigned long long* mm_start, const unsigned char* size,
+cudaError_t payload_launch(const unsigned char* bases, unsigned long long n_bases, const unsigned long long* value, const unsigned long long* mm_start, const unsigned char* size,
                            const unsigned char* mm_pos, unsigned long long n, int k, unsigned long long s8, unsigned int n_buckets, void* scratch,
                            unsigned long long* o_value, unsigned long long* o_mm, unsigned char* o_size, unsigned char* o_pos,
                            unsigned long long* o_pstart, unsigned long long* bucket_offsets, unsigned long long* words,
@@ -261,7 +273,7 @@ cudaError_t payload_launch(const unsigned char* bases, const unsigned long long*
                                                                   o_pos, o_pstart);
     e = scan_u64(o_pstart, n, sums, totals, stream);
     if (e != cudaSuccess) return e;
-    pl_pack<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(bases, o_mm, o_pos, o_pstart, o_size, k, n, words);
+    pl_pack<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(bases, o_mm, o_pos, o_pstart, o_size, k, n, n_bases, words);
     *launches = 10;
     return cudaGetLastError();
 }
