@@ -25,7 +25,7 @@ EXPORTS = [
     "blg_last_stats", "blg_async_count", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
     "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out", "blg_sorted_unique_kmers", "blg_kmer_jaccard",
-    "blg_sort_unique_u64", "blg_sorted_sets_jaccard", "blg_lower_bound_u64", "blg_partition_by_top_byte",
+    "blg_sort_unique_u64", "blg_sorted_sets_jaccard", "blg_lower_bound_u64", "blg_partition_by_top_byte", "blg_kmers_static_scratch",
 ]
 
 
@@ -130,6 +130,7 @@ def lib() -> C.CDLL:
     L.blg_sorted_sets_jaccard.argtypes = [vp, vp, sz, vp, sz, C.c_int, C.POINTER(JaccardOut)]
     L.blg_lower_bound_u64.argtypes = [vp, vp, sz, vp, sz, vp]
     L.blg_partition_by_top_byte.argtypes = [vp, vp, sz, C.c_int, vp, vp]
+    L.blg_kmers_static_scratch.argtypes = [vp, sz, C.c_uint8, C.c_int, vp, vp, vp, u64, vp, vp, C.POINTER(u64), C.c_char_p, sz]
     L.blg_synth_generate.argtypes = [u64, sz, vp]
     L.blg_synth_mutate.argtypes = [vp, sz, C.c_double, C.c_double, C.c_double, u64, vp, sz, C.POINTER(sz), vp, vp]
     _lib = L

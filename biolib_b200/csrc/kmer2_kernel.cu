@@ -257,6 +257,7 @@ __global__ void __launch_bounds__(K2T + 32, K2_MIN_BLOCKS) kmer2_kernel(const Km
     // bases of the tile about to be staged, requested one iteration ahead (word tid, and K2T + tid)
     bool have_pre = false;
     uint4 pre0 = make_uint4(0, 0, 0, 0), pre1 = pre0;
+    (void)pre1;                         // only the tiles with more than K2T staged words use the second register
     for (;;) {
         const bool have = tile < a.num_tiles;
         if (!have && !have_prev) break;
@@ -600,3 +601,107 @@ cudaError_t kmer2_launch(const KmerArgs& args, const KmerLaunchPlan& plan, cudaS
 }
 
 }  // namespace blg
+
+// ---- blg_kmers_static_scratch: the k-mer kernel for callers that may not allocate ----------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid it). Same kernel and same results as blg_kmers with device input
+// and device output; its scan scratch (ticket counter, record total, one look-back word per tile) lives in the file-scope device
+// array below instead of the context's cudaMalloc'ed buffers, so the call allocates nothing: no context, no cudaMalloc / cudaFree,
+// no allocating library routine. Every GPU that loads the library holds the array (129 KB) until the process exits.
+#include <cstdio>
+#include <mutex>
+#include "../../include/biolib_gpu.h"
+
+namespace {
+
+constexpr size_t K2_STATIC_MAX_BASES = (size_t)1 << 26;              // 64 Mi bases per call
+constexpr int K2_STATIC_MAX_TILES = 16384;                           // look-back words (64 Mi bases are 8457 of the small tiles at most)
+constexpr int K2_STATIC_CTRL = 32;                                   // words in front of them: [0] ticket counter, [1] record total
+// In host code this name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress (k2_static_setup).
+static __device__ __align__(256) unsigned long long k2_static_scratch[K2_STATIC_CTRL + K2_STATIC_MAX_TILES];
+
+struct K2StaticDev { unsigned long long* scratch; int sm_count; bool ready; };
+K2StaticDev k2_static_dev[64] = {};
+std::mutex k2_static_mutex;
+
+// once per device, with that device current: the array's address on THIS device, and the device's SM count
+cudaError_t k2_static_setup(int dev, K2StaticDev* out)
+{
+    std::lock_guard<std::mutex> lock(k2_static_mutex);
+    if (!k2_static_dev[dev].ready) {
+        unsigned long long* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), k2_static_scratch);
+        if (e != cudaSuccess) return e;
+        int sms = 0;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        k2_static_dev[dev] = {p, sms, true};
+    }
+    *out = k2_static_dev[dev];
+    return cudaSuccess;
+}
+
+int k2_static_fail(char* err, size_t err_len, int status, const char* what, const char* detail = "")
+{
+    if (err && err_len) snprintf(err, err_len, "blg_kmers_static_scratch: %s%s", what, detail);
+    return status;
+}
+
+}  // namespace
+
+extern "C" int blg_kmers_static_scratch(const char* d_bases, size_t n_bases, uint8_t k, int canonical, uint64_t* d_value_lo, uint64_t* d_value_hi,
+                                        uint64_t* d_position, uint64_t capacity, void* stream, uint64_t* d_count, uint64_t* count, char* err,
+                                        size_t err_len)
+{
+    using namespace blg;
+    if (err && err_len) err[0] = 0;
+    if (count) *count = 0;
+    if (k == 0 || k > 64) return k2_static_fail(err, err_len, BLG_E_INVALID, "need 1 <= k <= 64");
+    if (n_bases > K2_STATIC_MAX_BASES)
+        return k2_static_fail(err, err_len, BLG_E_CAPACITY, "n_bases exceeds the static scratch's limit of 67108864 (2^26) bases per call; use blg_kmers");
+    if (n_bases && !d_bases) return k2_static_fail(err, err_len, BLG_E_INVALID, "d_bases is null");
+    if (capacity && (!d_value_lo || (k > 32 && !d_value_hi))) return k2_static_fail(err, err_len, BLG_E_INVALID, "value arrays missing");
+    if (!d_count && !count) return k2_static_fail(err, err_len, BLG_E_INVALID, "give d_count (device) or count (host; the call then waits for the stream)");
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return k2_static_fail(err, err_len, BLG_E_CUDA, "cudaGetDevice: ", cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return k2_static_fail(err, err_len, BLG_E_UNSUPPORTED, "device ordinal above 63");
+    K2StaticDev sd;
+    if ((e = k2_static_setup(dev, &sd)) != cudaSuccess) return k2_static_fail(err, err_len, BLG_E_CUDA, "cudaGetSymbolAddress: ", cudaGetErrorString(e));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint64_t nwin = n_bases >= (size_t)k ? n_bases - k + 1 : 0;
+
+    KmerArgs a{};
+    a.bases = reinterpret_cast<const unsigned char*>(d_bases);
+    a.buf_lo = 0; a.buf_hi = (long long)n_bases;
+    a.win_lo = 0; a.win_hi = (long long)nwin;
+    a.k = k; a.canonical = canonical ? 1 : 0;
+    a.vec_ok = (reinterpret_cast<uintptr_t>(d_bases) & 15u) == 0;
+    a.value_lo = reinterpret_cast<unsigned long long*>(d_value_lo);
+    a.value_hi = k > 32 ? reinterpret_cast<unsigned long long*>(d_value_hi) : nullptr;
+    a.position = reinterpret_cast<unsigned long long*>(d_position);
+    a.capacity = capacity;
+    KmerLaunchPlan plan{};
+    if (nwin) {
+        if ((e = kmer2_plan(a, sd.sm_count, &plan)) != cudaSuccess) return k2_static_fail(err, err_len, BLG_E_CUDA, "kmer2_plan: ", cudaGetErrorString(e));
+        if (a.num_tiles > K2_STATIC_MAX_TILES) return k2_static_fail(err, err_len, BLG_E_CAPACITY, "more tiles than the static scratch holds");
+    }
+    // the array keeps the last call's contents: what the kernel expects to be zero is cleared here, on the caller's stream
+    const size_t clear_words = (size_t)K2_STATIC_CTRL + (size_t)(nwin ? a.num_tiles : 0);
+    if ((e = cudaMemsetAsync(sd.scratch, 0, clear_words * 8, st)) != cudaSuccess) return k2_static_fail(err, err_len, BLG_E_CUDA, "cudaMemsetAsync: ", cudaGetErrorString(e));
+    if (nwin) {
+        a.tile_counter = reinterpret_cast<unsigned int*>(sd.scratch);
+        a.total = sd.scratch + 1;
+        a.tile_status = sd.scratch + K2_STATIC_CTRL;
+        if ((e = kmer2_launch(a, plan, st)) != cudaSuccess) return k2_static_fail(err, err_len, BLG_E_CUDA, "launch: ", cudaGetErrorString(e));
+    }
+    if (d_count && (e = cudaMemcpyAsync(d_count, sd.scratch + 1, 8, cudaMemcpyDeviceToDevice, st)) != cudaSuccess)
+        return k2_static_fail(err, err_len, BLG_E_CUDA, "cudaMemcpyAsync: ", cudaGetErrorString(e));
+    if (count) {
+        unsigned long long total = 0;
+        if ((e = cudaMemcpyAsync(&total, sd.scratch + 1, 8, cudaMemcpyDeviceToHost, st)) != cudaSuccess || (e = cudaStreamSynchronize(st)) != cudaSuccess)
+            return k2_static_fail(err, err_len, BLG_E_CUDA, "reading the count: ", cudaGetErrorString(e));
+        *count = total;
+        if (total > capacity) return k2_static_fail(err, err_len, BLG_E_CAPACITY, "output capacity too small (*count holds the required size)");
+    }
+    return BLG_OK;
+}

@@ -209,6 +209,27 @@ int blg_hash_sampled_kmers(blg_ctx* ctx, const char* bases, size_t n_bases, cons
                            const blg_params* p, uint64_t threshold, blg_kmer_out* out);
 
 /*
+ * blg_kmers for callers that may not allocate. No counterpart in the reference: added for code
+ * that cannot call cudaMalloc (under CUDA graph capture, in tight serving loops, in harnesses that forbid it). The same kernel and
+ * the same (value, position) records as blg_kmers with BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT, one sequence, but context-free: it
+ * runs on the CURRENT device, on `stream` (a cudaStream_t; NULL = the legacy default stream), and its scan scratch is a static
+ * device array of the library (129 KB per GPU that loads the library, held until exit) instead of cudaMalloc'ed buffers. It calls
+ * no cudaMalloc, cudaFree or allocating library routine.
+ *   limit     n_bases <= 67108864 (2^26); beyond it BLG_E_CAPACITY (and the text in err). Longer inputs: blg_kmers, or several calls
+ *   inputs    d_bases (device, ASCII), k 1..64, canonical 0 / 1
+ *   outputs   d_value_lo[capacity], d_value_hi[capacity] (k > 32 only, else may be NULL), d_position[capacity] (may be NULL): device
+ *             memory of the caller; at most n_bases - k + 1 records
+ *   count     d_count (device, 8 bytes) and / or count (host). With `count` the call waits for the stream and returns BLG_E_CAPACITY if
+ *             the records did not fit (*count = required size); with d_count alone it only enqueues. One of the two is required
+ *   err       optional buffer for the error text (err_len bytes)
+ * All calls on a device share the one scratch array; the call clears what must start at zero on `stream` first. Calls that overlap on
+ * the GPU (different streams, or different threads without ordering between their streams) race on it: serialise them.
+ */
+int blg_kmers_static_scratch(const char* d_bases, size_t n_bases, uint8_t k, int canonical, uint64_t* d_value_lo, uint64_t* d_value_hi,
+                             uint64_t* d_position, uint64_t capacity, void* stream, uint64_t* d_count, uint64_t* count, char* err,
+                             size_t err_len);
+
+/*
  * The reference's one downstream pipeline (tests/test_jaccard.cpp:55-130) on the device, k <= 32:
  *   blg_sorted_unique_kmers  kmer_view values -> emem::external_memory_vector (sorted, include/external_memory_vector.hpp:186-196,
  *                            320-341) -> sampler::ordered_unique_sampler (include/ordered_unique_sampler.hpp:116-130): the distinct
