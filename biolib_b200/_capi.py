@@ -21,7 +21,7 @@ F_ASYNC = 0x80
 F_RUNS = 0x100
 
 EXPORTS = [
-    "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_last_error",
+    "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_set_pipeline", "blg_last_error",
     "blg_last_stats", "blg_async_count", "blg_device_info", "blg_host_alloc", "blg_host_free", "blg_kmers", "blg_minimizers",
     "blg_super_kmers", "blg_super_kmers_range", "blg_hash64", "blg_minimizer_positions", "blg_syncmers", "blg_hash_sampled_kmers", "blg_free_kmer_out", "blg_free_sk_out",
     "blg_synth_generate", "blg_synth_mutate", "blg_pack_bases", "blg_super_kmers_packed", "blg_parse_fastx", "blg_free_fastx_out", "blg_super_kmer_payloads", "blg_free_payload_out", "blg_sorted_unique_kmers", "blg_kmer_jaccard",
@@ -97,6 +97,7 @@ def lib() -> C.CDLL:
     L.blg_create.argtypes = [C.c_int, C.POINTER(vp)]
     L.blg_destroy.argtypes = [vp]
     L.blg_set_stream.argtypes = [vp, vp]
+    L.blg_set_pipeline.argtypes = [vp, C.c_int, C.c_int]
     L.blg_last_error.restype = C.c_char_p
     L.blg_last_error.argtypes = [vp]
     L.blg_last_stats.argtypes = [vp, C.POINTER(Stats)]

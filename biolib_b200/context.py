@@ -225,6 +225,21 @@ class Context:
             self.L.blg_free_sk_out(self.h, C.byref(out))
         return res
 
+    def super_kmers_packed_raw(self, codes_ptr: int, n_bases: int, break_start_ptr: int, break_len_ptr: int, n_breaks: int, k: int, m: int,
+                               seed: int, canonical: bool, value_ptr: int, mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int,
+                               flags: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0) -> int:
+        """blg_super_kmers_packed with caller-owned (pinned) host arrays; with F_RUNS the number of runs is left in self.last_n_runs."""
+        seq = _capi.PackedSeq(codes=codes_ptr, n_bases=n_bases, break_start=break_start_ptr or None, break_len=break_len_ptr or None,
+                              n_breaks=n_breaks)
+        p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
+        out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr or None, size=size_ptr or None,
+                    mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None, n_runs=0, run_capacity=run_capacity,
+                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None)
+        lo, hi = (0, 2**64 - 1) if win_range is None else win_range
+        self._check(self.L.blg_super_kmers_packed(self.h, C.byref(seq), None, 0, int(lo), int(hi), C.byref(p), C.byref(out)))
+        self.last_n_runs = int(out.n_runs)
+        return out.count
+
     def parse_fastx(self, text, fmt: int = -1):
         """blg_parse_fastx (device record splitter): FASTA / FASTQ text -> (bases uint8, seq_offsets uint64[n_seq + 1])."""
         t = _as_bytes_array(text)

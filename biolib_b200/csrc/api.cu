@@ -81,6 +81,8 @@ struct blg_ctx {
     bool async_call = false;                 // BLG_F_ASYNC: run_sk_once only enqueues
     uint64_t async_capacity = 0;
     const unsigned char* staged = nullptr;  // set while a packed-input call runs: the bases are already unpacked in `in`
+    const blg_packed_seq* packed_lazy = nullptr;   // ... or, for the chunked host path, still on the host: sk_pipelined uploads + unpacks piece by piece
+    size_t lazy_breaks = 0;
     DevBuf packed, brk, fx_text, fx_scratch; // packed codes + break list of a packed-input call; FASTA/FASTQ text and parser scratch
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
@@ -401,8 +403,9 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     int rc;
     if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
     const uint64_t cap = out->capacity > 0 ? out->capacity : estimate_records(nwin, w);
-    const bool staged = c->staged != nullptr;           // packed input: the bases are on the device already, nothing to upload
-    if (!staged && (rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
+    const blg_packed_seq* lazy = c->packed_lazy;        // packed input that is still on the host: uploaded and unpacked piece by piece below
+    const bool staged = c->staged != nullptr && !lazy;  // packed input that is on the device already, unpacked: nothing to upload
+    if (!staged && !lazy && (rc = ensure(c, c->in, n + 64)) != BLG_OK) return rc;
     if ((rc = ensure(c, c->o_value, cap * 8)) != BLG_OK || (rc = ensure(c, c->o_mm, cap * posb)) != BLG_OK) return rc;
     if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
     if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
@@ -449,12 +452,20 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         end = (end > n ? n : end);
         if (i < nch - 1) end = end / 16 * 16;
         if (staged) { up[i] = n; continue; }
-        if (end > sent) CK(c, cudaMemcpyAsync(d_in + sent, bases + sent, end - sent, cudaMemcpyHostToDevice, c->s_in));
+        if (end > sent && lazy) {
+            // 0.25 B per base over PCIe: the piece's packed words, then unpack + breaks on the upload stream (sent is a multiple of 16)
+            const size_t w0 = sent / 16, w1 = (end + 15) / 16;
+            CK(c, cudaMemcpyAsync(static_cast<char*>(c->packed.p) + w0 * 4, reinterpret_cast<const char*>(lazy->codes) + w0 * 4, (w1 - w0) * 4,
+                                  cudaMemcpyHostToDevice, c->s_in));
+            const unsigned long long* d_bs = static_cast<const unsigned long long*>(c->brk.p);
+            CK(c, unpack_range_launch(c->packed.p, w0, w1, n, d_bs, reinterpret_cast<const unsigned int*>(d_bs + c->lazy_breaks), c->lazy_breaks, d_in, c->s_in));
+            c->stats.kernel_launches += c->lazy_breaks ? 2 : 1;
+        } else if (end > sent) CK(c, cudaMemcpyAsync(d_in + sent, bases + sent, end - sent, cudaMemcpyHostToDevice, c->s_in));
         CK(c, cudaEventRecord(c->ev_in[i], c->s_in));
         sent = end > sent ? end : sent;
         up[i] = sent;
     }
-    if (!staged) c->stats.bytes_h2d += n;
+    if (!staged && !lazy) c->stats.bytes_h2d += n;
     uint64_t done = 0;
     bool overflow = false;
     for (int i = 0; i < nch && !overflow; ++i) {
@@ -783,6 +794,14 @@ int blg_set_stream(blg_ctx* c, void* s)
     return BLG_OK;
 }
 
+int blg_set_pipeline(blg_ctx* c, int chunk_mi, int first_div)
+{
+    if (!c || chunk_mi < 1 || chunk_mi > 1024 || first_div < 1 || first_div > 64) return BLG_E_INVALID;
+    c->pipe_chunk_m = chunk_mi;
+    c->pipe_first_div = first_div;
+    return BLG_OK;
+}
+
 const char* blg_last_error(blg_ctx* c) { return c ? c->err.c_str() : "no context"; }
 
 int blg_async_count(blg_ctx* c, uint64_t* count)
@@ -861,17 +880,29 @@ int blg_super_kmers_packed(blg_ctx* c, const blg_packed_seq* seq, const uint64_t
     c->stats = blg_stats{};
     unsigned long long* d_bs = static_cast<unsigned long long*>(c->brk.p);
     unsigned int* d_bl = reinterpret_cast<unsigned int*>(d_bs + seq->n_breaks);
-    if (words) CK(c, cudaMemcpyAsync(c->packed.p, seq->codes, words * 4, cudaMemcpyHostToDevice, c->stream));
+    // inputs that take the chunked host path (same test as sk_pipelined's) are uploaded and unpacked there, piece by piece, overlapped with
+    // the kernels and the record download; everything else is staged here in one go
+    uint64_t hi = n >= (size_t)p->k ? n - p->k + 1 : 0;
+    if (win_end < hi) hi = win_end;
+    const uint64_t lo = win_begin < hi ? win_begin : hi;
+    const bool lazy = !(p->flags & BLG_F_DEVICE_OUTPUT) && hi - lo >= (8u << 20);
+    cudaStream_t up = lazy ? c->s_in : c->stream;
     if (seq->n_breaks) {
-        CK(c, cudaMemcpyAsync(d_bs, seq->break_start, seq->n_breaks * 8, cudaMemcpyHostToDevice, c->stream));
-        CK(c, cudaMemcpyAsync(d_bl, seq->break_len, seq->n_breaks * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaMemcpyAsync(d_bs, seq->break_start, seq->n_breaks * 8, cudaMemcpyHostToDevice, up));
+        CK(c, cudaMemcpyAsync(d_bl, seq->break_len, seq->n_breaks * 4, cudaMemcpyHostToDevice, up));
     }
-    CK(c, unpack_launch(c->packed.p, n, d_bs, d_bl, seq->n_breaks, static_cast<unsigned char*>(c->in.p), c->stream));
     c->stats.bytes_h2d = words * 4 + seq->n_breaks * 12;
-    c->stats.kernel_launches = seq->n_breaks ? 2 : 1;
+    if (!lazy) {
+        if (words) CK(c, cudaMemcpyAsync(c->packed.p, seq->codes, words * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(c, unpack_launch(c->packed.p, n, d_bs, d_bl, seq->n_breaks, static_cast<unsigned char*>(c->in.p), c->stream));
+        c->stats.kernel_launches = seq->n_breaks ? 2 : 1;
+    }
     c->staged = static_cast<const unsigned char*>(c->in.p);
+    c->packed_lazy = lazy ? seq : nullptr;
+    c->lazy_breaks = seq->n_breaks;
     rc = sk_common(c, reinterpret_cast<const char*>(c->in.p), n, offs, n_seq, win_begin, win_end, p, out, true);
     c->staged = nullptr;
+    c->packed_lazy = nullptr;
     return rc;
 }
 

@@ -40,13 +40,14 @@ __global__ void __launch_bounds__(256) unpack_kernel(const u32* __restrict__ cod
     out[i] = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-__global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __restrict__ out, size_t n_bases, const u64* __restrict__ start,
+__global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __restrict__ out, size_t clip_lo, size_t clip_hi, const u64* __restrict__ start,
                                                            const u32* __restrict__ len, size_t n_breaks)
 {
+    // every break interval, clipped to the bases [clip_lo, clip_hi) that exist in `out` so far
     for (size_t b = blockIdx.x; b < n_breaks; b += gridDim.x) {
-        const u64 s = start[b];
-        const u64 l = len[b];
-        for (u64 i = threadIdx.x; i < l && s + i < n_bases; i += blockDim.x) out[s + i] = 'N';
+        const u64 s = start[b], e = s + len[b];
+        const u64 lo = s > clip_lo ? s : clip_lo, hi = e < clip_hi ? e : clip_hi;
+        for (u64 pos = lo + threadIdx.x; pos < hi; pos += blockDim.x) out[pos] = 'N';
     }
 }
 
@@ -286,17 +287,26 @@ __global__ void __launch_bounds__(FX_THREADS) fx_pass3(const unsigned char* __re
 
 }  // namespace
 
+// words [word_lo, word_hi) of the packed stream (codes points at word 0, on the device) -> bases [16 word_lo, 16 word_hi) of out, then the
+// break intervals that fall inside them. unpack_launch does the whole input in one go; the chunked host path goes piece by piece.
+cudaError_t unpack_range_launch(const void* codes, size_t word_lo, size_t word_hi, size_t n_bases, const unsigned long long* break_start,
+                                const unsigned int* break_len, size_t n_breaks, unsigned char* out, cudaStream_t stream)
+{
+    if (word_hi <= word_lo) return cudaSuccess;
+    const size_t nw = word_hi - word_lo;
+    unpack_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, stream>>>(static_cast<const u32*>(codes) + word_lo, nw, reinterpret_cast<uint4*>(out) + word_lo);
+    if (n_breaks) {
+        const unsigned grid = (unsigned)(n_breaks < 4096 ? n_breaks : 4096);
+        const size_t hi = word_hi * 16 < n_bases ? word_hi * 16 : n_bases;
+        stamp_breaks_kernel<<<grid, 128, 0, stream>>>(out, word_lo * 16, hi, break_start, break_len, n_breaks);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t unpack_launch(const void* codes, size_t n_bases, const unsigned long long* break_start, const unsigned int* break_len,
                           size_t n_breaks, unsigned char* out, cudaStream_t stream)
 {
-    const size_t n_words = (n_bases + 15) / 16;
-    if (n_words == 0) return cudaSuccess;
-    unpack_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, stream>>>(static_cast<const u32*>(codes), n_words, reinterpret_cast<uint4*>(out));
-    if (n_breaks) {
-        const unsigned grid = (unsigned)(n_breaks < 4096 ? n_breaks : 4096);
-        stamp_breaks_kernel<<<grid, 128, 0, stream>>>(out, n_bases, break_start, break_len, n_breaks);
-    }
-    return cudaGetLastError();
+    return unpack_range_launch(codes, 0, (n_bases + 15) / 16, n_bases, break_start, break_len, n_breaks, out, stream);
 }
 
 size_t fastx_scratch_bytes(size_t n_text)

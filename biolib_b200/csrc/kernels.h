@@ -149,6 +149,8 @@ cudaError_t record_ids_launch(const unsigned char* bases, long long n_bases, con
 cudaError_t minpos_launch(const unsigned long long* values, size_t n, int k, int m, unsigned char* out, int sm_count, cudaStream_t stream);
 
 // ingest_kernel.cu: 2-bit packed input -> ASCII; FASTA / FASTQ text -> bases + seq_offsets
+cudaError_t unpack_range_launch(const void* codes, size_t word_lo, size_t word_hi, size_t n_bases, const unsigned long long* break_start,
+                                const unsigned int* break_len, size_t n_breaks, unsigned char* out, cudaStream_t stream);
 cudaError_t unpack_launch(const void* codes, size_t n_bases, const unsigned long long* break_start, const unsigned int* break_len,
                           size_t n_breaks, unsigned char* out, cudaStream_t stream);
 size_t fastx_scratch_bytes(size_t n_text);

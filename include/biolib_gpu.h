@@ -143,6 +143,10 @@ int blg_destroy(blg_ctx* ctx);
  * Device-resident calls (BLG_F_DEVICE_INPUT|BLG_F_DEVICE_OUTPUT with caller arrays) then only
  * enqueue work and one 8-byte count read-back. */
 int blg_set_stream(blg_ctx* ctx, void* cuda_stream);
+/* Shape of the chunked host path (inputs of 8 Mi k-mer starts and more with host buffers: upload, kernel and download of successive
+ * pieces overlap): pieces of chunk_mi Mi k-mer starts (at most 16 pieces per call), the first piece 1 / first_div of a regular one so
+ * that the download starts early. The defaults are tuned on a PCIe Gen5 x16 B200 box; results never depend on them. */
+int blg_set_pipeline(blg_ctx* ctx, int chunk_mi, int first_div);
 int blg_abi_version(void);
 const char* blg_strerror(int status);
 const char* blg_last_error(blg_ctx* ctx);

@@ -143,3 +143,47 @@ def test_fastx_parser(gpu, oracle):
         assert np.array_equal(v[:cnt].cpu().numpy().view(np.uint64), o["value"]) and np.array_equal(mm[:cnt].cpu().numpy().view(np.uint64), o["mm_start"])
     finally:
         gpu.free_fastx(fx)
+
+
+@pytest.mark.gpu
+def test_packed_input_chunked_upload(gpu):
+    """Packed input on the chunked host path is uploaded and unpacked piece by piece: break runs across the piece boundaries, the
+    10-byte layout, caller arrays, and the fall-back to the plain path when the caller's arrays are too small."""
+    import biolib_b200
+    from biolib_b200 import _capi
+    from biolib_b200.context import expand_runs
+    rng = np.random.default_rng(33)
+    n = 30_000_000
+    s = rand_seq(rng, n, 0.00005)
+    nwin = n - 30
+    for cut in (nwin // 2 // 4, nwin // 2 // 4 + (nwin - nwin // 2 // 4), 12_000_000):      # around where the pieces meet
+        c16 = cut // 16 * 16
+        s[max(c16 - 3000, 0): min(c16 + 3000, n)] = ord("N")
+        s[min(c16 + 5000, n - 1): min(c16 + 5001, n)] = ord("N")
+    codes, bs, bl = gpu.pack_bases(s)
+    a = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False)
+    cap = a["n"] + 100
+    v, mm = np.zeros(cap, np.uint64), np.zeros(cap, np.uint64)
+    sz, mp = np.zeros(cap, np.uint8), np.zeros(cap, np.uint8)
+    rf, rs = np.zeros(1 << 16, np.uint64), np.zeros(1 << 16, np.uint64)
+    cnt = gpu.super_kmers_packed_raw(codes.ctypes.data, n, bs.ctypes.data, bl.ctypes.data, bs.size, 31, 19, 42, True, v.ctypes.data, mm.ctypes.data,
+                                     sz.ctypes.data, mp.ctypes.data, cap)
+    st = gpu.stats()
+    assert cnt == a["n"] and st["bytes_h2d"] < n // 4 + bs.size * 12 + 4096 and st["kernel_launches"] >= 4
+    assert np.array_equal(v[:cnt], a["value"]) and np.array_equal(mm[:cnt], a["mm_start"]) and np.array_equal(sz[:cnt], a["size"])
+    v[:] = 0
+    cnt = gpu.super_kmers_packed_raw(codes.ctypes.data, n, bs.ctypes.data, bl.ctypes.data, bs.size, 31, 19, 42, True, v.ctypes.data, 0,
+                                     sz.ctypes.data, mp.ctypes.data, cap, flags=_capi.F_RUNS, run_ptrs=(rf.ctypes.data, rs.ctypes.data), run_capacity=1 << 16)
+    nr = gpu.last_n_runs
+    assert cnt == a["n"] and 3 < nr < (1 << 16)
+    assert np.array_equal(v[:cnt], a["value"]) and np.array_equal(expand_runs(rf[:nr], rs[:nr], sz[:cnt], mp[:cnt]), a["mm_start"])
+    with pytest.raises(biolib_b200.BlgError) as e:
+        gpu.super_kmers_packed_raw(codes.ctypes.data, n, bs.ctypes.data, bl.ctypes.data, bs.size, 31, 19, 42, True, v.ctypes.data, mm.ctypes.data,
+                                   sz.ctypes.data, mp.ctypes.data, 1000)
+    assert e.value.status == 3
+    # a window range in the middle of the packed input
+    lo, hi = 5_000_003, 29_000_000
+    b = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False, win_range=(lo, hi))
+    cnt = gpu.super_kmers_packed_raw(codes.ctypes.data, n, bs.ctypes.data, bl.ctypes.data, bs.size, 31, 19, 42, True, v.ctypes.data, mm.ctypes.data,
+                                     sz.ctypes.data, mp.ctypes.data, cap, win_range=(lo, hi))
+    assert cnt == b["n"] and np.array_equal(v[:cnt], b["value"]) and np.array_equal(mm[:cnt], b["mm_start"])
