@@ -19,38 +19,68 @@ typedef unsigned char u8;
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ u64 rotl64(u64 x, int r) { return (x << r) | (x >> (64 - r)); }
 
-// h ^= h >> 33 only touches the low word: lo ^= hi >> 1. With BLG_HASH_FMA_SHIFTS the shift is issued as IMAD.HI
-// (hi * 2^31 >> 32) on the fma pipe instead of SHF on the ALU pipe (the busiest unit of the fused kernels); measured
-// 2 % slower while the kernel is latency-bound (IMAD.HI holds the fma-heavy pipe twice as long), so it is opt-in.
-__device__ __forceinline__ u64 xorshift33(u64 h)
-{
-#ifdef BLG_HASH_FMA_SHIFTS
-    u32 hi = (u32)(h >> 32), lo = (u32)h, s;
-    asm("mul.hi.u32 %0, %1, 0x80000000;" : "=r"(s) : "r"(hi));
-    return ((u64)hi << 32) | (lo ^ s);
-#else
-    return h ^ (h >> 33);
-#endif
-}
-
+#ifdef BLG_HASH_PLAIN
+// The arithmetic as written in the reference, lowered by nvcc (development A/B builds only): 48 instructions per hash, 25 of them
+// on the ALU pipe.
 __device__ __forceinline__ u64 fmix64(u64 h)
 {
-    h = xorshift33(h); h *= 0xff51afd7ed558ccdULL;
-    h = xorshift33(h); h *= 0xc4ceb9fe1a85ec53ULL;
-    return xorshift33(h);
+    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL;
+    h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL;
+    return h ^ (h >> 33);
 }
-
-__device__ __forceinline__ u64 murmur3_key8(u64 key, u64 s8)
+__device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
 {
     u64 k1 = key * 0x87c37b91114253d5ULL;
     k1 = rotl64(k1, 31);
     k1 *= 0x4cf5ad432745937fULL;
-    u64 h1 = k1 ^ s8;      // (seed ^ k1) ^ len
-    u64 h2 = s8;           // seed ^ len
+    u64 h1 = k1 ^ (u64)s8;      // (seed ^ k1) ^ len
+    u64 h2 = (u64)s8;           // seed ^ len
     h1 += h2; h2 += h1;
     h1 = fmix64(h1); h2 = fmix64(h2);
     return h1 + h2;
 }
+#else
+// The same arithmetic with the lowering chosen by hand, because the fused kernels are bound by the ALU pipe (LOP3 / SHF / IADD3)
+// while the FMA pipe (IMAD) has room: 39 instructions per hash, 17 of them on the ALU pipe.
+//   x * c (low 64 bits) = IMAD.WIDE of the low words + two IMADs that accumulate the cross products into the high word. nvcc's
+//   own lowering computes the cross products beside the wide product and joins them with an IADD3 (shorter dependency chain,
+//   one more instruction, on the ALU pipe);
+//   64-bit + 32-bit = IMAD.WIDE a * 1 + c instead of IADD3 + IADD3.X;
+//   h ^= h >> 33 only touches the low word: lo ^= hi >> 1.
+// Measured on the fused kernel (profiles/r02_zn_hash_lowering_ab.txt): 209 -> 219 Gbases/s at k=31 m=19, 181 -> 198 on 150-bp reads.
+__device__ __forceinline__ void mul64c(u32& xl, u32& xh, u64 c)
+{
+    u32 pl, ph;
+    asm("{\n\t.reg .u64 p;\n\tmul.wide.u32 p, %2, %4;\n\tmov.b64 {%0, %1}, p;\n\tmad.lo.u32 %1, %3, %4, %1;\n\tmad.lo.u32 %1, %2, %5, %1;\n\t}"
+        : "=&r"(pl), "=&r"(ph) : "r"(xl), "r"(xh), "r"((u32)c), "r"((u32)(c >> 32)));
+    xl = pl; xh = ph;
+}
+__device__ __forceinline__ u64 add32w(u32 a, u64 c)
+{
+    u64 r;
+    asm("mad.wide.u32 %0, %1, 1, %2;" : "=l"(r) : "r"(a), "l"(c));
+    return r;
+}
+__device__ __forceinline__ void fmix_step(u32& l, u32& h, u64 c) { l ^= h >> 1; mul64c(l, h, c); }
+
+// s8 = (uint32)seed ^ 8: the seed is 32 bits wide (hash.hpp:50), so the high words of both `^= s8` / `+= s8` vanish
+__device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
+{
+    u32 l = (u32)key, h = (u32)(key >> 32);
+    mul64c(l, h, 0x87c37b91114253d5ULL);
+    { const u32 nl = __funnelshift_l(h, l, 31), nh = __funnelshift_l(l, h, 31); l = nl; h = nh; }   // rotl64(k1, 31)
+    mul64c(l, h, 0x4cf5ad432745937fULL);
+    const u64 h1 = add32w(s8, ((u64)h << 32) | (l ^ s8));      // h1 = (k1 ^ s8) + h2, h2 = s8
+    const u64 h2 = add32w(s8, h1);                             // h2 += h1
+    u32 l1 = (u32)h1, u1 = (u32)(h1 >> 32), l2 = (u32)h2, u2 = (u32)(h2 >> 32);
+    fmix_step(l1, u1, 0xff51afd7ed558ccdULL); fmix_step(l2, u2, 0xff51afd7ed558ccdULL);
+    fmix_step(l1, u1, 0xc4ceb9fe1a85ec53ULL); fmix_step(l2, u2, 0xc4ceb9fe1a85ec53ULL);
+    l1 ^= u1 >> 1; l2 ^= u2 >> 1;
+    return add32w(l2, ((u64)u1 << 32) | l1) + ((u64)u2 << 32);
+}
+#endif
+
+__device__ __forceinline__ u64 murmur3_key8(u64 key, u64 s8) { return murmur3_key8_s32(key, (u32)s8); }
 
 // ---------------------------------------------------------------------------------------------
 // 2-bit streams. Bases are packed 16 per 32-bit word, base q of a word at bits [2q, 2q+2)

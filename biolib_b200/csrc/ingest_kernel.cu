@@ -9,9 +9,9 @@
 //                FASTA  a line whose first byte is '>' starts a record; every other line is sequence (multi-line allowed)
 //                FASTQ  four lines per record: '@' header, sequence, '+' line, qualities
 //              '\n' and '\r' are dropped, every other byte of a sequence line is kept as it is (the nt4 table decides
-//              later what is a base). Three passes over the text, each a grid of 4 KB blocks, with one-CTA scans between:
-//              (1) per block: newline count / state of its last line; (2) with the entry state known: kept bytes and
-//              record starts per block; (3) with the prefix sums known: scatter.
+//              later what is a base). Two passes over the text, each a grid of 4 KB blocks, with a one-CTA scan between:
+//              (1) per block, for every state it may be entered in: kept bytes, record starts, state at its end; (2) the scan;
+//              (3) with entry states and prefix sums known: compaction in shared memory, aligned 16-byte stores.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -52,14 +52,24 @@ __global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __rest
 }
 
 // ---------------------------------------------------------------------------------------------------- fastx
+// Two passes over the text (grids of 4 KB blocks, 16 bytes per thread) with ONE single-CTA scan between them:
+//   fx_summarise  per block, as a FUNCTION of the state the block is entered in: newlines (FASTQ: the state is the line number
+//                 mod 4) / state of the line open at its end (FASTA), kept bytes and record starts for every possible entry state
+//   fx_scan       entry state, first kept byte and first record of every block (1024 threads, runs of blocks per thread)
+//   fx_scatter    with all three known: kept bytes compacted in shared memory, written as whole 16-byte lines; record offsets
+// Per thread everything is bit arithmetic on 16-bit masks (newline / '\r' / '>' found four bytes at a time); the only loops run
+// over the newlines inside a thread's 16 bytes (0 or 1 for real files).
 constexpr int FX_THREADS = 256;
 constexpr int FX_BYTES_PER_THREAD = 16;
 constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 4 KB of text per CTA
+constexpr int FX_WARPS = FX_THREADS / 32;
 
-// state of a line: FASTA 0 = sequence line, 1 = header line; FASTQ = line number mod 4 (1 = sequence line)
-struct FxSummary {
-    u32 nl;          // newlines in the block
-    u32 last_state;  // FASTA: state of the line that is open at the block's end, valid if nl > 0
+// state of a line: FASTA 0 = sequence line, 1 = header line; FASTQ = line number mod 4 (1 = sequence line, 0 starts a record)
+struct FxSum {
+    u32 nl;                    // FASTQ: newlines in the block; FASTA: unused
+    u32 last_state;            // FASTA: state of the line open at the block's end, 3 = no line starts in the block
+    unsigned short keep[4];    // kept bytes if the block is entered in state e (FASTA: e = 0, 1)
+    unsigned short starts[4];  // record starts if the block is entered in state e (FASTA: [0], the entry state does not matter)
 };
 
 __device__ __forceinline__ uint4 load16(const unsigned char* text, size_t n, size_t pos)
@@ -79,209 +89,339 @@ __device__ __forceinline__ unsigned char byte_of(const uint4& v, int i)
     return (unsigned char)(w >> (8 * (i & 3)));
 }
 
-// pass 1: newline count of the block; FASTA: is the line open at the block's end a header line (known iff the block has a
-// newline: the first byte after its last newline says)
-__global__ void __launch_bounds__(FX_THREADS) fx_pass1(const unsigned char* __restrict__ text, size_t n, int fastq, FxSummary* __restrict__ sum)
+// bit q: byte q of w equals the byte replicated in pat (exact zero-byte test, then the four flags gathered by one multiply)
+__device__ __forceinline__ u32 eqmask4(u32 w, u32 pat)
 {
-    __shared__ u32 s_nl[FX_THREADS / 32];
-    __shared__ int s_last[FX_THREADS / 32];
-    const size_t base = (size_t)blockIdx.x * FX_BLOCK + (size_t)threadIdx.x * FX_BYTES_PER_THREAD;
-    u32 nl = 0;
-    int last = -1;        // offset (within the block) of the last newline seen by this thread
-    if (base < n) {
-        const uint4 v = load16(text, n, base);
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            if (base + i < n && byte_of(v, i) == '\n') { ++nl; last = threadIdx.x * FX_BYTES_PER_THREAD + i; }
+    const u32 x = w ^ pat;
+    const u32 z = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+    return (((z >> 7) * 0x00204081u) >> 21) & 0xFu;
+}
+__device__ __forceinline__ u32 eqmask16(const uint4& v, u32 pat)
+{
+    return eqmask4(v.x, pat) | (eqmask4(v.y, pat) << 4) | (eqmask4(v.z, pat) << 8) | (eqmask4(v.w, pat) << 12);
+}
+
+// what a thread knows about its 16 bytes without any context
+struct FxBits {
+    u32 valid;   // bytes below n
+    u32 nl;      // '\n'
+    u32 body;    // neither '\n' nor '\r'
+    u32 ls;      // first byte of a line
+    u32 hdr;     // first byte of a line and '>'
+};
+
+__device__ __forceinline__ FxBits fx_bits(const unsigned char* text, size_t n, size_t base, const uint4& v)
+{
+    FxBits b;
+    b.valid = base >= n ? 0u : (n - base >= 16 ? 0xFFFFu : ((1u << (n - base)) - 1u));
+    b.nl = eqmask16(v, 0x0A0A0A0Au) & b.valid;
+    b.body = ~(b.nl | eqmask16(v, 0x0D0D0D0Du)) & b.valid;
+    // is the thread's first byte the first byte of a line? the previous byte is the neighbour lane's last one
+    const u32 pw = __shfl_up_sync(0xffffffffu, v.w, 1);
+    u32 prev_nl;
+    if ((threadIdx.x & 31) == 0) prev_nl = base == 0 || (base <= n && text[base - 1] == '\n');
+    else prev_nl = (pw >> 24) == 0x0Au;
+    b.ls = ((b.nl << 1) | prev_nl) & b.valid;
+    b.hdr = b.ls & eqmask16(v, 0x3E3E3E3Eu);
+    return b;
+}
+
+__device__ __forceinline__ u32 below(int i) { return (1u << i) - 1u; }   // i <= 16
+
+// FASTA: bit i set = byte i lies on a header line, given the state the thread is entered in
+__device__ __forceinline__ u32 fasta_header_bytes(const FxBits& b, u32 entry)
+{
+    u32 in_hdr = entry ? 0xFFFFu : 0u;
+    for (u32 s = b.ls; s; s &= s - 1) {
+        const int p = __ffs((int)s) - 1;
+        const u32 m = 0xFFFFu & ~below(p);
+        in_hdr = ((b.hdr >> p) & 1u) ? (in_hdr | m) : (in_hdr & ~m);
     }
+    return in_hdr;
+}
+__device__ __forceinline__ u32 fasta_exit_state(const FxBits& b)   // 3: no line starts here, the entry state carries on
+{
+    return b.ls ? ((b.hdr >> (31 - __clz((int)b.ls))) & 1u) : 3u;
+}
+
+// FASTQ: keep / record-start masks, given the state the thread is entered in
+__device__ __forceinline__ void fastq_masks(const FxBits& b, u32 state, u32* keep_out, u32* start_out)
+{
+    u32 keep = 0, start = (b.ls & 1u) && state == 0u ? 1u : 0u;
+    int lo = 0;
+    for (u32 s = b.nl; s; s &= s - 1) {
+        const int p = __ffs((int)s) - 1;
+        if (state == 1u) keep |= below(p) & ~below(lo);
+        state = (state + 1u) & 3u;
+        lo = p + 1;
+        if (state == 0u) start |= 1u << lo;     // bit 16 (the next thread's first byte) is masked below
+    }
+    if (state == 1u) keep |= 0xFFFFu & ~below(lo);
+    *keep_out = keep & b.body;
+    *start_out = start & b.valid;
+}
+
+// FASTQ without the entry state: counts by LOCAL phase (newlines seen so far mod 4), one byte per phase
+__device__ __forceinline__ void fastq_phase_counts(const FxBits& b, u32* keep4, u32* start4)
+{
+    u32 kc = 0, sc = b.ls & 1u;
+    int lo = 0, j = 0;
+    for (u32 s = b.nl; s; s &= s - 1) {
+        const int p = __ffs((int)s) - 1;
+        kc += __popc(b.body & below(p) & ~below(lo)) << (8 * (j & 3));
+        ++j;
+        lo = p + 1;
+        if (lo < 16 && ((b.valid >> lo) & 1u)) sc += 1u << (8 * (j & 3));
+    }
+    kc += __popc(b.body & ~below(lo)) << (8 * (j & 3));
+    *keep4 = kc;
+    *start4 = sc;
+}
+
+// sum over the warp of four byte-wide counters each (<= 16 per lane): two 16-bit fields per word, one REDUX per word
+__device__ __forceinline__ void warp_sum4(u32 packed, u32* even, u32* odd)
+{
+    *even = __reduce_add_sync(0xffffffffu, packed & 0x00FF00FFu);           // counters 0 and 2
+    *odd = __reduce_add_sync(0xffffffffu, (packed >> 8) & 0x00FF00FFu);     // counters 1 and 3
+}
+
+// exclusive prefix over the block of a per-thread count (<= 16 per field, two 16-bit fields); *total = the block's sum
+__device__ __forceinline__ u32 block_exclusive2(u32 x, u32* s_warp /* [FX_WARPS] */, u32* total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u32 incl = x;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { nl += __shfl_xor_sync(0xffffffffu, nl, o); last = max(last, __shfl_xor_sync(0xffffffffu, last, o)); }
-    if ((threadIdx.x & 31) == 0) { s_nl[threadIdx.x >> 5] = nl; s_last[threadIdx.x >> 5] = last; }
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        u32 t = 0;
-        int l = -1;
-        for (int w = 0; w < FX_THREADS / 32; ++w) { t += s_nl[w]; l = max(l, s_last[w]); }
-        FxSummary s;
-        s.nl = t;
-        s.last_state = 0;
-        if (!fastq && l >= 0) {
-            const size_t p = (size_t)blockIdx.x * FX_BLOCK + l + 1;     // first byte of the line open at the block's end (it may be
-            s.last_state = p < n && text[p] == '>' ? 1u : 0u;           // the next block's first byte: same text)
+    u32 before = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < FX_WARPS; ++w) { const u32 t = s_warp[w]; if (w < warp) before += t; all += t; }
+    *total = all;
+    return before + incl - x;
+}
+
+// FASTA: the state a thread is entered in = exit state of the nearest earlier thread of the block that has a line start.
+// Returns it, or 2 when no earlier thread of the block has one (then it is the block's entry state). s_wst: [FX_WARPS].
+__device__ __forceinline__ u32 fasta_thread_entry(u32 exit_state, u32* s_wst, u32* block_exit)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u32 def = __ballot_sync(0xffffffffu, exit_state != 3u), hd = __ballot_sync(0xffffffffu, exit_state == 1u);
+    if (lane == 0) s_wst[warp] = def ? ((hd >> (31 - __clz((int)def))) & 1u) : 3u;
+    __syncthreads();
+    u32 e = 2u;
+    const u32 lower = def & ((1u << lane) - 1u);
+    if (lower) e = (hd >> (31 - __clz((int)lower))) & 1u;
+    else {
+        for (int w = warp - 1; w >= 0; --w) { const u32 t = s_wst[w]; if (t != 3u) { e = t; break; } }
+    }
+    u32 be = 3u;
+    for (int w = FX_WARPS - 1; w >= 0; --w) { const u32 t = s_wst[w]; if (t != 3u) { be = t; break; } }
+    *block_exit = be;
+    return e;
+}
+
+__global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* __restrict__ text, size_t n, int fastq, FxSum* __restrict__ sum)
+{
+    __shared__ u32 s_a[FX_WARPS], s_b[FX_WARPS], s_c[FX_WARPS], s_d[FX_WARPS], s_e[FX_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t base = (size_t)blockIdx.x * FX_BLOCK + (size_t)tid * FX_BYTES_PER_THREAD;
+    uint4 v = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
+    if (base < n) v = load16(text, n, base);
+    const FxBits b = fx_bits(text, n, base, v);
+    FxSum out;
+    out.nl = 0; out.last_state = 3u;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { out.keep[q] = 0; out.starts[q] = 0; }
+    if (fastq) {
+        u32 total;
+        const u32 pre = block_exclusive2(__popc(b.nl), s_a, &total);      // newlines of the block before this thread
+        u32 k4, s4;
+        fastq_phase_counts(b, &k4, &s4);
+        // a byte of local phase j has state (E + pre + j) mod 4: rotate the counters to the block's phases
+        const int rot = 8 * (int)(pre & 3u);
+        k4 = __funnelshift_l(k4, k4, rot);
+        s4 = __funnelshift_l(s4, s4, rot);
+        u32 ke, ko, se, so;
+        warp_sum4(k4, &ke, &ko);
+        warp_sum4(s4, &se, &so);
+        if (lane == 0) { s_b[warp] = ke; s_c[warp] = ko; s_d[warp] = se; s_e[warp] = so; }
+        __syncthreads();
+        if (tid == 0) {
+            u32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            for (int w = 0; w < FX_WARPS; ++w) { a0 += s_b[w]; a1 += s_c[w]; a2 += s_d[w]; a3 += s_e[w]; }
+            const u32 kq[4] = {a0 & 0xFFFFu, a1 & 0xFFFFu, a0 >> 16, a1 >> 16};   // kept bytes whose state is (E + q) mod 4 ... kept iff that is 1
+            const u32 sq[4] = {a2 & 0xFFFFu, a3 & 0xFFFFu, a2 >> 16, a3 >> 16};   // line starts whose state is (E + q) mod 4 ... records iff that is 0
+            out.nl = total;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { out.keep[e] = (unsigned short)kq[(1 - e) & 3]; out.starts[e] = (unsigned short)sq[(4 - e) & 3]; }
+            sum[blockIdx.x] = out;
         }
-        sum[blockIdx.x] = s;
+    } else {
+        u32 block_exit;
+        const u32 e = fasta_thread_entry(fasta_exit_state(b), s_a, &block_exit);
+        // bytes before the thread's first line start follow the entry state, the others do not depend on it
+        const int f = b.ls ? __ffs((int)b.ls) - 1 : 16;
+        const u32 var = __popc(b.body & below(f));
+        const u32 fix = __popc(~fasta_header_bytes(b, 0u) & b.body & ~below(f));
+        const u32 sure = fix + (e == 0u ? var : 0u), open = e == 2u ? var : 0u;
+        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 512 per field
+        const u32 st = __reduce_add_sync(0xffffffffu, (u32)__popc(b.hdr));
+        if (lane == 0) { s_b[warp] = x; s_c[warp] = st; }
+        __syncthreads();
+        if (tid == 0) {
+            u32 xs = 0, ss = 0;
+            for (int w = 0; w < FX_WARPS; ++w) { xs += s_b[w]; ss += s_c[w]; }
+            out.last_state = block_exit;
+            out.keep[0] = (unsigned short)((xs & 0xFFFFu) + (xs >> 16));
+            out.keep[1] = (unsigned short)(xs & 0xFFFFu);
+            out.starts[0] = (unsigned short)ss;
+            sum[blockIdx.x] = out;
+        }
     }
 }
 
-// scan 1 (one CTA of 1024 threads): entry state of every block. The carried state is associative -- FASTQ: the line count mod 4
-// (a sum); FASTA: the state after the last newline seen so far ("last defined value") -- so every thread summarises a contiguous
-// run of blocks, the 1024 summaries are scanned in shared memory, and every thread walks its run again to write the entries.
-__global__ void __launch_bounds__(1024) fx_scan1(const FxSummary* __restrict__ sum, size_t n_blocks, int fastq, const unsigned char* __restrict__ text,
-                                                 size_t n, u32* __restrict__ entry)
+// inclusive scan over the CTA's 1024 threads of an associative op (two shuffle levels)
+template <class Op>
+__device__ __forceinline__ u64 cta_inclusive_scan(u64 x, u64* s_w /* [32] */, Op op)
 {
-    __shared__ u64 s_lines[1024];
-    __shared__ u32 s_state[1024];                  // FASTA: state after the run's last newline, 3 = the run holds no newline
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u64 y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x = op(y, x);
+    }
+    __syncthreads();                 // s_w may still be read from the previous scan
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        u64 t = s_w[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u64 y = __shfl_up_sync(0xffffffffu, t, d);
+            if (lane >= d) t = op(y, t);
+        }
+        s_w[lane] = t;
+    }
+    __syncthreads();
+    if (warp > 0) x = op(s_w[warp - 1], x);
+    return x;
+}
+
+// one CTA of 1024 threads, every thread a contiguous run of blocks: entry state, first kept byte and first record of every
+// block; totals at index n_blocks. The carried state is associative: FASTQ a sum mod 4, FASTA "the last defined value".
+__global__ void __launch_bounds__(1024) fx_scan(const FxSum* __restrict__ sum, size_t n_blocks, int fastq, u32* __restrict__ entry,
+                                                u64* __restrict__ keep_off, u64* __restrict__ start_off)
+{
+    __shared__ u64 s_w[32];
     const int tid = threadIdx.x;
     const size_t per = (n_blocks + 1023) / 1024;
     const size_t lo = min(n_blocks, (size_t)tid * per), hi = min(n_blocks, lo + per);
-    u64 lines = 0;
-    u32 st = 3u;
+    // state: FASTQ newline count; FASTA 0 = undefined, 1 = sequence line, 2 = header line
+    u64 st = 0;
     for (size_t b = lo; b < hi; ++b) {
-        const FxSummary x = sum[b];
-        lines += x.nl;
-        if (x.nl > 0) st = x.last_state;
+        const FxSum x = sum[b];
+        if (fastq) st += x.nl;
+        else if (x.last_state != 3u) st = x.last_state + 1u;
     }
-    s_lines[tid] = lines;
-    s_state[tid] = st;
+    u64 incl = fastq ? cta_inclusive_scan(st, s_w, [](u64 a, u64 b) { return a + b; })
+                     : cta_inclusive_scan(st, s_w, [](u64 a, u64 b) { return b ? b : a; });
+    u64 excl = __shfl_up_sync(0xffffffffu, incl, 1);
     __syncthreads();
-    if (tid == 0) {
-        // exclusive scan over the 1024 run summaries (shared memory only)
-        u64 acc = 0;
-        u32 state = fastq ? 0u : (n > 0 && text[0] == '>' ? 1u : 0u);     // the first line starts at byte 0
-        for (int i = 0; i < 1024; ++i) {
-            const u64 l = s_lines[i];
-            const u32 t = s_state[i];
-            s_lines[i] = acc;
-            s_state[i] = state;
-            acc += l;
-            if (t != 3u) state = t;
-        }
-    }
+    if ((tid & 31) == 31) s_w[tid >> 5] = incl;
     __syncthreads();
-    u64 acc = s_lines[tid];
-    u32 state = fastq ? (u32)(acc & 3u) : s_state[tid];
+    if ((tid & 31) == 0) excl = tid ? s_w[(tid >> 5) - 1] : 0;
+    // the text's first byte starts a line, so no block ever reads the initial FASTA state
+    u32 state0 = fastq ? (u32)(excl & 3u) : (excl == 2u ? 1u : 0u);
+    u32 state = state0;
+    u64 kc = 0, sc = 0;
     for (size_t b = lo; b < hi; ++b) {
+        const FxSum x = sum[b];
+        kc += x.keep[state];
+        sc += x.starts[fastq ? state : 0u];
+        if (fastq) state = (state + x.nl) & 3u;
+        else if (x.last_state != 3u) state = x.last_state;
+    }
+    const u64 kin = cta_inclusive_scan(kc, s_w, [](u64 a, u64 b) { return a + b; });
+    const u64 sin = cta_inclusive_scan(sc, s_w, [](u64 a, u64 b) { return a + b; });
+    u64 ko = kin - kc, so = sin - sc;
+    state = state0;
+    for (size_t b = lo; b < hi; ++b) {
+        const FxSum x = sum[b];
         entry[b] = state;
-        const FxSummary x = sum[b];
-        if (fastq) { acc += x.nl; state = (u32)(acc & 3u); }
-        else if (x.nl > 0) state = x.last_state;
+        keep_off[b] = ko;
+        start_off[b] = so;
+        ko += x.keep[state];
+        so += x.starts[fastq ? state : 0u];
+        if (fastq) state = (state + x.nl) & 3u;
+        else if (x.last_state != 3u) state = x.last_state;
     }
+    if (tid == 1023) { keep_off[n_blocks] = kin; start_off[n_blocks] = sin; }
 }
 
-// the per-thread walk shared by passes 2 and 3: state at the thread's first byte from a block-wide scan of (newline count,
-// state of the last line) over the threads, then 16 bytes one by one. keep bit i: byte i is a sequence byte; start bit i: a
-// record starts at byte i (first byte of a FASTA header line / of a FASTQ line with number mod 4 == 0).
-struct FxWalk { u32 keep, start; };
-
-__device__ __forceinline__ FxWalk fx_walk(const unsigned char* text, size_t n, int fastq, u32 block_entry, size_t block_first_byte_is_line_start,
-                                          uint4* bytes_out)
+// scatter: kept bytes go through shared memory at the byte alignment they will have in `bases`, so that every 16-byte chunk of
+// the staging buffer is one aligned 16-byte chunk of the output
+__global__ void __launch_bounds__(FX_THREADS) fx_scatter(const unsigned char* __restrict__ text, size_t n, int fastq, const u32* __restrict__ entry,
+                                                         const u64* __restrict__ keep_off, const u64* __restrict__ start_off,
+                                                         unsigned char* __restrict__ bases, u64* __restrict__ offsets)
 {
-    __shared__ u32 s_nl[FX_THREADS];
-    __shared__ u32 s_state[FX_THREADS];     // FASTA: state after the thread's last newline (0/1), or 3 = no newline in the thread's bytes
+    __shared__ __align__(16) unsigned char s_out[FX_BLOCK + 32];
+    __shared__ u32 s_a[FX_WARPS], s_b[FX_WARPS];
     const int tid = threadIdx.x;
     const size_t base = (size_t)blockIdx.x * FX_BLOCK + (size_t)tid * FX_BYTES_PER_THREAD;
     uint4 v = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
     if (base < n) v = load16(text, n, base);
-    *bytes_out = v;
-    // thread summary
-    u32 nl = 0, st = 3;
-    {
-        int last = -1;
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            if (base + i < n && byte_of(v, i) == '\n') { ++nl; last = i; }
-        if (!fastq && last >= 0) {
-            const size_t p = base + last + 1;
-            st = p < n ? (text[p] == '>' ? 1u : 0u) : 0u;          // may read the next thread's / block's first byte: same text
-        }
-    }
-    s_nl[tid] = nl;
-    s_state[tid] = st;
-    __syncthreads();
-    // entry state of this thread: sequential look-back over the earlier threads of the block (256 at most; cheap next to the
-    // global traffic, and only thread summaries are touched)
-    u32 state = block_entry;
+    const FxBits b = fx_bits(text, n, base, v);
+    const u32 E = entry[blockIdx.x];
+    u32 keep, start;
     if (fastq) {
-        u32 lines = 0;
-        for (int j = 0; j < tid; ++j) lines += s_nl[j];
-        state = (block_entry + lines) & 3u;
+        u32 total;
+        const u32 pre = block_exclusive2(__popc(b.nl), s_a, &total);
+        fastq_masks(b, (E + pre) & 3u, &keep, &start);
     } else {
-        for (int j = tid - 1; j >= 0; --j)
-            if (s_state[j] != 3u) { state = s_state[j]; break; }
+        u32 block_exit;
+        u32 e = fasta_thread_entry(fasta_exit_state(b), s_a, &block_exit);
+        if (e == 2u) e = E;
+        keep = ~fasta_header_bytes(b, e) & b.body;
+        start = b.hdr;
     }
-    (void)block_first_byte_is_line_start;
-    FxWalk w{0u, 0u};
-    bool line_start = false;
-    if (base < n) {
-        // is the thread's first byte the first byte of a line?
-        line_start = base == 0 || text[base - 1] == '\n';
+    u32 total;
+    const u32 ex = block_exclusive2((u32)__popc(keep) | ((u32)__popc(start) << 16), s_b, &total);
+    const u64 k0 = keep_off[blockIdx.x];
+    const u32 kx = ex & 0xFFFFu, sx = ex >> 16, ktot = total & 0xFFFFu;
+    unsigned char* dst = bases + k0;
+    const u32 mis = (u32)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    {
+        u32 p = mis + kx;
+        if (keep == 0xFFFFu && (p & 3u) == 0u) {            // the usual thread of a sequence line, when the alignment allows words
+            u32* w = reinterpret_cast<u32*>(s_out + p);
+            w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+        } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            if (base + i >= n) break;
-            const unsigned char c = byte_of(v, i);
-            if (line_start) {
-                if (fastq) { if (state == 0u) w.start |= 1u << i; }
-                else { state = c == '>' ? 1u : 0u; if (state == 1u) w.start |= 1u << i; }
-                line_start = false;
-            }
-            if (c == '\n') { line_start = true; if (fastq) state = (state + 1u) & 3u; }
-            else if (c != '\r' && (fastq ? state == 1u : state == 0u)) w.keep |= 1u << i;
+            for (int i = 0; i < 16; ++i)
+                if ((keep >> i) & 1u) s_out[p++] = byte_of(v, i);
         }
     }
-    return w;
-}
-
-// pass 2: kept bytes and record starts of the block
-__global__ void __launch_bounds__(FX_THREADS) fx_pass2(const unsigned char* __restrict__ text, size_t n, int fastq, const u32* __restrict__ entry,
-                                                       u64* __restrict__ keep_cnt, u64* __restrict__ start_cnt)
-{
-    __shared__ u32 s_k[FX_THREADS / 32], s_s[FX_THREADS / 32];
-    uint4 v;
-    const FxWalk w = fx_walk(text, n, fastq, entry[blockIdx.x], 0, &v);
-    u32 k = __popc(w.keep), s = __popc(w.start);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { k += __shfl_xor_sync(0xffffffffu, k, o); s += __shfl_xor_sync(0xffffffffu, s, o); }
-    if ((threadIdx.x & 31) == 0) { s_k[threadIdx.x >> 5] = k; s_s[threadIdx.x >> 5] = s; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        u32 a = 0, b = 0;
-        for (int q = 0; q < FX_THREADS / 32; ++q) { a += s_k[q]; b += s_s[q]; }
-        keep_cnt[blockIdx.x] = a;
-        start_cnt[blockIdx.x] = b;
-    }
-}
-
-// scan 2 (one CTA of 1024 threads): exclusive prefix sums of the two per-block counts, totals at index n_blocks
-__global__ void __launch_bounds__(1024) fx_scan2(u64* __restrict__ a, u64* __restrict__ b, size_t n_blocks)
-{
-    __shared__ u64 sa[1024], sb[1024];
-    const int tid = threadIdx.x;
-    const size_t per = (n_blocks + 1023) / 1024;
-    const size_t lo = min(n_blocks, tid * per), hi = min(n_blocks, lo + per);
-    u64 ta = 0, tb = 0;
-    for (size_t i = lo; i < hi; ++i) { ta += a[i]; tb += b[i]; }
-    sa[tid] = ta; sb[tid] = tb;
-    __syncthreads();
-    if (tid == 0) {
-        u64 ra = 0, rb = 0;
-        for (int i = 0; i < 1024; ++i) { const u64 xa = sa[i], xb = sb[i]; sa[i] = ra; sb[i] = rb; ra += xa; rb += xb; }
-        a[n_blocks] = ra; b[n_blocks] = rb;
+    if (start) {
+        u64 sp = start_off[blockIdx.x] + sx;
+        for (u32 s = start; s; s &= s - 1) {
+            const int i = __ffs((int)s) - 1;
+            offsets[sp++] = k0 + kx + __popc(keep & below(i));
+        }
     }
     __syncthreads();
-    u64 ra = sa[tid], rb = sb[tid];
-    for (size_t i = lo; i < hi; ++i) { const u64 xa = a[i], xb = b[i]; a[i] = ra; b[i] = rb; ra += xa; rb += xb; }
-}
-
-// pass 3: scatter the kept bytes and the record offsets
-__global__ void __launch_bounds__(FX_THREADS) fx_pass3(const unsigned char* __restrict__ text, size_t n, int fastq, const u32* __restrict__ entry,
-                                                       const u64* __restrict__ keep_off, const u64* __restrict__ start_off,
-                                                       unsigned char* __restrict__ bases, u64* __restrict__ offsets)
-{
-    __shared__ u32 s_k[FX_THREADS], s_s[FX_THREADS];
-    uint4 v;
-    const FxWalk w = fx_walk(text, n, fastq, entry[blockIdx.x], 0, &v);
-    const int tid = threadIdx.x;
-    __syncthreads();                       // fx_walk's shared arrays are done with
-    s_k[tid] = __popc(w.keep);
-    s_s[tid] = __popc(w.start);
-    __syncthreads();
-    u32 ko = 0, so = 0;
-    for (int j = 0; j < tid; ++j) { ko += s_k[j]; so += s_s[j]; }
-    u64 kp = keep_off[blockIdx.x] + ko, sp = start_off[blockIdx.x] + so;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        if (w.start & (1u << i)) offsets[sp++] = kp;
-        if (w.keep & (1u << i)) bases[kp++] = byte_of(v, i);
+    const u32 end = mis + ktot;
+    unsigned char* dst0 = dst - mis;                                   // 16-byte aligned
+    for (u32 c = tid; c * 16u < end; c += FX_THREADS) {
+        const u32 lo = c * 16u, hi = lo + 16u;
+        if (lo >= mis && hi <= end) *reinterpret_cast<uint4*>(dst0 + lo) = *reinterpret_cast<const uint4*>(s_out + lo);
+        else {
+            const u32 a0 = lo < mis ? mis : lo, a1 = hi > end ? end : hi;
+            for (u32 q = a0; q < a1; ++q) dst0[q] = s_out[q];
+        }
     }
 }
 
@@ -312,10 +452,10 @@ cudaError_t unpack_launch(const void* codes, size_t n_bases, const unsigned long
 size_t fastx_scratch_bytes(size_t n_text)
 {
     const size_t nb = (n_text + FX_BLOCK - 1) / FX_BLOCK + 1;
-    return (nb * (sizeof(FxSummary) + sizeof(u32) + 2 * sizeof(u64)) + 511) / 256 * 256;
+    return (nb * (sizeof(FxSum) + sizeof(u32) + 2 * sizeof(u64)) + 511) / 256 * 256;
 }
 
-// Two stages, so that the caller can size the outputs exactly: fastx_count_launch runs passes 1-2 and the scans and leaves
+// Two stages, so that the caller can size the outputs exactly: fastx_count_launch summarises and scans and leaves
 // totals[0] = kept bytes, totals[1] = records on the device; fastx_emit_launch (same scratch, untouched in between) scatters
 // into bases (totals[0] bytes) and offsets (totals[1] entries; the caller appends the closing entry).
 cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned long long* totals, cudaStream_t stream,
@@ -327,13 +467,11 @@ cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fas
     char* p = static_cast<char*>(scratch);
     u64* keep = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
     u64* starts = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
-    FxSummary* sum = reinterpret_cast<FxSummary*>(p); p += nb * sizeof(FxSummary);
+    FxSum* sum = reinterpret_cast<FxSum*>(p); p += nb * sizeof(FxSum);
     u32* entry = reinterpret_cast<u32*>(p);
-    fx_pass1<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, sum);
-    fx_scan1<<<1, 1024, 0, stream>>>(sum, nb, fastq, text, n_text, entry);
-    fx_pass2<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts);
-    fx_scan2<<<1, 1024, 0, stream>>>(keep, starts, nb);
-    *launches = 4;
+    fx_summarise<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, sum);
+    fx_scan<<<1, 1024, 0, stream>>>(sum, nb, fastq, entry, keep, starts);
+    *launches = 2;
     cudaError_t e = cudaMemcpyAsync(totals, keep + nb, 8, cudaMemcpyDeviceToDevice, stream);
     if (e != cudaSuccess) return e;
     e = cudaMemcpyAsync(totals + 1, starts + nb, 8, cudaMemcpyDeviceToDevice, stream);
@@ -349,9 +487,9 @@ cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fast
     char* p = static_cast<char*>(scratch);
     u64* keep = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
     u64* starts = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
-    p += nb * sizeof(FxSummary);
+    p += nb * sizeof(FxSum);
     u32* entry = reinterpret_cast<u32*>(p);
-    fx_pass3<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets);
+    fx_scatter<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets);
     *launches += 1;
     return cudaGetLastError();
 }

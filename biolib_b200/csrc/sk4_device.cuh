@@ -27,6 +27,9 @@ namespace blg {
 
 namespace {
 
+#ifndef SK4_REORDER
+#define SK4_REORDER 0
+#endif
 constexpr int NT4 = 32;
 constexpr int WARPS4 = SK4_THREADS / 32;
 constexpr int PADF4 = 3;     // zero words in front of the big-endian stream
@@ -78,27 +81,6 @@ __device__ __forceinline__ u32 make_key(u32 h, u32 mask, u32 idx)
     u32 k;
     asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(h), "r"(mask), "r"(idx));
     return k;
-}
-
-// murmur3_key8 with a 32-bit s8 (the seed is 32 bits wide, hash.hpp:50): the high words of both `^= s8` / `+= s8` vanish.
-// (Taking the six `h >> 33` shifts from IMAD.HI on the FMA pipe instead of SHF on the ALU pipe was measured: slower at 1, 2 and 4
-// converted sites, profiles/r02_q_fma_shift_variants.txt.)
-__device__ __forceinline__ u64 fmix64_4(u64 h)
-{
-    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL;
-    h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL;
-    return h ^ (h >> 33);
-}
-__device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
-{
-    u64 k1 = key * 0x87c37b91114253d5ULL;
-    k1 = rotl64(k1, 31);
-    k1 *= 0x4cf5ad432745937fULL;
-    u64 h1 = k1 ^ (u64)s8;
-    u64 h2 = (u64)s8;
-    h1 += h2; h2 += h1;
-    h1 = fmix64_4(h1); h2 = fmix64_4(h2);
-    return h1 + h2;
 }
 
 // low NBITS bits: OR over d in [0, span) of bit (bitpos + i + d + shift) of the packed bit row, for i = 0 .. NBITS-1
@@ -719,6 +701,14 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
         if (!have && prev < 0) break;
         u32 n_rec = 0;
         u64 old = 0;
+#if SK4_REORDER >= 1
+        // the words the base of the tile to write out depends on are read BEFORE this iteration's tile is computed: its
+        // predecessors were handed out at least KB - 1 tiles ago, so the words are there almost always, and their latency
+        // (and that of the arrival count below) hides behind work instead of standing between compute and emit
+        const u64* bp = prev >= 0 ? tile_base_addr4(a, prev, t) : nullptr;
+        u64 bv = 0;
+        if (bp != nullptr) bv = ld_status(bp);
+#endif
         if (have) {
             n_rec = compute(b, tile, have_pre, pre);
             if (t == 0) {
@@ -726,9 +716,17 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
             }
         }
+#if SK4_REORDER >= 1
+        u64 base = 0;
+        if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
+        u32 nx = 0xFFFFFFFFu;
+        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
+        if (prev >= 0) emit(pb, prev, prev_n, base);
+#else
         const u64* bp = prev >= 0 ? tile_base_addr4(a, prev, t) : nullptr;
         u64 bv = 0;
         if (bp != nullptr) bv = ld_status(bp);
+#endif
         if (have) {
             // did this tile complete its group (the add counts arrivals)? then this warp resolves the group
             const long long g = tile / GS4;
@@ -745,11 +743,13 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
                 }
             }
         }
+#if SK4_REORDER < 1
         u64 base = 0;
         if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
         if (prev >= 0) emit(pb, prev, prev_n, base);
+#endif
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
