@@ -1023,30 +1023,24 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         if (first == '>') format = 0; else if (first == '@') format = 1;
         else { c->err = "text starts with neither '>' nor '@'"; return BLG_E_INVALID; }
     }
-    if ((rc = ensure(c, c->fx_scratch, fastx_scratch_bytes(n_text) + 64)) != BLG_OK) return rc;
-    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->fx_scratch.p) + fastx_scratch_bytes(n_text));
+    if ((rc = ensure(c, c->fx_scratch, fastx_scratch_bytes(n_text))) != BLG_OK) return rc;
+    // totals and the first record's offset arrive in the context's mapped pinned words [4..6]: no copy, one synchronise each
+    volatile unsigned long long* h_fx = c->h_total + 4;
+    h_fx[0] = h_fx[1] = 0; h_fx[2] = 1;
     int launches = 0;
-    cudaError_t e = fastx_count_launch(d_text, n_text, format, c->fx_scratch.p, d_tot, c->stream, &launches);
-    unsigned long long tot[2] = {0, 0};
-    if (e != cudaSuccess || cudaMemcpyAsync(tot, d_tot, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
-        cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "fastx: counting passes failed"; return BLG_E_CUDA; }
+    cudaError_t e = fastx_count_launch(d_text, n_text, format, c->fx_scratch.p, c->d_total + 4, c->stream, &launches);
+    if (e != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "fastx: counting passes failed"; return BLG_E_CUDA; }
+    const unsigned long long tot[2] = {h_fx[0], h_fx[1]};
     if (tot[1] == 0) { c->err = "text does not start with a record header"; return BLG_E_INVALID; }
     Owner* ow = new (std::nothrow) Owner{1, {}, {}, nullptr};
     if (!ow) return BLG_E_NOMEM;
     unsigned char* d_bases = nullptr;
     unsigned long long* d_offs = nullptr;
     if ((rc = alloc_owned(c, true, (size_t)tot[0] + 64, &d_bases, ow, 0)) != BLG_OK || (rc = alloc_owned(c, true, (size_t)tot[1] + 1, &d_offs, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
-    e = fastx_emit_launch(d_text, n_text, format, c->fx_scratch.p, d_bases, d_offs, c->stream, &launches);
+    e = fastx_emit_launch(d_text, n_text, format, c->fx_scratch.p, d_bases, d_offs, c->d_total + 6, c->stream, &launches);
     if (e != cudaSuccess) { free_owner(ow); c->err = cudaGetErrorString(e); return BLG_E_CUDA; }
     c->stats.kernel_launches += launches;
-    unsigned long long first_off = 1;
-    if (cudaMemcpyAsync(&first_off, d_offs, 8, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess || first_off != 0) {
-        free_owner(ow);
-        c->err = "text does not start with a record header";
-        return BLG_E_INVALID;
-    }
-    // close the offsets array: offsets[n_seq] = n_bases
-    if (cudaMemcpy(d_offs + tot[1], &tot[0], 8, cudaMemcpyHostToDevice) != cudaSuccess) { free_owner(ow); return BLG_E_CUDA; }
+    if (dev_out && cudaStreamSynchronize(c->stream) != cudaSuccess) { free_owner(ow); c->err = "fastx: scatter pass failed"; return BLG_E_CUDA; }
     out->n_bases = tot[0];
     out->n_seq = tot[1];
     c->stats.n_bases = tot[0];
@@ -1068,6 +1062,11 @@ int blg_parse_fastx(blg_ctx* c, const char* text, size_t n_text, int format, uin
         if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { free_owner(hw); c->err = "fastx: download failed"; return BLG_E_CUDA; }
         c->stats.bytes_d2h += tot[0] + (tot[1] + 1) * 8;
         out->bases = hb; out->seq_offsets = ho; out->owner = hw;
+    }
+    if (h_fx[2] != 0) {                      // bytes of a sequence line before the first header
+        blg_free_fastx_out(c, out);
+        c->err = "text does not start with a record header";
+        return BLG_E_INVALID;
     }
     c->stats.total_ms = tm.ms();
     return BLG_OK;

@@ -9,7 +9,7 @@
 //                FASTA  a line whose first byte is '>' starts a record; every other line is sequence (multi-line allowed)
 //                FASTQ  four lines per record: '@' header, sequence, '+' line, qualities
 //              '\n' and '\r' are dropped, every other byte of a sequence line is kept as it is (the nt4 table decides
-//              later what is a base). Two passes over the text, each a grid of 4 KB blocks, with a one-CTA scan between:
+//              later what is a base). Two passes over the text, each a grid of 8 KB blocks, with a one-CTA scan between:
 //              (1) per block, for every state it may be entered in: kept bytes, record starts, state at its end; (2) the scan;
 //              (3) with entry states and prefix sums known: compaction in shared memory, aligned 16-byte stores.
 #include "common.cuh"
@@ -52,16 +52,16 @@ __global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __rest
 }
 
 // ---------------------------------------------------------------------------------------------------- fastx
-// Two passes over the text (grids of 4 KB blocks, 16 bytes per thread) with ONE single-CTA scan between them:
+// Two passes over the text (grids of 8 KB blocks, 16 bytes per thread) with ONE single-CTA scan between them:
 //   fx_summarise  per block, as a FUNCTION of the state the block is entered in: newlines (FASTQ: the state is the line number
 //                 mod 4) / state of the line open at its end (FASTA), kept bytes and record starts for every possible entry state
-//   fx_scan       entry state, first kept byte and first record of every block (1024 threads, runs of blocks per thread)
+//   fx_scan       entry state, first kept byte and first record of every block (one CTA, 1024 summaries per step)
 //   fx_scatter    with all three known: kept bytes compacted in shared memory, written as whole 16-byte lines; record offsets
 // Per thread everything is bit arithmetic on 16-bit masks (newline / '\r' / '>' found four bytes at a time); the only loops run
 // over the newlines inside a thread's 16 bytes (0 or 1 for real files).
-constexpr int FX_THREADS = 256;
+constexpr int FX_THREADS = 512;
 constexpr int FX_BYTES_PER_THREAD = 16;
-constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 4 KB of text per CTA
+constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 8 KB of text per CTA
 constexpr int FX_WARPS = FX_THREADS / 32;
 
 // state of a line: FASTA 0 = sequence line, 1 = header line; FASTQ = line number mod 4 (1 = sequence line, 0 starts a record)
@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* 
         const u32 var = __popc(b.body & below(f));
         const u32 fix = __popc(~fasta_header_bytes(b, 0u) & b.body & ~below(f));
         const u32 sure = fix + (e == 0u ? var : 0u), open = e == 2u ? var : 0u;
-        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 512 per field
+        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 512 per field and warp, <= 8192 per block
         const u32 st = __reduce_add_sync(0xffffffffu, (u32)__popc(b.hdr));
         if (lane == 0) { s_b[warp] = x; s_c[warp] = st; }
         __syncthreads();
@@ -284,9 +284,10 @@ __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* 
     }
 }
 
-// inclusive scan over the CTA's 1024 threads of an associative op (two shuffle levels)
+// scan over the CTA's 1024 threads of an associative op whose identity is 0 (two shuffle levels); returns the inclusive value,
+// *excl = the exclusive one
 template <class Op>
-__device__ __forceinline__ u64 cta_inclusive_scan(u64 x, u64* s_w /* [32] */, Op op)
+__device__ __forceinline__ u64 cta_scan(u64 x, u64* s_w /* [32] */, Op op, u64* excl)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -294,6 +295,8 @@ __device__ __forceinline__ u64 cta_inclusive_scan(u64 x, u64* s_w /* [32] */, Op
         const u64 y = __shfl_up_sync(0xffffffffu, x, d);
         if (lane >= d) x = op(y, x);
     }
+    u64 before = __shfl_up_sync(0xffffffffu, x, 1);
+    if (lane == 0) before = 0;
     __syncthreads();                 // s_w may still be read from the previous scan
     if (lane == 31) s_w[warp] = x;
     __syncthreads();
@@ -307,66 +310,60 @@ __device__ __forceinline__ u64 cta_inclusive_scan(u64 x, u64* s_w /* [32] */, Op
         s_w[lane] = t;
     }
     __syncthreads();
-    if (warp > 0) x = op(s_w[warp - 1], x);
-    return x;
+    const u64 pre = warp > 0 ? s_w[warp - 1] : 0;
+    *excl = op(pre, before);
+    return op(pre, x);
 }
 
-// one CTA of 1024 threads, every thread a contiguous run of blocks: entry state, first kept byte and first record of every
-// block; totals at index n_blocks. The carried state is associative: FASTQ a sum mod 4, FASTA "the last defined value".
+// one CTA of 1024 threads walks the block summaries 1024 at a time (one per thread, coalesced): entry state, first kept byte
+// and first record of every block; totals at index n_blocks and in *totals. The carried state is associative: FASTQ a sum
+// mod 4, FASTA "the last defined value" (0 = undefined, 1 = sequence line, 2 = header line).
 __global__ void __launch_bounds__(1024) fx_scan(const FxSum* __restrict__ sum, size_t n_blocks, int fastq, u32* __restrict__ entry,
-                                                u64* __restrict__ keep_off, u64* __restrict__ start_off)
+                                                u64* __restrict__ keep_off, u64* __restrict__ start_off, unsigned long long* __restrict__ totals)
 {
     __shared__ u64 s_w[32];
+    __shared__ u64 s_carry[3];
     const int tid = threadIdx.x;
-    const size_t per = (n_blocks + 1023) / 1024;
-    const size_t lo = min(n_blocks, (size_t)tid * per), hi = min(n_blocks, lo + per);
-    // state: FASTQ newline count; FASTA 0 = undefined, 1 = sequence line, 2 = header line
-    u64 st = 0;
-    for (size_t b = lo; b < hi; ++b) {
-        const FxSum x = sum[b];
-        if (fastq) st += x.nl;
-        else if (x.last_state != 3u) st = x.last_state + 1u;
+    const auto add = [](u64 a, u64 b) { return a + b; };
+    const auto last = [](u64 a, u64 b) { return b ? b : a; };
+    u64 c_state = 0, c_keep = 0, c_start = 0;       // over all earlier chunks (the text's first byte starts a line: no block reads the initial FASTA state)
+    for (size_t chunk = 0; chunk < n_blocks; chunk += 1024) {
+        const size_t b = chunk + tid;
+        const bool have = b < n_blocks;
+        FxSum x;
+        x.nl = 0; x.last_state = 3u;
+        if (have) x = sum[b];
+        const u64 st = !have ? 0 : fastq ? x.nl : (x.last_state != 3u ? x.last_state + 1u : 0u);
+        u64 ex;
+        const u64 in = fastq ? cta_scan(st, s_w, add, &ex) : cta_scan(st, s_w, last, &ex);
+        u32 state;
+        if (fastq) state = (u32)((c_state + ex) & 3u);
+        else { const u64 e = ex ? ex : c_state; state = e == 2u ? 1u : 0u; }
+        const u64 kc = have ? x.keep[state] : 0, sc = have ? x.starts[fastq ? state : 0u] : 0;
+        u64 kex, sex;
+        const u64 kin = cta_scan(kc, s_w, add, &kex);
+        const u64 sin = cta_scan(sc, s_w, add, &sex);
+        if (have) { entry[b] = state; keep_off[b] = c_keep + kex; start_off[b] = c_start + sex; }
+        if (tid == 1023) {
+            s_carry[0] = fastq ? c_state + in : (in ? in : c_state);
+            s_carry[1] = c_keep + kin;
+            s_carry[2] = c_start + sin;
+        }
+        __syncthreads();
+        c_state = s_carry[0]; c_keep = s_carry[1]; c_start = s_carry[2];
+        __syncthreads();
     }
-    u64 incl = fastq ? cta_inclusive_scan(st, s_w, [](u64 a, u64 b) { return a + b; })
-                     : cta_inclusive_scan(st, s_w, [](u64 a, u64 b) { return b ? b : a; });
-    u64 excl = __shfl_up_sync(0xffffffffu, incl, 1);
-    __syncthreads();
-    if ((tid & 31) == 31) s_w[tid >> 5] = incl;
-    __syncthreads();
-    if ((tid & 31) == 0) excl = tid ? s_w[(tid >> 5) - 1] : 0;
-    // the text's first byte starts a line, so no block ever reads the initial FASTA state
-    u32 state0 = fastq ? (u32)(excl & 3u) : (excl == 2u ? 1u : 0u);
-    u32 state = state0;
-    u64 kc = 0, sc = 0;
-    for (size_t b = lo; b < hi; ++b) {
-        const FxSum x = sum[b];
-        kc += x.keep[state];
-        sc += x.starts[fastq ? state : 0u];
-        if (fastq) state = (state + x.nl) & 3u;
-        else if (x.last_state != 3u) state = x.last_state;
+    if (tid == 0) {
+        keep_off[n_blocks] = c_keep; start_off[n_blocks] = c_start;
+        totals[0] = c_keep; totals[1] = c_start;          // mapped pinned host memory: read by the host after a stream synchronise
     }
-    const u64 kin = cta_inclusive_scan(kc, s_w, [](u64 a, u64 b) { return a + b; });
-    const u64 sin = cta_inclusive_scan(sc, s_w, [](u64 a, u64 b) { return a + b; });
-    u64 ko = kin - kc, so = sin - sc;
-    state = state0;
-    for (size_t b = lo; b < hi; ++b) {
-        const FxSum x = sum[b];
-        entry[b] = state;
-        keep_off[b] = ko;
-        start_off[b] = so;
-        ko += x.keep[state];
-        so += x.starts[fastq ? state : 0u];
-        if (fastq) state = (state + x.nl) & 3u;
-        else if (x.last_state != 3u) state = x.last_state;
-    }
-    if (tid == 1023) { keep_off[n_blocks] = kin; start_off[n_blocks] = sin; }
 }
 
 // scatter: kept bytes go through shared memory at the byte alignment they will have in `bases`, so that every 16-byte chunk of
 // the staging buffer is one aligned 16-byte chunk of the output
 __global__ void __launch_bounds__(FX_THREADS) fx_scatter(const unsigned char* __restrict__ text, size_t n, int fastq, const u32* __restrict__ entry,
                                                          const u64* __restrict__ keep_off, const u64* __restrict__ start_off,
-                                                         unsigned char* __restrict__ bases, u64* __restrict__ offsets)
+                                                         unsigned char* __restrict__ bases, u64* __restrict__ offsets, u64* __restrict__ first_off)
 {
     __shared__ __align__(16) unsigned char s_out[FX_BLOCK + 32];
     __shared__ u32 s_a[FX_WARPS], s_b[FX_WARPS];
@@ -409,9 +406,12 @@ __global__ void __launch_bounds__(FX_THREADS) fx_scatter(const unsigned char* __
         u64 sp = start_off[blockIdx.x] + sx;
         for (u32 s = start; s; s &= s - 1) {
             const int i = __ffs((int)s) - 1;
-            offsets[sp++] = k0 + kx + __popc(keep & below(i));
+            const u64 off = k0 + kx + __popc(keep & below(i));
+            if (sp == 0) *first_off = off;                 // the caller checks that nothing is kept before the first record
+            offsets[sp++] = off;
         }
     }
+    if (blockIdx.x == 0 && tid == 0) offsets[start_off[gridDim.x]] = keep_off[gridDim.x];   // the closing entry: offsets[n_seq] = n_bases
     __syncthreads();
     const u32 end = mis + ktot;
     unsigned char* dst0 = dst - mis;                                   // 16-byte aligned
@@ -456,31 +456,28 @@ size_t fastx_scratch_bytes(size_t n_text)
 }
 
 // Two stages, so that the caller can size the outputs exactly: fastx_count_launch summarises and scans and leaves
-// totals[0] = kept bytes, totals[1] = records on the device; fastx_emit_launch (same scratch, untouched in between) scatters
-// into bases (totals[0] bytes) and offsets (totals[1] entries; the caller appends the closing entry).
+// totals[0] = kept bytes, totals[1] = records (totals: device address of mapped pinned host memory); fastx_emit_launch (same
+// scratch, untouched in between) scatters into bases (totals[0] bytes) and offsets (totals[1] + 1 entries, the closing one
+// included) and reports the first record's offset through *first_off (mapped pinned memory as well).
 cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned long long* totals, cudaStream_t stream,
                                int* launches)
 {
     const size_t nb = (n_text + FX_BLOCK - 1) / FX_BLOCK;
     *launches = 0;
-    if (nb == 0) return cudaMemsetAsync(totals, 0, 16, stream);
+    if (nb == 0) return cudaErrorInvalidValue;     // the caller returns early for empty text
     char* p = static_cast<char*>(scratch);
     u64* keep = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
     u64* starts = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
     FxSum* sum = reinterpret_cast<FxSum*>(p); p += nb * sizeof(FxSum);
     u32* entry = reinterpret_cast<u32*>(p);
     fx_summarise<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, sum);
-    fx_scan<<<1, 1024, 0, stream>>>(sum, nb, fastq, entry, keep, starts);
+    fx_scan<<<1, 1024, 0, stream>>>(sum, nb, fastq, entry, keep, starts, totals);
     *launches = 2;
-    cudaError_t e = cudaMemcpyAsync(totals, keep + nb, 8, cudaMemcpyDeviceToDevice, stream);
-    if (e != cudaSuccess) return e;
-    e = cudaMemcpyAsync(totals + 1, starts + nb, 8, cudaMemcpyDeviceToDevice, stream);
-    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
 cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
-                              cudaStream_t stream, int* launches)
+                              unsigned long long* first_off, cudaStream_t stream, int* launches)
 {
     const size_t nb = (n_text + FX_BLOCK - 1) / FX_BLOCK;
     if (nb == 0) return cudaSuccess;
@@ -489,7 +486,7 @@ cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fast
     u64* starts = reinterpret_cast<u64*>(p); p += (nb + 1) * sizeof(u64);
     p += nb * sizeof(FxSum);
     u32* entry = reinterpret_cast<u32*>(p);
-    fx_scatter<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets);
+    fx_scatter<<<(unsigned)nb, FX_THREADS, 0, stream>>>(text, n_text, fastq, entry, keep, starts, bases, offsets, first_off);
     *launches += 1;
     return cudaGetLastError();
 }

@@ -157,7 +157,7 @@ size_t fastx_scratch_bytes(size_t n_text);
 cudaError_t fastx_count_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned long long* totals, cudaStream_t stream,
                                int* launches);
 cudaError_t fastx_emit_launch(const unsigned char* text, size_t n_text, int fastq, void* scratch, unsigned char* bases, unsigned long long* offsets,
-                              cudaStream_t stream, int* launches);
+                              unsigned long long* first_off, cudaStream_t stream, int* launches);
 
 // payload_kernel.cu: records -> bucket-ordered records + their bases as one 2-bit packed stream
 size_t payload_scratch_bytes(unsigned long long n_records, unsigned int n_buckets);

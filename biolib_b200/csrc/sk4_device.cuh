@@ -27,9 +27,6 @@ namespace blg {
 
 namespace {
 
-#ifndef SK4_REORDER
-#define SK4_REORDER 0
-#endif
 constexpr int NT4 = 32;
 constexpr int WARPS4 = SK4_THREADS / 32;
 constexpr int PADF4 = 3;     // zero words in front of the big-endian stream
@@ -701,14 +698,6 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
         if (!have && prev < 0) break;
         u32 n_rec = 0;
         u64 old = 0;
-#if SK4_REORDER >= 1
-        // the words the base of the tile to write out depends on are read BEFORE this iteration's tile is computed: its
-        // predecessors were handed out at least KB - 1 tiles ago, so the words are there almost always, and their latency
-        // (and that of the arrival count below) hides behind work instead of standing between compute and emit
-        const u64* bp = prev >= 0 ? tile_base_addr4(a, prev, t) : nullptr;
-        u64 bv = 0;
-        if (bp != nullptr) bv = ld_status(bp);
-#endif
         if (have) {
             n_rec = compute(b, tile, have_pre, pre);
             if (t == 0) {
@@ -716,17 +705,9 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
             }
         }
-#if SK4_REORDER >= 1
-        u64 base = 0;
-        if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
-        u32 nx = 0xFFFFFFFFu;
-        if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
-        if (prev >= 0) emit(pb, prev, prev_n, base);
-#else
         const u64* bp = prev >= 0 ? tile_base_addr4(a, prev, t) : nullptr;
         u64 bv = 0;
         if (bp != nullptr) bv = ld_status(bp);
-#endif
         if (have) {
             // did this tile complete its group (the add counts arrivals)? then this warp resolves the group
             const long long g = tile / GS4;
@@ -743,13 +724,11 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
                 }
             }
         }
-#if SK4_REORDER < 1
         u64 base = 0;
         if (prev >= 0) base = tile_base_finish4(a, bp, bv, t);
         u32 nx = 0xFFFFFFFFu;
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
         if (prev >= 0) emit(pb, prev, prev_n, base);
-#endif
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
         have_pre = false;
         {
