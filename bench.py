@@ -10,9 +10,10 @@ the k+w-2 halo from the next shard: weak scaling, no data-path collective, one N
 
   value         Gbases/s, whole job, inputs resident in HBM, CUDA events on the launching stream around each step (the K steps
                 are enqueued with BLG_F_ASYNC, the record count is collected after the timed region), max over ranks
-  e2e           the same call with HOST (pinned) buffers and the smallest record layout (BLG_F_RUNS, 10 B per record + a run
-                list): H2D of the bases and D2H of the records inside the timing; e2e_compact14 = BLG_F_POS32 (14 B),
-                e2e_records18 = the default 18-byte layout
+  e2e           the same call with HOST (pinned) buffers and the smallest record layout (BLG_F_RUNS | BLG_F_TIGHT, 6 B per record
+                + a run list): H2D of the bases and D2H of the records inside the timing; e2e_runs10 = BLG_F_RUNS alone (10 B),
+                e2e_compact14 = BLG_F_POS32 (14 B), e2e_records18 = the default 18-byte layout; e2e_packed_input(_tight) = the
+                same fed 2-bit packed bases
   roofline      algorithmic bytes (1 B/base + 18 B/record) / kernel time vs the measured HBM copy peak
   roofline_int  why the HBM fraction is what it is: executed instructions per base and pipe utilisation (from the committed
                 ncu capture, with its git sha), hashes per second of this run against the hash rate the machine sustains
@@ -482,10 +483,12 @@ def run_gpu(args):
     run_cap = cap // 64 + 65536
     hp_runs = [ctx.host_alloc(run_cap * 8), ctx.host_alloc(run_cap * 8)]
     e2e = {}
-    for name, flags in (("records18", 0), ("compact14", _capi.F_POS32), ("runs10", _capi.F_RUNS)):
+    TIGHT = _capi.F_RUNS | _capi.F_TIGHT
+    for name, flags in (("records18", 0), ("compact14", _capi.F_POS32), ("runs10", _capi.F_RUNS), ("tight6", TIGHT)):
         def step_host():
             return ctx.super_kmers_raw(hp_in, n, K, M, SEED, CANON, hp[0], hp[1], hp[2], hp[3], cap, flags=flags, win_range=(win_lo, win_hi),
-                                       run_ptrs=hp_runs if flags & _capi.F_RUNS else None, run_capacity=run_cap if flags & _capi.F_RUNS else 0)
+                                       run_ptrs=hp_runs if flags & _capi.F_RUNS else None, run_capacity=run_cap if flags & _capi.F_RUNS else 0,
+                                       tight_ptrs=(hp[0], hp[2], hp[3]) if flags & _capi.F_TIGHT else None)
         for _ in range(2):
             c2 = step_host()
         assert c2 == count, (c2, count)
@@ -497,13 +500,17 @@ def run_gpu(args):
         torch.cuda.synchronize()
         e2e[name] = ((time.perf_counter() - t0) * 1e3 / e2e_steps, st["bytes_h2d"], st["bytes_d2h"])
         # parity of the host path: same records as the device-resident run (checksums over what landed in host memory)
-        hv = np_from_ptr(hp[0], cap * 8, np.uint64)[:count]
+        from biolib_b200.context import expand_runs, unpack_tight
+        if flags & _capi.F_TIGHT:
+            hv, h_size, h_pos = unpack_tight(np_from_ptr(hp[0], cap * 4, np.uint32)[:count], np_from_ptr(hp[2], cap, np.uint8)[:count],
+                                             np_from_ptr(hp[3], cap, np.uint8)[:count])
+        else:
+            hv = np_from_ptr(hp[0], cap * 8, np.uint64)[:count]
+            h_size, h_pos = np_from_ptr(hp[2], cap, np.uint8)[:count], np_from_ptr(hp[3], cap, np.uint8)[:count]
         assert int(hv.sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
         if flags & _capi.F_RUNS:
-            from biolib_b200.context import expand_runs
             nr = ctx.last_n_runs
-            pos = expand_runs(np_from_ptr(hp_runs[0], run_cap * 8, np.uint64)[:nr], np_from_ptr(hp_runs[1], run_cap * 8, np.uint64)[:nr],
-                              np_from_ptr(hp[2], cap, np.uint8)[:count], np_from_ptr(hp[3], cap, np.uint8)[:count])
+            pos = expand_runs(np_from_ptr(hp_runs[0], run_cap * 8, np.uint64)[:nr], np_from_ptr(hp_runs[1], run_cap * 8, np.uint64)[:nr], h_size, h_pos)
         else:
             pos = np_from_ptr(hp[1], cap * 8, np.uint32 if flags else np.uint64)[:count].astype(np.uint64) + np.uint64(win_lo if flags else 0)
         assert int(pos.sum(dtype=np.uint64)) == int(d_mm[:count].sum().item()) & (2**64 - 1)
@@ -527,18 +534,36 @@ def run_gpu(args):
     torch.cuda.synchronize()
     e2e["packed_in"] = ((time.perf_counter() - t0) * 1e3 / e2e_steps, st["bytes_h2d"], st["bytes_d2h"])
     assert int(np_from_ptr(hp[0], cap * 8, np.uint64)[:count].sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
+
+    def step_packed_tight():
+        return ctx.super_kmers_packed_raw(hp_codes, n, bs.ctypes.data if bs.size else 0, bl.ctypes.data if bl.size else 0, bs.size, K, M, SEED, CANON,
+                                          0, 0, 0, 0, cap, flags=TIGHT, win_range=(win_lo, win_hi), run_ptrs=hp_runs, run_capacity=run_cap,
+                                          tight_ptrs=(hp[0], hp[2], hp[3]))
+    for _ in range(2):
+        c2 = step_packed_tight()
+    assert c2 == count, (c2, count)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_packed_tight()
+        st = ctx.stats()
+    torch.cuda.synchronize()
+    e2e["packed_tight"] = ((time.perf_counter() - t0) * 1e3 / e2e_steps, st["bytes_h2d"], st["bytes_d2h"])
+    hv, _, _ = unpack_tight(np_from_ptr(hp[0], cap * 4, np.uint32)[:count], np_from_ptr(hp[2], cap, np.uint8)[:count], np_from_ptr(hp[3], cap, np.uint8)[:count])
+    assert int(hv.sum(dtype=np.uint64)) == int(d_value[:count].sum().item()) & (2**64 - 1)
     for p in [hp_in, hp_codes] + hp + hp_runs:
         ctx.host_free(p)
 
     ctx.set_stream(stream.cuda_stream)
     extras = None if args.no_extra else run_extras(torch, dist, ctx, dev, flush, world, rank)
 
-    t = torch.tensor([step_ms, e2e["runs10"][0], kernel_ms, e2e["records18"][0], e2e["compact14"][0], e2e["packed_in"][0]], dtype=torch.float64, device=dev)
+    t = torch.tensor([step_ms, e2e["tight6"][0], kernel_ms, e2e["records18"][0], e2e["compact14"][0], e2e["packed_in"][0], e2e["runs10"][0],
+                      e2e["packed_tight"][0]], dtype=torch.float64, device=dev)
     cnt = torch.tensor([count, nwin, exact_tiles], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)   # the path's only collective: per-GPU counts
-    step_ms, e2e_ms, kernel_ms, e2e18_ms, e2e14_ms, e2ep_ms = t.tolist()
+    step_ms, e2e_ms, kernel_ms, e2e18_ms, e2e14_ms, e2ep_ms, e2e10_ms, e2ept_ms = t.tolist()
     total_records, total_win, total_exact = cnt.tolist()
     total_bases = SHARD * world
 
@@ -557,10 +582,17 @@ def run_gpu(args):
                                    "uniform(42+shard) (BASELINE configs[1])",
                        "k": K, "m": M, "bases_per_gpu": SHARD, "records": total_records, "kmers": total_win,
                        "l2": "256 MiB flush write between timed steps", "sharding": f"chunk+halo x{world}",
-                       "host": numa, "e2e_layout": "BLG_F_RUNS: value u64 + size u8 + mm_pos u8 per record, plus (first record, start) per run of contiguous "
-                                     "super-k-mers; positions follow by adding sizes, as in the reference's own sequential view"},
-            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["runs10"][1]),
-                    "d2h_bytes_per_step": int(e2e["runs10"][2]), "steps": e2e_steps, "ms_per_step": e2e_ms},
+                       "host": numa, "e2e_layout": "BLG_F_RUNS | BLG_F_TIGHT: value in 5 bytes (u32 + u8 arrays) + one byte holding size - 1 and mm_pos per "
+                                     "record, plus (first record, start) per run of contiguous super-k-mers; positions follow by adding sizes, as in "
+                                     "the reference's own sequential view. ASCII bases in."},
+            "e2e": {"value": total_bases / (e2e_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["tight6"][1]),
+                    "d2h_bytes_per_step": int(e2e["tight6"][2]), "steps": e2e_steps, "ms_per_step": e2e_ms},
+            "e2e_runs10": {"value": total_bases / (e2e10_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["runs10"][1]),
+                           "d2h_bytes_per_step": int(e2e["runs10"][2]), "ms_per_step": e2e10_ms,
+                           "note": "BLG_F_RUNS alone: value u64 + size u8 + mm_pos u8 per record (the round's earlier headline layout)"},
+            "e2e_packed_input_tight": {"value": total_bases / (e2ept_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["packed_tight"][1]),
+                                       "d2h_bytes_per_step": int(e2e["packed_tight"][2]), "ms_per_step": e2ept_ms,
+                                       "note": "2-bit packed host input and 6-byte records: the fewest bytes over PCIe in both directions"},
             "e2e_compact14": {"value": total_bases / (e2e14_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["compact14"][1]),
                               "d2h_bytes_per_step": int(e2e["compact14"][2]), "ms_per_step": e2e14_ms},
             "e2e_packed_input": {"value": total_bases / (e2ep_ms * 1e-3) / 1e9, "unit": "Gbases/s", "h2d_bytes_per_step": int(e2e["packed_in"][1]),

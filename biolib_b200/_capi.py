@@ -19,6 +19,7 @@ F_DEVICE_INPUT, F_DEVICE_OUTPUT, F_EMIT_HASH, F_NO_SIZE, F_EMIT_ID, F_POS32 = 0x
 F_REF_DROP_LAST = 0x40
 F_ASYNC = 0x80
 F_RUNS = 0x100
+F_TIGHT = 0x200
 
 EXPORTS = [
     "blg_abi_version", "blg_strerror", "blg_create", "blg_destroy", "blg_set_stream", "blg_set_pipeline", "blg_last_error",
@@ -42,7 +43,8 @@ class KmerOut(C.Structure):
 class SkOut(C.Structure):
     _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value", C.c_void_p), ("mm_start", C.c_void_p),
                 ("size", C.c_void_p), ("mm_pos", C.c_void_p), ("hash", C.c_void_p), ("id", C.c_void_p), ("owner", C.c_void_p),
-                ("n_runs", C.c_uint64), ("run_capacity", C.c_uint64), ("run_first_record", C.c_void_p), ("run_start", C.c_void_p)]
+                ("n_runs", C.c_uint64), ("run_capacity", C.c_uint64), ("run_first_record", C.c_void_p), ("run_start", C.c_void_p),
+                ("value_lo32", C.c_void_p), ("value_hi8", C.c_void_p), ("size_pos", C.c_void_p)]
 
 
 class PackedSeq(C.Structure):

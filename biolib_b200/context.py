@@ -94,13 +94,14 @@ class Context:
         return res
 
     def super_kmers(self, seq, k: int, m: int, seed: int = 0, canonical: bool = False, offsets=None, want_hash=True,
-                    win_range=None, minimizers_only=False, want_id=False, pos32=False, runs=False) -> dict:
+                    win_range=None, minimizers_only=False, want_id=False, pos32=False, runs=False, tight=False) -> dict:
         """pos32: ask for the compact record layout (BLG_F_POS32: 32-bit positions relative to the range start); the
-        returned mm_start / sk_start are widened back to absolute uint64 so that both layouts compare equal."""
+        returned mm_start / sk_start are widened back to absolute uint64 so that both layouts compare equal.
+        tight (with runs): BLG_F_TIGHT, 6-byte records; unpacked here into the same value / size / mm_pos arrays."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
         p = Params(k=k, m=m, canonical=int(canonical), flags=(F_EMIT_HASH if want_hash else 0) | (_capi.F_EMIT_ID if want_id else 0) | (_capi.F_POS32 if pos32 else 0) |
-                   (_capi.F_RUNS if runs else 0), seed=seed & (2**64 - 1))
+                   (_capi.F_RUNS if runs else 0) | (_capi.F_TIGHT if tight else 0), seed=seed & (2**64 - 1))
         out = SkOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1)
         if win_range is not None:
@@ -112,21 +113,27 @@ class Context:
         self._check(st)
         n = out.count
         try:
+            if tight:
+                # BLG_F_TIGHT: value = lo32 | hi8 << 32, size_pos = (size - 1) | mm_pos << 4
+                value, sz, mp = unpack_tight(_copy(out.value_lo32, n, np.uint32), _copy(out.value_hi8, n, np.uint8) if out.value_hi8 else None,
+                                             _copy(out.size_pos, n, np.uint8))
             if runs:
                 # BLG_F_RUNS: no positions came back; rebuild them from the run list (what a streaming consumer does on the fly)
                 rf, rs = _copy(out.run_first_record, out.n_runs, np.uint64), _copy(out.run_start, out.n_runs, np.uint64)
-                mm = expand_runs(rf, rs, _copy(out.size, n, np.uint8), _copy(out.mm_pos, n, np.uint8))
+                if not tight:
+                    sz, mp = _copy(out.size, n, np.uint8), _copy(out.mm_pos, n, np.uint8)
+                mm = expand_runs(rf, rs, sz, mp)
             elif pos32:
                 base = 0 if win_range is None else min(int(win_range[0]), max(b.size - k + 1, 0))
                 mm = _copy(out.mm_start, n, np.uint32).astype(np.uint64) + np.uint64(base)
             else:
                 mm = _copy(out.mm_start, n, np.uint64)
-            res = dict(n=n, value=_copy(out.value, n, np.uint64), mm_start=mm)
+            res = dict(n=n, value=value if tight else _copy(out.value, n, np.uint64), mm_start=mm)
             if runs:
                 res["n_runs"] = int(out.n_runs)
             if not minimizers_only:
-                res["size"] = _copy(out.size, n, np.uint8)
-                res["mm_pos"] = _copy(out.mm_pos, n, np.uint8)
+                res["size"] = sz if tight else _copy(out.size, n, np.uint8)
+                res["mm_pos"] = mp if tight else _copy(out.mm_pos, n, np.uint8)
                 res["sk_start"] = res["mm_start"] - res["mm_pos"].astype(np.uint64)
             if want_hash:
                 res["hash"] = _copy(out.hash, n, np.uint64)
@@ -227,14 +234,17 @@ class Context:
 
     def super_kmers_packed_raw(self, codes_ptr: int, n_bases: int, break_start_ptr: int, break_len_ptr: int, n_breaks: int, k: int, m: int,
                                seed: int, canonical: bool, value_ptr: int, mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int,
-                               flags: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0) -> int:
-        """blg_super_kmers_packed with caller-owned (pinned) host arrays; with F_RUNS the number of runs is left in self.last_n_runs."""
+                               flags: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0, tight_ptrs=None) -> int:
+        """blg_super_kmers_packed with caller-owned (pinned) host arrays; with F_RUNS the number of runs is left in self.last_n_runs.
+        With F_TIGHT pass tight_ptrs=(value_lo32_ptr, value_hi8_ptr, size_pos_ptr) (value / size / mm_pos pointers are ignored)."""
         seq = _capi.PackedSeq(codes=codes_ptr, n_bases=n_bases, break_start=break_start_ptr or None, break_len=break_len_ptr or None,
                               n_breaks=n_breaks)
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
         out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr or None, size=size_ptr or None,
                     mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None, n_runs=0, run_capacity=run_capacity,
-                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None)
+                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None,
+                    value_lo32=tight_ptrs[0] if tight_ptrs else None, value_hi8=(tight_ptrs[1] or None) if tight_ptrs else None,
+                    size_pos=tight_ptrs[2] if tight_ptrs else None)
         lo, hi = (0, 2**64 - 1) if win_range is None else win_range
         self._check(self.L.blg_super_kmers_packed(self.h, C.byref(seq), None, 0, int(lo), int(hi), C.byref(p), C.byref(out)))
         self.last_n_runs = int(out.n_runs)
@@ -319,13 +329,16 @@ class Context:
 
     def super_kmers_raw(self, bases_ptr: int, n_bases: int, k: int, m: int, seed: int, canonical: bool, value_ptr: int,
                         mm_start_ptr: int, size_ptr: int, mm_pos_ptr: int, capacity: int, flags: int = 0,
-                        offsets_ptr: int = 0, n_seq: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0) -> int:
+                        offsets_ptr: int = 0, n_seq: int = 0, win_range=None, run_ptrs=None, run_capacity: int = 0, tight_ptrs=None) -> int:
         """Raw-pointer call with caller-owned arrays (host pointers unless the DEVICE flags are set). With F_RUNS pass
-        run_ptrs=(first_record_ptr, start_ptr) and run_capacity; the number of runs is left in self.last_n_runs."""
+        run_ptrs=(first_record_ptr, start_ptr) and run_capacity; the number of runs is left in self.last_n_runs. With F_TIGHT pass
+        tight_ptrs=(value_lo32_ptr, value_hi8_ptr, size_pos_ptr) (value / size / mm_pos pointers are ignored)."""
         p = Params(k=k, m=m, canonical=int(canonical), flags=flags, seed=seed & (2**64 - 1))
         out = SkOut(count=0, capacity=capacity, value=value_ptr, mm_start=mm_start_ptr or None, size=size_ptr or None,
                     mm_pos=mm_pos_ptr or None, hash=None, id=None, owner=None, n_runs=0, run_capacity=run_capacity,
-                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None)
+                    run_first_record=run_ptrs[0] if run_ptrs else None, run_start=run_ptrs[1] if run_ptrs else None,
+                    value_lo32=tight_ptrs[0] if tight_ptrs else None, value_hi8=(tight_ptrs[1] or None) if tight_ptrs else None,
+                    size_pos=tight_ptrs[2] if tight_ptrs else None)
         lo, hi = (0, 2**64 - 1) if win_range is None else win_range
         self._check(self.L.blg_super_kmers_range(self.h, C.c_void_p(bases_ptr), n_bases, C.c_void_p(offsets_ptr or 0), n_seq,
                                                  int(lo), int(hi), C.byref(p), C.byref(out)))
@@ -353,6 +366,14 @@ class Context:
         else:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         return out.count
+
+
+def unpack_tight(value_lo32, value_hi8, size_pos):
+    """BLG_F_TIGHT records -> (value uint64, size uint8, mm_pos uint8)."""
+    value = value_lo32.astype(np.uint64)
+    if value_hi8 is not None:
+        value |= value_hi8.astype(np.uint64) << np.uint64(32)
+    return value, (size_pos & np.uint8(15)) + np.uint8(1), size_pos >> np.uint8(4)
 
 
 def expand_runs(run_first_record, run_start, size, mm_pos) -> np.ndarray:

@@ -86,6 +86,8 @@ struct blg_ctx {
     DevBuf packed, brk, fx_text, fx_scratch; // packed codes + break list of a packed-input call; FASTA/FASTQ text and parser scratch
     DevBuf in, offs, status, small;  // small: [0] tile counter (u32 in a u64 slot), [1] total, [2] tiles redone exactly (sk4)
     DevBuf o_value, o_mm, o_size, o_pos, o_hash, o_id, rank, o_lo, o_hi, o_position;
+    DevBuf o_tlo, o_thi, o_tnib;            // BLG_F_TIGHT: packed value words / high bytes / size-position bytes
+    cudaEvent_t ev_pk[16] = {};             // ... the pack kernel of pipeline piece i is done
     unsigned long long* h_total = nullptr;  // pinned + mapped: [0] record count, [1] cumulative exact-path tiles (sk4 writes both itself)
     unsigned long long* d_total = nullptr;  // the device's address of h_total
     // sk4: scan scratch that is never zeroed between launches (epoch-tagged words, a ticket counter that only grows)
@@ -304,6 +306,14 @@ int validate_sk(blg_ctx* c, const blg_params* p, const blg_sk_out* out)
         c->err = "need 1 <= m <= min(k, 32) and k <= 64";
         return BLG_E_INVALID;
     }
+    if (p->flags & BLG_F_TIGHT) {
+        if (!(p->flags & BLG_F_RUNS) || p->m > 20 || p->k - p->m > 15 || (p->flags & (BLG_F_EMIT_HASH | BLG_F_EMIT_ID))) {
+            c->err = "BLG_F_TIGHT: with BLG_F_RUNS, m <= 20, k - m <= 15, no hash / id output";
+            return BLG_E_INVALID;
+        }
+        if (out->capacity > 0 && (!out->value_lo32 || !out->size_pos || (p->m > 16 && !out->value_hi8))) { c->err = "BLG_F_TIGHT: capacity > 0 needs value_lo32, size_pos (and value_hi8 for m > 16)"; return BLG_E_INVALID; }
+        return BLG_OK;
+    }
     if (out->capacity > 0 && (!out->value || (!out->mm_start && !(p->flags & BLG_F_RUNS)))) { c->err = "capacity > 0 needs value and mm_start arrays"; return BLG_E_INVALID; }
     return BLG_OK;
 }
@@ -396,9 +406,11 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     const bool want_id = (p->flags & BLG_F_EMIT_ID) != 0;
     const bool runs = (p->flags & BLG_F_RUNS) != 0;       // positions stay on the device; the run list is downloaded at the end
     const bool pos32 = (p->flags & BLG_F_POS32) != 0;
+    const bool tight = (p->flags & BLG_F_TIGHT) != 0;  // records leave as (value_lo32, value_hi8, size_pos), packed per piece on the device
     const size_t posb = pos32 ? 4 : 8;                 // bytes per position entry
     const uint64_t nwin = hi - lo;
     const int k = p->k, m = p->m, w = k - m + 1;
+    const bool thi = tight && m > 16;
     if (nwin < (8u << 20)) return BLG_OK;
     int rc;
     if ((rc = check_offsets_host(offs, n_seq, n)) != BLG_OK) { c->err = "seq_offsets must start at 0, end at n_bases and be non-decreasing"; return rc; }
@@ -410,6 +422,7 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (with_size && ((rc = ensure(c, c->o_size, cap)) != BLG_OK || (rc = ensure(c, c->o_pos, cap)) != BLG_OK)) return rc;
     if (want_hash && (rc = ensure(c, c->o_hash, cap * 8)) != BLG_OK) return rc;
     if (want_id && (rc = ensure(c, c->o_id, cap * 8)) != BLG_OK) return rc;
+    if (tight && ((rc = ensure(c, c->o_tlo, cap * 4)) != BLG_OK || (rc = ensure(c, c->o_tnib, cap)) != BLG_OK || (thi && (rc = ensure(c, c->o_thi, cap)) != BLG_OK))) return rc;
     const unsigned long long* d_offs = nullptr;
     if (offs) {
         const size_t ob = (n_seq + 1) * sizeof(uint64_t);
@@ -429,11 +442,15 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (out->capacity == 0) {
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
-        h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr;
-        if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK) return rc;
+        h.size = h.mm_pos = nullptr; h.hash = nullptr; h.id = nullptr; h.value = nullptr;
+        h.value_lo32 = nullptr; h.value_hi8 = h.size_pos = nullptr;
+        if (tight) {
+            if ((rc = alloc_owned(c, false, cap, &h.value_lo32, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.size_pos, ow, 3)) != BLG_OK) return rc;
+            if (thi && (rc = alloc_owned(c, false, cap, &h.value_hi8, ow, 2)) != BLG_OK) return rc;
+        } else if ((rc = alloc_owned(c, false, cap, &h.value, ow, 0)) != BLG_OK) return rc;
         h.mm_start = nullptr;
         if (!runs && (rc = alloc_owned(c, false, pos32 ? (cap + 1) / 2 : cap, &h.mm_start, ow, 1)) != BLG_OK) return rc;
-        if (with_size && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) return rc;
+        if (with_size && !tight && ((rc = alloc_owned(c, false, cap, &h.size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.mm_pos, ow, 3)) != BLG_OK)) return rc;
         if (want_hash && (rc = alloc_owned(c, false, cap, &h.hash, ow, 4)) != BLG_OK) return rc;
         if (want_id && (rc = alloc_owned(c, false, cap, &h.id, ow, 5)) != BLG_OK) return rc;
     }
@@ -489,7 +506,20 @@ int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         uint64_t cnt = 0;
         if ((rc = run_sk_once(c, a, &cnt)) != BLG_OK) return rc;   // returns after the kernel: count is known
         if (cnt > cap - done) { overflow = true; done += cnt; break; }
-        if (cnt) {
+        if (cnt && tight) {
+            // 6 bytes per record instead of 10: pack on the compute stream, download behind it
+            unsigned int* t_lo = static_cast<unsigned int*>(c->o_tlo.p) + done;
+            unsigned char* t_hi = thi ? static_cast<unsigned char*>(c->o_thi.p) + done : nullptr;
+            unsigned char* t_nb = static_cast<unsigned char*>(c->o_tnib.p) + done;
+            CK(c, tight_pack_launch(a.value, a.size, a.mm_pos, cnt, t_lo, t_hi, t_nb, c->stream));
+            c->stats.kernel_launches += 1;
+            CK(c, cudaEventRecord(c->ev_pk[i], c->stream));
+            CK(c, cudaStreamWaitEvent(c->s_out, c->ev_pk[i], 0));
+            CK(c, cudaMemcpyAsync(h.value_lo32 + done, t_lo, cnt * 4, cudaMemcpyDeviceToHost, c->s_out));
+            if (thi) CK(c, cudaMemcpyAsync(h.value_hi8 + done, t_hi, cnt, cudaMemcpyDeviceToHost, c->s_out));
+            CK(c, cudaMemcpyAsync(h.size_pos + done, t_nb, cnt, cudaMemcpyDeviceToHost, c->s_out));
+            c->stats.bytes_d2h += cnt * (thi ? 6 : 5);
+        } else if (cnt) {
             CK(c, cudaMemcpyAsync(h.value + done, a.value, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
             if (!runs) CK(c, cudaMemcpyAsync(reinterpret_cast<char*>(h.mm_start) + done * posb, static_cast<char*>(c->o_mm.p) + done * posb, cnt * posb, cudaMemcpyDeviceToHost, c->s_out));
             c->stats.bytes_d2h += cnt * (8 + (runs ? 0 : posb));
@@ -557,9 +587,10 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     const size_t posb = pos32 ? 4 : 8;
     if (pos32 && want_id) { c->err = "BLG_F_POS32 cannot be combined with BLG_F_EMIT_ID"; return BLG_E_INVALID; }
     const bool runs = (p->flags & BLG_F_RUNS) != 0;
+    const bool tight = (p->flags & BLG_F_TIGHT) != 0, thi = tight && m > 16;
     if (runs && (dev_out || pos32 || !with_size || (p->flags & BLG_F_NO_SIZE))) { c->err = "BLG_F_RUNS: host output of the super-k-mer calls only, without BLG_F_POS32"; return BLG_E_INVALID; }
     with_size = with_size && !(p->flags & BLG_F_NO_SIZE);
-    if (out->capacity > 0 && with_size && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
+    if (out->capacity > 0 && with_size && !tight && (!out->size || !out->mm_pos)) { c->err = "size / mm_pos arrays missing"; return BLG_E_INVALID; }
     if (out->capacity > 0 && want_hash && !out->hash) { c->err = "BLG_F_EMIT_HASH needs a hash array"; return BLG_E_INVALID; }
     if (out->capacity > 0 && want_id && !out->id) { c->err = "BLG_F_EMIT_ID needs an id array"; return BLG_E_INVALID; }
 
@@ -570,7 +601,11 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     out->count = 0;
     if (pos32 && nwin + (uint64_t)w > 0xFFFFFFFFull) { c->err = "BLG_F_POS32: the window range does not fit 32-bit positions"; return BLG_E_INVALID; }
     if (nwin == 0) {
-        if (out->capacity == 0) { out->value = out->mm_start = out->hash = out->id = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr; }
+        if (out->capacity == 0) {
+            out->value = out->mm_start = out->hash = out->id = nullptr; out->size = out->mm_pos = nullptr; out->owner = nullptr;
+            if (tight) { out->value_lo32 = nullptr; out->value_hi8 = out->size_pos = nullptr; }
+            if (runs) { out->n_runs = 0; out->run_first_record = out->run_start = nullptr; }
+        }
         c->stats.total_ms = tm.ms();
         return BLG_OK;
     }
@@ -675,16 +710,37 @@ int sk_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, siz
     } else {
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
-        out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr;
-        if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK) { free_owner(ow); return rc; }
+        out->size = out->mm_pos = nullptr; out->hash = nullptr; out->id = nullptr; out->value = nullptr;
+        if (tight) {
+            out->value_hi8 = nullptr;
+            if ((rc = alloc_owned(c, false, total, &out->value_lo32, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->size_pos, ow, 3)) != BLG_OK ||
+                (thi && (rc = alloc_owned(c, false, total, &out->value_hi8, ow, 2)) != BLG_OK)) { free_owner(ow); return rc; }
+        } else if ((rc = alloc_owned(c, false, total, &out->value, ow, 0)) != BLG_OK) { free_owner(ow); return rc; }
         out->mm_start = nullptr;
         if (!runs && (rc = alloc_owned(c, false, pos32 ? (total + 1) / 2 : total, &out->mm_start, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
-        if (with_size && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
+        if (with_size && !tight && ((rc = alloc_owned(c, false, total, &out->size, ow, 2)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->mm_pos, ow, 3)) != BLG_OK)) { free_owner(ow); return rc; }
         if (want_hash && (rc = alloc_owned(c, false, total, &out->hash, ow, 4)) != BLG_OK) { free_owner(ow); return rc; }
         if (want_id && (rc = alloc_owned(c, false, total, &out->id, ow, 5)) != BLG_OK) { free_owner(ow); return rc; }
         out->owner = ow;
     }
-    if (total) {
+    if (total && tight) {
+        if ((rc = ensure(c, c->o_tlo, total * 4)) != BLG_OK || (rc = ensure(c, c->o_tnib, total)) != BLG_OK || (thi && (rc = ensure(c, c->o_thi, total)) != BLG_OK)) {
+            if (out->capacity == 0) { free_owner(ow); out->owner = nullptr; }
+            return rc;
+        }
+        unsigned char* t_hi = thi ? static_cast<unsigned char*>(c->o_thi.p) : nullptr;
+        CK(c, tight_pack_launch(a.value, a.size, a.mm_pos, total, static_cast<unsigned int*>(c->o_tlo.p), t_hi, static_cast<unsigned char*>(c->o_tnib.p), c->stream));
+        c->stats.kernel_launches += 1;
+        CK(c, cudaMemcpyAsync(out->value_lo32, c->o_tlo.p, total * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (thi) CK(c, cudaMemcpyAsync(out->value_hi8, t_hi, total, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaMemcpyAsync(out->size_pos, c->o_tnib.p, total, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * (thi ? 6 : 5);
+        CK(c, cudaStreamSynchronize(c->stream));
+        if ((rc = emit_runs(c, a.mm_start, a.mm_pos, a.size, total, out, out->capacity == 0 ? ow : nullptr)) != BLG_OK) {
+            if (out->capacity == 0) { free_owner(ow); out->owner = nullptr; }
+            return rc;
+        }
+    } else if (total) {
         CK(c, cudaMemcpyAsync(out->value, a.value, total * 8, cudaMemcpyDeviceToHost, c->stream));
         if (!runs) CK(c, cudaMemcpyAsync(out->mm_start, pos32 ? static_cast<void*>(a.mm_start32) : static_cast<void*>(a.mm_start), total * posb, cudaMemcpyDeviceToHost, c->stream));
         c->stats.bytes_d2h += total * (8 + (runs ? 0 : posb));
@@ -760,6 +816,7 @@ int blg_create(int device, blg_ctx** out)
               cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < 2; ++i) ok = cudaEventCreateWithFlags(&c->ev_dl[i], cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < PIPE_MAX; ++i) ok = cudaEventCreateWithFlags(&c->ev_pk[i], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { blg_destroy(c); return BLG_E_CUDA; }
     *out = c;
     return BLG_OK;
@@ -771,7 +828,7 @@ int blg_destroy(blg_ctx* c)
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
     for (DevBuf* b : {&c->in, &c->offs, &c->status, &c->small, &c->packed, &c->brk, &c->fx_text, &c->fx_scratch, &c->sk4_status, &c->sk4_small, &c->o_value, &c->o_mm, &c->o_size, &c->o_pos, &c->o_hash,
-                      &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position})
+                      &c->o_id, &c->rank, &c->o_lo, &c->o_hi, &c->o_position, &c->o_tlo, &c->o_thi, &c->o_tnib})
         if (b->p) cudaFree(b->p);
     for (auto& b : c->pool_dev.free_blocks) cudaFree(b.p);
     for (auto& b : c->pool_pinned.free_blocks) cudaFreeHost(b.p);
@@ -781,6 +838,7 @@ int blg_destroy(blg_ctx* c)
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     for (cudaEvent_t e : c->ev_in) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : c->ev_dl) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_pk) if (e) cudaEventDestroy(e);
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_out) cudaStreamDestroy(c->s_out);
     delete c;
@@ -1615,6 +1673,7 @@ void blg_free_sk_out(blg_ctx* c, blg_sk_out* out)
         out->size = out->mm_pos = nullptr;
         out->run_first_record = out->run_start = nullptr;
         out->n_runs = 0;
+        out->value_lo32 = nullptr; out->value_hi8 = out->size_pos = nullptr;
         out->owner = nullptr;
         out->count = 0;
     }

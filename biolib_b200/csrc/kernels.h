@@ -186,6 +186,8 @@ cudaError_t lower_bound_u64(const unsigned long long* keys, unsigned long long n
                             unsigned long long* d_out, cudaStream_t stream);
 
 // BLG_F_RUNS: the maximal runs of records in which every record starts where the previous one ended
+cudaError_t tight_pack_launch(const unsigned long long* value, const unsigned char* size, const unsigned char* mm_pos, unsigned long long n,
+                              unsigned int* lo32, unsigned char* hi8, unsigned char* size_pos, cudaStream_t stream);
 size_t runs_scratch_bytes(unsigned long long n);
 cudaError_t runs_launch(const unsigned long long* mm_start, const unsigned char* mm_pos, const unsigned char* size, unsigned long long n, void* scratch,
                         unsigned long long** first, unsigned long long** start, unsigned long long* d_total, cudaStream_t stream, int* launches);

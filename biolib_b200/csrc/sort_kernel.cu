@@ -370,6 +370,28 @@ __global__ void __launch_bounds__(IX_THREADS) intersect_count_kernel(const u64* 
 
 }  // namespace
 
+// BLG_F_TIGHT: (value u64, size u8, mm_pos u8) -> (value bits 0..31, bits 32..39, (size - 1) | mm_pos << 4): 6 bytes per record over PCIe
+namespace {
+__global__ void __launch_bounds__(256) tight_pack_kernel(const u64* __restrict__ value, const u8* __restrict__ size, const u8* __restrict__ mm_pos, u64 n,
+                                                         u32* __restrict__ lo32, u8* __restrict__ hi8, u8* __restrict__ size_pos)
+{
+    const u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 v = value[i];
+    lo32[i] = (u32)v;
+    if (hi8 != nullptr) hi8[i] = (u8)(v >> 32);
+    size_pos[i] = (u8)(((u32)size[i] - 1u) | ((u32)mm_pos[i] << 4));
+}
+}  // namespace
+
+cudaError_t tight_pack_launch(const unsigned long long* value, const unsigned char* size, const unsigned char* mm_pos, unsigned long long n,
+                              unsigned int* lo32, unsigned char* hi8, unsigned char* size_pos, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    tight_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(value, size, mm_pos, n, lo32, hi8, size_pos);
+    return cudaGetLastError();
+}
+
 size_t runs_scratch_bytes(unsigned long long n) { return (size_t)((3 * n + (n + SC_BLOCK - 1) / SC_BLOCK + 16) * 8 + 256); }
 
 // scratch: [flags n][first n][start n][sums]; *d_total (device) = number of runs; first / start are returned as pointers into scratch

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define BLG_ABI_VERSION 2
+#define BLG_ABI_VERSION 3
 
 typedef enum blg_status {
     BLG_OK = 0,
@@ -67,6 +67,11 @@ typedef enum blg_status {
                                     *   run_first_record[j]  index of the first record of run j      run_start[j]  its sk_start
                                     * so that sk_start[r] = run_start[j] + sum of size[run_first_record[j] .. r), mm_start = sk_start + mm_pos.
                                     * 10 instead of 18 bytes per record. With caller arrays set run_capacity and the two run arrays. */
+#define BLG_F_TIGHT         0x200u /* with BLG_F_RUNS, for m <= 20 and k - m <= 15: the same records in 6 bytes (5 for m <= 16) instead of 10 over PCIe.
+                                    * out->value / size / mm_pos stay NULL; instead
+                                    *   value_lo32[i]  bits 0..31 of the minimizer value      value_hi8[i]  bits 32..39 (NULL / untouched for m <= 16)
+                                    *   size_pos[i]    (size - 1) | mm_pos << 4
+                                    * (packed on the device by one more small kernel per piece). Not combinable with BLG_F_EMIT_HASH / _ID. */
 #define BLG_F_EMIT_ID       0x10u /* also fill out->id (minimizer_context_t::id; one extra pass over the bases) */
 
 typedef struct blg_params {
@@ -120,6 +125,10 @@ typedef struct blg_sk_out {
     uint64_t run_capacity;      /* in, with caller arrays */
     uint64_t* run_first_record;
     uint64_t* run_start;
+    /* only with BLG_F_TIGHT (ABI version 3) */
+    uint32_t* value_lo32;
+    uint8_t* value_hi8;
+    uint8_t* size_pos;
 } blg_sk_out;
 
 typedef struct blg_stats {

@@ -648,6 +648,48 @@ def test_runs_layout_pipelined(gpu):
     assert st["bytes_d2h"] < a["n"] * 10 + b["n_runs"] * 16 + 4096
 
 
+@pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (31, 16), (35, 20), (8, 4), (16, 1)])
+def test_tight_layout(gpu, oracle, k, m):
+    """BLG_F_TIGHT: the BLG_F_RUNS records in 6 bytes (5 for m <= 16): value_lo32 / value_hi8 / (size - 1) | mm_pos << 4."""
+    rng = np.random.default_rng(k * 7 + m)
+    s = rand_seq(rng, 150_000, 0.0008, 0.02)
+    offs = np.concatenate([[0], np.cumsum(rng.integers(0, 3000, size=90))]).astype(np.uint64)
+    offs = np.concatenate([offs[offs < s.size], [s.size]]).astype(np.uint64)
+    for canon in (False, True):
+        for o in (None, offs):
+            a = gpu.super_kmers(s, k, m, 42, canon, offsets=o, want_hash=False)
+            b = gpu.super_kmers(s, k, m, 42, canon, offsets=o, want_hash=False, runs=True, tight=True)
+            st = gpu.stats()
+            assert a["n"] == b["n"] > 0
+            for key in ("value", "mm_start", "sk_start", "size", "mm_pos"):
+                assert np.array_equal(a[key], b[key]), (key, k, m)
+            assert st["bytes_d2h"] <= a["n"] * (6 if m > 16 else 5) + b["n_runs"] * 16 + 64     # + the count words of the kernels that copy them
+    o = oracle.super_kmers(s, k, m, 42, True)
+    assert np.array_equal(b["value"], oracle.super_kmers(s, k, m, 42, True, offsets=offs)["value"]) and o["n"] > 0
+    assert gpu.super_kmers(np.zeros(0, np.uint8), k, m, 42, True, want_hash=False, runs=True, tight=True)["n"] == 0
+
+
+def test_tight_layout_rejects_what_does_not_fit(gpu):
+    import biolib_b200
+    s = rand_seq(np.random.default_rng(5), 5000)
+    for k, m, kw in ((31, 21, dict(runs=True)), (40, 19, dict(runs=True)), (31, 19, dict(runs=False)), (31, 19, dict(runs=True, want_hash=True))):
+        with pytest.raises(biolib_b200.BlgError):
+            gpu.super_kmers(s, k, m, 42, True, tight=True, **{"want_hash": False, **kw})
+
+
+def test_tight_layout_pipelined(gpu):
+    """The chunked host path with BLG_F_TIGHT: 6 bytes per record over PCIe, packed piece by piece on the device."""
+    rng = np.random.default_rng(79)
+    s = rand_seq(rng, 20_000_000, 0.00005)
+    a = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False)
+    b = gpu.super_kmers(s, 31, 19, 42, True, want_hash=False, runs=True, tight=True)
+    st = gpu.stats()
+    assert a["n"] == b["n"] > 2_000_000 and b["n_runs"] > 100
+    for key in ("value", "mm_start", "size", "mm_pos"):
+        assert np.array_equal(a[key], b[key]), key
+    assert st["bytes_d2h"] < a["n"] * 6 + b["n_runs"] * 16 + 4096
+
+
 @pytest.mark.parametrize("k,canon,multi", [(31, True, False), (63, True, True), (21, False, True)])
 def test_kmers_pipelined_host_path(gpu, oracle, k, canon, multi):
     """blg_kmers / blg_syncmers / blg_hash_sampled_kmers above 8 Mi k-mer starts: upload, kernel and download overlap piece by

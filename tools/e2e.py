@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Development tool: end-to-end (pinned host in, pinned host out) time of blg_super_kmers for the bench workload, over the
-shapes of the chunked host path (blg_set_pipeline) and the three record layouts.
+shapes of the chunked host path (blg_set_pipeline) and the four record layouts.
 
-    python tools/e2e.py [--layouts runs,pos32,full] [--chunks 4,6,8,12,16] [--divs 2,4,8]
+    python tools/e2e.py [--layouts tight,runs,pos32,full] [--chunks 4,6,8,12,16] [--divs 2,4,8]
 """
 import argparse
 import ctypes as C
@@ -36,13 +36,14 @@ def main():
     npp(hin, n, np.uint8)[:] = s
     hp = [ctx.host_alloc(cap * 8), ctx.host_alloc(cap * 8), ctx.host_alloc(cap), ctx.host_alloc(cap)]
     hr = [ctx.host_alloc(run_cap * 8), ctx.host_alloc(run_cap * 8)]
-    flags = {"full": 0, "pos32": _capi.F_POS32, "runs": _capi.F_RUNS}
+    flags = {"full": 0, "pos32": _capi.F_POS32, "runs": _capi.F_RUNS, "tight": _capi.F_RUNS | _capi.F_TIGHT}
     for lay in a.layouts.split(","):
         f = flags[lay]
 
         def call():
             return ctx.super_kmers_raw(hin, n, 31, 19, 42, True, hp[0], hp[1], hp[2], hp[3], cap, flags=f,
-                                       run_ptrs=hr if f & _capi.F_RUNS else None, run_capacity=run_cap if f & _capi.F_RUNS else 0)
+                                       run_ptrs=hr if f & _capi.F_RUNS else None, run_capacity=run_cap if f & _capi.F_RUNS else 0,
+                                       tight_ptrs=(hp[0], hp[2], hp[3]) if f & _capi.F_TIGHT else None)
         for ch in (int(x) for x in a.chunks.split(",")):
             for dv in (int(x) for x in a.divs.split(",")):
                 ctx._check(ctx.L.blg_set_pipeline(ctx.h, ch, dv))
