@@ -61,6 +61,8 @@ __device__ __forceinline__ u64 add32w(u32 a, u64 c)
     asm("mad.wide.u32 %0, %1, 1, %2;" : "=l"(r) : "r"(a), "l"(c));
     return r;
 }
+// (h >> 1 as IMAD.HI by 2^31 on the FMA pipe instead of SHF on the ALU pipe: measured again with this lowering, slower at 2, 4 and 6
+// of the six sites -- 0.454 -> 0.459 / 0.472 / 0.485 ms per 100 Mbp, profiles/r02_zs_hash_imad_hi_ab.txt.)
 __device__ __forceinline__ void fmix_step(u32& l, u32& h, u64 c) { l ^= h >> 1; mul64c(l, h, c); }
 
 // s8 = (uint32)seed ^ 8: the seed is 32 bits wide (hash.hpp:50), so the high words of both `^= s8` / `+= s8` vanish
