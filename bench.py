@@ -457,6 +457,14 @@ def run_gpu(args):
     exact_tiles = 0
     barrier()
     sampler.start()
+    # a few milliseconds of device-side delay in front of the timed steps: the host enqueues the K steps while it runs, so that a
+    # launch that arrives late (eight ranks and their clock samplers share the box's cores) does not sit between a step's two events
+    try:
+        with torch.cuda.stream(stream):
+            torch.cuda._sleep(int(4e-3 * 1.9e9))
+    except Exception:
+        for _ in range(16):
+            flush.zero_()
     for s, e in ev:
         flush.zero_()           # L2 flush between timed iterations (outside the event pair)
         s.record(stream)
