@@ -177,3 +177,25 @@ def test_hash_sampler_threshold_rate_one_is_clamped():
     assert Context.hash_sampler_threshold(0.5) == int(0.5 * float(2**64 - 1))
     with pytest.raises(ValueError):
         Context.hash_sampler_threshold(1.5)
+
+
+def test_run_list_and_tight_records_unpack(oracle):
+    """Host side of BLG_F_RUNS / BLG_F_TIGHT: positions rebuilt from the run list and values / sizes rebuilt from the 6-byte records
+    equal the oracle's records (the packing is restated here the way include/biolib_gpu.h documents it)."""
+    from biolib_b200.context import expand_runs, unpack_tight
+    rng = np.random.default_rng(11)
+    s = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=30_000)
+    s[5000:5003] = ord("N"); s[20_000] = ord("N")
+    o = oracle.super_kmers(s, 31, 19, 42, True)
+    n = o["n"]
+    value, sk_start, size, mm_start = o["value"][:n], o["sk_start"][:n], o["size"][:n].astype(np.uint8), o["mm_start"][:n]
+    mm_pos = (mm_start - sk_start).astype(np.uint8)
+    # run list: a record starts a run iff it does not start where its predecessor ended
+    first = np.flatnonzero(np.concatenate([[True], sk_start[1:] != sk_start[:-1] + size[:-1]])).astype(np.uint64)
+    assert first.size == 3
+    assert np.array_equal(expand_runs(first, sk_start[first.astype(np.int64)], size, mm_pos), mm_start)
+    lo32, hi8, nib = (value & np.uint64(0xFFFFFFFF)).astype(np.uint32), (value >> np.uint64(32)).astype(np.uint8), ((size - 1) | (mm_pos << 4)).astype(np.uint8)
+    v2, s2, p2 = unpack_tight(lo32, hi8, nib)
+    assert np.array_equal(v2, value) and np.array_equal(s2, size) and np.array_equal(p2, mm_pos)
+    v3, _, _ = unpack_tight(lo32, None, nib)
+    assert np.array_equal(v3, value & np.uint64(0xFFFFFFFF))
