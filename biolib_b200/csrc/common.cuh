@@ -41,11 +41,12 @@ __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
 }
 #else
 // The same arithmetic with the lowering chosen by hand, because the fused kernels are bound by the ALU pipe (LOP3 / SHF / IADD3)
-// while the FMA pipe (IMAD) has room: 39 instructions per hash, 17 of them on the ALU pipe.
+// while the FMA pipe (IMAD) has room: 39 instructions per hash, 18 of them on the ALU pipe in the fused kernel.
 //   x * c (low 64 bits) = IMAD.WIDE of the low words + two IMADs that accumulate the cross products into the high word. nvcc's
 //   own lowering computes the cross products beside the wide product and joins them with an IADD3 (shorter dependency chain,
 //   one more instruction, on the ALU pipe);
-//   64-bit + 32-bit = IMAD.WIDE a * 1 + c instead of IADD3 + IADD3.X;
+//   64-bit + 32-bit written as mad.wide.u32 a * 1 + c: ptxas emits IADD3 + IMAD.X (the carry into the high word goes to the FMA
+//   pipe) where the plain C addition gave IADD3 + IADD3.X;
 //   h ^= h >> 33 only touches the low word: lo ^= hi >> 1.
 // Measured on the fused kernel (profiles/r02_zn_hash_lowering_ab.txt): 209 -> 219 Gbases/s at k=31 m=19, 181 -> 198 on 150-bp reads.
 __device__ __forceinline__ void mul64c(u32& xl, u32& xh, u64 c)
