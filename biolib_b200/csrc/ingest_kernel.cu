@@ -185,9 +185,11 @@ __device__ __forceinline__ void warp_sum4(u32 packed, u32* even, u32* odd)
     *odd = __reduce_add_sync(0xffffffffu, (packed >> 8) & 0x00FF00FFu);     // counters 1 and 3
 }
 
-// exclusive prefix over the block of a per-thread count (<= 16 per field, two 16-bit fields); *total = the block's sum
+// exclusive prefix over the block of a per-thread count (<= 16 per field, two 16-bit fields); *total = the block's sum.
+// The per-warp totals are scanned by every warp for itself (lane w holds warp w's total): no serial walk over the warps.
 __device__ __forceinline__ u32 block_exclusive2(u32 x, u32* s_warp /* [FX_WARPS] */, u32* total)
 {
+    static_assert(FX_WARPS <= 32, "one lane per warp total");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     u32 incl = x;
 #pragma unroll
@@ -197,31 +199,35 @@ __device__ __forceinline__ u32 block_exclusive2(u32 x, u32* s_warp /* [FX_WARPS]
     }
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    u32 before = 0, all = 0;
+    u32 t = lane < FX_WARPS ? s_warp[lane] : 0u;
 #pragma unroll
-    for (int w = 0; w < FX_WARPS; ++w) { const u32 t = s_warp[w]; if (w < warp) before += t; all += t; }
-    *total = all;
+    for (int d = 1; d < FX_WARPS; d <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+    }
+    *total = __shfl_sync(0xffffffffu, t, FX_WARPS - 1);
+    const u32 before = warp > 0 ? __shfl_sync(0xffffffffu, t, (warp + 31) & 31) : 0u;     // inclusive total of warp - 1
     return before + incl - x;
 }
 
 // FASTA: the state a thread is entered in = exit state of the nearest earlier thread of the block that has a line start.
 // Returns it, or 2 when no earlier thread of the block has one (then it is the block's entry state). s_wst: [FX_WARPS].
+// "Nearest earlier one that is defined" is the highest set bit below one's own position, within the warp (ballots over the
+// lanes) and then over the warps (ballots over lanes that each hold one warp's summary).
 __device__ __forceinline__ u32 fasta_thread_entry(u32 exit_state, u32* s_wst, u32* block_exit)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const u32 def = __ballot_sync(0xffffffffu, exit_state != 3u), hd = __ballot_sync(0xffffffffu, exit_state == 1u);
     if (lane == 0) s_wst[warp] = def ? ((hd >> (31 - __clz((int)def))) & 1u) : 3u;
     __syncthreads();
-    u32 e = 2u;
+    const u32 ws = lane < FX_WARPS ? s_wst[lane] : 3u;
+    const u32 wdef = __ballot_sync(0xffffffffu, ws != 3u), whd = __ballot_sync(0xffffffffu, ws == 1u);
+    *block_exit = wdef ? ((whd >> (31 - __clz((int)wdef))) & 1u) : 3u;
     const u32 lower = def & ((1u << lane) - 1u);
-    if (lower) e = (hd >> (31 - __clz((int)lower))) & 1u;
-    else {
-        for (int w = warp - 1; w >= 0; --w) { const u32 t = s_wst[w]; if (t != 3u) { e = t; break; } }
-    }
-    u32 be = 3u;
-    for (int w = FX_WARPS - 1; w >= 0; --w) { const u32 t = s_wst[w]; if (t != 3u) { be = t; break; } }
-    *block_exit = be;
-    return e;
+    if (lower) return (hd >> (31 - __clz((int)lower))) & 1u;
+    const u32 wlower = wdef & ((1u << warp) - 1u);
+    if (wlower) return (whd >> (31 - __clz((int)wlower))) & 1u;
+    return 2u;
 }
 
 __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* __restrict__ text, size_t n, int fastq, FxSum* __restrict__ sum)
