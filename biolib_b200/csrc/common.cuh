@@ -86,6 +86,30 @@ __device__ __forceinline__ u64 murmur3_key8_s32(u64 key, u32 s8)
 __device__ __forceinline__ u64 murmur3_key8(u64 key, u64 s8) { return murmur3_key8_s32(key, (u32)s8); }
 
 // ---------------------------------------------------------------------------------------------
+// One-dimensional bulk async copy global -> shared (cp.async.bulk, the TMA unit without a tensor map) with completion on an
+// mbarrier: the staging the fused kernels and kmer2_kernel use for the next tile's ASCII bytes.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, u32 bytes, unsigned long long* b)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, u32 phase)
+{
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}"
+                 ::"r"(smem_u32(b)), "r"(phase) : "memory");
+}
+// generic-proxy accesses to shared memory before this point are ordered before async-proxy (bulk copy) writes after it
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------------------------
 // 2-bit streams. Bases are packed 16 per 32-bit word, base q of a word at bits [2q, 2q+2)
 // (little-endian stream: earlier base = lower bits). With that geometry
 //   reverse-complement word of bases [p, p+len)  = ~stream & mask            (free)

@@ -46,7 +46,7 @@ struct Geo4 {
     // per-warp shared memory, byte offsets
     static constexpr int OFF_BAD = 0;                               // u32 [NROW]   bit x: base a0 + x is not ACGTU
     static constexpr int OFF_SEQ = OFF_BAD + NROW * 4;              // u32 [NROW]   bit x: a sequence starts at a0 + x
-    static constexpr int OFF_FLAG = OFF_SEQ + NROW * 4;             // int [4]
+    static constexpr int OFF_FLAG = (OFF_SEQ + NROW * 4 + 7) / 8 * 8;  // int [2], then the warp's mbarrier (8 bytes)
     static constexpr int PBLK = Q == 1 ? 1 : NB;                    // blocks per lane whose prefix keys another lane reads
     static constexpr int OFF_P = (OFF_FLAG + 16 + 15) / 16 * 16;    // uint4 [PBLK][BQ][32] (+1)  prefix keys, [block][quad][lane]
     static constexpr int OFF_IDX2 = OFF_P + NP * (PBLK * BQ * 32 + 1) * 16;   // NP = 2 (syncmers, both strands): a second row of prefix keys
@@ -64,6 +64,10 @@ struct Geo4 {
     static constexpr int KB = Q == 1 ? 3 : 2;                       // Q = 2: three sets would leave 12 warps per SM
 #endif
     static constexpr int WARP_BYTES = (OFF_BUF + KB * BUF_BYTES + 127) / 128 * 128;
+    // the next tile's ASCII bytes (16 NWORDS) land in the REC area of the buffer set the tile will be staged into; the
+    // area is free from the end of that set's emit until the tile's own record slots are written, after staging has consumed the bytes
+    static constexpr int RAW_BYTES = 16 * NWORDS;
+    static_assert(BUF_REC % 16 == 0 && (R + 8) * 2 >= RAW_BYTES, "the raw ASCII of a tile must fit the record-slot area");
 };
 
 __device__ __forceinline__ u32 pairrev32_4(u32 x)
@@ -238,10 +242,9 @@ __device__ __forceinline__ u32 record_slots4(unsigned short* REC, u32 start, int
 // from the 16-base boundary the staged range begins at.
 template <int B, int NB, int Q, int NP>
 __device__ __forceinline__ u32 stage_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
-                                           bool have_pre, const uint4 (&pre)[3], int* o_out)
+                                           int have_pre, int* o_out)
 {
     using G = Geo4<B, NB, Q, NP>;
-    static_assert(G::NWORDS <= 3 * NT4, "three prefetch registers per lane");
     constexpr int L = G::L;
     constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
     const long long g0 = a.org + tile * (long long)G::R - B;     // global position of local start 0 (block 0 = left margin)
@@ -257,6 +260,10 @@ __device__ __forceinline__ u32 stage_tile4(const SkArgs& a, unsigned char* wsm, 
     u32* EBW = reinterpret_cast<u32*>(buf + G::BUF_EBW);
     // ---- stage: ASCII -> packed streams + bad-byte bits -----------------------------------------------------------
     int anybad = 0;
+    // have_pre: bit 0 = the tile's bytes were requested by a bulk async copy (tile_loop4), bit 1 = the parity of that copy's mbarrier
+    // phase. They sit in the record-slot area of this buffer set until the record slots are written at the end of the tile.
+    const unsigned char* raw = buf + G::BUF_REC;
+    if (have_pre) mbar_wait(reinterpret_cast<unsigned long long*>(wsm + G::OFF_FLAG + 8), (u32)(have_pre >> 1) & 1u);
     {
         unsigned short* BAD16 = reinterpret_cast<unsigned short*>(BAD);
 #pragma unroll
@@ -266,7 +273,7 @@ __device__ __forceinline__ u32 stage_tile4(const SkArgs& a, unsigned char* wsm, 
                 const long long P16 = a0 + 16LL * wi;
                 u32 w0, w1, w2, w3;
                 if (have_pre) {
-                    const uint4 v = wi < NT4 ? pre[0] : wi < 2 * NT4 ? pre[1] : pre[2];
+                    const uint4 v = *reinterpret_cast<const uint4*>(raw + 16 * wi);
                     w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
                 } else if (a.vec_ok && P16 >= a.buf_lo && P16 + 16 <= a.buf_hi) {
                     const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bases + (P16 - a.buf_lo)));
@@ -334,14 +341,14 @@ __device__ __forceinline__ u32 stage_tile4(const SkArgs& a, unsigned char* wsm, 
 // Stage + hash + window minima + record starts of one tile into buffer set b. Returns the tile's record count.
 template <int B, int NB, int Q, int LW, bool CANON, bool MW>
 __device__ __forceinline__ u32 compute_tile4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, int b, long long tile, int t,
-                                             bool have_pre, const uint4 (&pre)[3])
+                                             int have_pre)
 {
     using G = Geo4<B, NB, Q>;
     constexpr int L = G::L;
     constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
     const long long g0 = a.org + tile * (long long)G::R - B;
     int o;
-    const u32 V = stage_tile4<B, NB, Q, 1>(a, wsm, c, b, tile, t, have_pre, pre, &o);
+    const u32 V = stage_tile4<B, NB, Q, 1>(a, wsm, c, b, tile, t, have_pre, &o);
     unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
     uint4* P = reinterpret_cast<uint4*>(wsm + G::OFF_P);
     u32* CW = reinterpret_cast<u32*>(buf + G::BUF_CW);
@@ -670,14 +677,18 @@ __device__ __forceinline__ u64 tile_base_finish4(const SkArgs& a, const u64* p, 
     return g + s;
 }
 
-// The loop every warp runs on its own: compute tile i (`compute(b, tile, have_pre, pre)` -> its record count), publish the count,
+// The loop every warp runs on its own: compute tile i (`compute(b, tile, have_pre)` -> its record count), publish the count,
 // write out tile i-(KB-1) from its buffer set (`emit(b, tile, n_rec, base)`). A ticket is taken only when nothing can block any
 // more before that tile is published (a warp that waits for a prefix while it holds an uncomputed tile stalls that tile's group,
 // the groups behind it, and so itself: convoys).
 template <class G, class ComputeF, class EmitF>
-__device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF compute, EmitF emit)
+__device__ __forceinline__ void tile_loop4(const SkArgs& a, unsigned char* wsm, int t, ComputeF compute, EmitF emit)
 {
     const long long num_groups = (a.num_tiles + GS4 - 1) / GS4;
+    unsigned long long* mbar = reinterpret_cast<unsigned long long*>(wsm + G::OFF_FLAG + 8);   // completion of the warp's bulk copies
+    if (t == 0) mbar_init(mbar, 1);
+    __syncwarp();
+    u32 bulk_phase = 0;
     u32 tk = 0;
     if (t == 0) tk = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
     long long tile = __shfl_sync(0xffffffffu, tk, 0);
@@ -685,8 +696,7 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
     long long t0 = -1, t1 = -1;
     u32 n0 = 0, n1 = 0;
     int b0 = 0, b1 = 0;
-    bool have_pre = false;
-    uint4 pre[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+    int have_pre = 0;
     int b = 0;                          // buffer set of the tile computed in this iteration
     for (;;) {
         const bool have = tile < a.num_tiles;
@@ -699,7 +709,7 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
         u32 n_rec = 0;
         u64 old = 0;
         if (have) {
-            n_rec = compute(b, tile, have_pre, pre);
+            n_rec = compute(b, tile, have_pre);
             if (t == 0) {
                 st_status(&a.tile_status[tile], ((u64)tile_tag4(a) << 32) | n_rec);
                 old = atomicAdd(&a.grp_acc[tile / GS4], ACC_ONE4 | (u64)n_rec);
@@ -730,15 +740,21 @@ __device__ __forceinline__ void tile_loop4(const SkArgs& a, int t, ComputeF comp
         if (have && t == 0) nx = atomicAdd(a.tile_counter, 1u) - a.ticket_base;
         if (prev >= 0) emit(pb, prev, prev_n, base);
         const long long next_tile = __shfl_sync(0xffffffffu, nx, 0);
-        have_pre = false;
+        have_pre = 0;
         {
             const long long ng0 = a.org + next_tile * (long long)G::R - G::B_;
             const long long P0 = (ng0 & ~15LL) - a.buf_lo;
             if (next_tile < a.num_tiles && a.vec_ok && P0 >= 0 && P0 + 16LL * G::NWORDS <= a.buf_hi - a.buf_lo) {
-                have_pre = true;
-#pragma unroll
-                for (int q = 0; q < 3; ++q)
-                    if (G::NWORDS > q * NT4 && t < G::NWORDS - q * NT4) pre[q] = __ldg(reinterpret_cast<const uint4*>(a.bases + P0) + q * NT4 + t);
+                // ONE bulk async copy per tile (cp.async.bulk + mbarrier, issued by lane 0) into the record-slot area of the buffer
+                // set the next tile uses: the emit above was the last reader of that area (it ends with __syncwarp), and the bytes
+                // are consumed by the next stage before its record slots are written. Nothing is held in registers across the emit
+                // (the first version kept three LDG.128 results per lane there: same speed, profiles/r02_zx_sk4_bulk_staging_ab.txt).
+                have_pre = 1 | (int)(bulk_phase << 1);
+                bulk_phase ^= 1u;
+                if (t == 0) {
+                    fence_proxy_async_smem();
+                    bulk_load(wsm + G::OFF_BUF + ((b + 1) % G::KB) * G::BUF_BYTES + G::BUF_REC, a.bases + P0, (u32)G::RAW_BYTES, mbar);
+                }
             }
         }
         // queue: drop what was written, push what was computed
@@ -770,8 +786,8 @@ __global__ void __launch_bounds__(SK4_THREADS, Q == 1 ? SK4_MIN_BLOCKS : 4) sk4_
     const int t = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char* wsm = smem_raw + warp * G::WARP_BYTES;
     const TileConst4 c = tile_const4(a, MW);
-    tile_loop4<G>(a, t,
-                  [&](int b, long long tile, bool have_pre, const uint4 (&pre)[3]) { return compute_tile4<B, NB, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre, pre); },
+    tile_loop4<G>(a, wsm, t,
+                  [&](int b, long long tile, int have_pre) { return compute_tile4<B, NB, Q, LW, CANON, MW>(a, wsm, c, b, tile, t, have_pre); },
                   [&](int b, long long tile, u32 n_rec, u64 base) { emit_tile4<B, NB, Q, CANON, MW>(a, wsm, c, b, tile, t, n_rec, base); });
 }
 

@@ -242,7 +242,7 @@ __device__ __forceinline__ u32 strand_bits4(const u32* CW, const u32* EW, const 
 // Stage + both rows + keep bits + slots of the kept k-mers of one tile into buffer set b. Returns the number of kept k-mers.
 template <int B, int NB, int LW, bool CANON, bool MW>
 __device__ __forceinline__ u32 compute_sync4(const SkArgs& a, unsigned char* wsm, const TileConst4& c, const SyncConst4& sc, int b, long long tile,
-                                             int t, bool have_pre, const uint4 (&pre)[3])
+                                             int t, int have_pre)
 {
     constexpr int NP = CANON ? 2 : 1;
     using G = Geo4<B, NB, 1, NP>;
@@ -250,7 +250,7 @@ __device__ __forceinline__ u32 compute_sync4(const SkArgs& a, unsigned char* wsm
     constexpr u32 ML = L >= 32 ? 0xFFFFFFFFu : ((1u << (L & 31)) - 1u);
     const long long g0 = a.org + tile * (long long)G::R - B;
     int o;
-    const u32 V = stage_tile4<B, NB, 1, NP>(a, wsm, c, b, tile, t, have_pre, pre, &o);
+    const u32 V = stage_tile4<B, NB, 1, NP>(a, wsm, c, b, tile, t, have_pre, &o);
     unsigned char* buf = wsm + G::OFF_BUF + b * G::BUF_BYTES;
     uint4* PF = reinterpret_cast<uint4*>(wsm + G::OFF_P);
     uint4* PR = PF + (G::BQ * 32 + 1);
@@ -338,8 +338,8 @@ __global__ void __launch_bounds__(SK4_THREADS, CANON ? 4 : SK4_MIN_BLOCKS) sy4_k
     sc.tF0 = s * 0x01010101u; sc.tF1 = e * 0x01010101u;
     sc.tR0 = (s == 0x7Fu ? 0x7Fu : (u32)a.w - 1u - s) * 0x01010101u;
     sc.tR1 = (e == 0x7Fu ? 0x7Fu : (u32)a.w - 1u - e) * 0x01010101u;
-    tile_loop4<G>(a, t,
-                  [&](int b, long long tile, bool have_pre, const uint4 (&pre)[3]) { return compute_sync4<B, NB, LW, CANON, MW>(a, wsm, c, sc, b, tile, t, have_pre, pre); },
+    tile_loop4<G>(a, wsm, t,
+                  [&](int b, long long tile, int have_pre) { return compute_sync4<B, NB, LW, CANON, MW>(a, wsm, c, sc, b, tile, t, have_pre); },
                   [&](int b, long long tile, u32 n_rec, u64 base) { emit_sync4<B, NB, CANON>(a, wsm, c, sc, b, tile, t, n_rec, base); });
 }
 
