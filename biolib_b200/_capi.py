@@ -37,7 +37,8 @@ class Params(C.Structure):
 
 class KmerOut(C.Structure):
     _fields_ = [("count", C.c_uint64), ("capacity", C.c_uint64), ("value_lo", C.c_void_p), ("value_hi", C.c_void_p),
-                ("position", C.c_void_p), ("owner", C.c_void_p)]
+                ("position", C.c_void_p), ("owner", C.c_void_p),
+                ("n_runs", C.c_uint64), ("run_capacity", C.c_uint64), ("run_first_record", C.c_void_p), ("run_start", C.c_void_p)]
 
 
 class SkOut(C.Structure):

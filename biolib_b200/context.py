@@ -70,12 +70,13 @@ class Context:
         return n.value, buf.value.decode()
 
     # ------------------------------------------------------------------ host in, host out
-    def kmers(self, seq, k: int, canonical: bool = False, offsets=None, syncmer=None, hash_sample=None) -> dict:
+    def kmers(self, seq, k: int, canonical: bool = False, offsets=None, syncmer=None, hash_sample=None, runs=False) -> dict:
         """Valid k-mers in position order; syncmer=(m, start_offset, end_offset) keeps only those that
-        sampler::syncmer_sampler over hash::minimizer_position_extractor(k, m) would (blg_syncmers)."""
+        sampler::syncmer_sampler over hash::minimizer_position_extractor(k, m) would (blg_syncmers).
+        runs: BLG_F_RUNS (blg_kmers only): no position array comes back, it is rebuilt here from the run list."""
         b = _as_bytes_array(seq)
         o = None if offsets is None else np.ascontiguousarray(offsets, dtype=np.uint64)
-        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=0,
+        p = Params(k=k, m=0 if syncmer is None else syncmer[0], canonical=int(canonical), flags=_capi.F_RUNS if runs else 0,
                    seed=0 if hash_sample is None else hash_sample[0] & (2**64 - 1))
         out = KmerOut()
         args = (self.h, b.ctypes.data, b.size, o.ctypes.data if o is not None else None, 0 if o is None else len(o) - 1, C.byref(p))
@@ -87,8 +88,15 @@ class Context:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         n = out.count
         try:
-            res = dict(lo=_copy(out.value_lo, n, np.uint64), pos=_copy(out.position, n, np.uint64),
+            if runs:
+                rf, rs = _copy(out.run_first_record, out.n_runs, np.uint64), _copy(out.run_start, out.n_runs, np.uint64)
+                pos = expand_kmer_runs(rf, rs, n)
+            else:
+                pos = _copy(out.position, n, np.uint64)
+            res = dict(lo=_copy(out.value_lo, n, np.uint64), pos=pos,
                        hi=_copy(out.value_hi, n, np.uint64) if out.value_hi else np.zeros(n, np.uint64))
+            if runs:
+                res["n_runs"] = int(out.n_runs)
         finally:
             self.L.blg_free_kmer_out(self.h, C.byref(out))
         return res
@@ -366,6 +374,15 @@ class Context:
         else:
             self._check(self.L.blg_syncmers(*args, int(syncmer[1]), int(syncmer[2]), C.byref(out)))
         return out.count
+
+
+def expand_kmer_runs(run_first_record, run_start, n) -> np.ndarray:
+    """position of every k-mer from the BLG_F_RUNS outputs of blg_kmers: consecutive positions inside a run."""
+    if n == 0:
+        return np.zeros(0, np.uint64)
+    first = run_first_record.astype(np.int64)
+    run_of = np.searchsorted(first, np.arange(n), side="right") - 1
+    return (run_start.astype(np.int64)[run_of] + (np.arange(n) - first[run_of])).astype(np.uint64)
 
 
 def unpack_tight(value_lo32, value_hi8, size_pos):

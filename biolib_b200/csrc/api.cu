@@ -399,6 +399,54 @@ int emit_runs(blg_ctx* c, const unsigned long long* d_mm, const unsigned char* d
     return BLG_OK;
 }
 
+// BLG_F_RUNS for blg_kmers: the run list of `total` device-resident k-mer positions, appended to two host vectors with the
+// record indices shifted by `record_base` (the chunked path calls this once per piece)
+int append_kmer_runs(blg_ctx* c, const unsigned long long* d_pos, uint64_t total, uint64_t record_base, std::vector<uint64_t>& first,
+                     std::vector<uint64_t>& start)
+{
+    if (total == 0) return BLG_OK;
+    int rc = ensure(c, c->rank, runs_scratch_bytes(total) + 64);
+    if (rc != BLG_OK) return rc;
+    unsigned long long* d_tot = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->rank.p) + runs_scratch_bytes(total) / 8 * 8);
+    unsigned long long *d_first = nullptr, *d_start = nullptr, nr = 0;
+    int launches = 0;
+    CK(c, runs_launch(d_pos, nullptr, nullptr, total, c->rank.p, &d_first, &d_start, d_tot, c->stream, &launches));
+    c->stats.kernel_launches += launches;
+    CK(c, cudaMemcpyAsync(&nr, d_tot, 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    const size_t at = first.size();
+    first.resize(at + nr); start.resize(at + nr);
+    CK(c, cudaMemcpyAsync(first.data() + at, d_first, nr * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaMemcpyAsync(start.data() + at, d_start, nr * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    c->stats.bytes_d2h += nr * 16 + 8;
+    size_t w = at;
+    for (size_t j = at; j < at + nr; ++j) {
+        const uint64_t f = first[j] + record_base, s = start[j];
+        // a piece boundary inside a stretch of valid bases: the run goes on
+        if (w > 0 && j == at && start[w - 1] + (f - first[w - 1]) == s) continue;
+        first[w] = f; start[w] = s; ++w;
+    }
+    first.resize(w); start.resize(w);
+    return BLG_OK;
+}
+
+// hands the collected run list to the caller: library-owned pinned arrays (slots 3 and 4 of `ow`) or the caller's
+int deliver_kmer_runs(blg_ctx* c, const std::vector<uint64_t>& first, const std::vector<uint64_t>& start, blg_kmer_out* out, Owner* ow)
+{
+    const uint64_t nr = first.size();
+    out->n_runs = nr;
+    if (ow) {
+        int rc;
+        if ((rc = alloc_owned(c, false, nr, &out->run_first_record, ow, 3)) != BLG_OK || (rc = alloc_owned(c, false, nr, &out->run_start, ow, 4)) != BLG_OK) return rc;
+    } else if (nr > out->run_capacity || !out->run_first_record || !out->run_start) {
+        c->err = "run arrays too small (out->n_runs holds the required size)";
+        return BLG_E_CAPACITY;
+    }
+    if (nr) { memcpy(out->run_first_record, first.data(), nr * 8); memcpy(out->run_start, start.data(), nr * 8); }
+    return BLG_OK;
+}
+
 int sk_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, uint64_t lo, uint64_t hi,
                  const blg_params* p, blg_sk_out* out, bool with_size, bool want_hash, int* done_flag)
 {
@@ -1144,9 +1192,10 @@ namespace {
 // one record slot per k-mer start of the whole input. `est` sizes library-owned host arrays; when a piece does not fit what
 // is left of them (or of the caller's capacity) *done_flag stays 0 and the caller takes the plain path, which knows the count.
 int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, size_t n_seq, const KmerArgs& proto, uint64_t est,
-                    blg_kmer_out* out, int* done_flag)
+                    blg_kmer_out* out, int* done_flag, bool runs)
 {
     *done_flag = 0;
+    std::vector<uint64_t> run_first, run_start;     // BLG_F_RUNS: collected piece by piece
     const int k = proto.k;
     const bool wide = k > 32;
     const uint64_t nwin = n - (size_t)k + 1;
@@ -1184,10 +1233,11 @@ int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* off
     if (out->capacity == 0) {
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
-        h.value_hi = nullptr;
-        if ((rc = alloc_owned(c, false, cap, &h.value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, cap, &h.position, ow, 2)) != BLG_OK) return rc;
+        h.value_hi = nullptr; h.position = nullptr;
+        if ((rc = alloc_owned(c, false, cap, &h.value_lo, ow, 0)) != BLG_OK || (!runs && (rc = alloc_owned(c, false, cap, &h.position, ow, 2)) != BLG_OK)) return rc;
         if (wide && (rc = alloc_owned(c, false, cap, &h.value_hi, ow, 1)) != BLG_OK) return rc;
     }
+    if (runs) h.position = nullptr;                 // never downloaded
     unsigned char* d_in = static_cast<unsigned char*>(c->in.p);
     const size_t halo = (size_t)k + 64;
     size_t sent = 0;
@@ -1226,6 +1276,8 @@ int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* off
             if (h.position) CK(c, cudaMemcpyAsync(h.position + done, a.position, cnt * 8, cudaMemcpyDeviceToHost, c->s_out));
             c->stats.bytes_d2h += cnt * ((wide ? 16 : 8) + (h.position ? 8 : 0));
             CK(c, cudaEventRecord(c->ev_dl[b], c->s_out));
+            // the positions stay on the device: their run list (a few entries per break / sequence) is all that is downloaded
+            if (runs && (rc = append_kmer_runs(c, a.position, cnt, done, run_first, run_start)) != BLG_OK) return rc;
             used[b] = 1;
             b ^= 1;
         }
@@ -1234,6 +1286,14 @@ int kmers_pipelined(blg_ctx* c, const char* bases, size_t n, const uint64_t* off
     CK(c, cudaStreamSynchronize(c->s_out));
     CK(c, cudaStreamSynchronize(c->s_in));
     if (overflow) return BLG_OK;       // the guard gives library arrays back; the plain path reports the exact count
+    if (runs) {
+        h.run_capacity = out->run_capacity; h.run_first_record = out->run_first_record; h.run_start = out->run_start;
+        if ((rc = deliver_kmer_runs(c, run_first, run_start, &h, out->capacity == 0 ? ow : nullptr)) != BLG_OK) {
+            if (rc == BLG_E_CAPACITY) { out->n_runs = h.n_runs; out->count = done; }
+            return rc;
+        }
+        if (out->capacity > 0) out->n_runs = h.n_runs;
+    }
     guard.armed = false;
     if (out->capacity == 0) { *out = h; out->owner = ow; out->capacity = 0; }
     out->count = done;
@@ -1254,6 +1314,11 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     if (threshold && p->k > 32) { c->err = "hash sampling needs k <= 32 (hash64 of a 64-bit value)"; return BLG_E_INVALID; }
     const bool wide = p->k > 32;
     if (out->capacity > 0 && (!out->value_lo || (wide && !out->value_hi))) { c->err = "value arrays missing"; return BLG_E_INVALID; }
+    const bool runs = want_pos && (p->flags & BLG_F_RUNS) != 0;    // positions stay on the device; their run list is downloaded
+    if (runs && (sync_s >= 0 || threshold || (p->flags & BLG_F_DEVICE_OUTPUT))) {
+        c->err = "BLG_F_RUNS: host output of blg_kmers only (sampled k-mers are not contiguous)";
+        return BLG_E_INVALID;
+    }
     Timer tm;
     c->stats = blg_stats{};
     c->stats.n_bases = n;
@@ -1263,8 +1328,12 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     const int k = p->k;
     const uint64_t nwin = n >= (size_t)k ? n - k + 1 : 0;
     out->count = 0;
+    if (runs) out->n_runs = 0;
     if (nwin == 0) {
-        if (out->capacity == 0) { out->value_lo = out->value_hi = out->position = nullptr; out->owner = nullptr; }
+        if (out->capacity == 0) {
+            out->value_lo = out->value_hi = out->position = nullptr; out->owner = nullptr;
+            if (runs) out->run_first_record = out->run_start = nullptr;
+        }
         c->stats.total_ms = tm.ms();
         return BLG_OK;
     }
@@ -1280,7 +1349,7 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
         if (threshold) est = (uint64_t)((double)nwin * ((double)*threshold / 18446744073709551616.0) * 1.25) + 65536;
         if (est > nwin) est = nwin;
         int produced = 0;
-        if ((rc = kmers_pipelined(c, bases, n, offs, n_seq, a, est, out, &produced)) != BLG_OK) return rc;
+        if ((rc = kmers_pipelined(c, bases, n, offs, n_seq, a, est, out, &produced, runs)) != BLG_OK) return rc;
         if (produced) { c->stats.total_ms = tm.ms(); return BLG_OK; }
     }
     const unsigned char* d_bases = nullptr;
@@ -1338,17 +1407,26 @@ int kmers_common(blg_ctx* c, const char* bases, size_t n, const uint64_t* offs, 
     } else {
         ow = new (std::nothrow) Owner{0, {}, {}, nullptr};
         if (!ow) return BLG_E_NOMEM;
-        out->value_hi = nullptr;
-        if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK) { free_owner(ow); return rc; }
+        out->value_hi = nullptr; out->position = nullptr;
+        if ((rc = alloc_owned(c, false, total, &out->value_lo, ow, 0)) != BLG_OK || (!runs && (rc = alloc_owned(c, false, total, &out->position, ow, 2)) != BLG_OK)) { free_owner(ow); return rc; }
         if (wide && (rc = alloc_owned(c, false, total, &out->value_hi, ow, 1)) != BLG_OK) { free_owner(ow); return rc; }
         out->owner = ow;
     }
     if (total) {
+        const bool dl_pos = !runs && out->position != nullptr;
         CK(c, cudaMemcpyAsync(out->value_lo, a.value_lo, total * 8, cudaMemcpyDeviceToHost, c->stream));
         if (wide) CK(c, cudaMemcpyAsync(out->value_hi, a.value_hi, total * 8, cudaMemcpyDeviceToHost, c->stream));
-        if (out->position) CK(c, cudaMemcpyAsync(out->position, a.position, total * 8, cudaMemcpyDeviceToHost, c->stream));
-        c->stats.bytes_d2h += total * (wide ? 24 : 16);
+        if (dl_pos) CK(c, cudaMemcpyAsync(out->position, a.position, total * 8, cudaMemcpyDeviceToHost, c->stream));
+        c->stats.bytes_d2h += total * ((wide ? 16 : 8) + (dl_pos ? 8 : 0));
         CK(c, cudaStreamSynchronize(c->stream));
+    }
+    if (runs) {
+        std::vector<uint64_t> run_first, run_start;
+        if ((rc = append_kmer_runs(c, a.position, total, 0, run_first, run_start)) != BLG_OK ||
+            (rc = deliver_kmer_runs(c, run_first, run_start, out, out->capacity == 0 ? ow : nullptr)) != BLG_OK) {
+            if (out->capacity == 0) { free_owner(ow); out->owner = nullptr; out->value_lo = out->value_hi = nullptr; out->run_first_record = out->run_start = nullptr; }
+            return rc;
+        }
     }
     c->stats.total_ms = tm.ms();
     return BLG_OK;
@@ -1658,6 +1736,8 @@ void blg_free_kmer_out(blg_ctx* c, blg_kmer_out* out)
     if (out->owner) {
         free_owner(static_cast<Owner*>(out->owner));
         out->value_lo = out->value_hi = out->position = nullptr;
+        out->run_first_record = out->run_start = nullptr;
+        out->n_runs = 0;
         out->owner = nullptr;
         out->count = 0;
     }

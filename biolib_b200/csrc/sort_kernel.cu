@@ -308,6 +308,8 @@ __global__ void run_flags(const u64* __restrict__ mm_start, const u8* __restrict
 {
     const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
     if (r >= n) return;
+    // mm_pos == nullptr: k-mer positions (blg_kmers with BLG_F_RUNS): every record starts at mm_start and is one position long
+    if (mm_pos == nullptr) { f[r] = (r == 0 || mm_start[r] != mm_start[r - 1] + 1) ? 1 : 0; return; }
     const u64 sk = mm_start[r] - mm_pos[r];
     f[r] = (r == 0 || sk != mm_start[r - 1] - mm_pos[r - 1] + size[r - 1]) ? 1 : 0;
 }
@@ -317,7 +319,7 @@ __global__ void run_scatter(const u64* __restrict__ mm_start, const u8* __restri
     const u64 r = blockIdx.x * (u64)blockDim.x + threadIdx.x;
     if (r >= n) return;
     const u64 here = f_excl[r], next = r + 1 < n ? f_excl[r + 1] : *total;
-    if (next != here) { first[here] = r; start[here] = mm_start[r] - mm_pos[r]; }
+    if (next != here) { first[here] = r; start[here] = mm_start[r] - (mm_pos != nullptr ? mm_pos[r] : 0); }
 }
 
 // |A n B| of two sorted distinct arrays (algorithm::jaccard's merge, include/jaccard.hpp:8-38, as a count): a block takes 2048

@@ -61,7 +61,7 @@ typedef enum blg_status {
 #define BLG_F_ASYNC         0x80u /* with BLG_F_DEVICE_INPUT | BLG_F_DEVICE_OUTPUT and caller arrays: only enqueue the kernel on the context's
                                    * stream and return; out->count stays 0. The record count (and a BLG_E_CAPACITY verdict) comes from
                                    * blg_async_count(), which waits for the stream. Several calls may be in flight; the count is the last one's */
-#define BLG_F_RUNS          0x100u /* smallest records over PCIe (host output of the super-k-mer calls): mm_start is NOT returned (out->mm_start stays
+#define BLG_F_RUNS          0x100u /* (blg_kmers with host output: see blg_kmer_out.) Smallest records over PCIe (host output of the super-k-mer calls): mm_start is NOT returned (out->mm_start stays
                                     * NULL / untouched); instead the records come with the list of RUNS -- maximal stretches of records in which
                                     * every record starts where the previous one ended (one run for a sequence without breaks):
                                     *   run_first_record[j]  index of the first record of run j      run_start[j]  its sk_start
@@ -96,6 +96,14 @@ typedef struct blg_kmer_out {
     uint64_t* value_hi;
     uint64_t* position;
     void* owner;        /* library bookkeeping for blg_free_*; leave NULL */
+    /* only with BLG_F_RUNS (blg_kmers with host output; ABI version 3): `position` is NOT returned (stays NULL / untouched). The
+     * k-mers of a stretch of valid bases start at consecutive positions, so the list of those stretches says where every k-mer is:
+     *   position[i] = run_start[j] + (i - run_first_record[j])   for run_first_record[j] <= i < run_first_record[j + 1]
+     * 8 instead of 16 bytes per k-mer over PCIe (16 instead of 24 for k > 32): the dense layout of SURVEY 8(d). */
+    uint64_t n_runs;            /* out (required size on BLG_E_CAPACITY) */
+    uint64_t run_capacity;      /* in, with caller arrays */
+    uint64_t* run_first_record;
+    uint64_t* run_start;
 } blg_kmer_out;
 
 /*

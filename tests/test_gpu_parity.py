@@ -648,6 +648,46 @@ def test_runs_layout_pipelined(gpu):
     assert st["bytes_d2h"] < a["n"] * 10 + b["n_runs"] * 16 + 4096
 
 
+@pytest.mark.parametrize("k,canon", [(31, True), (63, True), (5, False), (32, False)])
+def test_kmers_runs_layout(gpu, oracle, k, canon):
+    """BLG_F_RUNS for blg_kmers: values + the list of stretches of consecutive positions instead of a position per k-mer."""
+    import biolib_b200
+    rng = np.random.default_rng(k)
+    s = rand_seq(rng, 120_000, 0.0006, 0.02)
+    offs = np.concatenate([[0], np.cumsum(rng.integers(0, 2500, size=90))]).astype(np.uint64)
+    offs = np.concatenate([offs[offs < s.size], [s.size]]).astype(np.uint64)
+    for o in (None, offs):
+        a = gpu.kmers(s, k, canon, offsets=o)
+        b = gpu.kmers(s, k, canon, offsets=o, runs=True)
+        st = gpu.stats()
+        assert len(a["lo"]) == len(b["lo"]) > 0 and 0 < b["n_runs"] < len(b["lo"])
+        for key in ("lo", "hi", "pos"):
+            assert np.array_equal(a[key], b[key]), (key, k)
+        assert st["bytes_d2h"] <= len(a["lo"]) * (16 if k > 32 else 8) + b["n_runs"] * 16 + 64
+    ok = oracle.kmers(s, k, canon, offsets=offs)
+    assert np.array_equal(b["lo"], ok["lo"]) and np.array_equal(b["pos"], ok["pos"])
+    clean = rand_seq(rng, 40_000)
+    assert gpu.kmers(clean, k, canon, runs=True)["n_runs"] == 1
+    assert len(gpu.kmers(np.zeros(0, np.uint8), k, canon, runs=True)["lo"]) == 0
+    with pytest.raises(biolib_b200.BlgError):
+        gpu.kmers(clean, 31, canon, syncmer=(19, 0, 12), runs=True)
+
+
+def test_kmers_runs_layout_pipelined(gpu):
+    """The chunked host path of blg_kmers with BLG_F_RUNS: half the download; runs that cross a piece boundary are joined."""
+    rng = np.random.default_rng(80)
+    s = rand_seq(rng, 30_000_000, 0.00002)
+    a = gpu.kmers(s, 31, True)
+    b = gpu.kmers(s, 31, True, runs=True)
+    st = gpu.stats()
+    assert len(a["lo"]) == len(b["lo"]) > 25_000_000
+    assert np.array_equal(a["lo"], b["lo"]) and np.array_equal(a["pos"], b["pos"])
+    # maximal runs: no run starts where the previous one would have continued
+    nb = int(np.count_nonzero(np.diff(a["pos"].astype(np.int64)) != 1)) + 1
+    assert b["n_runs"] == nb
+    assert st["bytes_d2h"] < len(a["lo"]) * 8 + b["n_runs"] * 16 + 4096
+
+
 @pytest.mark.parametrize("k,m", [(31, 19), (21, 11), (31, 16), (35, 20), (8, 4), (16, 1)])
 def test_tight_layout(gpu, oracle, k, m):
     """BLG_F_TIGHT: the BLG_F_RUNS records in 6 bytes (5 for m <= 16): value_lo32 / value_hi8 / (size - 1) | mm_pos << 4."""

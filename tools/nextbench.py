@@ -87,6 +87,20 @@ def main():
         cnt = o.count
         ctx.L.blg_free_kmer_out(ctx.h, C.byref(o))
         return cnt
+    pk_runs = biolib_b200.context.Params(k=31, m=19, canonical=1, flags=_capi.F_RUNS, seed=42)
+
+    def kmer_runs_call():
+        o = _capi.KmerOut()
+        st = ctx.L.blg_kmers(ctx.h, hp, n, None, 0, C.byref(pk_runs), C.byref(o))
+        assert st == 0, st
+        cnt = o.count
+        ctx.L.blg_free_kmer_out(ctx.h, C.byref(o))
+        return cnt
+    kmer_runs_call()
+    dt, cnt = timed(kmer_runs_call)
+    st = ctx.stats()
+    out["kmers_runs_e2e_k31"] = {"bases": n, "records": int(cnt), "ms": dt * 1e3, "Gbases_per_s": n / dt / 1e9, "h2d": st["bytes_h2d"], "d2h": st["bytes_d2h"],
+                                 "note": "BLG_F_RUNS: values + run list, no position array (8 B per k-mer over PCIe)"}
     for which in ("kmers", "syncmers", "hash_sampled"):
         kmer_call(which)
         dt, cnt = timed(lambda: kmer_call(which))
