@@ -610,6 +610,7 @@ def run_gpu(args):
                               "d2h_bytes_per_step": int(e2e["records18"][2]), "ms_per_step": e2e18_ms},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "frac_of_nominal_8000": achieved / 8000.0,      # north_star's ~8 TB/s figure (report against both)
                          "traffic": traffic.get("dram_bytes_per_launch"), "traffic_capture": {"git_sha": traffic.get("git_sha"), "kernel": traffic.get("kernel")},
                          "peak_kind": peak_kind, "kernel": "sk4_kernel", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_base": algo_bytes / nwin},
