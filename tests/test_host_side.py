@@ -199,3 +199,16 @@ def test_run_list_and_tight_records_unpack(oracle):
     assert np.array_equal(v2, value) and np.array_equal(s2, size) and np.array_equal(p2, mm_pos)
     v3, _, _ = unpack_tight(lo32, None, nib)
     assert np.array_equal(v3, value & np.uint64(0xFFFFFFFF))
+
+
+def test_flag_values_match_header(built, tmp_path):
+    """The Python mirror's BLG_F_* values and the ABI version are the header's."""
+    names = ["DEVICE_INPUT", "DEVICE_OUTPUT", "EMIT_HASH", "NO_SIZE", "EMIT_ID", "POS32", "REF_DROP_LAST", "ASYNC", "RUNS", "TIGHT"]
+    src = tmp_path / "flags.c"
+    src.write_text('#include <stdio.h>\n#include "biolib_gpu.h"\nint main(void){ printf("%d' + " %u" * len(names) + '\\n", BLG_ABI_VERSION, '
+                   + ", ".join("BLG_F_" + n for n in names) + "); return 0; }\n")
+    exe = tmp_path / "flags"
+    subprocess.check_call(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = list(map(int, subprocess.check_output([str(exe)]).split()))
+    assert got[0] == built.lib().blg_abi_version() == 3
+    assert got[1:] == [getattr(built, "F_" + n) for n in names]
