@@ -394,11 +394,25 @@ struct sk_records {
         return minimizer_context_t<MinimizerType>{o.value[i], static_cast<std::size_t>(o.mm_start[i] + 1),     // D7: 1-based start
                                                   static_cast<std::size_t>(o.id ? o.id[i] : i)};
     }
-    void run(char const* s, std::size_t n, uint8_t k, uint8_t m, uint64_t seed, bool canon, bool with_size)
+    // streaming form (super_kmer_view with want_ids = false): the smallest records the library has -- BLG_F_RUNS, and BLG_F_TIGHT
+    // where (k, m) allow it -- no positions and no ids come back; a forward iterator rebuilds the positions by adding the sizes
+    // inside a run, exactly what the reference's sequential view keeps implicitly
+    bool streaming = false;
+    bool tight() const noexcept { return o.size_pos != nullptr; }
+    MinimizerType value_at(std::size_t i) const noexcept
+    {
+        if (!tight()) return o.value[i];
+        return static_cast<MinimizerType>(o.value_lo32[i]) | (o.value_hi8 ? static_cast<MinimizerType>(o.value_hi8[i]) << 32 : 0);
+    }
+    uint8_t size_at(std::size_t i) const noexcept { return tight() ? static_cast<uint8_t>((o.size_pos[i] & 15u) + 1u) : o.size[i]; }
+    uint8_t mm_pos_at(std::size_t i) const noexcept { return tight() ? static_cast<uint8_t>(o.size_pos[i] >> 4) : o.mm_pos[i]; }
+    void run(char const* s, std::size_t n, uint8_t k, uint8_t m, uint64_t seed, bool canon, bool with_size, bool want_ids = true)
     {
         context& c = context::thread_default();
         blg_params p{};
         p.k = k; p.m = m; p.canonical = canon ? 1 : 0; p.seed = seed; p.flags = BLG_F_EMIT_ID;
+        streaming = with_size && !want_ids;
+        if (streaming) p.flags = BLG_F_RUNS | ((m <= 20 && k >= m && k - m <= 15) ? BLG_F_TIGHT : 0u);
         const int st = with_size ? blg_super_kmers(c.get(), s, n, nullptr, 0, &p, &o) : blg_minimizers(c.get(), s, n, nullptr, 0, &p, &o);
         ctx = &c;
         c.check(st, with_size ? "blg_super_kmers" : "blg_minimizers");
@@ -508,21 +522,36 @@ class super_kmer_view
                 super_kmer_view const* parent;
                 std::size_t idx;
                 value_type current_sk;
+                std::size_t run = 0;          // streaming form: the run the record belongs to, and where its first k-mer starts
+                uint64_t sk_start = 0;
                 void load()
                 {
-                    if (idx < parent->rec.size()) current_sk = value_type{parent->rec.minimizer(idx), parent->rec.o.mm_pos[idx], parent->rec.o.size[idx]};
+                    auto const& r = parent->rec;
+                    if (idx >= r.size()) return;
+                    if (!r.streaming) { current_sk = value_type{r.minimizer(idx), r.o.mm_pos[idx], r.o.size[idx]}; return; }
+                    // records are visited in order (forward iterator): a record starts where its predecessor's k-mers end, unless it
+                    // opens the next run (a break or the start of the input lies between the two)
+                    if (run < r.o.n_runs && r.o.run_first_record[run] == idx) sk_start = r.o.run_start[run++];
+                    else sk_start += r.size_at(idx - 1);
+                    const uint8_t mp = r.mm_pos_at(idx);
+                    current_sk = value_type{minimizer_context_t<MinimizerType>{r.value_at(idx), static_cast<std::size_t>(sk_start + mp + 1), idx},
+                                            mp, r.size_at(idx)};
                 }
         };
 
-        // the reference's constructors have no seed (super_kmer_view.hpp:48-49); it is added LAST with the default 0
-        super_kmer_view(char const* contig, std::size_t contig_len, uint8_t k, uint8_t m, bool canonical = false, uint64_t seed = 0)
-            : seq(contig), slen(contig_len), klen(k), mlen(m), mseed(seed), canon(canonical), done(false)
+        // the reference's constructors have no seed (super_kmer_view.hpp:48-49); it is added LAST with the default 0.
+        // want_ids = false selects the streaming form: minimizer.id then holds the record's ordinal instead of SURVEY D9's m-mer
+        // count, iterators must be advanced from cbegin() (they are forward iterators anyway), and the call moves 6 or 10 bytes per
+        // record over PCIe instead of 26 (the id pass over the bases is skipped as well)
+        super_kmer_view(char const* contig, std::size_t contig_len, uint8_t k, uint8_t m, bool canonical = false, uint64_t seed = 0,
+                        bool want_ids = true)
+            : seq(contig), slen(contig_len), klen(k), mlen(m), mseed(seed), canon(canonical), ids(want_ids), done(false)
         {
             if (!contig && contig_len) throw std::runtime_error("[super k-mer view] null contig");
             if (2u * klen > 8 * sizeof(KmerType)) throw std::invalid_argument("[biolib::gpu::super_kmer_view] k does not fit KmerType");
         }
-        super_kmer_view(std::string const& contig, uint8_t k, uint8_t m, bool canonical = false, uint64_t seed = 0)
-            : super_kmer_view(contig.data(), contig.size(), k, m, canonical, seed) {}
+        super_kmer_view(std::string const& contig, uint8_t k, uint8_t m, bool canonical = false, uint64_t seed = 0, bool want_ids = true)
+            : super_kmer_view(contig.data(), contig.size(), k, m, canonical, seed, want_ids) {}
         const_iterator cbegin() const { run(); return const_iterator(this, 0); }
         const_iterator cend() const { run(); return const_iterator(this, rec.size()); }
         const_iterator begin() const { return cbegin(); }
@@ -535,13 +564,13 @@ class super_kmer_view
         std::size_t slen;
         uint8_t klen, mlen;
         uint64_t mseed;
-        bool canon;
+        bool canon, ids;
         mutable bool done;
         mutable detail::sk_records<MinimizerType> rec;
         void run() const
         {
             if (done) return;
-            rec.run(seq, slen, klen, mlen, mseed, canon, true);
+            rec.run(seq, slen, klen, mlen, mseed, canon, true, ids);
             done = true;
         }
 };

@@ -491,6 +491,13 @@ int main(int argc, char** argv) {
         std::printf("S %llu %zu %zu %u %u\n", (unsigned long long)(*it).minimizer.value, (*it).minimizer.position, (*it).minimizer.id,
                     (unsigned)(*it).mm_pos, (unsigned)(*it).size);
     {
+        // streaming form: smallest records over PCIe, positions rebuilt by the forward iterator, id = the record's ordinal
+        biolib::gpu::super_kmer_view<uint64_t, uint64_t, hash::hash64> st(s, k, m, canon, 42, false);
+        for (auto it = st.cbegin(); it != st.cend(); ++it)
+            std::printf("T %llu %zu %zu %u %u\n", (unsigned long long)(*it).minimizer.value, (*it).minimizer.position, (*it).minimizer.id,
+                        (unsigned)(*it).mm_pos, (unsigned)(*it).size);
+    }
+    {
         biolib::gpu::minimizer_position_extractor ex(k, m);
         std::vector<uint64_t> vals;
         for (auto it = kv.cbegin(); it != kv.cend(); ++it) if ((*it).value) vals.push_back(*(*it).value);
@@ -551,6 +558,8 @@ def test_cpp_shim_views(gpu, oracle, tmp_path):
             want_m = list(zip(o["value"].tolist(), (o["mm_start"] + 1).tolist(), ids))       # D7: position = start + 1
             assert M == want_m, (seq[:20], k, m, canon)
             assert S == [a + (int(p), int(z)) for a, p, z in zip(want_m, (o["mm_start"] - o["sk_start"]).tolist(), o["size"].tolist())]
+            T = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("T ")]
+            assert T == [(v, p, i, mp, z) for i, ((v, p, _), mp, z) in enumerate(zip(want_m, (o["mm_start"] - o["sk_start"]).tolist(), o["size"].tolist()))], (seq[:20], k, m, canon)
             Y = [tuple(map(int, l.split()[1:])) for l in out if l.startswith("Y ")]
             sy = oracle.syncmer_stream(seq, k, m, 0, k - m, canon)
             assert Y == list(zip(sy["lo"].tolist(), sy["pos"].tolist())), (seq[:20], k, m, canon)
