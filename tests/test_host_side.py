@@ -212,3 +212,16 @@ def test_flag_values_match_header(built, tmp_path):
     got = list(map(int, subprocess.check_output([str(exe)]).split()))
     assert got[0] == built.lib().blg_abi_version() == 3
     assert got[1:] == [getattr(built, "F_" + n) for n in names]
+
+
+def test_kmer_run_list_expands_to_positions(oracle):
+    """Host side of blg_kmers + BLG_F_RUNS: positions rebuilt from the run list equal the oracle's k-mer positions."""
+    from biolib_b200.context import expand_kmer_runs
+    rng = np.random.default_rng(12)
+    s = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=20_000)
+    s[3000:3004] = ord("N"); s[9000] = ord("n"); s[9050] = ord("N")
+    pos = oracle.kmers(s, 31, True)["pos"]
+    first = np.flatnonzero(np.concatenate([[True], np.diff(pos.astype(np.int64)) != 1])).astype(np.uint64)
+    assert first.size == 4
+    assert np.array_equal(expand_kmer_runs(first, pos[first.astype(np.int64)], pos.size), pos)
+    assert expand_kmer_runs(np.zeros(0, np.uint64), np.zeros(0, np.uint64), 0).size == 0
