@@ -52,15 +52,15 @@ __global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __rest
 }
 
 // ---------------------------------------------------------------------------------------------------- fastx
-// Two passes over the text (grids of 8 KB blocks, 16 bytes per thread) with ONE single-CTA scan between them:
+// Two passes over the text (grids of 8 KB blocks, 32 bytes per thread) with ONE single-CTA scan between them:
 //   fx_summarise  per block, as a FUNCTION of the state the block is entered in: newlines (FASTQ: the state is the line number
 //                 mod 4) / state of the line open at its end (FASTA), kept bytes and record starts for every possible entry state
 //   fx_scan       entry state, first kept byte and first record of every block (one CTA, 1024 summaries per step)
 //   fx_scatter    with all three known: kept bytes compacted in shared memory, written as whole 16-byte lines; record offsets
-// Per thread everything is bit arithmetic on 16-bit masks (newline / '\r' / '>' found four bytes at a time); the only loops run
-// over the newlines inside a thread's 16 bytes (0 or 1 for real files).
-constexpr int FX_THREADS = 512;
-constexpr int FX_BYTES_PER_THREAD = 16;
+// Per thread everything is bit arithmetic on 32-bit masks (newline / '\r' / '>' found four bytes at a time); the only loops run
+// over the newlines inside a thread's 32 bytes (0 or 1 for real files).
+constexpr int FX_THREADS = 256;
+constexpr int FX_BYTES_PER_THREAD = 32;
 constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 8 KB of text per CTA
 constexpr int FX_WARPS = FX_THREADS / 32;
 
@@ -72,21 +72,31 @@ struct FxSum {
     unsigned short starts[4];  // record starts if the block is entered in state e (FASTA: [0], the entry state does not matter)
 };
 
-__device__ __forceinline__ uint4 load16(const unsigned char* text, size_t n, size_t pos)
+// a thread's 32 bytes
+struct Fx32 { uint4 a, b; };
+
+__device__ __forceinline__ Fx32 load32(const unsigned char* text, size_t n, size_t pos)
 {
-    if (pos + 16 <= n) return __ldg(reinterpret_cast<const uint4*>(text + pos));   // text is 16-byte aligned (checked by the caller)
-    unsigned char b[16];
+    Fx32 v;
+    if (pos + 32 <= n) {                                       // text is 16-byte aligned (checked by the caller)
+        v.a = __ldg(reinterpret_cast<const uint4*>(text + pos));
+        v.b = __ldg(reinterpret_cast<const uint4*>(text + pos) + 1);
+        return v;
+    }
+    unsigned char t[32];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) b[i] = pos + i < n ? text[pos + i] : (unsigned char)'\n';   // the end of the text closes the last line
-    uint4 v;
-    memcpy(&v, b, 16);
+    for (int i = 0; i < 32; ++i) t[i] = pos + i < n ? text[pos + i] : (unsigned char)'\n';   // the end of the text closes the last line
+    memcpy(&v.a, t, 16);
+    memcpy(&v.b, t + 16, 16);
     return v;
 }
 
-__device__ __forceinline__ unsigned char byte_of(const uint4& v, int i)
+__device__ __forceinline__ unsigned char byte_of(const Fx32& v, int i)
 {
-    const u32 w = i < 4 ? v.x : i < 8 ? v.y : i < 12 ? v.z : v.w;
-    return (unsigned char)(w >> (8 * (i & 3)));
+    const uint4& q = i < 16 ? v.a : v.b;
+    const int j = i & 15;
+    const u32 w = j < 4 ? q.x : j < 8 ? q.y : j < 12 ? q.z : q.w;
+    return (unsigned char)(w >> (8 * (j & 3)));
 }
 
 // bit q: byte q of w equals the byte replicated in pat (exact zero-byte test, then the four flags gathered by one multiply)
@@ -100,8 +110,9 @@ __device__ __forceinline__ u32 eqmask16(const uint4& v, u32 pat)
 {
     return eqmask4(v.x, pat) | (eqmask4(v.y, pat) << 4) | (eqmask4(v.z, pat) << 8) | (eqmask4(v.w, pat) << 12);
 }
+__device__ __forceinline__ u32 eqmask32(const Fx32& v, u32 pat) { return eqmask16(v.a, pat) | (eqmask16(v.b, pat) << 16); }
 
-// what a thread knows about its 16 bytes without any context
+// what a thread knows about its 32 bytes without any context
 struct FxBits {
     u32 valid;   // bytes below n
     u32 nl;      // '\n'
@@ -110,31 +121,31 @@ struct FxBits {
     u32 hdr;     // first byte of a line and '>'
 };
 
-__device__ __forceinline__ FxBits fx_bits(const unsigned char* text, size_t n, size_t base, const uint4& v)
+__device__ __forceinline__ u32 below(int i) { return i >= 32 ? 0xFFFFFFFFu : ((1u << i) - 1u); }   // bits 0 .. i-1, i <= 32
+
+__device__ __forceinline__ FxBits fx_bits(const unsigned char* text, size_t n, size_t base, const Fx32& v)
 {
     FxBits b;
-    b.valid = base >= n ? 0u : (n - base >= 16 ? 0xFFFFu : ((1u << (n - base)) - 1u));
-    b.nl = eqmask16(v, 0x0A0A0A0Au) & b.valid;
-    b.body = ~(b.nl | eqmask16(v, 0x0D0D0D0Du)) & b.valid;
+    b.valid = base >= n ? 0u : below(n - base >= 32 ? 32 : (int)(n - base));
+    b.nl = eqmask32(v, 0x0A0A0A0Au) & b.valid;
+    b.body = ~(b.nl | eqmask32(v, 0x0D0D0D0Du)) & b.valid;
     // is the thread's first byte the first byte of a line? the previous byte is the neighbour lane's last one
-    const u32 pw = __shfl_up_sync(0xffffffffu, v.w, 1);
+    const u32 pw = __shfl_up_sync(0xffffffffu, v.b.w, 1);
     u32 prev_nl;
     if ((threadIdx.x & 31) == 0) prev_nl = base == 0 || (base <= n && text[base - 1] == '\n');
     else prev_nl = (pw >> 24) == 0x0Au;
     b.ls = ((b.nl << 1) | prev_nl) & b.valid;
-    b.hdr = b.ls & eqmask16(v, 0x3E3E3E3Eu);
+    b.hdr = b.ls & eqmask32(v, 0x3E3E3E3Eu);
     return b;
 }
-
-__device__ __forceinline__ u32 below(int i) { return (1u << i) - 1u; }   // i <= 16
 
 // FASTA: bit i set = byte i lies on a header line, given the state the thread is entered in
 __device__ __forceinline__ u32 fasta_header_bytes(const FxBits& b, u32 entry)
 {
-    u32 in_hdr = entry ? 0xFFFFu : 0u;
+    u32 in_hdr = entry ? 0xFFFFFFFFu : 0u;
     for (u32 s = b.ls; s; s &= s - 1) {
         const int p = __ffs((int)s) - 1;
-        const u32 m = 0xFFFFu & ~below(p);
+        const u32 m = ~below(p);
         in_hdr = ((b.hdr >> p) & 1u) ? (in_hdr | m) : (in_hdr & ~m);
     }
     return in_hdr;
@@ -154,9 +165,9 @@ __device__ __forceinline__ void fastq_masks(const FxBits& b, u32 state, u32* kee
         if (state == 1u) keep |= below(p) & ~below(lo);
         state = (state + 1u) & 3u;
         lo = p + 1;
-        if (state == 0u) start |= 1u << lo;     // bit 16 (the next thread's first byte) is masked below
+        if (state == 0u && lo < 32) start |= 1u << lo;     // lo == 32 is the next thread's first byte
     }
-    if (state == 1u) keep |= 0xFFFFu & ~below(lo);
+    if (state == 1u) keep |= ~below(lo);
     *keep_out = keep & b.body;
     *start_out = start & b.valid;
 }
@@ -171,21 +182,21 @@ __device__ __forceinline__ void fastq_phase_counts(const FxBits& b, u32* keep4, 
         kc += __popc(b.body & below(p) & ~below(lo)) << (8 * (j & 3));
         ++j;
         lo = p + 1;
-        if (lo < 16 && ((b.valid >> lo) & 1u)) sc += 1u << (8 * (j & 3));
+        if (lo < 32 && ((b.valid >> lo) & 1u)) sc += 1u << (8 * (j & 3));
     }
     kc += __popc(b.body & ~below(lo)) << (8 * (j & 3));
     *keep4 = kc;
     *start4 = sc;
 }
 
-// sum over the warp of four byte-wide counters each (<= 16 per lane): two 16-bit fields per word, one REDUX per word
+// sum over the warp of four byte-wide counters each (<= 32 per lane): two 16-bit fields per word, one REDUX per word
 __device__ __forceinline__ void warp_sum4(u32 packed, u32* even, u32* odd)
 {
     *even = __reduce_add_sync(0xffffffffu, packed & 0x00FF00FFu);           // counters 0 and 2
     *odd = __reduce_add_sync(0xffffffffu, (packed >> 8) & 0x00FF00FFu);     // counters 1 and 3
 }
 
-// exclusive prefix over the block of a per-thread count (<= 16 per field, two 16-bit fields); *total = the block's sum.
+// exclusive prefix over the block of a per-thread count (<= 32 per field, two 16-bit fields); *total = the block's sum.
 // The per-warp totals are scanned by every warp for itself (lane w holds warp w's total): no serial walk over the warps.
 __device__ __forceinline__ u32 block_exclusive2(u32 x, u32* s_warp /* [FX_WARPS] */, u32* total)
 {
@@ -235,8 +246,9 @@ __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* 
     __shared__ u32 s_a[FX_WARPS], s_b[FX_WARPS], s_c[FX_WARPS], s_d[FX_WARPS], s_e[FX_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t base = (size_t)blockIdx.x * FX_BLOCK + (size_t)tid * FX_BYTES_PER_THREAD;
-    uint4 v = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
-    if (base < n) v = load16(text, n, base);
+    Fx32 v;
+    v.a = v.b = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
+    if (base < n) v = load32(text, n, base);
     const FxBits b = fx_bits(text, n, base, v);
     FxSum out;
     out.nl = 0; out.last_state = 3u;
@@ -270,11 +282,11 @@ __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* 
         u32 block_exit;
         const u32 e = fasta_thread_entry(fasta_exit_state(b), s_a, &block_exit);
         // bytes before the thread's first line start follow the entry state, the others do not depend on it
-        const int f = b.ls ? __ffs((int)b.ls) - 1 : 16;
+        const int f = b.ls ? __ffs((int)b.ls) - 1 : 32;
         const u32 var = __popc(b.body & below(f));
         const u32 fix = __popc(~fasta_header_bytes(b, 0u) & b.body & ~below(f));
         const u32 sure = fix + (e == 0u ? var : 0u), open = e == 2u ? var : 0u;
-        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 512 per field and warp, <= 8192 per block
+        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 1024 per field and warp, <= 8192 per block
         const u32 st = __reduce_add_sync(0xffffffffu, (u32)__popc(b.hdr));
         if (lane == 0) { s_b[warp] = x; s_c[warp] = st; }
         __syncthreads();
@@ -375,8 +387,9 @@ __global__ void __launch_bounds__(FX_THREADS) fx_scatter(const unsigned char* __
     __shared__ u32 s_a[FX_WARPS], s_b[FX_WARPS];
     const int tid = threadIdx.x;
     const size_t base = (size_t)blockIdx.x * FX_BLOCK + (size_t)tid * FX_BYTES_PER_THREAD;
-    uint4 v = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
-    if (base < n) v = load16(text, n, base);
+    Fx32 v;
+    v.a = v.b = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
+    if (base < n) v = load32(text, n, base);
     const FxBits b = fx_bits(text, n, base, v);
     const u32 E = entry[blockIdx.x];
     u32 keep, start;
@@ -399,12 +412,13 @@ __global__ void __launch_bounds__(FX_THREADS) fx_scatter(const unsigned char* __
     const u32 mis = (u32)(reinterpret_cast<uintptr_t>(dst) & 15u);
     {
         u32 p = mis + kx;
-        if (keep == 0xFFFFu && (p & 3u) == 0u) {            // the usual thread of a sequence line, when the alignment allows words
+        if (keep == 0xFFFFFFFFu && (p & 3u) == 0u) {        // the usual thread of a sequence line, when the alignment allows words
             u32* w = reinterpret_cast<u32*>(s_out + p);
-            w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+            w[0] = v.a.x; w[1] = v.a.y; w[2] = v.a.z; w[3] = v.a.w;
+            w[4] = v.b.x; w[5] = v.b.y; w[6] = v.b.z; w[7] = v.b.w;
         } else {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
+            for (int i = 0; i < 32; ++i)
                 if ((keep >> i) & 1u) s_out[p++] = byte_of(v, i);
         }
     }
