@@ -9,7 +9,7 @@
 //                FASTA  a line whose first byte is '>' starts a record; every other line is sequence (multi-line allowed)
 //                FASTQ  four lines per record: '@' header, sequence, '+' line, qualities
 //              '\n' and '\r' are dropped, every other byte of a sequence line is kept as it is (the nt4 table decides
-//              later what is a base). Two passes over the text, each a grid of 8 KB blocks, with a one-CTA scan between:
+//              later what is a base). Two passes over the text, each a grid of 16 KB blocks, with a one-CTA scan between:
 //              (1) per block, for every state it may be entered in: kept bytes, record starts, state at its end; (2) the scan;
 //              (3) with entry states and prefix sums known: compaction in shared memory, aligned 16-byte stores.
 #include "common.cuh"
@@ -52,16 +52,16 @@ __global__ void __launch_bounds__(128) stamp_breaks_kernel(unsigned char* __rest
 }
 
 // ---------------------------------------------------------------------------------------------------- fastx
-// Two passes over the text (grids of 8 KB blocks, 32 bytes per thread) with ONE single-CTA scan between them:
+// Two passes over the text (grids of 16 KB blocks, 32 bytes per thread) with ONE single-CTA scan between them:
 //   fx_summarise  per block, as a FUNCTION of the state the block is entered in: newlines (FASTQ: the state is the line number
 //                 mod 4) / state of the line open at its end (FASTA), kept bytes and record starts for every possible entry state
 //   fx_scan       entry state, first kept byte and first record of every block (one CTA, 1024 summaries per step)
 //   fx_scatter    with all three known: kept bytes compacted in shared memory, written as whole 16-byte lines; record offsets
 // Per thread everything is bit arithmetic on 32-bit masks (newline / '\r' / '>' found four bytes at a time); the only loops run
 // over the newlines inside a thread's 32 bytes (0 or 1 for real files).
-constexpr int FX_THREADS = 256;
+constexpr int FX_THREADS = 512;
 constexpr int FX_BYTES_PER_THREAD = 32;
-constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 8 KB of text per CTA
+constexpr int FX_BLOCK = FX_THREADS * FX_BYTES_PER_THREAD;   // 16 KB of text per CTA
 constexpr int FX_WARPS = FX_THREADS / 32;
 
 // state of a line: FASTA 0 = sequence line, 1 = header line; FASTQ = line number mod 4 (1 = sequence line, 0 starts a record)
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(FX_THREADS) fx_summarise(const unsigned char* 
         const u32 var = __popc(b.body & below(f));
         const u32 fix = __popc(~fasta_header_bytes(b, 0u) & b.body & ~below(f));
         const u32 sure = fix + (e == 0u ? var : 0u), open = e == 2u ? var : 0u;
-        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 1024 per field and warp, <= 8192 per block
+        const u32 x = __reduce_add_sync(0xffffffffu, sure | (open << 16));          // <= 1024 per field and warp, <= 16384 per block
         const u32 st = __reduce_add_sync(0xffffffffu, (u32)__popc(b.hdr));
         if (lane == 0) { s_b[warp] = x; s_c[warp] = st; }
         __syncthreads();
